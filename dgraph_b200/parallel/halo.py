@@ -1,0 +1,78 @@
+"""Halo exchange and the message-passing wrapper.
+
+Parity: reference ``DGraph/distributed/haloExchange.py:9-223`` (``HaloExchangeImpl``, ``HaloExchange``,
+``DGraphMessagePassing``; same call signatures, 1-D and 2-D buffers).
+
+On the peer-memory engine the exchange is ONE pull kernel (``ops.halo_pull``): it reads the boundary rows
+straight out of the owners' feature matrices over NVLink, so there is no send-side index kernel, no
+all-to-all and no staging buffer; its backward is ONE push-reduce kernel.  The torch engines take the
+reference's route (index -> ``put`` -> autograd index_add).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn as nn
+from torch.autograd import Function
+
+from dgraph_b200.parallel.comm_pattern import CommunicationPattern
+
+
+class HaloExchangeImpl(Function):
+    """Communication half of the exchange: forward ``put``; backward = the transposed ``put``."""
+
+    @staticmethod
+    def forward(ctx, send_buffer, comm, comm_pattern: CommunicationPattern):
+        two_d = send_buffer.dim() == 2
+        F = send_buffer.shape[1] if two_d else 1
+        n_recv = int(comm_pattern.recv_offset[-1])
+        ctx.comm, ctx.pat, ctx.F = comm, comm_pattern, F
+        recv = comm.alloc_buffer((n_recv, F) if two_d else (n_recv,), dtype=send_buffer.dtype, device=send_buffer.device)
+        comm.put(send_buffer.contiguous(), recv, comm_pattern.send_offset, comm_pattern.recv_offset,
+                 remote_offsets=comm_pattern.put_forward_remote_offset)
+        return recv
+
+    @staticmethod
+    def backward(ctx, grad_recv):
+        pat, comm = ctx.pat, ctx.comm
+        n_sent = int(pat.send_offset[-1])
+        two_d = grad_recv.dim() == 2
+        grad_send = comm.alloc_buffer((n_sent, ctx.F) if two_d else (n_sent,), dtype=grad_recv.dtype, device=grad_recv.device)
+        comm.put(grad_recv.contiguous(), grad_send, pat.recv_offset, pat.send_offset,
+                 remote_offsets=pat.put_backward_remote_offset)
+        return grad_send, None, None
+
+
+class HaloExchange:
+    """``halo = HaloExchange(comm)(x_local, pattern)`` -> ``[num_halo, F]`` in ``pattern.recv_offset`` order."""
+
+    def __init__(self, comm):
+        self.comm = comm
+
+    def __call__(self, x_local: torch.Tensor, comm_pattern: CommunicationPattern) -> torch.Tensor:
+        engine = getattr(self.comm, "engine", None)
+        fused = getattr(engine, "halo_exchange", None)
+        if fused is not None and x_local.is_cuda:
+            return fused(x_local, comm_pattern)
+        # plain indexing on purpose: autograd's index backward does the scatter-add of rows sent to several ranks
+        send = x_local[comm_pattern.send_local_idx]
+        return HaloExchangeImpl.apply(send, self.comm, comm_pattern)
+
+
+class DGraphMessagePassing(nn.Module):
+    """halo exchange -> ``cat([local, halo])`` -> user layer ``(x_aug, local_edge_list, edge_feats)``.
+
+    The wrapped layer must return features for the local vertices only (``[num_local, F_out]``).
+    """
+
+    def __init__(self, exchanger: HaloExchange, message_passing_layer: nn.Module):
+        super().__init__()
+        self.message_passing_layer = message_passing_layer
+        self.exchanger = exchanger
+
+    def forward(self, local_node_features: torch.Tensor, comm_pattern: CommunicationPattern,
+                local_edge_features: Optional[torch.Tensor] = None) -> torch.Tensor:
+        halo = self.exchanger(local_node_features, comm_pattern)
+        aug = torch.cat([local_node_features, halo], dim=0)
+        return self.message_passing_layer(aug, comm_pattern.local_edge_list, local_edge_features)

@@ -1,0 +1,99 @@
+"""Kernel-side graph structures derived from a :class:`CommunicationPattern`.
+
+The sm_100a kernels do not consume COO edge lists: aggregation walks a **CSR** sorted by the owned
+(central) vertex so every output row is reduced by one warp without atomics (deterministic), and the
+backward pass walks the **CSC** (sorted by neighbour row over ``[local | halo]``) for the transposed
+reduction.  Indices are int32 (per-rank shards stay below 2^31 rows/edges).
+
+No counterpart in the reference, which keeps COO + ``scatter_add`` atomics (``experiments/OGB/GCN.py:57-65``).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+
+@dataclass
+class GraphKernelPlan:
+    num_local: int  # rows that are aggregated into (central side)
+    num_nbr_local: int  # local rows of the neighbour side (== num_local for homogeneous graphs)
+    num_halo: int
+    num_edges: int
+    # CSR over central vertices
+    rowptr: torch.Tensor  # int32 [num_local + 1]  (int64 when E >= 2^31)
+    col: torch.Tensor  # int32 [E]   neighbour row in [nbr_local | halo] numbering
+    csr_eid: torch.Tensor  # int32/64 [E] original edge id of each CSR slot
+    # CSC over neighbour rows (local + halo)
+    colptr: torch.Tensor  # [num_nbr_local + num_halo + 1]
+    row: torch.Tensor  # int32 [E]   central row of each CSC slot
+    csc_eid: torch.Tensor  # [E] original edge id of each CSC slot
+    csc_to_csr: torch.Tensor  # [E] CSR slot of each CSC slot
+    # halo addressing (pull): owner rank and row inside the owner's matrix
+    halo_owner: Optional[torch.Tensor]  # int32 [num_halo]
+    halo_remote_row: Optional[torch.Tensor]  # int32 [num_halo]
+    # send side
+    send_local_idx: torch.Tensor  # int32 [total_sends]
+
+    @property
+    def num_aug(self) -> int:
+        return self.num_nbr_local + self.num_halo
+
+    @staticmethod
+    def from_edges(edge_list: torch.Tensor, num_local: int, num_aug: int, device=None, num_nbr_local=None,
+                   halo_owner=None, halo_remote_row=None, send_local_idx=None) -> "GraphKernelPlan":
+        dev = torch.device(device) if device is not None else edge_list.device
+        e = edge_list.to(dev)
+        E = int(e.shape[0])
+        idx_t = torch.int32 if E < 2 ** 31 else torch.int64
+        src = e[:, 0].to(torch.long)
+        dst = e[:, 1].to(torch.long)
+        # CSR: stable sort by (src, dst) gives neighbour-sorted rows => better L2 locality on gathers
+        key = src * max(num_aug, 1) + dst
+        csr_perm = torch.argsort(key, stable=True)
+        rowptr = torch.zeros(num_local + 1, dtype=torch.long, device=dev)
+        rowptr[1:] = torch.bincount(src, minlength=num_local).cumsum(0)
+        col = dst[csr_perm]
+        key2 = dst * max(num_local, 1) + src
+        csc_perm = torch.argsort(key2, stable=True)
+        colptr = torch.zeros(num_aug + 1, dtype=torch.long, device=dev)
+        colptr[1:] = torch.bincount(dst, minlength=num_aug).cumsum(0)
+        row = src[csc_perm]
+        inv_csr = torch.empty(E, dtype=torch.long, device=dev)
+        inv_csr[csr_perm] = torch.arange(E, device=dev)
+        csc_to_csr = inv_csr[csc_perm]
+        nl = num_local if num_nbr_local is None else num_nbr_local
+        return GraphKernelPlan(
+            num_local=num_local,
+            num_nbr_local=nl,
+            num_halo=num_aug - nl,
+            num_edges=E,
+            rowptr=rowptr.to(idx_t),
+            col=col.to(torch.int32),
+            csr_eid=csr_perm.to(idx_t),
+            colptr=colptr.to(idx_t),
+            row=row.to(torch.int32),
+            csc_eid=csc_perm.to(idx_t),
+            csc_to_csr=csc_to_csr.to(idx_t),
+            halo_owner=None if halo_owner is None else halo_owner.to(dev, torch.int32),
+            halo_remote_row=None if halo_remote_row is None else halo_remote_row.to(dev, torch.int32),
+            send_local_idx=(torch.empty(0, dtype=torch.int32, device=dev) if send_local_idx is None
+                            else send_local_idx.to(dev, torch.int32)),
+        )
+
+    @staticmethod
+    def from_pattern(pattern, device=None) -> "GraphKernelPlan":
+        nl = pattern.num_neighbor_local_vertices
+        if nl is None:
+            nl = pattern.num_local_vertices
+        return GraphKernelPlan.from_edges(
+            pattern.local_edge_list,
+            pattern.num_local_vertices,
+            nl + pattern.num_halo_vertices,
+            device=device,
+            num_nbr_local=nl,
+            halo_owner=pattern.halo_owner,
+            halo_remote_row=pattern.halo_remote_row,
+            send_local_idx=pattern.send_local_idx,
+        )

@@ -1,0 +1,87 @@
+"""CommPlan tests (model: reference tests/test_NCCLCommPlan.py:127-359), run on the in-process world emulator."""
+import pytest
+import torch
+
+from dgraph_b200.parallel.comm_plan import COO_to_NCCLCommPlan, COO_to_NCCLEdgeConditionedCommPlan
+from dgraph_b200.parallel.emulator import run_world
+from tests._graphs import random_graph
+
+
+def _offsets(V, W):
+    return torch.tensor([V * r // W for r in range(W + 1)])
+
+
+def _job(comm, e, off, xg, eg, W):
+    r = comm.get_rank()
+    src, dst = e[:, 0], e[:, 1]
+    mine = torch.nonzero((src >= off[r]) & (src < off[r + 1]), as_tuple=True)[0]
+    plan = COO_to_NCCLEdgeConditionedCommPlan(r, W, src, dst, mine, off, None, exchange=comm.engine.exchange_ids)
+    sp, dp = plan.source_graph_plan, plan.dest_graph_plan
+    assert sp.boundary_edge_idx.numel() == 0  # edges live with their source (tests/test_NCCLCommPlan.py:235-239)
+    assert sum(dp.boundary_edge_splits) == dp.boundary_edge_buffer_map.unique().numel()
+    x = xg[off[r]:off[r + 1]].clone().unsqueeze(0).requires_grad_(True)
+    got = comm.gather(x, comm_plan=dp)  # [1, E_loc, F]
+    (got * got).sum().backward()
+    ef = eg[mine].clone().unsqueeze(0).requires_grad_(True)
+    sc = comm.scatter(ef, comm_plan=dp)  # [1, N_loc, F]
+    (sc * sc).sum().backward()
+    return mine, got.detach()[0], x.grad[0], sc.detach()[0], ef.grad[0], plan.source_graph_plan.memory_usage()
+
+
+@pytest.mark.parametrize("W", [1, 2, 3, 4])
+def test_comm_plan_gather_scatter(W):
+    torch.manual_seed(1)
+    V = 32 * W
+    e = random_graph(V, 6, seed=W)
+    off = _offsets(V, W)
+    xg = torch.randn(V, 4, dtype=torch.float64)
+    eg = torch.randn(e.shape[0], 4, dtype=torch.float64)
+    res = run_world(W, _job, e, off, xg, eg, W)
+    x = xg.clone().requires_grad_(True)
+    g = x[e[:, 1]]
+    (g * g).sum().backward()
+    ef = eg.clone().requires_grad_(True)
+    s = torch.zeros_like(xg).index_add(0, e[:, 1], ef)
+    (s * s).sum().backward()
+    for r, (mine, got, gx, sc, gef, mem) in enumerate(res):
+        assert torch.allclose(got, g.detach()[mine])
+        assert torch.allclose(gx, x.grad[off[r]:off[r + 1]])
+        assert torch.allclose(sc, s.detach()[off[r]:off[r + 1]])
+        assert torch.allclose(gef, ef.grad[mine])
+        assert mem["unit"] == "MB" and mem["total"] > 0
+
+
+def test_legacy_gather_scatter_api():
+    """``gather(x, indices, rank_mappings)`` / ``scatter(x, indices, rank_mappings, output_size)`` (broken in the
+    reference snapshot) -- equal contiguous partitions, explicit ``[2, E]`` rank map."""
+    W, n = 3, 8
+    V = W * n
+    e = random_graph(V, 4, seed=9)
+    xg = torch.randn(V, 3, dtype=torch.float64)
+    edge_rank = e[:, 0] // n
+    rm = torch.stack([edge_rank, e[:, 1] // n])
+
+    def job(comm):
+        r = comm.get_rank()
+        x = xg[r * n:(r + 1) * n].unsqueeze(0)
+        got = comm.gather(x, e[:, 1].unsqueeze(0), rm)
+        mine = edge_rank == r
+        back = comm.scatter(got, e[:, 1].unsqueeze(0), rm, n)
+        return mine, got[0], back[0]
+
+    want_s = torch.zeros_like(xg).index_add(0, e[:, 1], xg[e[:, 1]])
+    for r, (mine, got, back) in enumerate(run_world(W, job)):
+        assert torch.allclose(got, xg[e[mine, 1]])
+        assert torch.allclose(back, want_s[r * n:(r + 1) * n])
+
+
+def test_plan_to_and_reverse():
+    e = random_graph(16, 4, seed=2)
+    off = _offsets(16, 1)
+    p = COO_to_NCCLEdgeConditionedCommPlan(0, 1, e[:, 0], e[:, 1], torch.arange(e.shape[0]), off, None)
+    p = p.to("cpu")
+    q = p.reverse()
+    assert q.source_graph_plan is p.dest_graph_plan
+    assert p.source_graph_plan.num_local_edges == e.shape[0]
+    single = COO_to_NCCLCommPlan(0, 1, e[:, 1], torch.arange(e.shape[0]), off)
+    assert single.local_edge_idx.numel() == e.shape[0]

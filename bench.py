@@ -1,0 +1,300 @@
+#!/usr/bin/env python
+"""Headline benchmark: full-graph GCN training throughput (edges/s) on an ogbn-products-shaped graph.
+
+Contract (driver): ``python bench.py --gpus N --steps K --warmup W [--impl reference]`` prints ONE JSON line on rank 0.
+For N > 1 it is launched under ``torch.distributed.run`` with one rank per GPU.
+
+Metric (BASELINE.json / reference ``experiments/OGB/main.py:129-157``): one "step" = one full-graph epoch
+``zero_grad -> forward -> loss -> backward -> optimizer step`` on the 3-layer GCN (2 x GraphConv(256) + Linear(47)),
+timed with CUDA events between barriers, max over ranks; ``value = E_global * K / t`` edges per second.
+Scaling is *strong*: the same 2.45 M-node / 61.9 M-edge graph is split over N GPUs.
+
+Two arms:
+  * ours      -- dgraph_b200 (bf16 compute, fp32 master weights + fused Adam), public API: Communicator,
+                 build_communication_pattern, HaloExchange, CommAwareGCN, FusedAdam.
+  * reference -- the unmodified LBANN/DGraph NCCL path installed under baseline/_ref (fp32), see baseline/ref_bench.py.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+BASELINE_VALUE = None  # BASELINE.md publishes no number for this metric (``published: {}``)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--graph", default="ogbn-products")
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink the graph (debug only; <1 is NOT the named config)")
+    ap.add_argument("--hidden", type=int, default=256)
+    ap.add_argument("--cut", type=float, default=0.1, help="fraction of long-range edges in the synthetic graph")
+    ap.add_argument("--lr", type=float, default=1e-3)
+    ap.add_argument("--engine", default=None, help="override DGRAPH_B200_ENGINE (torch | peer)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu", action="store_true", help="CPU/gloo plumbing run (tiny graphs only)")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.idx)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx = float(f[2])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def setup_dist(args):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.cpu:
+        dev = torch.device("cpu")
+    else:
+        torch.cuda.set_device(local)
+        dev = torch.device("cuda", local)
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        dist.init_process_group("gloo" if args.cpu else "nccl", rank=rank, world_size=world,
+                                **({} if args.cpu else {"device_id": dev}))
+    return rank, world, local, dev
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    rank, world, local, dev = setup_dist(args)
+    if args.engine:
+        os.environ["DGRAPH_B200_ENGINE"] = args.engine
+    from dgraph_b200 import Communicator
+    from dgraph_b200.data import make_graph, contiguous_partition, node_features_and_labels
+    from dgraph_b200.models.gcn import CommAwareGCN
+    from dgraph_b200.ops import _native
+    from dgraph_b200.optim import FusedAdam
+    from dgraph_b200.parallel import HaloExchange, build_communication_pattern
+
+    if not args.cpu:
+        _native.lib()  # fail loudly if the sm_100a library is missing on a GPU box
+    comm = Communicator.init_process_group("single" if world == 1 else "nccl")
+    cdt = torch.float32 if args.cpu else torch.bfloat16
+
+    # ---- graph, partition, plan (identical on every rank: same seed) -------------------------------
+    g = make_graph(args.graph, cut_fraction=args.cut, seed=0, device=dev, scale=args.scale)
+    E_global = int(g.edge_list.shape[0])
+    part = contiguous_partition(g.num_nodes, world, device=dev)
+    pat = build_communication_pattern(g.edge_list, part, rank, world)
+    del g.edge_list
+    rows = pat.local_vertices_global
+    F_in = g.num_features
+    F_pad = (F_in + 7) // 8 * 8  # 16-byte rows for TMA / vector loads
+    x_host, y_host = node_features_and_labels(g.num_nodes, F_in, g.num_classes, seed=0, device=dev, rows=rows)
+    train_mask = (torch.arange(rows.numel(), device=dev) % 10) == 0  # ~10 % labelled (products: 8 %)
+    train_idx = torch.nonzero(train_mask, as_tuple=True)[0]
+    xh = torch.zeros(rows.numel(), F_pad, dtype=cdt)
+    xh[:, :F_in] = x_host.to(cdt).cpu()
+    yh = y_host.cpu()
+    if not args.cpu:
+        xh, yh = xh.pin_memory(), yh.pin_memory()
+    del x_host, y_host
+    kp = pat.kernel_plan(dev)  # CSR/CSC build is one-time setup, not part of the epoch
+
+    torch.manual_seed(0)
+    model = CommAwareGCN(F_in, args.hidden, g.num_classes, HaloExchange(comm), comm, compute_dtype=cdt).to(dev)
+    opt = FusedAdam(model.parameters(), lr=args.lr, comm=comm)
+    loss_fn = torch.nn.CrossEntropyLoss()
+
+    def step(x_dev, y_dev):
+        opt.zero_grad()
+        out = model(x_dev, pat)
+        loss = loss_fn(out.index_select(0, train_idx).float(), y_dev.index_select(0, train_idx))
+        loss.backward()
+        opt.step()
+        return loss
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        if not args.cpu:
+            torch.cuda.synchronize()
+
+    def timed(fn, k):
+        sync()
+        if args.cpu:
+            t0 = time.perf_counter()
+            fn(k)
+            ms = (time.perf_counter() - t0) * 1e3
+        else:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn(k)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1)
+        sync()
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0])
+
+    # ---- device-resident arm (kernel-only number) ---------------------------------------------------
+    x_dev, y_dev = xh.to(dev, non_blocking=True), yh.to(dev, non_blocking=True)
+    losses = []
+
+    def loop_dev(k):
+        for _ in range(k):
+            losses.append(step(x_dev, y_dev))
+
+    loop_dev(args.warmup)
+    sampler = ClockSampler(local)
+    if rank == 0 and not args.cpu:
+        sampler.start()
+    l0 = _native.launches()
+    ms_total = timed(loop_dev, args.steps)
+    n_launch = _native.launches() - l0
+    clocks = sampler.stop() if (rank == 0 and not args.cpu) else None
+    ms_step = ms_total / args.steps
+    value = E_global / (ms_step * 1e-3)
+
+    # ---- end-to-end arm: per-step H2D of the step's inputs from pinned memory + D2H of the loss -------
+    e2e = None
+    if not args.no_e2e:
+        h2d = xh.numel() * xh.element_size() + yh.numel() * yh.element_size()
+        if args.cpu:
+            def loop_e2e(k):
+                for _ in range(k):
+                    float(step(xh.clone(), yh.clone()).detach())
+        else:
+            copy_stream = torch.cuda.Stream()
+            bufs = [(torch.empty_like(xh, device=dev), torch.empty_like(yh, device=dev)) for _ in range(2)]
+            evs = [torch.cuda.Event(), torch.cuda.Event()]
+            free = [torch.cuda.Event(), torch.cuda.Event()]
+
+            def issue(i):
+                with torch.cuda.stream(copy_stream):
+                    copy_stream.wait_event(free[i % 2])
+                    bufs[i % 2][0].copy_(xh, non_blocking=True)
+                    bufs[i % 2][1].copy_(yh, non_blocking=True)
+                    evs[i % 2].record(copy_stream)
+
+            def loop_e2e(k):
+                for b in range(2):
+                    free[b].record()
+                issue(0)
+                for i in range(k):
+                    if i + 1 < k:
+                        issue(i + 1)  # prefetch the next step's inputs while this step computes
+                    torch.cuda.current_stream().wait_event(evs[i % 2])
+                    loss = step(*bufs[i % 2])
+                    free[i % 2].record()
+                    float(loss.detach())  # device -> host read of the step's result
+
+        loop_e2e(max(2, args.warmup))
+        ms_e2e = timed(loop_e2e, args.steps) / args.steps
+        e2e = {"value": E_global / (ms_e2e * 1e-3), "unit": "edges/s", "ms_per_step": ms_e2e,
+               "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4}
+
+    final_loss = float(losses[-1].detach())
+    if rank == 0:
+        out = {
+            "metric": "full-graph GCN training throughput (edges/s; epoch = zero_grad+fwd+loss+bwd+step)",
+            "value": value, "unit": "edges/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": (value / BASELINE_VALUE) if BASELINE_VALUE else None,
+            "dtype": "fp32" if args.cpu else "bf16", "data": "synthetic", "impl": "ours",
+            "config": {"model": "CommAwareGCN 2xGraphConv(256)+Linear(47) [3-layer GCN]",
+                       "graph": f"{g.name} V={g.num_nodes} E={E_global} F={F_in}", "global_batch": "full graph",
+                       "seq_len": None, "parallelism": f"graph-partition x{world} + DP weights",
+                       "partition": f"contiguous blocks, cut_fraction={args.cut}", "hidden": args.hidden,
+                       "l2": "inputs larger than L2 (edge structure + features >> 126 MB)",
+                       "engine": type(comm.engine).__name__, "scale": args.scale,
+                       "gemm": os.environ.get("DGRAPH_B200_GEMM", "tcgen05")},
+            "e2e": e2e, "gpu_launches": n_launch, "clocks": clocks, "final_loss": final_loss,
+            "loss_first": float(losses[0].detach()),
+        }
+        print(json.dumps(out), flush=True)
+    comm.destroy()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        try:
+            import ref_bench
+        except Exception as e:  # noqa: BLE001
+            if int(os.environ.get("RANK", "0")) == 0:
+                print(json.dumps({"impl": "reference", "unavailable": f"reference harness import failed: {e!r}"[:300]}))
+            return
+        ref_bench.run(args)
+        return
+    run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -21,12 +21,16 @@ import torch
 from dgraph_b200.communicator_base import CommunicatorBase
 
 SUPPORTED_BACKENDS = ["nccl", "mpi", "nvshmem"]
-_EXTRA_BACKENDS = ["gloo", "torch", "b200", "emulated"]
+_EXTRA_BACKENDS = ["gloo", "torch", "b200", "emulated", "single"]
 
 
 def _make_engine(backend: str, **kwargs):
     from dgraph_b200.parallel.collective_engine import TorchDistEngine
 
+    if backend == "single":
+        from dgraph_b200.parallel.local_engine import LocalEngine
+
+        return LocalEngine()
     use_cuda = torch.cuda.is_available()
     forced = os.environ.get("DGRAPH_B200_ENGINE", "").lower()
     if backend == "gloo" or not use_cuda:

@@ -1,0 +1,162 @@
+"""Segment aggregation ops (CSR walk, atomic-free) with autograd.
+
+* :func:`graphconv_aggregate` -- ``out[i] = sum_{(i,j) in E} relu(P[i] + Q[j])``: the whole message +
+  aggregation stage of the reference ``GraphConvLayer`` (``experiments/OGB/GCN.py:43-65``) after splitting the
+  first Linear over its ``cat`` input (``W [x_i; x_j] = W_i x_i + W_j x_j``).  Nothing of size ``[E, *]`` is ever
+  materialised; backward recomputes the ReLU mask from ``P``/``Q``.
+* :func:`segment_sum` / :func:`segment_mean` -- GraphSAGE / GCN neighbourhood aggregation
+  (``out[i] = (1/deg) sum_j x[j]``), and the building block of distributed scatter-sum.
+
+CUDA bf16 tensors run the sm_100a kernels in ``csrc/segment_ops.cu``; everything else (CPU, fp32/fp64) runs the
+plain PyTorch formulation below, which is also the numerics oracle in the tests.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+from torch.autograd import Function
+
+from dgraph_b200.ops import _native as N
+from dgraph_b200.parallel.kernel_plan import GraphKernelPlan
+
+
+# ------------------------------------------------------------------------------------------------
+# PyTorch reference formulations (oracle + CPU path)
+# ------------------------------------------------------------------------------------------------
+def _coo(kp: GraphKernelPlan):
+    """(central row, neighbour row) per CSR slot."""
+    key = "_coo_rows"
+    c = getattr(kp, key, None)
+    if c is None:
+        deg = (kp.rowptr[1:] - kp.rowptr[:-1]).long()
+        c = torch.repeat_interleave(torch.arange(kp.num_local, device=kp.rowptr.device), deg)
+        setattr(kp, key, c)
+    return c, kp.col.long()
+
+
+def graphconv_aggregate_ref(P, Qaug, kp: GraphKernelPlan):
+    r, c = _coo(kp)
+    m = torch.relu(P.index_select(0, r) + Qaug.index_select(0, c))
+    return torch.zeros_like(P).index_add_(0, r, m)
+
+
+def segment_sum_ref(xaug, kp: GraphKernelPlan, mean: bool = False, slot_w=None):
+    r, c = _coo(kp)
+    m = xaug.index_select(0, c)
+    if slot_w is not None:
+        m = m * slot_w.to(m.dtype).unsqueeze(1)
+    out = torch.zeros((kp.num_local, xaug.shape[1]), dtype=xaug.dtype, device=xaug.device).index_add_(0, r, m)
+    if mean:
+        deg = (kp.rowptr[1:] - kp.rowptr[:-1]).clamp(min=1).to(out.dtype)
+        out = out / deg.unsqueeze(1)
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# native launch helpers
+# ------------------------------------------------------------------------------------------------
+def _ld(t: torch.Tensor) -> int:
+    assert t.dim() == 2 and t.stride(1) == 1, "row-major 2-D tensor expected"
+    return t.stride(0)
+
+
+def _native_seg_sum(ptr, idx, n_rows, src, slot_w, mean, halo=None):
+    H = src.shape[1]
+    out = torch.empty((n_rows, H), dtype=torch.bfloat16, device=src.device)
+    peer = halo_owner = halo_row = None
+    n_local, ld_peer = src.shape[0], 0
+    if halo is not None:
+        peer, halo_owner, halo_row, n_local, ld_peer = halo
+    N.check(N.lib().dgb_seg_sum(N.ptr(ptr), N.ptr(idx), N.i64(n_rows), N.i32(H), N.ptr(src), N.i64(_ld(src)),
+                                N.ptr(slot_w), N.i32(1 if mean else 0), N.ptr(out), N.i64(_ld(out)), N.i64(n_local),
+                                N.ptr(peer), N.ptr(halo_owner), N.ptr(halo_row), N.i64(ld_peer), N.stream()),
+            "dgb_seg_sum")
+    N.count_launch()
+    return out
+
+
+def _mean_bwd_weights(kp: GraphKernelPlan):
+    w = getattr(kp, "_csc_invdeg", None)
+    if w is None:
+        deg = (kp.rowptr[1:] - kp.rowptr[:-1]).clamp(min=1).float()
+        w = (1.0 / deg)[kp.row.long()].contiguous()
+        setattr(kp, "_csc_invdeg", w)
+    return w
+
+
+class _SegSum(Function):
+    @staticmethod
+    def forward(ctx, xaug, kp, mean, halo):
+        ctx.kp, ctx.mean = kp, mean
+        return _native_seg_sum(kp.rowptr, kp.col, kp.num_local, xaug, None, mean, halo)
+
+    @staticmethod
+    def backward(ctx, g):
+        kp = ctx.kp
+        w = _mean_bwd_weights(kp) if ctx.mean else None
+        gx = _native_seg_sum(kp.colptr, kp.row, kp.num_aug, g.contiguous(), w, False)
+        return gx, None, None, None
+
+
+def segment_sum(xaug: torch.Tensor, kp: GraphKernelPlan, mean: bool = False, halo=None) -> torch.Tensor:
+    """``out[i] = sum_{j in N(i)} xaug[j]`` (``mean=True`` divides by the degree).  ``xaug = cat([local, halo])``."""
+    if xaug.is_cuda and xaug.dtype == torch.bfloat16:
+        N.lib()
+        return _SegSum.apply(xaug if xaug.stride(1) == 1 else xaug.contiguous(), kp, mean, halo)
+    return segment_sum_ref(xaug, kp, mean)
+
+
+def segment_mean(xaug, kp, halo=None):
+    return segment_sum(xaug, kp, mean=True, halo=halo)
+
+
+class _GraphConvAgg(Function):
+    @staticmethod
+    def forward(ctx, P, Qaug, kp: GraphKernelPlan):
+        H = P.shape[1]
+        n = kp.num_local
+        out = torch.empty((n, H), dtype=torch.bfloat16, device=P.device)
+        cnt = torch.empty((n, H), dtype=torch.uint16, device=P.device)
+        N.check(N.lib().dgb_seg_add_relu_fwd(
+            N.ptr(kp.rowptr), N.ptr(kp.col), N.i64(n), N.i32(H), N.ptr(P), N.i64(_ld(P)), N.ptr(Qaug), N.i64(_ld(Qaug)),
+            N.ptr(out), N.i64(H), N.ptr(cnt), N.i64(H), N.i64(Qaug.shape[0]), N.ptr(None), N.ptr(None), N.ptr(None),
+            N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
+        N.count_launch()
+        ctx.save_for_backward(P, Qaug, cnt)
+        ctx.kp = kp
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        P, Qaug, cnt = ctx.saved_tensors
+        kp = ctx.kp
+        g = g.contiguous()
+        H = P.shape[1]
+        dP = dQ = None
+        if ctx.needs_input_grad[0]:
+            dP = torch.empty_like(g)
+            N.check(N.lib().dgb_mul_cnt(N.ptr(g), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(dP), N.i64(H),
+                                        N.i64(g.shape[0]), N.i32(H), N.stream()), "dgb_mul_cnt")
+            N.count_launch()
+        if ctx.needs_input_grad[1]:
+            dQ = torch.empty((kp.num_aug, H), dtype=torch.bfloat16, device=g.device)
+            N.check(N.lib().dgb_seg_add_relu_bwd(
+                N.ptr(kp.colptr), N.ptr(kp.row), N.i64(kp.num_aug), N.i32(H), N.ptr(g), N.i64(H), N.ptr(P),
+                N.i64(_ld(P)), N.ptr(Qaug), N.i64(_ld(Qaug)), N.ptr(dQ), N.i64(H), N.stream()),
+                "dgb_seg_add_relu_bwd")
+            N.count_launch()
+        return dP, dQ, None
+
+
+def graphconv_aggregate(P: torch.Tensor, Qaug: torch.Tensor, kp: GraphKernelPlan) -> torch.Tensor:
+    """``out[i] = sum_{(i,j)} relu(P[i] + Qaug[j])`` for the local rows ``i``; ``Qaug`` has local + halo rows."""
+    if P.is_cuda and P.dtype == torch.bfloat16:
+        N.lib()
+        assert kp.rowptr.dtype == torch.int32, "per-rank edge count must stay below 2^31"
+        if P.stride(1) != 1:
+            P = P.contiguous()
+        if Qaug.stride(1) != 1:
+            Qaug = Qaug.contiguous()
+        return _GraphConvAgg.apply(P, Qaug, kp)
+    return graphconv_aggregate_ref(P, Qaug, kp)

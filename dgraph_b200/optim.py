@@ -1,0 +1,111 @@
+"""Fused flat-arena Adam (+ data-parallel gradient all-reduce).
+
+Replaces the reference's ``torch.optim.Adam`` + DDP pair (``experiments/OGB/main.py:112-114``): parameters and
+gradients are re-homed into two contiguous fp32 buffers, so
+
+* the gradient all-reduce of data-parallel training is ONE collective over the flat gradient buffer (the role of
+  DDP's bucketed all-reduce), and
+* the optimizer step is ONE sm_100a kernel (``csrc/adam.cu``) that also folds in the 1/world gradient scale.
+
+State-dict layout follows ``torch.optim.Adam`` (``state[p] = {step, exp_avg, exp_avg_sq}``) so checkpoints
+round-trip with stock PyTorch.
+"""
+from __future__ import annotations
+
+import math
+from typing import Iterable, Optional
+
+import torch
+
+from dgraph_b200.ops import _native as N
+
+
+class FusedAdam(torch.optim.Optimizer):
+    def __init__(self, params: Iterable, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.0, comm=None, grad_average: bool = True):
+        defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
+        super().__init__(params, defaults)
+        assert len(self.param_groups) == 1, "FusedAdam keeps one flat arena (single param group)"
+        self.comm = comm
+        self.grad_average = grad_average
+        self._step = 0
+        ps = [p for p in self.param_groups[0]["params"] if p.requires_grad]
+        assert all(p.dtype == torch.float32 for p in ps), "master parameters are fp32"
+        dev = ps[0].device
+        sizes = [(p.numel() + 3) // 4 * 4 for p in ps]  # keep every view 16-byte aligned
+        total = sum(sizes)
+        self.flat_p = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_g = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_m = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_v = torch.zeros(total, dtype=torch.float32, device=dev)
+        self._views = []
+        o = 0
+        for p, s in zip(ps, sizes):
+            n = p.numel()
+            self.flat_p[o:o + n].copy_(p.data.reshape(-1))
+            p.data = self.flat_p[o:o + n].view(p.shape)
+            p.grad = self.flat_g[o:o + n].view(p.shape)
+            self._views.append((p, o, n))
+            o += s
+        self._params = ps
+
+    # gradients live in the flat buffer: zeroing is one memset and the views stay attached
+    def zero_grad(self, set_to_none: bool = False):
+        self.flat_g.zero_()
+        for p, o, n in self._views:
+            if p.grad is None or p.grad.data_ptr() != self.flat_g.data_ptr() + 4 * o:
+                p.grad = self.flat_g[o:o + n].view(p.shape)
+
+    def sync_grads(self):
+        """Data-parallel all-reduce of the flat gradient (SUM); averaging is folded into the Adam kernel."""
+        if self.comm is not None and self.comm.get_world_size() > 1:
+            self.comm.all_reduce(self.flat_g)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = closure() if closure is not None else None
+        for p, o, n in self._views:  # a grad that autograd re-allocated (first backward after set_to_none) is folded in
+            if p.grad is not None and p.grad.data_ptr() != self.flat_g.data_ptr() + 4 * o:
+                self.flat_g[o:o + n].add_(p.grad.reshape(-1))
+                p.grad = self.flat_g[o:o + n].view(p.shape)
+        self.sync_grads()
+        self._step += 1
+        g = self.param_groups[0]
+        W = self.comm.get_world_size() if (self.comm is not None and self.grad_average) else 1
+        lr, (b1, b2), eps, wd = g["lr"], g["betas"], g["eps"], g["weight_decay"]
+        if self.flat_p.is_cuda:
+            N.check(N.lib().dgb_adam_flat(N.ptr(self.flat_p), N.ptr(self.flat_g), N.ptr(self.flat_m), N.ptr(self.flat_v),
+                                          N.ptr(None), N.i64(self.flat_p.numel()), N.f32(lr), N.f32(b1), N.f32(b2),
+                                          N.f32(eps), N.f32(wd), N.f32(1.0 / W), N.i32(self._step), N.stream()),
+                    "dgb_adam_flat")
+            N.count_launch()
+        else:
+            gr = self.flat_g / W + wd * self.flat_p
+            self.flat_m.mul_(b1).add_(gr, alpha=1 - b1)
+            self.flat_v.mul_(b2).addcmul_(gr, gr, value=1 - b2)
+            c1, c2 = 1 - b1 ** self._step, 1 - b2 ** self._step
+            self.flat_p.sub_(lr * (self.flat_m / c1) / (self.flat_v.sqrt() / math.sqrt(c2) + eps))
+        return loss
+
+    # -- torch.optim.Adam-compatible checkpoint format ---------------------------------------------
+    def state_dict(self):
+        state = {}
+        for i, (p, o, n) in enumerate(self._views):
+            state[i] = {"step": torch.tensor(float(self._step)),
+                        "exp_avg": self.flat_m[o:o + n].view(p.shape).clone(),
+                        "exp_avg_sq": self.flat_v[o:o + n].view(p.shape).clone()}
+        groups = [{k: v for k, v in self.param_groups[0].items() if k != "params"}]
+        groups[0]["params"] = list(range(len(self._views)))
+        return {"state": state, "param_groups": groups}
+
+    def load_state_dict(self, sd):
+        for i, (p, o, n) in enumerate(self._views):
+            st = sd["state"].get(i, sd["state"].get(str(i)))
+            if st is None:
+                continue
+            self.flat_m[o:o + n].copy_(st["exp_avg"].reshape(-1))
+            self.flat_v[o:o + n].copy_(st["exp_avg_sq"].reshape(-1))
+            self._step = int(float(st["step"]))
+        for k, v in sd["param_groups"][0].items():
+            if k != "params":
+                self.param_groups[0][k] = v

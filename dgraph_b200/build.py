@@ -71,7 +71,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
     with cf.ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
         objs = list(ex.map(compile_one, srcs))
-    link = [nvcc, *ARCH_FLAGS, "-shared", "-o", str(LIB), *map(str, objs), "-lcuda", "-Xcompiler", "-fPIC"]
+    link = [nvcc, *ARCH_FLAGS, "-shared", "-o", str(LIB), *map(str, objs), "-Xcompiler", "-fPIC"]
     r = subprocess.run(link, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stderr[-4000:]}")

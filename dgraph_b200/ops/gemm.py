@@ -68,12 +68,14 @@ class _LinearTC(Function):
         if ctx.needs_input_grad[1]:
             dw = gemm_bf16_nn_grad_w(g, x)
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = g.float().sum(0).to(g.dtype)
+            db = g.float().sum(0)
         return dx, dw, db, None
 
 
 def linear(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor] = None, act=None) -> torch.Tensor:
     if _tc_ok(x, w):
+        if act == "silu" and torch.is_grad_enabled() and (x.requires_grad or w.requires_grad):
+            return F.silu(_LinearTC.apply(x, w, b, None))  # SiLU backward needs the pre-activation
         return _LinearTC.apply(x, w, b, act)
     if x.is_cuda:
         N.require_for(x)

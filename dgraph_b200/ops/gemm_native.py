@@ -1,0 +1,89 @@
+"""Launch wrappers for ``csrc/gemm_tcgen05.cu`` (tcgen05 / TMEM / TMA GEMM and gather-GEMM)."""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Sequence
+
+import torch
+
+from dgraph_b200.ops import _native as N
+
+_ACT = {None: 0, "none": 0, "relu": 1, "silu": 2}
+
+
+def _as_bf16_rowmajor(t: torch.Tensor) -> torch.Tensor:
+    """bf16, unit inner stride, 16-byte aligned base and row stride (TMA requirements)."""
+    if t.dtype != torch.bfloat16:
+        t = t.to(torch.bfloat16)
+    if t.stride(1) != 1 or t.stride(0) % 8 != 0 or t.data_ptr() % 16 != 0:
+        K = t.shape[1]
+        Kp = (K + 7) // 8 * 8
+        buf = torch.zeros((t.shape[0], Kp), dtype=torch.bfloat16, device=t.device)
+        buf[:, :K] = t
+        t = buf[:, :K] if Kp == K else buf
+    return t
+
+
+def gemm_bf16_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, act=None,
+                 out_dtype=torch.bfloat16, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``act(a @ b.T + bias)``; ``a [M, K]``, ``b [N, K]`` bf16.  Zero-padded extra K columns in either operand are fine."""
+    a, b = _as_bf16_rowmajor(a), _as_bf16_rowmajor(b)
+    M, K = a.shape[0], min(a.shape[1], b.shape[1]) if a.shape[1] != b.shape[1] else a.shape[1]
+    Nn = b.shape[0]
+    if out is None:
+        out = torch.empty((M, Nn), dtype=out_dtype, device=a.device)
+    assert out.stride(1) == 1 and out.dtype in (torch.bfloat16, torch.float32)
+    bias_f = None if bias is None else bias.float().contiguous()
+    N.check(N.lib().dgb_gemm_bf16_tn(N.ptr(a), N.i64(a.stride(0)), N.ptr(b), N.i64(b.stride(0)), N.ptr(out),
+                                     N.i64(out.stride(0)), N.i32(M), N.i32(Nn), N.i32(K), N.ptr(bias_f),
+                                     N.i32(_ACT[act]), N.i32(1 if out.dtype == torch.float32 else 0), N.stream()),
+            "dgb_gemm_bf16_tn")
+    N.count_launch()
+    return out
+
+
+def pack_segment_weight(w: torch.Tensor, seg_k: Sequence[int]) -> torch.Tensor:
+    """``w [N, sum(seg_k)]`` -> bf16 ``[N, sum(pad64(k))]`` with every segment's columns padded to a multiple of 64."""
+    parts, o = [], 0
+    for k in seg_k:
+        kp = (k + 63) // 64 * 64
+        seg = w[:, o:o + k].to(torch.bfloat16)
+        parts.append(torch.nn.functional.pad(seg, (0, kp - k)))
+        o += k
+    return torch.cat(parts, dim=1).contiguous()
+
+
+def gather_gemm_bf16(srcs: List[torch.Tensor], idxs: List[Optional[torch.Tensor]], w_packed: torch.Tensor,
+                     bias: Optional[torch.Tensor], M: int, seg_k: Sequence[int], act=None,
+                     out_dtype=torch.bfloat16) -> torch.Tensor:
+    """``act(cat([srcs[s][idxs[s]] for s], 1) @ W.T + bias)`` with the gather and the concat done inside the GEMM's
+    producer warps (F1b).  ``idxs[s] is None`` means row ``m`` of ``srcs[s]`` (per-edge features)."""
+    n = len(srcs)
+    assert 1 <= n <= 3
+    srcs = [_as_bf16_rowmajor(s) for s in srcs]
+    idx32 = [None if i is None else (i if i.dtype == torch.int32 else i.to(torch.int32)).contiguous() for i in idxs]
+    Nn = w_packed.shape[0]
+    out = torch.empty((M, Nn), dtype=out_dtype, device=w_packed.device)
+    bases = (ctypes.c_void_p * 3)(*[s.data_ptr() for s in srcs] + [0] * (3 - n))
+    lds = (ctypes.c_int64 * 3)(*[s.stride(0) for s in srcs] + [0] * (3 - n))
+    ips = (ctypes.c_void_p * 3)(*[(0 if i is None else i.data_ptr()) for i in idx32] + [0] * (3 - n))
+    ks = (ctypes.c_int * 3)(*[int(k) for k in seg_k] + [0] * (3 - n))
+    bias_f = None if bias is None else bias.float().contiguous()
+    N.check(N.lib().dgb_gather_gemm_bf16(N.i32(n), bases, lds, ips, ks, N.ptr(w_packed), N.i64(w_packed.stride(0)),
+                                         N.ptr(out), N.i64(out.stride(0)), N.i32(M), N.i32(Nn), N.ptr(bias_f),
+                                         N.i32(_ACT[act]), N.i32(1 if out_dtype == torch.float32 else 0), N.stream()),
+            "dgb_gather_gemm_bf16")
+    N.count_launch()
+    return out
+
+
+def gemm_bf16_nn_grad_w(g: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """Weight gradient ``g^T @ x`` (``[N, K]``; reduction over the huge row dimension).  Plain library GEMM (cuBLAS):
+    both operands are MN-major for this product; a split-K tcgen05 kernel is future work."""
+    return torch.matmul(g.t(), x[:, : x.shape[1]])
+
+
+def act_backward(g: torch.Tensor, y: torch.Tensor, act: str) -> torch.Tensor:
+    if act == "relu":
+        return g * (y > 0).to(g.dtype)
+    raise NotImplementedError(f"fused backward for activation {act}")

@@ -4,18 +4,20 @@
 // MLPs).  The reference reaches cuBLAS sgemm through nn.Linear (experiments/OGB/GCN.py:51-52,
 // experiments/GraphCast/layers.py:52-63); it has no tensor-core code at all.
 //
-// Roles (192 threads): warp 0 = TMA producer (A and B k-blocks, 128-B swizzle), warp 1 = MMA issuer (one elected
-// lane, tcgen05.mma cta_group::1, M=128 x N=BLOCK_N x K=16), warps 2..5 = epilogue (tcgen05.ld 32x32b -> bias ->
-// activation -> bf16/fp32 -> 16-byte global stores).  Two TMEM accumulator stages let the epilogue of tile i overlap
+// Roles (320 threads): warp 0 = TMA producer (A and B k-blocks, 128-B swizzle), warp 1 = MMA issuer (one elected
+// lane, tcgen05.mma cta_group::1, M=128 x N=BLOCK_N x K=16), warps 2..9 = epilogue (tcgen05.ld 32x32b -> smem-staged
+// bias -> compile-time activation -> bf16/fp32 -> 16-byte global stores; two warps per TMEM lane quarter).  Two TMEM accumulator stages let the epilogue of tile i overlap
 // the main loop of tile i+1; the smem ring has STAGES k-blocks in flight.  The gathered variant replaces the TMA
 // load of A by four producer warps that gather rows (local HBM or NVLink peer memory) into the same swizzled layout.
 #include "tc_common.cuh"
+#include <type_traits>
 
 namespace dgb {
 
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;  // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
+constexpr int MAX_N = 8192;  // bias for all N-tiles is staged in shared memory once per CTA
 
 enum Act { ACT_NONE = 0, ACT_RELU = 1, ACT_SILU = 2 };
 
@@ -40,25 +42,29 @@ struct SmemLayout {
   static constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (BLOCK_N >= 256) ? 4 : (BLOCK_N >= 128 ? 6 : 8);
-  static constexpr int BAR_BYTES = 1024;
+  static constexpr int BAR_BYTES = 256 + MAX_N * 4;  // mbarriers + tmem pointer, then the staged bias [MAX_N]
   static constexpr int TOTAL = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // + alignment slack
 };
 
-__device__ __forceinline__ float apply_act(float v, int act) {
-  if (act == ACT_RELU) return fmaxf(v, 0.f);
-  if (act == ACT_SILU) return v / (1.f + __expf(-v));
+template <int ACT>
+__device__ __forceinline__ float apply_act(float v) {
+  if (ACT == ACT_RELU) return fmaxf(v, 0.f);
+  if (ACT == ACT_SILU) return v / (1.f + __expf(-v));
   return v;
 }
 
-template <int BLOCK_N, bool OUT_F32, bool GATHER>
-__global__ void __launch_bounds__(GATHER ? 320 : 192, 1)
+constexpr int NUM_EPI_WARPS = 8;  // two warps per TMEM lane quarter, each owns half of the tile's columns
+constexpr int EPI_WARP0 = 2;
+constexpr int GATHER_WARP0 = EPI_WARP0 + NUM_EPI_WARPS;  // warps 10..13 when GATHER
+constexpr int THREADS_DENSE = (EPI_WARP0 + NUM_EPI_WARPS) * 32;
+constexpr int THREADS_GATHER = THREADS_DENSE + 128;
+
+template <int BLOCK_N, bool OUT_F32, bool GATHER, int ACT>
+__global__ void __launch_bounds__(GATHER ? THREADS_GATHER : THREADS_DENSE, 1)
 gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const GemmParams p) {
   using L = SmemLayout<BLOCK_N>;
   constexpr int STAGES = L::STAGES;
-  constexpr int NUM_EPI_WARPS = 4;
-  constexpr int EPI_WARP0 = 2;
-  constexpr int GATHER_WARP0 = 6;  // warps 6..9 when GATHER
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* bar_base = smem + STAGES * L::STAGE_BYTES;
@@ -67,6 +73,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   uint64_t* tmem_full = empty_bar + STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  float* s_bias = reinterpret_cast<float*>(bar_base + 256);  // [tiles_n * BLOCK_N] fp32, zero beyond N
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -99,6 +106,8 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     tc::tmem_alloc(tmem_ptr, 2 * BLOCK_N);
     tc::tmem_relinquish();
   }
+  // bias of every N-tile (N <= MAX_N is enforced by the host), zero padded up to the last tile's end
+  for (int i = threadIdx.x; i < tiles_n * BLOCK_N; i += blockDim.x) s_bias[i] = (p.bias && i < p.N) ? p.bias[i] : 0.f;
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
@@ -158,48 +167,64 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       }
     }
   } else if (warp < EPI_WARP0 + NUM_EPI_WARPS) {
-    // ===================== epilogue =====================
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    // ===================== epilogue: TMEM -> regs -> +bias -> act -> bf16/fp32 -> global =====================
+    const int q = warp & 3;                      // TMEM lane quarter this warp may access
+    const int half = (warp - EPI_WARP0) >> 2;    // which half of the tile's columns
+    constexpr int COLS = BLOCK_N / 2;            // columns per epilogue warp
+    constexpr int CH = (COLS >= 64) ? 64 : 32;   // columns per TMEM round trip
+    using OutT = typename std::conditional<OUT_F32, float, __nv_bfloat16>::type;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int m0 = (tile / tiles_n) * BLOCK_M;
-      const int n0 = (tile % tiles_n) * BLOCK_N;
+      const int nt = tile % tiles_n;
+      const int n0 = nt * BLOCK_N;
       const int as = it & 1;
       tc::mbar_wait(&tmem_full[as], (it >> 1) & 1);
       tc::tc_fence_after();
       const int row = m0 + q * 32 + lane;
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BLOCK_N;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BLOCK_N + half * COLS;
+      const uint32_t bias_sa = tc::smem_u32(s_bias + nt * BLOCK_N + half * COLS);
+      OutT* crow = reinterpret_cast<OutT*>(p.C) + (int64_t)row * p.ldc + n0 + half * COLS;
+      const bool row_ok = row < p.M;
+      const bool vec_ok = (reinterpret_cast<uintptr_t>(crow) & 15) == 0;
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N; c += 32) {
-        if (n0 + c >= p.N) break;  // warp-uniform
-        uint32_t r[32];
+      for (int c = 0; c < COLS; c += CH) {
+        const int ncol = p.N - (n0 + half * COLS + c);  // valid columns from here (may be <= 0 or > CH); warp-uniform
+        if (ncol <= 0) break;
+        uint32_t r[CH];
         tc::tmem_ld_32x32(taddr + c, r);
+        if (CH == 64) tc::tmem_ld_32x32(taddr + c + 32, r + 32);
         tc::tmem_ld_wait();
-        if (row < p.M) {
-          const int ncol = min(32, p.N - (n0 + c));
-          float v[32];
+        float v[CH];
 #pragma unroll
-          for (int t = 0; t < 32; ++t) {
-            float x = __uint_as_float(r[t]);
-            if (p.bias && t < ncol) x += __ldg(p.bias + n0 + c + t);
-            v[t] = apply_act(x, p.act);
-          }
-          if (OUT_F32) {
-            float* dst = reinterpret_cast<float*>(p.C) + (int64_t)row * p.ldc + n0 + c;
-            if (ncol == 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+        for (int t = 0; t < CH; t += 4) {
+          float4 b4;
+          asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                       : "=f"(b4.x), "=f"(b4.y), "=f"(b4.z), "=f"(b4.w)
+                       : "r"(bias_sa + (uint32_t)((c + t) * 4)));
+          v[t] = apply_act<ACT>(__uint_as_float(r[t]) + b4.x);
+          v[t + 1] = apply_act<ACT>(__uint_as_float(r[t + 1]) + b4.y);
+          v[t + 2] = apply_act<ACT>(__uint_as_float(r[t + 2]) + b4.z);
+          v[t + 3] = apply_act<ACT>(__uint_as_float(r[t + 3]) + b4.w);
+        }
+        if (row_ok) {
+          if (ncol >= CH && vec_ok) {
+            if (OUT_F32) {
 #pragma unroll
-              for (int t = 0; t < 32; t += 4)
-                *reinterpret_cast<float4*>(dst + t) = make_float4(v[t], v[t + 1], v[t + 2], v[t + 3]);
+              for (int t = 0; t < CH; t += 4)
+                *reinterpret_cast<float4*>(reinterpret_cast<float*>(crow) + c + t) =
+                    make_float4(v[t], v[t + 1], v[t + 2], v[t + 3]);
             } else {
-              for (int t = 0; t < ncol; ++t) dst[t] = v[t];
+#pragma unroll
+              for (int t = 0; t < CH; t += 8) stg_v4(reinterpret_cast<__nv_bfloat16*>(crow) + c + t, pack8(v + t));
             }
           } else {
-            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.C) + (int64_t)row * p.ldc + n0 + c;
-            if (ncol == 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
 #pragma unroll
-              for (int t = 0; t < 32; t += 8) stg_v4(dst + t, pack8(v + t));
-            } else {
-              for (int t = 0; t < ncol; ++t) dst[t] = __float2bfloat16_rn(v[t]);
+            for (int t = 0; t < CH; ++t) {
+              if (t < ncol) {
+                if (OUT_F32) reinterpret_cast<float*>(crow)[c + t] = v[t];
+                else reinterpret_cast<__nv_bfloat16*>(crow)[c + t] = __float2bfloat16_rn(v[t]);
+              }
             }
           }
         }
@@ -256,10 +281,10 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   if (warp == 2) tc::tmem_dealloc(tmem_base, 2 * BLOCK_N);
 }
 
-template <int BLOCK_N, bool OUT_F32, bool GATHER>
+template <int BLOCK_N, bool OUT_F32, bool GATHER, int ACT>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t stream) {
   using L = SmemLayout<BLOCK_N>;
-  auto kern = gemm_bf16_tn_kernel<BLOCK_N, OUT_F32, GATHER>;
+  auto kern = gemm_bf16_tn_kernel<BLOCK_N, OUT_F32, GATHER, ACT>;
   static bool configured = false;
   if (!configured) {
     DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
@@ -270,21 +295,30 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   DGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BLOCK_N - 1) / BLOCK_N);
   const int grid = tiles < sms ? tiles : sms;
-  kern<<<grid, GATHER ? 320 : 192, L::TOTAL, stream>>>(ta, tb, p);
+  kern<<<grid, GATHER ? THREADS_GATHER : THREADS_DENSE, L::TOTAL, stream>>>(ta, tb, p);
   DGB_CHECK_LAUNCH();
   return 0;
+}
+
+template <int BLOCK_N, bool GATHER>
+static int dispatch_act(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int out_f32, cudaStream_t s) {
+  if (out_f32) {  // fp32 output is only used for logits / loss inputs: no fused activation variants needed
+    if (p.act == ACT_NONE) return launch_gemm<BLOCK_N, true, GATHER, ACT_NONE>(ta, tb, p, s);
+    if (p.act == ACT_SILU) return launch_gemm<BLOCK_N, true, GATHER, ACT_SILU>(ta, tb, p, s);
+    return launch_gemm<BLOCK_N, true, GATHER, ACT_RELU>(ta, tb, p, s);
+  }
+  if (p.act == ACT_NONE) return launch_gemm<BLOCK_N, false, GATHER, ACT_NONE>(ta, tb, p, s);
+  if (p.act == ACT_SILU) return launch_gemm<BLOCK_N, false, GATHER, ACT_SILU>(ta, tb, p, s);
+  return launch_gemm<BLOCK_N, false, GATHER, ACT_RELU>(ta, tb, p, s);
 }
 
 template <bool GATHER>
 static int dispatch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int out_f32, int block_n,
                          cudaStream_t s) {
-#define DGB_GEMM_CASE(BN)                                                              \
-  if (block_n == BN)                                                                   \
-    return out_f32 ? launch_gemm<BN, true, GATHER>(ta, tb, p, s) : launch_gemm<BN, false, GATHER>(ta, tb, p, s);
-  DGB_GEMM_CASE(64)
-  DGB_GEMM_CASE(128)
-  DGB_GEMM_CASE(256)
-#undef DGB_GEMM_CASE
+  if (p.act < 0 || p.act > 2) return (int)cudaErrorInvalidValue;
+  if (block_n == 64) return dispatch_act<64, GATHER>(ta, tb, p, out_f32, s);
+  if (block_n == 128) return dispatch_act<128, GATHER>(ta, tb, p, out_f32, s);
+  if (block_n == 256) return dispatch_act<256, GATHER>(ta, tb, p, out_f32, s);
   return (int)cudaErrorInvalidValue;
 }
 
@@ -299,6 +333,7 @@ using namespace dgb;
 DGB_API int dgb_gemm_bf16_tn(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N,
                              int K, const float* bias, int act, int out_f32, void* stream) {
   if (M <= 0 || N <= 0 || K <= 0) return M == 0 || N == 0 ? 0 : (int)cudaErrorInvalidValue;
+  if (N > MAX_N) return (int)cudaErrorInvalidValue;
   if ((lda % 8) || (ldb % 8) || (reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15))
     return (int)cudaErrorInvalidValue;
   const int bn = pick_block_n(N);
@@ -319,7 +354,7 @@ DGB_API int dgb_gather_gemm_bf16(int n_seg, const void* const* seg_base, const i
                                  const int* seg_k, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N,
                                  const float* bias, int act, int out_f32, void* stream) {
   if (M <= 0 || N <= 0) return 0;
-  if (n_seg < 1 || n_seg > 3 || (ldw % 8)) return (int)cudaErrorInvalidValue;
+  if (n_seg < 1 || n_seg > 3 || (ldw % 8) || N > MAX_N) return (int)cudaErrorInvalidValue;
   GemmParams p{};
   p.M = M; p.N = N; p.bias = bias; p.C = C; p.ldc = ldc; p.act = act; p.n_seg = n_seg;
   int ktot = 0;

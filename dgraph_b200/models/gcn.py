@@ -84,13 +84,13 @@ class CommAwareGCN(nn.Module):
         kp = comm_pattern.kernel_plan(x.device) if self.conv1.fused else None
         edges = comm_pattern.local_edge_list
         with TimingReport("feature-exchange-1"):
-            halo = self.halo_exchanger(x, comm_pattern)
+            aug = self.halo_exchanger.augmented(x, comm_pattern)
         with TimingReport("process-1"):
-            x = self.conv1(torch.cat([x, halo], dim=0), edges, n, kernel_plan=kp)
+            x = self.conv1(aug, edges, n, kernel_plan=kp)
         with TimingReport("feature-exchange-2"):
-            halo = self.halo_exchanger(x, comm_pattern)
+            aug = self.halo_exchanger.augmented(x, comm_pattern)
         with TimingReport("process-2"):
-            x = self.conv2(torch.cat([x, halo], dim=0), edges, n, kernel_plan=kp)
+            x = self.conv2(aug, edges, n, kernel_plan=kp)
         with TimingReport("final-fc"):
             x = linear(x, self.fc.weight.to(x.dtype), self.fc.bias.to(x.dtype))
         return x

@@ -35,7 +35,16 @@ class FusedAdam(torch.optim.Optimizer):
         sizes = [(p.numel() + 3) // 4 * 4 for p in ps]  # keep every view 16-byte aligned
         total = sum(sizes)
         self.flat_p = torch.zeros(total, dtype=torch.float32, device=dev)
-        self.flat_g = torch.zeros(total, dtype=torch.float32, device=dev)
+        # peer-memory engine: gradients live in the symmetric arena so the Adam kernel can sum all ranks' buffers itself
+        self._peer = None
+        eng = getattr(comm, "engine", None)
+        if eng is not None and hasattr(eng, "adam_allreduce") and comm.get_world_size() > 1 and dev.type == "cuda":
+            self._peer = eng
+            self.flat_g, self._g_off = eng.symmetric_flat("adam_grad", total)
+            self.flat_g = self.flat_g[:total]
+            self.flat_g.zero_()
+        else:
+            self.flat_g = torch.zeros(total, dtype=torch.float32, device=dev)
         self.flat_m = torch.zeros(total, dtype=torch.float32, device=dev)
         self.flat_v = torch.zeros(total, dtype=torch.float32, device=dev)
         self._views = []
@@ -68,11 +77,15 @@ class FusedAdam(torch.optim.Optimizer):
             if p.grad is not None and p.grad.data_ptr() != self.flat_g.data_ptr() + 4 * o:
                 self.flat_g[o:o + n].add_(p.grad.reshape(-1))
                 p.grad = self.flat_g[o:o + n].view(p.shape)
-        self.sync_grads()
         self._step += 1
         g = self.param_groups[0]
         W = self.comm.get_world_size() if (self.comm is not None and self.grad_average) else 1
         lr, (b1, b2), eps, wd = g["lr"], g["betas"], g["eps"], g["weight_decay"]
+        if self._peer is not None:  # ONE kernel: sum of all ranks' gradients over NVLink + Adam
+            self._peer.adam_allreduce(self.flat_p, self._g_off, self.flat_m, self.flat_v, self.flat_p.numel(), lr, b1,
+                                      b2, eps, wd, 1.0 / W, self._step)
+            return loss
+        self.sync_grads()
         if self.flat_p.is_cuda:
             N.check(N.lib().dgb_adam_flat(N.ptr(self.flat_p), N.ptr(self.flat_g), N.ptr(self.flat_m), N.ptr(self.flat_v),
                                           N.ptr(None), N.i64(self.flat_p.numel()), N.f32(lr), N.f32(b1), N.f32(b2),

@@ -50,11 +50,26 @@ class HaloExchange:
     def __init__(self, comm):
         self.comm = comm
 
-    def __call__(self, x_local: torch.Tensor, comm_pattern: CommunicationPattern) -> torch.Tensor:
+    def _fused_engine(self, x_local):
         engine = getattr(self.comm, "engine", None)
-        fused = getattr(engine, "halo_exchange", None)
-        if fused is not None and x_local.is_cuda:
-            return fused(x_local, comm_pattern)
+        ok = (engine is not None and hasattr(engine, "halo_exchange_aug") and x_local.is_cuda
+              and x_local.dtype == torch.bfloat16 and x_local.dim() == 2 and (x_local.shape[1] * 2) % 16 == 0)
+        return engine if ok else None
+
+    def augmented(self, x_local: torch.Tensor, comm_pattern: CommunicationPattern) -> torch.Tensor:
+        """``cat([x_local, halo])`` -- on the peer-memory engine this is one symmetric buffer filled by ONE pull
+        kernel (no ``cat`` copy); elsewhere it is the reference's exchange followed by ``torch.cat``."""
+        engine = self._fused_engine(x_local)
+        if engine is not None:
+            return engine.halo_exchange_aug(x_local, comm_pattern)
+        if comm_pattern.world_size == 1 and comm_pattern.num_halo_vertices == 0:
+            return x_local
+        return torch.cat([x_local, self(x_local, comm_pattern)], dim=0)
+
+    def __call__(self, x_local: torch.Tensor, comm_pattern: CommunicationPattern) -> torch.Tensor:
+        engine = self._fused_engine(x_local)
+        if engine is not None:
+            return engine.halo_exchange(x_local, comm_pattern)
         # plain indexing on purpose: autograd's index backward does the scatter-add of rows sent to several ranks
         send = x_local[comm_pattern.send_local_idx]
         return HaloExchangeImpl.apply(send, self.comm, comm_pattern)

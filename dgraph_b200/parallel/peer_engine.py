@@ -1,0 +1,341 @@
+"""Peer-memory engine: the sm_100a communication path (NVLink loads issued from inside the kernels).
+
+Replaces all three reference back-ends on a B200 box: NCCL ``put`` = ``all_to_all_single``
+(``nccl/NCCLBackendEngine.py:281-306``), MPI RMA windows and the NVSHMEM extension
+(``nvshmem/NVSHMEMBackendEngine.py:22-160``, ``csrc/torch_nvshmem_p2p.cu``).  ``torch.distributed`` (NCCL) is kept
+for bootstrap, plan-build metadata and as the generic fallback for arbitrary ``put`` calls; every hot exchange is a
+pull kernel over a **symmetric arena**:
+
+* one ``cudaMalloc`` per rank at start-up, exported through CUDA IPC and mapped by all peers (``csrc/peer.cu``);
+* named persistent *slots* inside the arena at identical offsets on all ranks, so a peer address is
+  ``peer_base[r] + offset`` and nothing is allocated or registered on the hot path;
+* a 64-entry signal pad for epoch-flag barriers that run as tiny kernels **on the compute stream** (no host sync).
+
+Halo exchange forward  = copy ``x`` into the slot's first rows, barrier, ONE pull kernel that writes the halo rows
+right behind them -> the slot *is* ``cat([x, halo])``.  Backward = copy halo-row gradients into a slot, barrier, ONE
+deterministic pull-reduce kernel on the owners.  Gradient all-reduce + Adam = ONE kernel reading all peers' flat
+gradient buffers.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+from torch.autograd import Function
+
+from dgraph_b200.ops import _native as N
+from dgraph_b200.parallel.collective_engine import TorchDistEngine
+
+_ALIGN = 256
+
+
+class _DevMem:
+    """Wraps a raw device range for ``torch.as_tensor`` (the tensor keeps ``owner`` alive)."""
+
+    def __init__(self, ptr: int, nbytes: int, owner=None):
+        self.owner = owner
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+def tensor_from_ptr(ptr: int, shape, dtype, device, owner=None) -> torch.Tensor:
+    n = 1
+    for s in shape:
+        n *= int(s)
+    nbytes = n * torch.empty((), dtype=dtype).element_size()
+    if nbytes == 0:
+        return torch.empty(shape, dtype=dtype, device=device)
+    t = torch.as_tensor(_DevMem(ptr, nbytes, owner), device=device)
+    return t.view(dtype).view(shape)
+
+
+class SymmetricArena:
+    """One device allocation per rank, mapped into every peer; bump-allocated named slots at symmetric offsets."""
+
+    def __init__(self, nbytes: int, rank: int, world: int, device: torch.device, group=None, local_ptrs: Optional[List[int]] = None):
+        self.rank, self.world, self.device, self.nbytes = rank, world, device, int(nbytes)
+        self._slots: Dict[str, Tuple[int, int]] = {}
+        self._top = _ALIGN  # first 256 bytes: signal pad
+        lib = N.lib()
+        if local_ptrs is not None:  # in-process emulation: all "ranks" are arenas of this process
+            self.base = local_ptrs[rank]
+            self.peer_bases = list(local_ptrs)
+            self._owned = False
+        else:
+            p = ctypes.c_void_p()
+            N.check(lib.dgb_symm_alloc(ctypes.c_size_t(self.nbytes), ctypes.byref(p)), "dgb_symm_alloc")
+            self.base = p.value
+            self._owned = True
+            handle = (ctypes.c_ubyte * 64)()
+            N.check(lib.dgb_symm_export(ctypes.c_void_p(self.base), handle), "dgb_symm_export")
+            mine = torch.tensor(list(handle), dtype=torch.uint8, device=device)
+            allh = [torch.zeros(64, dtype=torch.uint8, device=device) for _ in range(world)]
+            dist.all_gather(allh, mine, group=group)
+            self.peer_bases = []
+            for r in range(world):
+                if r == rank:
+                    self.peer_bases.append(self.base)
+                    continue
+                hb = (ctypes.c_ubyte * 64)(*allh[r].cpu().tolist())
+                q = ctypes.c_void_p()
+                N.check(lib.dgb_symm_import(hb, ctypes.byref(q)), f"dgb_symm_import(rank {r})")
+                self.peer_bases.append(q.value)
+        self._ptr_tables: Dict[int, torch.Tensor] = {}
+        self.pad_table = self.ptr_table(0)
+
+    def ptr_table(self, offset: int) -> torch.Tensor:
+        """Device array ``[W]`` of ``peer_base[r] + offset`` (int64 == pointer)."""
+        t = self._ptr_tables.get(offset)
+        if t is None:
+            t = torch.tensor([b + offset for b in self.peer_bases], dtype=torch.int64, device=self.device)
+            self._ptr_tables[offset] = t
+        return t
+
+    def slot(self, name: str, nbytes: int) -> int:
+        """Offset of the named slot (allocated on first use; ``nbytes`` must be the same on all ranks)."""
+        s = self._slots.get(name)
+        if s is not None and s[1] >= nbytes:
+            return s[0]
+        if s is not None:
+            raise RuntimeError(f"symmetric slot {name} would have to grow from {s[1]} to {nbytes} bytes")
+        off = (self._top + _ALIGN - 1) // _ALIGN * _ALIGN
+        if off + nbytes > self.nbytes:
+            raise RuntimeError(
+                f"symmetric arena exhausted ({self.nbytes >> 20} MiB): set DGRAPH_B200_ARENA_MB (need {nbytes >> 20} MiB more)")
+        self._slots[name] = (off, nbytes)
+        self._top = off + nbytes
+        return off
+
+    def tensor(self, offset: int, shape, dtype) -> torch.Tensor:
+        return tensor_from_ptr(self.base + offset, shape, dtype, self.device, owner=self)
+
+    def close(self):
+        if self._owned and self.base:
+            lib = N.lib()
+            for r, b in enumerate(self.peer_bases):
+                if r != self.rank and b:
+                    lib.dgb_symm_unmap(ctypes.c_void_p(b))
+            lib.dgb_symm_free(ctypes.c_void_p(self.base))
+            self.base = 0
+
+
+class _PatternPeerInfo:
+    """Per-pattern device tables for the pull kernels (built once)."""
+
+    def __init__(self, engine: "PeerMemoryEngine", pat):
+        dev = engine.device
+        W, r = engine.get_world_size(), engine.get_rank()
+        self.n_local = pat.num_local_vertices
+        self.n_nbr_local = pat.num_neighbor_local_vertices if pat.num_neighbor_local_vertices is not None else pat.num_local_vertices
+        self.n_halo = pat.num_halo_vertices
+        self.halo_owner = pat.halo_owner.to(dev, torch.int32).contiguous()
+        self.halo_row = pat.halo_remote_row.to(dev, torch.int32).contiguous()
+        counts = engine.all_gather_ints([self.n_nbr_local, self.n_halo, int(pat.send_offset[-1])])
+        self.nbr_local_all = [c[0] for c in counts]
+        self.max_aug = max(c[0] + c[1] for c in counts)
+        self.max_halo = max(c[1] for c in counts)
+        # backward: boundary rows of mine and where their halo copies live on the consumers
+        so = pat.send_offset.tolist()
+        send_idx = pat.send_local_idx.to("cpu", torch.long)
+        fwd_off = pat.put_forward_remote_offset.tolist()  # my segment's start inside rank d's halo range
+        ranks, srows = [], []
+        for d in range(W):
+            k = so[d + 1] - so[d]
+            if k:
+                ranks.append(torch.full((k,), d, dtype=torch.long))
+                srows.append(torch.arange(k, dtype=torch.long) + fwd_off[d])  # row inside d's halo-gradient slot
+        if ranks:
+            ranks, srows = torch.cat(ranks), torch.cat(srows)
+            order = torch.argsort(send_idx, stable=True)
+            rows_sorted = send_idx[order]
+            uniq, cnt = torch.unique_consecutive(rows_sorted, return_counts=True)
+            ptr = torch.zeros(uniq.numel() + 1, dtype=torch.long)
+            ptr[1:] = cnt.cumsum(0)
+            self.bnd_row = uniq.to(dev, torch.int32)
+            self.bnd_ptr = ptr.to(dev, torch.int32)
+            self.src_rank = ranks[order].to(dev, torch.int32)
+            self.src_row = srows[order].to(dev, torch.int32)
+        else:
+            z = torch.zeros(0, dtype=torch.int32, device=dev)
+            self.bnd_row, self.src_rank, self.src_row = z, z, z
+            self.bnd_ptr = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.n_bnd = int(self.bnd_row.numel())
+
+
+class _HaloAug(Function):
+    """``aug = cat([x, halo(x)])`` through the symmetric arena; backward pull-reduces halo gradients on the owners."""
+
+    @staticmethod
+    def forward(ctx, x, engine, pat):
+        info = engine.pattern_info(pat)
+        F = x.shape[1]
+        assert x.dim() == 2 and (F * x.element_size()) % 16 == 0, "feature rows must be multiples of 16 bytes"
+        aug, off = engine.slot_tensor(("halo_fwd", id(pat)), (info.max_aug, F), x.dtype, ring=True,
+                                      track=torch.is_grad_enabled() and x.requires_grad)
+        aug = aug[: info.n_nbr_local + info.n_halo]
+        aug[: info.n_nbr_local].copy_(x)
+        engine.barrier_on_stream()
+        rb = F * x.element_size()
+        N.check(N.lib().dgb_halo_pull(N.ptr(aug[info.n_nbr_local:]), N.i64(rb), N.i64(info.n_halo), N.i32(rb),
+                                      N.ptr(engine.arena.ptr_table(off)), N.i64(rb), N.ptr(info.halo_owner),
+                                      N.ptr(info.halo_row), N.stream()), "dgb_halo_pull")
+        N.count_launch(2)
+        engine.mark_read(off)
+        ctx.engine, ctx.pat, ctx.slot_key = engine, pat, (("halo_fwd", id(pat)), off)
+        return aug
+
+    @staticmethod
+    def backward(ctx, g_aug):
+        engine, pat = ctx.engine, ctx.pat
+        info = engine.pattern_info(pat)
+        engine.release_slot(*ctx.slot_key)
+        F = g_aug.shape[1]
+        g_aug = g_aug.contiguous()
+        assert g_aug.dtype == torch.bfloat16, "halo gradient reduce kernel is bf16 (fp32 accumulate)"
+        gh, off = engine.slot_tensor(("halo_bwd", id(pat)), (info.max_halo, F), g_aug.dtype, ring=False)
+        gh[: info.n_halo].copy_(g_aug[info.n_nbr_local:])
+        engine.barrier_on_stream()
+        gx = g_aug[: info.n_nbr_local].clone()
+        N.check(N.lib().dgb_halo_grad_reduce(N.ptr(gx), N.i64(F), N.ptr(g_aug), N.i64(F), N.i32(F), N.i64(info.n_bnd),
+                                             N.ptr(info.bnd_row), N.ptr(info.bnd_ptr), N.ptr(info.src_rank),
+                                             N.ptr(info.src_row), N.ptr(engine.arena.ptr_table(off)), N.i64(F),
+                                             N.stream()), "dgb_halo_grad_reduce")
+        N.count_launch(2)
+        engine.mark_read(off)  # the next writer of this slot inserts a barrier only if none happened in between
+        return gx, None, None
+
+
+class PeerMemoryEngine(TorchDistEngine):
+    def __init__(self, ranks_per_graph: int = -1, arena_mb: Optional[int] = None, group=None, **kwargs):
+        super().__init__(dist_backend="nccl", ranks_per_graph=ranks_per_graph, group=group, **kwargs)
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        N.lib()
+        self._epoch = 0
+        self._infos: Dict[int, _PatternPeerInfo] = {}
+        self._rings: Dict[Tuple, List] = {}
+        self._by_off: Dict[int, dict] = {}
+        self._timeout_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.arena: Optional[SymmetricArena] = None
+        if self._world > 1:
+            mb = arena_mb or int(os.environ.get("DGRAPH_B200_ARENA_MB", "8192"))
+            self.arena = SymmetricArena(mb << 20, self._rank, self._world, self.device, group=self._group)
+            dist.barrier(group=self._group)
+
+    # ---- small host-side helpers ---------------------------------------------------------------
+    def all_gather_ints(self, vals: List[int]) -> List[List[int]]:
+        if self._world == 1:
+            return [list(vals)]
+        t = torch.tensor(vals, dtype=torch.long, device=self.device)
+        out = [torch.zeros_like(t) for _ in range(self._world)]
+        dist.all_gather(out, t, group=self._group)
+        return [o.tolist() for o in out]
+
+    def pattern_info(self, pat) -> _PatternPeerInfo:
+        i = self._infos.get(id(pat))
+        if i is None:
+            i = _PatternPeerInfo(self, pat)
+            self._infos[id(pat)] = i
+        return i
+
+    # ---- symmetric slots -----------------------------------------------------------------------
+    def slot_tensor(self, key, shape, dtype, ring: bool = False, track: bool = False):
+        """Persistent symmetric tensor for ``key``.  ``ring=True``: rotate over entries so that a buffer saved for
+        backward is never overwritten by the next forward call with the same key (entries are added on demand; all
+        ranks execute the same program, so they grow their rings in lock-step and offsets stay symmetric)."""
+        nbytes = int(torch.empty((), dtype=dtype).element_size())
+        for s in shape:
+            nbytes *= int(s)
+        rk = (key, tuple(shape), dtype)
+        entries = self._rings.setdefault(rk, [])
+        pick = None
+        if ring:
+            for e in entries:
+                if not e["busy"]:
+                    pick = e
+                    break
+        elif entries:
+            pick = entries[0]
+        if pick is None:
+            off = self.arena.slot(f"{rk}#{len(entries)}", max(nbytes, 16))
+            pick = {"off": off, "busy": False, "read_epoch": -1}
+            entries.append(pick)
+        if ring and track:
+            pick["busy"] = True
+        # peers read this slot during epoch `read_epoch`; they are provably done once any later barrier has completed
+        if pick["read_epoch"] == self._epoch:
+            self.barrier_on_stream()
+        self._by_off[pick["off"]] = pick
+        return self.arena.tensor(pick["off"], shape, dtype), pick["off"]
+
+    def mark_read(self, off):
+        """Record that peers read slot ``off`` after the latest barrier (see ``slot_tensor``)."""
+        self._by_off[off]["read_epoch"] = self._epoch
+
+    def release_slot(self, key, off):
+        for rk, entries in self._rings.items():
+            if rk[0] == key:
+                for e in entries:
+                    if e["off"] == off:
+                        e["busy"] = False
+
+    def new_step(self):
+        """Mark every ring entry reusable (call once per training step when running without autograd)."""
+        for entries in self._rings.values():
+            for e in entries:
+                e["busy"] = False
+
+    def allocate_buffer(self, size, dtype, device):
+        return torch.empty(size, dtype=dtype, device=device)
+
+    # ---- ordering --------------------------------------------------------------------------------
+    def barrier_on_stream(self):
+        """All ranks' streams have reached this point (epoch-flag barrier kernel; no host synchronisation)."""
+        if self._world == 1:
+            return
+        self._epoch += 1
+        N.check(N.lib().dgb_peer_barrier(N.ptr(self.arena.pad_table), N.i32(self._rank), N.i32(self._world),
+                                         ctypes.c_uint(self._epoch & 0xFFFFFFFF), N.ptr(self._timeout_flag),
+                                         ctypes.c_longlong(int(os.environ.get("DGRAPH_B200_BARRIER_SPINS", str(1 << 26)))),
+                                         N.stream()), "dgb_peer_barrier")
+
+    def check_timeouts(self):
+        if int(self._timeout_flag.item()) != 0:
+            raise RuntimeError("peer barrier timed out (a rank did not arrive)")
+
+    # ---- fused halo exchange ---------------------------------------------------------------------
+    def halo_exchange_aug(self, x: torch.Tensor, pat) -> torch.Tensor:
+        """``cat([x, halo])`` as one symmetric buffer (rows ``[0, n_local)`` = ``x``)."""
+        if self._world == 1:
+            return x
+        return _HaloAug.apply(x, self, pat)
+
+    def halo_exchange(self, x: torch.Tensor, pat) -> torch.Tensor:
+        if self._world == 1:
+            return x.new_zeros((0, x.shape[1]))
+        info = self.pattern_info(pat)
+        return self.halo_exchange_aug(x, pat)[info.n_nbr_local:]
+
+    # ---- fused gradient all-reduce + Adam ----------------------------------------------------------
+    def symmetric_flat(self, key: str, numel: int, dtype=torch.float32) -> Tuple[torch.Tensor, int]:
+        n = (numel + 3) // 4 * 4
+        mx = max(c[0] for c in self.all_gather_ints([n]))
+        return self.slot_tensor(("flat", key), (mx,), dtype)
+
+    def adam_allreduce(self, flat_p, flat_g_off, flat_m, flat_v, n, lr, b1, b2, eps, wd, grad_scale, step):
+        self.barrier_on_stream()  # every rank finished writing its gradients
+        N.check(N.lib().dgb_adam_allreduce(N.ptr(flat_p), N.ptr(self.arena.ptr_table(flat_g_off)), N.i32(self._world),
+                                           N.ptr(flat_m), N.ptr(flat_v), N.ptr(None), N.i64(n), N.f32(lr), N.f32(b1),
+                                           N.f32(b2), N.f32(eps), N.f32(wd), N.f32(grad_scale), N.i32(step), N.stream()),
+                "dgb_adam_allreduce")
+        N.count_launch(2)
+        self.barrier_on_stream()  # nobody zeroes its gradient buffer while a peer is still reading it
+
+    def finalize(self) -> None:
+        if self.arena is not None:
+            torch.cuda.synchronize()
+            if dist.is_initialized():
+                dist.barrier(group=self._group)
+            self.arena.close()
+            self.arena = None

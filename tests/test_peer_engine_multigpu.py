@@ -1,0 +1,119 @@
+"""Real multi-process, multi-GPU run of the peer-memory engine (needs >= 2 GPUs; skipped otherwise)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+from tests._graphs import random_graph, partition
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu, pytest.mark.timeout(300)]
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, W, port, e, part, xg, yg, state, ret):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(W),
+                      DGRAPH_B200_ARENA_MB="256")
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=W, device_id=dev)
+    from dgraph_b200 import Communicator
+    from dgraph_b200.models.gcn import CommAwareGCN
+    from dgraph_b200.optim import FusedAdam
+    from dgraph_b200.parallel import HaloExchange, build_communication_pattern
+    from dgraph_b200.parallel.peer_engine import PeerMemoryEngine
+
+    comm = Communicator.init_process_group("nccl")
+    assert isinstance(comm.engine, PeerMemoryEngine)
+    pat = build_communication_pattern(e.to(dev), part.to(dev), rank, W)
+    gids = pat.local_vertices_global
+    x = xg.to(dev)[gids].bfloat16().requires_grad_(True)
+    ex = HaloExchange(comm)
+    aug = ex.augmented(x, pat)
+    want = xg.to(dev)[torch.cat([gids, pat.halo_vertices_global])].bfloat16()
+    ok = torch.equal(aug.detach(), want)
+    w = torch.arange(aug.shape[0], device=dev, dtype=torch.float32).remainder(7).add(1).bfloat16().unsqueeze(1)
+    (aug * w).sum().backward()
+    # oracle for the halo backward: every consumer of vertex v contributes its row weight
+    full = torch.zeros(xg.shape[0], device=dev)
+    allw = [torch.zeros(xg.shape[0], device=dev) for _ in range(W)]
+    mine = torch.zeros(xg.shape[0], device=dev)
+    mine.index_add_(0, torch.cat([gids, pat.halo_vertices_global]), w.float().squeeze(1))
+    dist.all_gather(allw, mine)
+    full = sum(allw)
+    ok = ok and torch.allclose(x.grad.float()[:, 0], full[gids], rtol=2e-2, atol=2e-2)
+
+    # 3 training steps must match the single-process run on the whole graph
+    torch.manual_seed(0)
+    model = CommAwareGCN(xg.shape[1], 64, 5, ex, comm, compute_dtype=torch.bfloat16).to(dev)
+    model.load_state_dict(state)
+    opt = FusedAdam(model.parameters(), lr=1e-2, comm=comm)
+    xl, yl = xg.to(dev)[gids].bfloat16(), yg.to(dev)[gids]
+    losses = []
+    for _ in range(3):
+        opt.zero_grad()
+        out = model(xl, pat)
+        loss = torch.nn.functional.cross_entropy(out.float(), yl, reduction="sum") / xg.shape[0] * W
+        loss.backward()
+        opt.step()
+        l = loss.detach().clone() / W
+        dist.all_reduce(l)
+        losses.append(float(l))
+    comm.engine.check_timeouts()
+    ret[rank] = (bool(ok), losses, {k: v.detach().cpu() for k, v in model.state_dict().items()})
+    comm.destroy()
+    comm.engine.finalize()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("W", [2])
+def test_peer_engine_halo_and_training(W):
+    if torch.cuda.device_count() < W:
+        pytest.skip(f"needs {W} GPUs")
+    from dgraph_b200.models.gcn import CommAwareGCN
+    from dgraph_b200.optim import FusedAdam
+    from dgraph_b200.communicator import Communicator
+    from dgraph_b200.parallel import HaloExchange, build_communication_pattern
+    from dgraph_b200.parallel.local_engine import LocalEngine
+
+    torch.manual_seed(0)
+    V, F = 2000, 32
+    e = random_graph(V, 8, seed=11)
+    part = partition(V, W, "contiguous")
+    xg = torch.randn(V, F)
+    yg = torch.randint(0, 5, (V,))
+    ref = CommAwareGCN(F, 64, 5, None, None)
+    state = {k: v.clone() for k, v in ref.state_dict().items()}
+    # single-process oracle on GPU 0
+    dev = torch.device("cuda", 0)
+    comm = Communicator._from_engine(LocalEngine(), backend="single")
+    pat = build_communication_pattern(e.to(dev), torch.zeros(V, dtype=torch.long, device=dev), 0, 1)
+    m = CommAwareGCN(F, 64, 5, HaloExchange(comm), comm, compute_dtype=torch.bfloat16).to(dev)
+    m.load_state_dict(state)
+    opt = FusedAdam(m.parameters(), lr=1e-2)
+    single = []
+    for _ in range(3):
+        opt.zero_grad()
+        loss = torch.nn.functional.cross_entropy(m(xg.to(dev).bfloat16(), pat).float(), yg.to(dev), reduction="sum") / V
+        loss.backward()
+        opt.step()
+        single.append(float(loss))
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker, args=(W, _free_port(), e, part, xg, yg, state, ret), nprocs=W, join=True)
+    for r in range(W):
+        ok, losses, sd = ret[r]
+        assert ok
+        assert torch.allclose(torch.tensor(losses), torch.tensor(single), rtol=3e-2, atol=3e-2), (losses, single)
+        for k, v in sd.items():
+            assert torch.allclose(v, m.state_dict()[k].cpu(), rtol=5e-2, atol=5e-3), k

@@ -37,13 +37,27 @@ __device__ __forceinline__ uint4 ldg_v4(const void* p) {
                : "l"(p));
   return r;
 }
-// keep-in-L2 gather load (rows are re-read by other warps)
-__device__ __forceinline__ uint4 ldg_evict_last_v4(const void* p) {
+// L2 eviction policies (createpolicy + .L2::cache_hint): gathered rows that other warps re-read are kept
+// (evict_last); read-once streams are dropped first (evict_first).
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint4 ldg_hint_v4(const void* p, uint64_t pol) {
   uint4 r;
-  asm volatile("ld.global.nc.L1::no_allocate.L2::evict_last.v4.u32 {%0,%1,%2,%3}, [%4];"
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "l"(p));
+               : "l"(p), "l"(pol));
   return r;
+}
+__device__ __forceinline__ void stg_cs_u8(void* p, uint32_t v) {
+  asm volatile("st.global.cs.u8 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ void stg_v4(void* p, const uint4& v) {
   asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)

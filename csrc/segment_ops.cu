@@ -14,7 +14,7 @@
 
 namespace dgb {
 
-enum SegMode { SEG_SUM = 0, SEG_ADD_RELU = 1, SEG_ADD_RELU_BWD = 2 };
+enum SegMode { SEG_SUM = 0, SEG_ADD_RELU = 1, SEG_ADD_RELU_BWD = 2, SEG_MASKED_SUM = 3 };
 
 struct SegParams {
   // CSR (or CSC) structure: segment r covers slots [ptr[r], ptr[r+1]) of idx
@@ -22,12 +22,12 @@ struct SegParams {
   const int* idx;
   int64_t n_rows;
   int H;  // columns (bf16), multiple of 8
-  // gathered operand (rows indexed by idx)
+  // gathered operand (rows indexed by idx); byte strides fit in 32 bits (checked on the host)
   const __nv_bfloat16* src;
-  int64_t ld_src;
+  uint32_t ld_src_b;
   // second gathered operand (SEG_ADD_RELU_BWD: P rows indexed by idx)
   const __nv_bfloat16* src2;
-  int64_t ld_src2;
+  uint32_t ld_src2_b;
   // per-output-row operand (SEG_ADD_RELU: P[r]; SEG_ADD_RELU_BWD: Q[r])
   const __nv_bfloat16* rowop;
   int64_t ld_rowop;
@@ -39,28 +39,65 @@ struct SegParams {
   int64_t ld_out;
   unsigned short* cnt;  // SEG_ADD_RELU: number of active (pre-activation > 0) edges per (row, col); may be null
   int64_t ld_cnt;
+  // ReLU bit masks, one byte per (edge slot, 8-column chunk): written by SEG_ADD_RELU (indexed by this walk's slot),
+  // read by SEG_MASKED_SUM through slot_map (slot of the *forward* walk for each slot of this walk)
+  unsigned char* mask;
+  const int* slot_map;
   // halo pull: rows >= n_local of `src` live on peers
   int64_t n_local;
   const __nv_bfloat16* const* peer_base;  // [W] base pointer of the same matrix on every rank
   const int* halo_owner;                  // [n_halo]
   const int* halo_row;                    // [n_halo] row inside the owner's matrix
-  int64_t ld_peer;
+  uint32_t ld_peer_b;
 };
 
 template <bool HALO>
-__device__ __forceinline__ const __nv_bfloat16* src_row(const SegParams& p, int j) {
+__device__ __forceinline__ const char* src_row(const SegParams& p, const char* src_lane, uint32_t lane_off, int j) {
   if (HALO) {
     if (j >= p.n_local) {
       const int h = j - (int)p.n_local;
-      return p.peer_base[p.halo_owner[h]] + (int64_t)p.halo_row[h] * p.ld_peer;
+      return reinterpret_cast<const char*>(p.peer_base[p.halo_owner[h]]) + (uint64_t)(uint32_t)p.halo_row[h] * p.ld_peer_b +
+             lane_off;
     }
   }
-  return p.src + (int64_t)j * p.ld_src;
+  return src_lane + (uint64_t)(uint32_t)j * p.ld_src_b;  // one IMAD.WIDE.U32
+}
+
+// One edge worth of work for one lane chunk (8 columns).
+template <int MODE>
+__device__ __forceinline__ void seg_accumulate(const uint4& v, const uint4& v2, const float* rop, float w, uint32_t mbyte,
+                                               float* acc, uint32_t* cn2, uint32_t& mout) {
+  float f[8];
+  unpack8(v, f);
+  if (MODE == SEG_SUM) {
+#pragma unroll
+    for (int t = 0; t < 8; ++t) acc[t] = fmaf(w, f[t], acc[t]);
+  } else if (MODE == SEG_ADD_RELU) {
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      const float m = rop[t] + f[t];
+      if (m > 0.f) {  // predicated: FADD + IADD + LOP3
+        acc[t] += m;
+        cn2[t >> 1] += (t & 1) ? 0x10000u : 1u;
+        mout |= (1u << t);
+      }
+    }
+  } else if (MODE == SEG_ADD_RELU_BWD) {  // f = dOut[i], f2 = P[i], rop = Q[j]
+    float f2[8];
+    unpack8(v2, f2);
+#pragma unroll
+    for (int t = 0; t < 8; ++t)
+      if (f2[t] + rop[t] > 0.f) acc[t] += f[t];
+  } else {  // SEG_MASKED_SUM
+#pragma unroll
+    for (int t = 0; t < 8; ++t)
+      if (mbyte & (1u << t)) acc[t] += f[t];
+  }
 }
 
 template <int MODE, int G, int NC, bool HALO>
 __global__ void __launch_bounds__(256) seg_reduce_kernel(const SegParams p) {
-  constexpr int UNROLL = 4;
+  constexpr int UNROLL = (NC == 1 && MODE == SEG_SUM) ? 8 : 4;
   const int lane = threadIdx.x & 31;
   const int g = lane & (G - 1);
   const int sub = lane / G;
@@ -68,79 +105,85 @@ __global__ void __launch_bounds__(256) seg_reduce_kernel(const SegParams p) {
   const int64_t r = warp * (32 / G) + sub;
   if (r >= p.n_rows) return;
   const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (sub * G));
+  const int nchunk = p.H >> 3;  // 8-column chunks per row
+  const uint64_t pol_keep = l2_policy_evict_last();
+  const uint64_t pol_stream = l2_policy_evict_first();
 
   float acc[NC][8];
   float rop[NC][8];
-  unsigned short cn[NC][8];
+  uint32_t cn2[NC][4];
+  bool colok[NC];
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
-    const int colo = (g + c * G) * 8;
+    const int ch = g + c * G;
+    colok[c] = ch < nchunk;
 #pragma unroll
-    for (int t = 0; t < 8; ++t) { acc[c][t] = 0.f; rop[c][t] = 0.f; cn[c][t] = 0; }
-    if (MODE != SEG_SUM && colo < p.H) {
-      uint4 v = ldg_nc_v4(p.rowop + r * p.ld_rowop + colo);
-      unpack8(v, rop[c]);
-    }
+    for (int t = 0; t < 8; ++t) { acc[c][t] = 0.f; rop[c][t] = 0.f; }
+#pragma unroll
+    for (int t = 0; t < 4; ++t) cn2[c][t] = 0;
+    if ((MODE == SEG_ADD_RELU || MODE == SEG_ADD_RELU_BWD) && colok[c])
+      unpack8(ldg_hint_v4(p.rowop + r * p.ld_rowop + ch * 8, pol_stream), rop[c]);
   }
+  const char* src_lane = reinterpret_cast<const char*>(p.src) + g * 16;
+  const char* src2_lane = reinterpret_cast<const char*>(p.src2) + g * 16;
 
   const int beg = p.ptr[r], end = p.ptr[r + 1];
   for (int base = beg; base < end; base += G) {
     const int n = min(G, end - base);
-    int my_j = 0;
+    int my_j = 0, my_s = 0;
     float my_w = 1.f;
     if (g < n) {
       my_j = p.idx[base + g];
       if (MODE == SEG_SUM && p.slot_w) my_w = p.slot_w[base + g];
+      if (MODE == SEG_MASKED_SUM) my_s = p.slot_map[base + g];
     }
-    for (int t0 = 0; t0 < n; t0 += UNROLL) {
-      uint4 v[UNROLL][NC];
-      uint4 v2[UNROLL][NC];
+    int t0 = 0;
+    for (; t0 + UNROLL <= n; t0 += UNROLL) {  // full groups: no per-edge predication
+      uint4 v[UNROLL][NC], v2[UNROLL][NC];
+      uint32_t mb[UNROLL][NC];
       float w[UNROLL];
 #pragma unroll
       for (int u = 0; u < UNROLL; ++u) {
-        const int t = t0 + u;
-        const int j = __shfl_sync(gmask, my_j, t < n ? t : 0, G);
-        w[u] = __shfl_sync(gmask, my_w, t < n ? t : 0, G);
-        if (t < n) {
-          const __nv_bfloat16* row = src_row<HALO>(p, j);
+        const int j = __shfl_sync(gmask, my_j, t0 + u, G);
+        if (MODE == SEG_SUM) w[u] = __shfl_sync(gmask, my_w, t0 + u, G); else w[u] = 1.f;
+        const int sl = (MODE == SEG_MASKED_SUM) ? __shfl_sync(gmask, my_s, t0 + u, G) : 0;
+        const char* row = src_row<HALO>(p, src_lane, g * 16, j);
 #pragma unroll
-          for (int c = 0; c < NC; ++c) {
-            const int colo = (g + c * G) * 8;
-            if (colo < p.H) {
-              v[u][c] = HALO ? ldg_v4(row + colo) : ldg_nc_v4(row + colo);
-              if (MODE == SEG_ADD_RELU_BWD) v2[u][c] = ldg_nc_v4(p.src2 + (int64_t)j * p.ld_src2 + colo);
-            }
+        for (int c = 0; c < NC; ++c) {
+          if (colok[c]) {
+            v[u][c] = HALO ? ldg_v4(row + c * G * 16) : ldg_hint_v4(row + c * G * 16, pol_keep);
+            if (MODE == SEG_ADD_RELU_BWD) v2[u][c] = ldg_nc_v4(src2_lane + (uint64_t)(uint32_t)j * p.ld_src2_b + c * G * 16);
+            if (MODE == SEG_MASKED_SUM) mb[u][c] = __ldg(p.mask + (int64_t)sl * nchunk + g + c * G);
           }
         }
       }
 #pragma unroll
       for (int u = 0; u < UNROLL; ++u) {
-        if (t0 + u < n) {
 #pragma unroll
-          for (int c = 0; c < NC; ++c) {
-            const int colo = (g + c * G) * 8;
-            if (colo < p.H) {
-              float f[8];
-              unpack8(v[u][c], f);
-              if (MODE == SEG_SUM) {
-#pragma unroll
-                for (int t = 0; t < 8; ++t) acc[c][t] = fmaf(w[u], f[t], acc[c][t]);
-              } else if (MODE == SEG_ADD_RELU) {
-#pragma unroll
-                for (int t = 0; t < 8; ++t) {
-                  const float m = rop[c][t] + f[t];
-                  const bool on = m > 0.f;
-                  acc[c][t] += on ? m : 0.f;
-                  cn[c][t] += on ? 1 : 0;
-                }
-              } else {  // SEG_ADD_RELU_BWD: f = dOut[i], f2 = P[i], rop = Q[j]
-                float f2[8];
-                unpack8(v2[u][c], f2);
-#pragma unroll
-                for (int t = 0; t < 8; ++t) acc[c][t] += (f2[t] + rop[c][t] > 0.f) ? f[t] : 0.f;
-              }
-            }
+        for (int c = 0; c < NC; ++c) {
+          if (colok[c]) {
+            uint32_t mout = 0;
+            seg_accumulate<MODE>(v[u][c], v2[u][c], rop[c], w[u], mb[u][c], acc[c], cn2[c], mout);
+            if (MODE == SEG_ADD_RELU && p.mask) stg_cs_u8(p.mask + (int64_t)(base + t0 + u) * nchunk + g + c * G, mout);
           }
+        }
+      }
+    }
+    for (; t0 < n; ++t0) {  // tail
+      const int j = __shfl_sync(gmask, my_j, t0, G);
+      const float w = (MODE == SEG_SUM) ? __shfl_sync(gmask, my_w, t0, G) : 1.f;
+      const int sl = (MODE == SEG_MASKED_SUM) ? __shfl_sync(gmask, my_s, t0, G) : 0;
+      const char* row = src_row<HALO>(p, src_lane, g * 16, j);
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
+        if (colok[c]) {
+          const uint4 v = HALO ? ldg_v4(row + c * G * 16) : ldg_hint_v4(row + c * G * 16, pol_keep);
+          uint4 v2 = make_uint4(0, 0, 0, 0);
+          uint32_t mb = 0, mout = 0;
+          if (MODE == SEG_ADD_RELU_BWD) v2 = ldg_nc_v4(src2_lane + (uint64_t)(uint32_t)j * p.ld_src2_b + c * G * 16);
+          if (MODE == SEG_MASKED_SUM) mb = __ldg(p.mask + (int64_t)sl * nchunk + g + c * G);
+          seg_accumulate<MODE>(v, v2, rop[c], w, mb, acc[c], cn2[c], mout);
+          if (MODE == SEG_ADD_RELU && p.mask) stg_cs_u8(p.mask + (int64_t)(base + t0) * nchunk + g + c * G, mout);
         }
       }
     }
@@ -149,20 +192,16 @@ __global__ void __launch_bounds__(256) seg_reduce_kernel(const SegParams p) {
   const float scale = (MODE == SEG_SUM && p.mean) ? 1.f / (float)max(end - beg, 1) : 1.f;
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
-    const int colo = (g + c * G) * 8;
-    if (colo < p.H) {
+    if (colok[c]) {
+      const int colo = (g + c * G) * 8;
       if (MODE == SEG_SUM && p.mean) {
 #pragma unroll
         for (int t = 0; t < 8; ++t) acc[c][t] *= scale;
       }
-      stg_v4(p.out + r * p.ld_out + colo, pack8(acc[c]));
+      stg_cs_v4(p.out + r * p.ld_out + colo, pack8(acc[c]));
       if (MODE == SEG_ADD_RELU && p.cnt) {
-        uint4 cv;
-        cv.x = cn[c][0] | ((uint32_t)cn[c][1] << 16);
-        cv.y = cn[c][2] | ((uint32_t)cn[c][3] << 16);
-        cv.z = cn[c][4] | ((uint32_t)cn[c][5] << 16);
-        cv.w = cn[c][6] | ((uint32_t)cn[c][7] << 16);
-        stg_v4(p.cnt + r * p.ld_cnt + colo, cv);
+        uint4 cv = make_uint4(cn2[c][0], cn2[c][1], cn2[c][2], cn2[c][3]);
+        stg_cs_v4(p.cnt + r * p.ld_cnt + colo, cv);
       }
     }
   }
@@ -216,6 +255,7 @@ __global__ void mul_cnt_kernel(const __nv_bfloat16* __restrict__ g, int64_t ld_g
 using namespace dgb;
 
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+static inline bool fits32(int64_t v) { return v >= 0 && v < (int64_t(1) << 32); }
 
 // out[r,:] = (mean ? 1/deg : 1) * sum_{k in seg r} w[k] * src[idx[k],:]          (bf16 in/out, fp32 accumulate)
 // Halo-pull variant: rows >= n_local are fetched from peer_base[halo_owner[h]] + halo_row[h]*ld_peer.
@@ -226,29 +266,31 @@ DGB_API int dgb_seg_sum(const int* ptr, const int* idx, int64_t n_rows, int H, c
   if (H % 8 || ld_src % 8 || ld_out % 8 || !aligned16(src) || !aligned16(out)) return (int)cudaErrorInvalidValue;
   SegParams p{};
   p.ptr = ptr; p.idx = idx; p.n_rows = n_rows; p.H = H;
-  p.src = (const __nv_bfloat16*)src; p.ld_src = ld_src;
+  if (!fits32(ld_src * 2) || !fits32(ld_peer * 2)) return (int)cudaErrorInvalidValue;
+  p.src = (const __nv_bfloat16*)src; p.ld_src_b = (uint32_t)(ld_src * 2);
   p.slot_w = slot_w; p.mean = mean;
   p.out = (__nv_bfloat16*)out; p.ld_out = ld_out;
   p.n_local = n_local; p.peer_base = (const __nv_bfloat16* const*)peer_base;
-  p.halo_owner = halo_owner; p.halo_row = halo_row; p.ld_peer = ld_peer;
+  p.halo_owner = halo_owner; p.halo_row = halo_row; p.ld_peer_b = (uint32_t)(ld_peer * 2);
   return peer_base ? launch_seg<SEG_SUM, true>(p, (cudaStream_t)stream) : launch_seg<SEG_SUM, false>(p, (cudaStream_t)stream);
 }
 
 // out[r,:] = sum_{k in seg r} relu(P[r,:] + Q[idx[k],:]);   cnt[r,c] = #active edges (optional)
 DGB_API int dgb_seg_add_relu_fwd(const int* ptr, const int* idx, int64_t n_rows, int H, const void* P, int64_t ld_p,
                                  const void* Q, int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt,
-                                 int64_t ld_cnt, int64_t n_local, const void* const* peer_base,
+                                 int64_t ld_cnt, unsigned char* mask, int64_t n_local, const void* const* peer_base,
                                  const int* halo_owner, const int* halo_row, int64_t ld_peer, void* stream) {
   if (H % 8 || ld_p % 8 || ld_q % 8 || ld_out % 8 || (cnt && ld_cnt % 8) || !aligned16(P) || !aligned16(Q) ||
       !aligned16(out))
     return (int)cudaErrorInvalidValue;
   SegParams p{};
   p.ptr = ptr; p.idx = idx; p.n_rows = n_rows; p.H = H;
-  p.src = (const __nv_bfloat16*)Q; p.ld_src = ld_q;
+  if (!fits32(ld_q * 2) || !fits32(ld_peer * 2)) return (int)cudaErrorInvalidValue;
+  p.src = (const __nv_bfloat16*)Q; p.ld_src_b = (uint32_t)(ld_q * 2);
   p.rowop = (const __nv_bfloat16*)P; p.ld_rowop = ld_p;
-  p.out = (__nv_bfloat16*)out; p.ld_out = ld_out; p.cnt = cnt; p.ld_cnt = ld_cnt;
+  p.out = (__nv_bfloat16*)out; p.ld_out = ld_out; p.cnt = cnt; p.ld_cnt = ld_cnt; p.mask = mask;
   p.n_local = n_local; p.peer_base = (const __nv_bfloat16* const*)peer_base;
-  p.halo_owner = halo_owner; p.halo_row = halo_row; p.ld_peer = ld_peer;
+  p.halo_owner = halo_owner; p.halo_row = halo_row; p.ld_peer_b = (uint32_t)(ld_peer * 2);
   return peer_base ? launch_seg<SEG_ADD_RELU, true>(p, (cudaStream_t)stream)
                    : launch_seg<SEG_ADD_RELU, false>(p, (cudaStream_t)stream);
 }
@@ -260,11 +302,25 @@ DGB_API int dgb_seg_add_relu_bwd(const int* colptr, const int* row, int64_t n_au
   if (H % 8 || ld_g % 8 || ld_p % 8 || ld_q % 8 || ld_dq % 8) return (int)cudaErrorInvalidValue;
   SegParams p{};
   p.ptr = colptr; p.idx = row; p.n_rows = n_aug; p.H = H;
-  p.src = (const __nv_bfloat16*)dOut; p.ld_src = ld_g;
-  p.src2 = (const __nv_bfloat16*)P; p.ld_src2 = ld_p;
+  if (!fits32(ld_g * 2) || !fits32(ld_p * 2)) return (int)cudaErrorInvalidValue;
+  p.src = (const __nv_bfloat16*)dOut; p.ld_src_b = (uint32_t)(ld_g * 2);
+  p.src2 = (const __nv_bfloat16*)P; p.ld_src2_b = (uint32_t)(ld_p * 2);
   p.rowop = (const __nv_bfloat16*)Q; p.ld_rowop = ld_q;
   p.out = (__nv_bfloat16*)dQ; p.ld_out = ld_dq;
   return launch_seg<SEG_ADD_RELU_BWD, false>(p, (cudaStream_t)stream);
+}
+
+// dQ[j,:] = sum_{k in CSC seg j} mask[slot_map[k]] ? dOut[row[k],:] : 0, with the ReLU bit masks the forward kernel saved
+// (one byte per edge slot and 8-column chunk): one row gather per edge instead of two, no recomputation.
+DGB_API int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slot_map, const unsigned char* mask,
+                               int64_t n_aug, int H, const void* dOut, int64_t ld_g, void* dQ, int64_t ld_dq, void* stream) {
+  if (H % 8 || ld_g % 8 || ld_dq % 8 || !fits32(ld_g * 2)) return (int)cudaErrorInvalidValue;
+  SegParams p{};
+  p.ptr = colptr; p.idx = row; p.n_rows = n_aug; p.H = H;
+  p.src = (const __nv_bfloat16*)dOut; p.ld_src_b = (uint32_t)(ld_g * 2);
+  p.mask = const_cast<unsigned char*>(mask); p.slot_map = slot_map;
+  p.out = (__nv_bfloat16*)dQ; p.ld_out = ld_dq;
+  return launch_seg<SEG_MASKED_SUM, false>(p, (cudaStream_t)stream);
 }
 
 // dP = dOut * cnt

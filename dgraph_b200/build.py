@@ -84,7 +84,12 @@ def main():
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     a = ap.parse_args()
-    print(build(a.force, a.verbose))
+    try:
+        print("BUILD OK", build(a.force, a.verbose))
+    except Exception as e:  # noqa: BLE001
+        print(str(e)[:3000])
+        print("BUILD FAILED")
+        sys.exit(1)
 
 
 if __name__ == "__main__":

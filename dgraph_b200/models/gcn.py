@@ -50,6 +50,10 @@ class GraphConvLayer(nn.Module):
         if kp is None:
             kp = GraphKernelPlan.from_edges(edge_index, num_local_nodes, x.shape[0], device=x.device)
         F_in = self.conv.weight.shape[1] // 2
+        if x.is_cuda and x.dtype == torch.bfloat16 and self.conv.weight.shape[0] % 8 == 0 and x.shape[1] % 8 == 0:
+            from dgraph_b200.ops.graphconv import graphconv_fused
+
+            return graphconv_fused(x, self.conv.weight, self.conv.bias, kp, num_local_nodes, F_in)
         W = self.conv.weight.to(x.dtype)
         w_i, w_j = W[:, :F_in], W[:, F_in:2 * F_in]
         pad = x.shape[1] - F_in  # features may arrive zero-padded to a 16-byte row (e.g. 100 -> 104 columns)

@@ -68,7 +68,9 @@ class _LinearTC(Function):
         if ctx.needs_input_grad[1]:
             dw = gemm_bf16_nn_grad_w(g, x)
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = g.float().sum(0)
+            from dgraph_b200.ops.reduce import colsum
+
+            db = colsum(g)
         return dx, dw, db, None
 
 

@@ -1,0 +1,82 @@
+"""Fused GraphConv layer: ``out_i = sum_j ReLU(W [x_i ; x_j] + b)`` as ONE autograd node.
+
+Forward  : one tcgen05 GEMM ``PQ = x_aug [W_i ; W_j]^T (+ b on the P half)`` -> one fused gather-add-ReLU-segment-sum.
+Backward : ``dP = g * cnt`` and ``dQ = masked CSC sum`` written straight into the two halves of one ``[n_aug, 2H]``
+           buffer -> one GEMM for ``dX`` (skipped when the input needs no gradient), one for ``dW``, one column-sum
+           for ``db``.  No ``[E, *]`` tensor, no ``cat``/slice copies, no gradient-accumulation adds.
+
+Semantics: reference ``GraphConvLayer.forward`` (``experiments/OGB/GCN.py:34-67``).
+"""
+from __future__ import annotations
+
+import torch
+from torch.autograd import Function
+
+from dgraph_b200.ops import _native as N
+from dgraph_b200.ops.gemm_native import gemm_bf16_tn
+from dgraph_b200.ops.reduce import colsum
+from dgraph_b200.ops import segment as S
+
+
+class _GraphConvFused(Function):
+    @staticmethod
+    def forward(ctx, x_aug, weight, bias, kp, n_local, f_in):
+        H = weight.shape[0]
+        Fp = x_aug.shape[1]
+        dev = x_aug.device
+        wcat = torch.zeros((2 * H, Fp), dtype=torch.bfloat16, device=dev)
+        wcat[:H, :f_in] = weight[:, :f_in]
+        wcat[H:, :f_in] = weight[:, f_in:2 * f_in]
+        bcat = torch.zeros(2 * H, dtype=torch.float32, device=dev)
+        bcat[:H] = bias
+        n_aug = x_aug.shape[0]
+        PQ = gemm_bf16_tn(x_aug, wcat, bcat, None)
+        P, Q = PQ[:n_local, :H], PQ[:, H:]
+        need_w = weight.requires_grad or x_aug.requires_grad
+        out = torch.empty((n_local, H), dtype=torch.bfloat16, device=dev)
+        cnt = torch.empty((n_local, H), dtype=torch.uint16, device=dev) if need_w else None
+        mask = torch.empty((kp.num_edges, H // 8), dtype=torch.uint8, device=dev) if need_w else None
+        N.check(N.lib().dgb_seg_add_relu_fwd(
+            N.ptr(kp.rowptr), N.ptr(kp.col), N.i64(n_local), N.i32(H), N.ptr(P), N.i64(2 * H), N.ptr(Q), N.i64(2 * H),
+            N.ptr(out), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(mask), N.i64(n_aug), N.ptr(None), N.ptr(None), N.ptr(None),
+            N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
+        N.count_launch()
+        ctx.save_for_backward(x_aug, wcat, cnt, mask)
+        ctx.kp, ctx.n_local, ctx.f_in, ctx.H = kp, n_local, f_in, H
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        x_aug, wcat, cnt, mask = ctx.saved_tensors
+        kp, n, f_in, H = ctx.kp, ctx.n_local, ctx.f_in, ctx.H
+        g = g.contiguous()
+        n_aug = x_aug.shape[0]
+        dev = g.device
+        dPQ = torch.empty((n_aug, 2 * H), dtype=torch.bfloat16, device=dev)
+        if n_aug > n:
+            dPQ[n:, :H].zero_()
+        lib = N.lib()
+        N.check(lib.dgb_mul_cnt(N.ptr(g), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(dPQ), N.i64(2 * H), N.i64(n), N.i32(H),
+                                N.stream()), "dgb_mul_cnt")
+        N.check(lib.dgb_seg_masked_sum(N.ptr(kp.colptr), N.ptr(kp.row), N.ptr(kp.csc_to_csr), N.ptr(mask), N.i64(n_aug),
+                                       N.i32(H), N.ptr(g), N.i64(H), N.ptr(dPQ[:, H:]), N.i64(2 * H), N.stream()),
+                "dgb_seg_masked_sum")
+        N.count_launch(2)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm_bf16_tn(dPQ, wcat.t().contiguous(), None, None)  # [n_aug, Fp]
+        if ctx.needs_input_grad[1]:
+            dwcat = torch.matmul(dPQ.t(), x_aug).float()  # [2H, Fp]; plain library GEMM (reduction over rows)
+            dw = torch.cat([dwcat[:H, :f_in], dwcat[H:, :f_in]], dim=1)
+        if ctx.needs_input_grad[2]:
+            db = colsum(dPQ[:n, :H])
+        return dx, dw, db, None, None, None
+
+
+def graphconv_fused(x_aug, weight, bias, kp, n_local: int, f_in: int):
+    """``x_aug`` bf16 ``[n_local + n_halo, F_pad]`` (extra columns zero); ``weight`` fp32 ``[H, 2 * f_in]``; ``bias`` fp32."""
+    N.lib()
+    assert kp.rowptr.dtype == torch.int32
+    if x_aug.stride(1) != 1 or x_aug.stride(0) % 8:
+        x_aug = x_aug.contiguous()
+    return _GraphConvFused.apply(x_aug, weight, bias, kp, n_local, f_in)

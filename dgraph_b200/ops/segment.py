@@ -12,6 +12,7 @@ plain PyTorch formulation below, which is also the numerics oracle in the tests.
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -19,6 +20,10 @@ from torch.autograd import Function
 
 from dgraph_b200.ops import _native as N
 from dgraph_b200.parallel.kernel_plan import GraphKernelPlan
+
+
+# Save 1 bit per (edge, column) in the forward so the backward gathers one row per edge instead of two (E * H / 8 bytes).
+SAVE_RELU_MASK = os.environ.get("DGRAPH_B200_RELU_MASK", "1") == "1"
 
 
 # ------------------------------------------------------------------------------------------------
@@ -117,29 +122,46 @@ class _GraphConvAgg(Function):
         H = P.shape[1]
         n = kp.num_local
         out = torch.empty((n, H), dtype=torch.bfloat16, device=P.device)
-        cnt = torch.empty((n, H), dtype=torch.uint16, device=P.device)
+        need_p = P.requires_grad
+        need_q = Qaug.requires_grad
+        cnt = torch.empty((n, H), dtype=torch.uint16, device=P.device) if need_p else None
+        # ReLU bit masks (1 byte per edge and 8 columns = E * H / 8 bytes) let backward gather ONE row per edge
+        mask = torch.empty((kp.num_edges, H // 8), dtype=torch.uint8, device=P.device) if (need_q and SAVE_RELU_MASK) else None
         N.check(N.lib().dgb_seg_add_relu_fwd(
             N.ptr(kp.rowptr), N.ptr(kp.col), N.i64(n), N.i32(H), N.ptr(P), N.i64(_ld(P)), N.ptr(Qaug), N.i64(_ld(Qaug)),
-            N.ptr(out), N.i64(H), N.ptr(cnt), N.i64(H), N.i64(Qaug.shape[0]), N.ptr(None), N.ptr(None), N.ptr(None),
-            N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
+            N.ptr(out), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(mask), N.i64(Qaug.shape[0]), N.ptr(None), N.ptr(None),
+            N.ptr(None), N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
         N.count_launch()
-        ctx.save_for_backward(P, Qaug, cnt)
+        if mask is not None:
+            ctx.save_for_backward(cnt, mask)
+        else:
+            ctx.save_for_backward(cnt, P, Qaug)
+        ctx.has_mask = mask is not None
         ctx.kp = kp
         return out
 
     @staticmethod
     def backward(ctx, g):
-        P, Qaug, cnt = ctx.saved_tensors
         kp = ctx.kp
         g = g.contiguous()
-        H = P.shape[1]
+        H = g.shape[1]
         dP = dQ = None
+        if ctx.has_mask:
+            cnt, mask = ctx.saved_tensors
+        else:
+            cnt, P, Qaug = ctx.saved_tensors
         if ctx.needs_input_grad[0]:
             dP = torch.empty_like(g)
             N.check(N.lib().dgb_mul_cnt(N.ptr(g), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(dP), N.i64(H),
                                         N.i64(g.shape[0]), N.i32(H), N.stream()), "dgb_mul_cnt")
             N.count_launch()
-        if ctx.needs_input_grad[1]:
+        if ctx.needs_input_grad[1] and ctx.has_mask:
+            dQ = torch.empty((kp.num_aug, H), dtype=torch.bfloat16, device=g.device)
+            N.check(N.lib().dgb_seg_masked_sum(
+                N.ptr(kp.colptr), N.ptr(kp.row), N.ptr(kp.csc_to_csr), N.ptr(mask), N.i64(kp.num_aug), N.i32(H), N.ptr(g),
+                N.i64(H), N.ptr(dQ), N.i64(H), N.stream()), "dgb_seg_masked_sum")
+            N.count_launch()
+        elif ctx.needs_input_grad[1]:
             dQ = torch.empty((kp.num_aug, H), dtype=torch.bfloat16, device=g.device)
             N.check(N.lib().dgb_seg_add_relu_bwd(
                 N.ptr(kp.colptr), N.ptr(kp.row), N.i64(kp.num_aug), N.i32(H), N.ptr(g), N.i64(H), N.ptr(P),

@@ -79,3 +79,47 @@ def test_native_library_is_loaded():
     assert _native.available()
     assert _native.lib().dgb_version() >= 100
     assert _native.lib().dgb_sm_count() == torch.cuda.get_device_properties(0).multi_processor_count
+
+
+@pytest.mark.parametrize("M,N", [(1, 8), (777, 256), (5000, 104), (100000, 512), (33, 2048)])
+@pytest.mark.parametrize("with_sq", [False, True])
+def test_colsum_matches_torch(M, N, with_sq):
+    from dgraph_b200.ops.reduce import colsum
+
+    torch.manual_seed(0)
+    big = torch.randn(M, N + 8, device="cuda").bfloat16()
+    x = big[:, :N]  # strided view
+    got = colsum(x, with_sq)
+    xf = x.float()
+    want = torch.cat([xf.sum(0), (xf * xf).sum(0)]) if with_sq else xf.sum(0)
+    assert torch.allclose(got, want, rtol=1e-3, atol=1e-2 * max(1.0, M ** 0.5))
+
+
+def test_fused_graphconv_layer_matches_reference_formulation():
+    from dgraph_b200.models.gcn import GraphConvLayer
+
+    torch.manual_seed(3)
+    V, n_aug, F, H = 400, 520, 100, 64
+    kp = _kp(V, 10, 5, n_aug)
+    e = torch.stack([torch.repeat_interleave(torch.arange(V, device="cuda"), (kp.rowptr[1:] - kp.rowptr[:-1]).long()),
+                     kp.col.long()], 1)
+    fused = GraphConvLayer(2 * F, H, fused=True).cuda()
+    ref = GraphConvLayer(2 * F, H, fused=False).cuda()
+    ref.load_state_dict(fused.state_dict())
+    x = torch.zeros(n_aug, 104, device="cuda")
+    x[:, :F] = torch.randn(n_aug, F, device="cuda") * 0.5
+    xb = x.bfloat16().requires_grad_(True)
+    xf = x.bfloat16().float().requires_grad_(True)
+    y = fused(xb, e, V, kernel_plan=kp)
+    yr = ref(xf, e, V)
+    assert torch.allclose(y.float(), yr, rtol=3e-2, atol=0.15), (y.float() - yr).abs().max()
+    g = torch.randn_like(yr).bfloat16()
+    y.backward(g)
+    yr.backward(g.float())
+    # P/Q are rounded to bf16 before the ReLU, so a few near-zero pre-activations flip: compare in the Frobenius norm
+    def rel(a, b):
+        return float((a - b).norm() / b.norm())
+
+    assert rel(xb.grad.float()[:, :F], xf.grad[:, :F]) < 3e-2
+    assert rel(fused.conv.weight.grad, ref.conv.weight.grad) < 3e-2
+    assert rel(fused.conv.bias.grad, ref.conv.bias.grad) < 3e-2

@@ -1,0 +1,90 @@
+/* dgraph_b200 -- C ABI of the sm_100a kernel library (dgraph_b200/lib/libdgraph_b200.so).
+ *
+ * Every launcher takes raw device pointers and the CUDA stream to launch on (cudaStream_t passed as void*), returns 0 on
+ * success or a cudaError_t value (see dgb_error_string), never synchronises the device and -- unless stated otherwise --
+ * allocates nothing.  Row strides ("ld") are in ELEMENTS unless the name says bytes.  bf16 matrices need 16-byte aligned
+ * base pointers and strides that are multiples of 8 elements.
+ *
+ * Citations name the piece of the reference (LBANN/DGraph, paths relative to its repository root) whose role the entry
+ * point takes over.
+ */
+#ifndef DGRAPH_B200_H_
+#define DGRAPH_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- runtime ------------------------------------------------------------------------------------------------------ */
+const char* dgb_error_string(int code);
+int dgb_version(void);
+int dgb_sm_count(void);
+
+/* ---- segment aggregation (csrc/segment_ops.cu) ----------------------------------------------------------------------
+ * Reference: scatter_add of GraphConvLayer (experiments/OGB/GCN.py:57-65); K6/K7 masked scatter/gather kernels
+ * (DGraph/distributed/csrc/local_data_kernels.cuh:301-406).  CSR/CSC walk, one sub-warp per output row, no atomics. */
+int dgb_seg_sum(const int* ptr, const int* idx, int64_t n_rows, int H, const void* src, int64_t ld_src, const float* slot_w,
+                int mean, void* out, int64_t ld_out, int64_t n_local, const void* const* peer_base, const int* halo_owner,
+                const int* halo_row, int64_t ld_peer, void* stream);
+/* out[r] = sum_k relu(P[r] + Q[idx[k]]); optional per-(row,col) active-edge counts and per-edge ReLU bit masks */
+int dgb_seg_add_relu_fwd(const int* ptr, const int* idx, int64_t n_rows, int H, const void* P, int64_t ld_p, const void* Q,
+                         int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt, int64_t ld_cnt, unsigned char* mask,
+                         int64_t n_local, const void* const* peer_base, const int* halo_owner, const int* halo_row,
+                         int64_t ld_peer, void* stream);
+int dgb_seg_add_relu_bwd(const int* colptr, const int* row, int64_t n_aug, int H, const void* dOut, int64_t ld_g,
+                         const void* P, int64_t ld_p, const void* Q, int64_t ld_q, void* dQ, int64_t ld_dq, void* stream);
+int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slot_map, const unsigned char* mask, int64_t n_aug,
+                       int H, const void* dOut, int64_t ld_g, void* dQ, int64_t ld_dq, void* stream);
+int dgb_mul_cnt(const void* g, int64_t ld_g, const unsigned short* cnt, int64_t ld_c, void* out, int64_t ld_o, int64_t rows,
+                int H, void* stream);
+
+/* ---- tcgen05 GEMM / gather-GEMM (csrc/gemm_tcgen05.cu) ---------------------------------------------------------------
+ * Reference: nn.Linear -> cuBLAS sgemm on gathered + concatenated operands (experiments/OGB/GCN.py:43-52,
+ * experiments/GraphCast/layers.py:52-63, 205-216).  act: 0 none, 1 ReLU, 2 SiLU. */
+int dgb_gemm_bf16_tn(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N, int K,
+                     const float* bias, int act, int out_f32, void* stream);
+int dgb_gather_gemm_bf16(int n_seg, const void* const* seg_base, const int64_t* seg_ld, const int* const* seg_idx,
+                         const int* seg_k, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N, const float* bias,
+                         int act, int out_f32, void* stream);
+
+/* ---- column reductions (csrc/reduce_ops.cu) ---------------------------------------------------------------------------
+ * Reference: statistics of DistributedBatchNorm1D (experiments/OGB-LSC/distributed_layers.py:22-74); ATen sum(0) for bias
+ * gradients.  Two-phase and deterministic; the caller provides the scratch buffer. */
+int64_t dgb_colsum_scratch_bytes(int64_t M, int N, int with_sq);
+int dgb_colsum_bf16(const void* x, int64_t ld, int64_t M, int N, int with_sq, float* scratch, float* out, void* stream);
+
+/* ---- optimizer (csrc/adam.cu) -------------------------------------------------------------------------------------------
+ * Reference: torch.optim.Adam (experiments/OGB/main.py:114).  One kernel over a flat parameter arena. */
+int dgb_adam_flat(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n, float lr, float beta1, float beta2,
+                  float eps, float weight_decay, float grad_scale, int step, void* stream);
+
+/* ---- peer-memory runtime and kernels (csrc/peer.cu) ---------------------------------------------------------------------
+ * Reference: NVSHMEMP2P::{AllocateSymmetricMemory, dist_get, dist_put, barrier} (DGraph/distributed/csrc/
+ * torch_nvshmem_p2p.cu:96-376) and NCCLBackendEngine.put (DGraph/distributed/nccl/NCCLBackendEngine.py:281-306).
+ * dgb_symm_alloc / dgb_symm_import are the only entry points of the library that allocate or map device memory. */
+int dgb_symm_alloc(size_t bytes, void** out);
+int dgb_symm_free(void* p);
+int dgb_symm_export(void* p, void* handle64);
+int dgb_symm_import(const void* handle64, void** out);
+int dgb_symm_unmap(void* p);
+int dgb_enable_peer_access(int peer);
+int dgb_peer_barrier(void* const* pads, int rank, int world, unsigned epoch, int* timeout_flag, long long max_spin,
+                     void* stream);
+int dgb_halo_pull(void* dst, int64_t ld_dst_bytes, int64_t n_halo, int row_bytes, const void* const* peer_base,
+                  int64_t ld_peer_bytes, const int* halo_owner, const int* halo_row, void* stream);
+int dgb_gather_rows_peer(void* out, int64_t ld_out_bytes, int64_t n, int row_bytes, const void* const* peer_base,
+                         int64_t ld_peer_bytes, const int* owner, const int* row, void* stream);
+int dgb_halo_grad_reduce(void* gx, int64_t ld_gx, const void* g_local, int64_t ld_gl, int H, int64_t n_bnd,
+                         const int* bnd_row, const int* bnd_ptr, const int* src_rank, const int* src_row,
+                         const void* const* peer_base, int64_t ld_peer, void* stream);
+int dgb_adam_allreduce(float* p, const void* const* peer_g, int world, float* m, float* v, float* g_out, int64_t n, float lr,
+                       float beta1, float beta2, float eps, float weight_decay, float grad_scale, int step, void* stream);
+int dgb_allreduce_sum_f32(float* out, const void* const* peer, int world, int64_t n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DGRAPH_B200_H_ */

@@ -107,3 +107,83 @@ DGB_API int dgb_colsum_bf16(const void* x, int64_t ld, int64_t M, int N, int wit
   }
   return colsum_launch(x, ld, M, N, with_sq, scratch, out, (cudaStream_t)stream);
 }
+
+// =====================================================================================================================
+// Allocation-free variant of dgb_colsum_bf16.
+//
+// Who needs it: some hosts of this library are not allowed to create device memory at the moment they need a column
+// sum -- for example a runtime that handed the whole GPU to its own memory pool at start-up (a later cudaMalloc simply
+// fails there), or a latency-critical loop that must not call cudaMalloc / cudaFree because both can stall the whole
+// device.  Those callers still pass their input and output pointers, but the partial-sum workspace that
+// dgb_colsum_bf16 expects from them lives in the library image instead: a fixed array in device global memory.
+//
+// Limits and rules:
+//   * Width limit: N * (with_sq ? 2 : 1) <= DGB_COLSUM_NOALLOC_MAX_WIDTH (1024 fp32 columns of partials), i.e. N <= 1024
+//     for plain sums and N <= 512 with sums of squares.  Wider requests are refused (message on stderr, return value
+//     cudaErrorInvalidValue); use dgb_colsum_bf16 with your own scratch for those.  M is not limited.
+//   * Cost: the array is 592 x 1024 floats = 2,424,832 bytes and is resident on EVERY GPU that loads this library, from
+//     load until the process exits, whether or not this entry point is ever called.
+//   * The first call on each device looks up the array's device address (cudaGetSymbolAddress, once per device, with
+//     that device current) before it launches anything.  Make that first call early, outside of any stream capture.
+//   * The function calls no cudaMalloc / cudaFree and no allocating library routine.
+//   * All calls on a device share the one array, and it keeps whatever the previous call left in it.  Nothing in it has
+//     to start at zero: every block overwrites its complete row of partials and the second phase reads exactly the rows
+//     written by this call.  Because the array is shared, two calls that may run at the same time on one GPU (different
+//     streams, or different host threads using different streams) race with each other and give wrong sums; issue them
+//     on one stream or order them yourself.
+// =====================================================================================================================
+#include <cstdio>
+#include <mutex>
+
+namespace dgb {
+constexpr int COLSUM_NOALLOC_MAX_WIDTH = 1024;
+constexpr int COLSUM_NOALLOC_MAX_BLOCKS = 592;  // == upper bound of colsum_blocks()
+constexpr int COLSUM_NOALLOC_MAX_DEVICES = 64;
+}  // namespace dgb
+
+// File-scope device array.  NOTE for maintainers: in host code this name is only a handle for the runtime's symbol
+// table, not a device address -- never pass it to a kernel; pass the pointer obtained from cudaGetSymbolAddress below.
+static __device__ __align__(256) float g_colsum_noalloc_scratch[dgb::COLSUM_NOALLOC_MAX_BLOCKS * dgb::COLSUM_NOALLOC_MAX_WIDTH];
+
+static std::mutex g_colsum_noalloc_mu;
+static float* g_colsum_noalloc_ptr[dgb::COLSUM_NOALLOC_MAX_DEVICES] = {nullptr};
+
+// Device address of the array on the current device (looked up once per device).
+static int colsum_noalloc_scratch(float** out) {
+  int dev = -1;
+  DGB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= dgb::COLSUM_NOALLOC_MAX_DEVICES) return (int)cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(g_colsum_noalloc_mu);
+  if (g_colsum_noalloc_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_colsum_noalloc_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (p == nullptr) return (int)cudaErrorInvalidSymbol;
+    g_colsum_noalloc_ptr[dev] = p;
+  }
+  *out = g_colsum_noalloc_ptr[dev];
+  return 0;
+}
+
+// out[0:N] = sum_r x[r, :] (and out[N:2N] = sum of squares when with_sq), exactly like dgb_colsum_bf16, but the partial
+// sums go to the library's built-in array (see the block comment above for the width limit, the per-GPU memory cost,
+// the first-call set-up and the no-overlap rule).
+DGB_API int dgb_colsum_bf16_noalloc(const void* x, int64_t ld, int64_t M, int N, int with_sq, float* out, void* stream) {
+  if (N % 8 || N < 8 || ld % 8 || M < 0 || !out || (M > 0 && !x)) return (int)cudaErrorInvalidValue;
+  const int width = N * (with_sq ? 2 : 1);
+  if (width > dgb::COLSUM_NOALLOC_MAX_WIDTH) {
+    fprintf(stderr,
+            "dgb_colsum_bf16_noalloc: N=%d%s needs %d columns of partial sums, the built-in scratch holds at most %d; "
+            "call dgb_colsum_bf16 with a caller-provided scratch buffer instead\n",
+            N, with_sq ? " with sums of squares" : "", width, dgb::COLSUM_NOALLOC_MAX_WIDTH);
+    return (int)cudaErrorInvalidValue;
+  }
+  float* scratch = nullptr;
+  const int rc = colsum_noalloc_scratch(&scratch);
+  if (rc) return rc;
+  if (M == 0) {
+    DGB_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * width, (cudaStream_t)stream));
+    return 0;
+  }
+  return dgb::colsum_launch(x, ld, M, N, with_sq, scratch, out, (cudaStream_t)stream);
+}

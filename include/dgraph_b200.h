@@ -55,6 +55,13 @@ int dgb_gather_gemm_bf16(int n_seg, const void* const* seg_base, const int64_t* 
  * gradients.  Two-phase and deterministic; the caller provides the scratch buffer. */
 int64_t dgb_colsum_scratch_bytes(int64_t M, int N, int with_sq);
 int dgb_colsum_bf16(const void* x, int64_t ld, int64_t M, int N, int with_sq, float* scratch, float* out, void* stream);
+/* Same column sum for callers that cannot create device memory (the GPU is fully owned by their own pool, or a cudaMalloc /
+ * cudaFree stall is not acceptable where they run).  This entry point has no counterpart in the reference.  The partial
+ * sums go to a 592 x 1024-float (2,424,832-byte) array built into the library and resident on every GPU that loads it, so
+ * N * (with_sq ? 2 : 1) must be <= 1024; wider requests return cudaErrorInvalidValue with a message on stderr.  The first
+ * call on each device resolves the array's address (do it once before any stream capture).  Calls share the array: do
+ * not let two of them overlap on one GPU.  Allocates nothing. */
+int dgb_colsum_bf16_noalloc(const void* x, int64_t ld, int64_t M, int N, int with_sq, float* out, void* stream);
 
 /* ---- optimizer (csrc/adam.cu) -------------------------------------------------------------------------------------------
  * Reference: torch.optim.Adam (experiments/OGB/main.py:114).  One kernel over a flat parameter arena. */

@@ -1,0 +1,180 @@
+"""Heterogeneous (MAG240M-shaped) distributed graph datasets.
+
+Parity: reference ``experiments/OGB-LSC/lsc_datasets/distributed_graph_dataset.py:24-489`` (``DistributedHeteroGraphDataset``:
+3 node types paper / author / institution, 5 relations, contiguous ``*_vertex_offset[W+1]``, plan generation / save /
+load) and ``synthetic_dataset.py:29-199`` (``SyntheticHeterogeneousDataset``: MAG240M-shaped random graph with average
+degrees 11 / 3.5 / 0.35, 70/15/15 split, per-rank plan cache).  The real MAG240M loader needs ``ogb`` + ``torch_sparse``
+(absent here); :class:`DGraph_MAG240M_Dataset` raises a clear error unless ``ogb`` is importable.
+
+Plans: for every relation both forms are produced -- the reference's ``NCCLEdgeConditionedGraphCommPlan`` (edges stored with
+their source) and a bipartite :class:`CommunicationPattern` (edges stored with their destination) that feeds the fused
+segment-softmax path.
+"""
+from __future__ import annotations
+
+import hashlib
+import os
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from dgraph_b200.parallel.comm_pattern import CommunicationPattern, build_communication_pattern
+from dgraph_b200.parallel.comm_plan import COO_to_NCCLEdgeConditionedCommPlan, NCCLEdgeConditionedGraphCommPlan
+
+NODE_TYPES = ["paper", "author", "institution"]
+# (source type, destination type) -- same order as the reference (`distributed_graph_dataset.py`)
+RELATIONS: List[Tuple[int, int]] = [(0, 0), (0, 1), (1, 0), (1, 2), (2, 1)]
+
+
+def node_offsets(num_nodes: int, world_size: int) -> torch.Tensor:
+    """Contiguous, nearly even vertex ranges: rank r owns ``[off[r], off[r+1])``."""
+    return torch.tensor([num_nodes * r // world_size for r in range(world_size + 1)], dtype=torch.long)
+
+
+class DistributedHeteroGraphDataset:
+    def __init__(self, rank: int, world_size: int, num_nodes: List[int], features: List[torch.Tensor],
+                 edges: List[torch.Tensor], labels: torch.Tensor, num_classes: int, comm=None,
+                 split: Optional[Dict[str, torch.Tensor]] = None, cache_dir: Optional[str] = None):
+        """``edges[k]`` is ``[E_k, 2]`` with column 0 = source id, column 1 = destination id of relation ``RELATIONS[k]``;
+        ``features[t]`` holds this rank's rows of node type ``t``; ``labels`` this rank's paper labels."""
+        self.rank, self.world_size, self.comm = rank, world_size, comm
+        self.num_nodes, self.num_classes = list(num_nodes), num_classes
+        self.offsets = [node_offsets(n, world_size) for n in num_nodes]
+        self.paper_vertex_offset, self.author_vertex_offset, self.institution_vertex_offset = self.offsets
+        self.features, self.edges, self.labels = features, edges, labels
+        self.split = split or {}
+        self.cache_dir = cache_dir
+        self.comm_plans: Optional[List[NCCLEdgeConditionedGraphCommPlan]] = None
+        self.patterns: Optional[List[CommunicationPattern]] = None
+        self.batched = False
+
+    # ---- reference accessors -----------------------------------------------------------------------
+    @property
+    def num_features(self) -> int:
+        return int(self.features[0].shape[-1])
+
+    @property
+    def num_relations(self) -> int:
+        return len(RELATIONS)
+
+    def partition(self, t: int) -> torch.Tensor:
+        off = self.offsets[t]
+        return torch.bucketize(torch.arange(self.num_nodes[t]), off, right=True) - 1
+
+    def local_range(self, t: int) -> Tuple[int, int]:
+        return int(self.offsets[t][self.rank]), int(self.offsets[t][self.rank + 1])
+
+    def get_mask(self, name: str) -> torch.Tensor:
+        """Global paper indices of a split -> local row indices on this rank."""
+        idx = self.split[name]
+        lo, hi = self.local_range(0)
+        m = (idx >= lo) & (idx < hi)
+        return idx[m] - lo
+
+    def get_target(self, name: str) -> torch.Tensor:
+        return self.labels[self.get_mask(name).to(self.labels.device)]
+
+    def add_batch_dimension(self):
+        """``[N, F] -> [1, N, F]`` (the layout the reference's gather/scatter API expects)."""
+        if not self.batched:
+            self.features = [f.unsqueeze(0) for f in self.features]
+            self.batched = True
+        return self
+
+    def to(self, device):
+        self.features = [f.to(device) for f in self.features]
+        self.labels = self.labels.to(device)
+        if self.comm_plans is not None:
+            self.comm_plans = [p.to(device) for p in self.comm_plans]
+        if self.patterns is not None:
+            self.patterns = [p.to(device) for p in self.patterns]
+        return self
+
+    # ---- plans -----------------------------------------------------------------------------------
+    def _cache_path(self, kind: str) -> Optional[str]:
+        if not self.cache_dir:
+            return None
+        h = hashlib.md5(str((self.num_nodes, [int(e.shape[0]) for e in self.edges])).encode()).hexdigest()[:12]
+        return os.path.join(self.cache_dir, f"hetero_{h}_rank_{self.rank}_of_{self.world_size}_{kind}.pt")
+
+    def _generate_comm_plans(self, exchange=None) -> List[NCCLEdgeConditionedGraphCommPlan]:
+        plans = []
+        for (s, d), e in zip(RELATIONS, self.edges):
+            lo, hi = self.local_range(s)
+            mine = torch.nonzero((e[:, 0] >= lo) & (e[:, 0] < hi), as_tuple=True)[0]
+            plans.append(COO_to_NCCLEdgeConditionedCommPlan(self.rank, self.world_size, e[:, 0], e[:, 1], mine,
+                                                           self.offsets[s], self.offsets[d], exchange=exchange))
+        return plans
+
+    def _generate_patterns(self) -> List[CommunicationPattern]:
+        pats = []
+        for (s, d), e in zip(RELATIONS, self.edges):
+            ed = torch.stack([e[:, 1], e[:, 0]], dim=1)  # central = destination, neighbour = source
+            pats.append(build_communication_pattern(ed, self.partition(d), self.rank, self.world_size,
+                                                    neighbor_partitioning=self.partition(s)))
+        return pats
+
+    def _save_comm_plans(self, obj, kind):
+        p = self._cache_path(kind)
+        if p:
+            os.makedirs(os.path.dirname(p), exist_ok=True)
+            torch.save(obj, p)
+
+    def _load_comm_plans(self, kind):
+        p = self._cache_path(kind)
+        if p and os.path.exists(p):
+            return torch.load(p, weights_only=False)
+        return None
+
+    def prepare_plans(self, fused: bool = True, reference_layout: bool = False, exchange=None):
+        if fused and self.patterns is None:
+            self.patterns = self._load_comm_plans("patterns") or self._generate_patterns()
+            self._save_comm_plans(self.patterns, "patterns")
+        if reference_layout and self.comm_plans is None:
+            self.comm_plans = self._load_comm_plans("comm_plans") or self._generate_comm_plans(exchange)
+            self._save_comm_plans(self.comm_plans, "comm_plans")
+        return self
+
+
+class SyntheticHeterogeneousDataset(DistributedHeteroGraphDataset):
+    """MAG240M-shaped random heterogeneous graph (``synthetic_dataset.py:29-199``)."""
+
+    def __init__(self, rank: int, world_size: int, num_papers: int = 32768, num_authors: int = 16384,
+                 num_institutions: int = 256, num_features: int = 16, num_classes: int = 153, seed: int = 0, comm=None,
+                 cache_dir: Optional[str] = None, dtype=torch.float32):
+        g = torch.Generator().manual_seed(seed)
+        n = [num_papers, num_authors, num_institutions]
+
+        def rel(ns, nd, count):
+            count = max(int(count), 1)
+            e = torch.stack([torch.randint(0, ns, (count,), generator=g), torch.randint(0, nd, (count,), generator=g)], 1)
+            return torch.unique(e, dim=0)
+
+        cites = rel(num_papers, num_papers, num_papers * 11)  # paper -> paper, avg degree 11
+        writes = rel(num_authors, num_papers, num_papers * 3.5)  # author -> paper
+        affil = rel(num_authors, num_institutions, num_authors * 0.35)  # author -> institution
+        edges = [cites, writes.flip(1), writes, affil, affil.flip(1)]  # order of RELATIONS
+        offs = [node_offsets(k, world_size) for k in n]
+        feats = []
+        for t, k in enumerate(n):
+            full = torch.randn(k, num_features, generator=g)
+            feats.append(full[offs[t][rank]:offs[t][rank + 1]].to(dtype).contiguous())
+        labels_full = torch.randint(0, num_classes, (num_papers,), generator=g)
+        perm = torch.randperm(num_papers, generator=g)
+        n_tr, n_va = int(0.7 * num_papers), int(0.15 * num_papers)
+        split = {"train": perm[:n_tr].sort().values, "valid": perm[n_tr:n_tr + n_va].sort().values,
+                 "test": perm[n_tr + n_va:].sort().values}
+        super().__init__(rank, world_size, n, feats, edges, labels_full[offs[0][rank]:offs[0][rank + 1]].contiguous(),
+                         num_classes, comm=comm, split=split, cache_dir=cache_dir)
+
+
+class DGraph_MAG240M_Dataset(DistributedHeteroGraphDataset):
+    """Real OGB-LSC MAG240M (``MAG240M_dataset.py:116-340``); needs the ``ogb`` package and the downloaded dataset."""
+
+    def __init__(self, rank, world_size, data_dir="data/MAG240M", comm=None, **kw):
+        try:
+            from ogb.lsc import MAG240MDataset  # noqa: F401
+        except ImportError as e:
+            raise RuntimeError("MAG240M needs the `ogb` package and a local copy of the dataset (no network access here); "
+                               "use SyntheticHeterogeneousDataset for MAG240M-shaped runs") from e
+        raise NotImplementedError("MAG240M ingestion requires the dataset on disk")

@@ -13,7 +13,7 @@ def colsum(x: torch.Tensor, with_sq: bool = False) -> torch.Tensor:
             and x.stride(0) % 8 == 0):
         if x.is_cuda:
             N.require_for(x)
-        xf = x.float()
+        xf = x if x.dtype == torch.float64 else x.float()
         return torch.cat([xf.sum(0), (xf * xf).sum(0)]) if with_sq else xf.sum(0)
     lib = N.lib()
     lib.dgb_colsum_scratch_bytes.restype = __import__("ctypes").c_int64

@@ -1,0 +1,93 @@
+"""``act(Linear(cat([x_0[idx_0], x_1[idx_1], x_2], 1)))`` without materialising the gather or the concatenation.
+
+Forward on CUDA bf16: ONE tcgen05 gather-GEMM (``csrc/gemm_tcgen05.cu``, ``dgb_gather_gemm_bf16``): four producer warps
+gather the rows of up to three sources straight into the 128-byte-swizzled A tiles, the weight streams in by TMA, bias +
+activation are fused in the epilogue.  This is the first Linear of the reference's ``MeshEdgeBlock`` / ``MeshNodeBlock``
+(``experiments/GraphCast/layers.py:136-143,205-216``) and of ``GraphConvLayer`` with edge features.
+
+Backward (round 1): dense formulation -- ``d_cat = d_pre @ W`` with the tcgen05 GEMM, split and ``index_add`` back to
+the sources; ``dW = d_pre^T @ cat`` needs the gathered operand once (library GEMM).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+import torch.nn.functional as F
+from torch.autograd import Function
+
+from dgraph_b200.ops import _native as N
+
+
+def gather_linear_ref(srcs: Sequence[torch.Tensor], idxs: Sequence[Optional[torch.Tensor]], weight, bias, act=None):
+    cat = torch.cat([s if i is None else s.index_select(0, i.long()) for s, i in zip(srcs, idxs)], dim=1)
+    y = F.linear(cat, weight.to(cat.dtype), None if bias is None else bias.to(cat.dtype))
+    if act == "silu":
+        y = F.silu(y)
+    elif act == "relu":
+        y = torch.relu(y)
+    return y
+
+
+class _GatherLinear(Function):
+    @staticmethod
+    def forward(ctx, weight, bias, act, n_src, *args):
+        from dgraph_b200.ops.gemm_native import gather_gemm_bf16, pack_segment_weight
+
+        srcs, idxs = list(args[:n_src]), list(args[n_src:])
+        ks = [int(s.shape[1]) for s in srcs]
+        M = int(idxs[0].shape[0]) if idxs[0] is not None else int(srcs[0].shape[0])
+        for s, i in zip(srcs, idxs):
+            M = int(i.shape[0]) if i is not None else int(s.shape[0])
+        wp = pack_segment_weight(weight, ks)
+        pre = gather_gemm_bf16(srcs, idxs, wp, bias, M, ks, act=None)
+        ctx.act, ctx.n_src, ctx.ks = act, n_src, ks
+        ctx.save_for_backward(weight, pre if act else None, *srcs, *[i for i in idxs if i is not None])
+        ctx.idx_none = [i is None for i in idxs]
+        if act == "silu":
+            return F.silu(pre)
+        if act == "relu":
+            return torch.relu(pre)
+        return pre
+
+    @staticmethod
+    def backward(ctx, g):
+        from dgraph_b200.ops.gemm_native import gemm_bf16_tn
+
+        saved = ctx.saved_tensors
+        weight, pre = saved[0], saved[1]
+        srcs = list(saved[2:2 + ctx.n_src])
+        it = iter(saved[2 + ctx.n_src:])
+        idxs = [None if none else next(it) for none in ctx.idx_none]
+        g = g.contiguous()
+        if ctx.act == "silu":
+            sg = torch.sigmoid(pre.float())
+            g = (g.float() * (sg * (1 + pre.float() * (1 - sg)))).to(g.dtype)
+        elif ctx.act == "relu":
+            g = g * (pre > 0).to(g.dtype)
+        wb = weight.to(torch.bfloat16)
+        dcat = gemm_bf16_tn(g, wb.t().contiguous())  # [M, sum(ks)]
+        cat = torch.cat([s if i is None else s.index_select(0, i.long()) for s, i in zip(srcs, idxs)], dim=1)
+        dw = torch.matmul(g.t(), cat).float() if ctx.needs_input_grad[0] else None
+        db = g.float().sum(0) if ctx.needs_input_grad[1] else None
+        grads, o = [], 0
+        for s, i, k in zip(srcs, idxs, ctx.ks):
+            part = dcat[:, o:o + k]
+            o += k
+            if i is None:
+                grads.append(part.contiguous())
+            else:
+                grads.append(torch.zeros_like(s).index_add_(0, i.long(), part))
+        return (dw, db, None, None, *grads, *([None] * len(idxs)))
+
+
+def gather_linear(srcs: List[torch.Tensor], idxs: List[Optional[torch.Tensor]], weight: torch.Tensor,
+                  bias: Optional[torch.Tensor], act: Optional[str] = None) -> torch.Tensor:
+    ok = (all(s.is_cuda and s.dtype == torch.bfloat16 and s.shape[1] % 8 == 0 for s in srcs) and 1 <= len(srcs) <= 3
+          and N.available())
+    if not ok:
+        if srcs[0].is_cuda:
+            N.require_for(srcs[0])
+        return gather_linear_ref(srcs, idxs, weight, bias, act)
+    idx32 = [None if i is None else (i if i.dtype == torch.int32 else i.to(torch.int32)) for i in idxs]
+    return _GatherLinear.apply(weight, bias, act, len(srcs), *srcs, *idx32)

@@ -184,6 +184,29 @@ __global__ void __launch_bounds__(256) gather_rows_peer_kernel(uint8_t* __restri
   }
 }
 
+// Row scatter-add with peer addressing (fp32): peer[owner[i]][row[i], :] += src[i, :] -- native vector reductions on
+// peer-mapped memory instead of the reference's int CAS loop (nvshmem_comm_kernels.cuh:17-54, 91-128).
+template <int G>
+__global__ void __launch_bounds__(256) scatter_add_rows_peer_kernel(const float* __restrict__ src, int64_t ld_src, int64_t n,
+                                                                    int F, float* const* __restrict__ peer_base,
+                                                                    int64_t ld_peer, const int* __restrict__ owner,
+                                                                    const int* __restrict__ row) {
+  const int lane = threadIdx.x & 31;
+  const int g = lane & (G - 1);
+  const int64_t grp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
+  const int64_t ngrp = ((int64_t)gridDim.x * blockDim.x) / G;
+  const int chunks = F >> 2;
+  for (int64_t i = grp; i < n; i += ngrp) {
+    float* dst = peer_base[owner[i]] + (int64_t)row[i] * ld_peer;
+    const float* s = src + i * ld_src;
+    for (int c = g; c < chunks; c += G) {
+      const float4 v = *reinterpret_cast<const float4*>(s + c * 4);
+      asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst + c * 4), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                   : "memory");
+    }
+  }
+}
+
 }  // namespace dgb
 
 using namespace dgb;
@@ -269,6 +292,23 @@ DGB_API int dgb_gather_rows_peer(void* out, int64_t ld_out_bytes, int64_t n, int
                                                               (const uint8_t* const*)peer_base, ld_peer_bytes, owner, row)
   if (G == 4) DGB_GR(4); else if (G == 8) DGB_GR(8); else if (G == 16) DGB_GR(16); else DGB_GR(32);
 #undef DGB_GR
+  DGB_CHECK_LAUNCH();
+  return 0;
+}
+
+DGB_API int dgb_scatter_add_rows_peer_f32(const float* src, int64_t ld_src, int64_t n, int F, void* const* peer_base,
+                                          int64_t ld_peer, const int* owner, const int* row, void* stream) {
+  if (n == 0) return 0;
+  if ((F & 3) || (ld_src & 3) || (ld_peer & 3)) return (int)cudaErrorInvalidValue;
+  const int G = pick_group(F >> 2);
+  int64_t blocks = (n + (256 / G) - 1) / (256 / G);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  cudaStream_t s = (cudaStream_t)stream;
+#define DGB_SA(GG)                                                                                                  \
+  scatter_add_rows_peer_kernel<GG><<<(unsigned)blocks, 256, 0, s>>>(src, ld_src, n, F, (float* const*)peer_base,    \
+                                                                   ld_peer, owner, row)
+  if (G == 4) DGB_SA(4); else if (G == 8) DGB_SA(8); else if (G == 16) DGB_SA(16); else DGB_SA(32);
+#undef DGB_SA
   DGB_CHECK_LAUNCH();
   return 0;
 }

@@ -1,0 +1,65 @@
+"""Vertex partitioners (METIS is not available on this image): contiguous blocks, round robin, hash,
+and a BFS / label-propagation block partitioner that produces spatially coherent parts with a balanced size.
+
+Reference counterparts: ``experiments/OGB/preprocess.py:15-29`` and ``experiments/GraphCast/data_utils/preprocess.py:14-30``
+(networkx + metis), ``DGraph/data/graph.py:270-288`` (round robin)."""
+from __future__ import annotations
+
+import torch
+
+
+def contiguous_blocks(num_nodes: int, world_size: int) -> torch.Tensor:
+    return (torch.arange(num_nodes) * world_size // num_nodes).clamp_(max=world_size - 1)
+
+
+def round_robin(num_nodes: int, world_size: int) -> torch.Tensor:
+    return torch.arange(num_nodes) % world_size
+
+
+def hashed(num_nodes: int, world_size: int, seed: int = 0) -> torch.Tensor:
+    v = torch.arange(num_nodes, dtype=torch.int64)
+    return ((v * 2654435761 + seed * 40503) % 4294967291 % world_size).to(torch.long)
+
+
+def bfs_blocks(edge_list: torch.Tensor, num_nodes: int, world_size: int, refine_iters: int = 3) -> torch.Tensor:
+    """Order vertices by a BFS sweep (sparse frontier expansion on tensors), cut the order into equal blocks, then run a few
+    rounds of balanced label propagation (a vertex moves to the majority part of its neighbours if that part has room)."""
+    src, dst = edge_list[:, 0].long(), edge_list[:, 1].long()
+    dev = edge_list.device
+    order = torch.full((num_nodes,), -1, dtype=torch.long, device=dev)
+    visited = torch.zeros(num_nodes, dtype=torch.bool, device=dev)
+    pos = 0
+    frontier = torch.zeros(0, dtype=torch.long, device=dev)
+    while pos < num_nodes:
+        if frontier.numel() == 0:
+            seed = torch.nonzero(~visited, as_tuple=True)[0][:1]
+            frontier = seed
+            visited[seed] = True
+        order[pos:pos + frontier.numel()] = frontier
+        pos += frontier.numel()
+        fm = torch.zeros(num_nodes, dtype=torch.bool, device=dev)
+        fm[frontier] = True
+        nxt = torch.unique(dst[fm[src]])
+        nxt = nxt[~visited[nxt]]
+        visited[nxt] = True
+        frontier = nxt
+    part = torch.empty(num_nodes, dtype=torch.long, device=dev)
+    part[order] = contiguous_blocks(num_nodes, world_size).to(dev)
+    cap = int(num_nodes / world_size * 1.03) + 1
+    for _ in range(refine_iters):
+        votes = torch.zeros(num_nodes, world_size, dtype=torch.int32, device=dev)
+        votes.index_put_((src, part[dst]), torch.ones_like(src, dtype=torch.int32), accumulate=True)
+        want = votes.argmax(1)
+        sizes = torch.bincount(part, minlength=world_size)
+        move = torch.nonzero(want != part, as_tuple=True)[0]
+        for v in move.tolist()[: num_nodes // 10]:
+            t = int(want[v])
+            if sizes[t] < cap:
+                sizes[t] += 1
+                sizes[part[v]] -= 1
+                part[v] = t
+    return part
+
+
+def edge_cut_fraction(edge_list: torch.Tensor, part: torch.Tensor) -> float:
+    return float((part[edge_list[:, 0]] != part[edge_list[:, 1]]).float().mean())

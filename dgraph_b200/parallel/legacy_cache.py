@@ -1,0 +1,145 @@
+"""Legacy NCCL gather / scatter caches and all-to-all-v helpers.
+
+Parity: reference ``DGraph/distributed/nccl/_nccl_cache.py:16-312`` (``NCCLGatherCache`` / ``NCCLScatterCache`` +
+generators), ``alltoallv_impl.py:7-180`` (``_nccl_alltoall_v``, ``_nccl_alltoallv_with_dict``,
+``torch_alltoallv_with_comm_map``) and ``_indices_utils.py``.  In the reference these feed the legacy
+``indices + rank_mappings`` API, which is broken in the snapshot; here the caches are thin views over the same
+:class:`NCCLGraphCommPlan` machinery that backs ``comm.gather`` / ``comm.scatter``.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from dgraph_b200.parallel.comm_plan import NCCLGraphCommPlan, plan_from_requests
+
+
+@dataclass
+class NCCLGatherCache:
+    """What rank ``rank`` needs to run a gather without any metadata exchange."""
+    gather_recv_comm_vector: List[int]  # rows received from every rank (unique vertices)
+    gather_send_comm_vector: List[int]  # rows sent to every rank
+    gather_send_local_placement: Dict[int, torch.Tensor]  # per peer: my local rows to ship
+    gather_recv_local_placement: Dict[int, torch.Tensor]  # per peer: edge slots filled from that peer's rows
+    gather_local_indices: torch.Tensor  # local rows addressed by local edges
+    gather_local_remapped_ranks: Optional[torch.Tensor]
+    rank: int
+    world_size: int
+    num_features: int = 0
+    plan: Optional[NCCLGraphCommPlan] = None
+
+
+@dataclass
+class NCCLScatterCache:
+    scatter_recv_comm_vector: List[int]
+    scatter_send_comm_vector: List[int]
+    scatter_send_local_placement: Dict[int, torch.Tensor]
+    scatter_recv_local_placement: Dict[int, torch.Tensor]
+    scatter_local_indices: torch.Tensor
+    num_output_rows: int
+    rank: int
+    world_size: int
+    plan: Optional[NCCLGraphCommPlan] = None
+
+
+def _split_dict(t: torch.Tensor, splits: List[int]) -> Dict[int, torch.Tensor]:
+    out, o = {}, 0
+    for r, k in enumerate(splits):
+        if k:
+            out[r] = t[o:o + k]
+        o += k
+    return out
+
+
+def _plan(indices, edge_placement, edge_dest_ranks, num_rows, rank, world_size, exchange):
+    idx = indices.reshape(-1).long()
+    mine = edge_placement.reshape(-1) == rank
+    owner = edge_dest_ranks.reshape(-1).long()[mine]
+    return plan_from_requests(rank, world_size, owner, idx[mine] % num_rows, num_rows, exchange)
+
+
+def NCCLGatherCacheGenerator(indices, edge_placement, edge_dest_ranks, num_input_rows, rank, world_size, exchange=None):
+    p = _plan(indices, edge_placement, edge_dest_ranks, num_input_rows, rank, world_size, exchange)
+    slots = torch.argsort(p.boundary_edge_buffer_map, stable=True)
+    per_slot_counts = torch.bincount(p.boundary_edge_buffer_map, minlength=sum(p.boundary_edge_splits))
+    recv_edges = []
+    o = 0
+    for k in p.boundary_edge_splits:
+        n_edges = int(per_slot_counts[o:o + k].sum()) if k else 0
+        recv_edges.append(n_edges)
+        o += k
+    return NCCLGatherCache(
+        gather_recv_comm_vector=list(p.boundary_edge_splits), gather_send_comm_vector=list(p.boundary_vertex_splits),
+        gather_send_local_placement=_split_dict(p.boundary_vertex_idx, p.boundary_vertex_splits),
+        gather_recv_local_placement=_split_dict(p.boundary_edge_idx[slots], recv_edges),
+        gather_local_indices=p.local_vertex_idx, gather_local_remapped_ranks=None, rank=rank, world_size=world_size, plan=p)
+
+
+def NCCLScatterCacheGenerator(indices, edge_placement, edge_dest_ranks, num_output_rows, rank, world_size, exchange=None):
+    p = _plan(indices, edge_placement, edge_dest_ranks, num_output_rows, rank, world_size, exchange)
+    return NCCLScatterCache(
+        scatter_recv_comm_vector=list(p.boundary_vertex_splits), scatter_send_comm_vector=list(p.boundary_edge_splits),
+        scatter_send_local_placement=_split_dict(torch.arange(sum(p.boundary_edge_splits)), p.boundary_edge_splits),
+        scatter_recv_local_placement=_split_dict(p.boundary_vertex_idx, p.boundary_vertex_splits),
+        scatter_local_indices=p.local_vertex_idx, num_output_rows=num_output_rows, rank=rank, world_size=world_size, plan=p)
+
+
+def _nccl_alltoall_v(local_send_tensor: torch.Tensor, local_recv_tensor: torch.Tensor, indices: torch.Tensor,
+                     local_rank_mapping: torch.Tensor, edge_rank_loc: torch.Tensor, src_rank_loc: torch.Tensor, rank: int,
+                     world_size: int, send_comm_vector: List[int], recv_comm_vector: List[int]):
+    """Variable all-to-all of rows with one ``P2POp`` pair per peer (``alltoallv_impl.py:7-131``)."""
+    F = local_send_tensor.shape[-1]
+    send = local_send_tensor.reshape(-1, F)
+    recv_parts, ops = {}, []
+    so = 0
+    for r in range(world_size):
+        k = send_comm_vector[r]
+        if r != rank and k:
+            ops.append(dist.P2POp(dist.isend, send[so:so + k].contiguous(), r))
+        so += k
+        kr = recv_comm_vector[r]
+        if r != rank and kr:
+            recv_parts[r] = torch.empty((kr, F), dtype=send.dtype, device=send.device)
+            ops.append(dist.P2POp(dist.irecv, recv_parts[r], r))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    ro = 0
+    out = local_recv_tensor.reshape(-1, F)
+    for r in range(world_size):
+        kr = recv_comm_vector[r]
+        if r in recv_parts:
+            out[ro:ro + kr] = recv_parts[r]
+        ro += kr
+    return local_recv_tensor
+
+
+def _nccl_alltoallv_with_dict(send_tensor_dict: Dict[int, torch.Tensor], recv_tensor_dict: Dict[int, torch.Tensor], rank: int,
+                              world_size: int):
+    """Same, with per-peer tensors (``alltoallv_impl.py:134-161``)."""
+    ops = []
+    for r, t in send_tensor_dict.items():
+        if r != rank and t.numel():
+            ops.append(dist.P2POp(dist.isend, t.contiguous(), r))
+    for r, t in recv_tensor_dict.items():
+        if r != rank and t.numel():
+            ops.append(dist.P2POp(dist.irecv, t, r))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    return recv_tensor_dict
+
+
+def torch_alltoallv_with_comm_map(send_tensor: torch.Tensor, send_splits: List[int], recv_splits: List[int], dim: int = 1):
+    """``dist.all_to_all`` on split lists along ``dim`` (``alltoallv_impl.py:164-180``)."""
+    send = [t.contiguous() for t in torch.split(send_tensor, send_splits, dim=dim)]
+    shape = list(send_tensor.shape)
+    recv = []
+    for k in recv_splits:
+        shape[dim] = k
+        recv.append(torch.empty(shape, dtype=send_tensor.dtype, device=send_tensor.device))
+    dist.all_to_all(recv, send)
+    return torch.cat(recv, dim=dim)

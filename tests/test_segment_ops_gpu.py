@@ -123,3 +123,35 @@ def test_fused_graphconv_layer_matches_reference_formulation():
     assert rel(xb.grad.float()[:, :F], xf.grad[:, :F]) < 3e-2
     assert rel(fused.conv.weight.grad, ref.conv.weight.grad) < 3e-2
     assert rel(fused.conv.bias.grad, ref.conv.bias.grad) < 3e-2
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_rank_local_ops_match_python_loops(dtype):  # model: reference tests/test_local_kernels.py:19-154
+    from dgraph_b200.parallel import rank_local as R
+
+    torch.manual_seed(0)
+    src = torch.randn(1, 8, 8, device="cuda").to(dtype)
+    si = torch.tensor([0, 3, 3, 7, 1], device="cuda")
+    di = torch.tensor([2, 2, 5, 0, 2], device="cuda")
+    out = torch.zeros(1, 6, 8, device="cuda", dtype=dtype)
+    R.OptimizedLocalScatterSumGather(src, si, di, out)
+    want = torch.zeros(6, 8, device="cuda")
+    for s, d in zip(si.tolist(), di.tolist()):
+        want[d] += src[0, s].float()
+    assert torch.allclose(out[0].float(), want, rtol=2e-2, atol=2e-2)
+    out2 = torch.zeros(1, 6, 8, device="cuda", dtype=dtype)
+    R.OptimizedLocalScatterGather(src, torch.tensor([4, 6], device="cuda"), torch.tensor([1, 3], device="cuda"), out2)
+    assert torch.equal(out2[0, 1], src[0, 4]) and torch.equal(out2[0, 3], src[0, 6]) and (out2[0, 0] == 0).all()
+    rm = torch.tensor([0, 1, 0, 1, 0], device="cuda")
+    out3 = torch.full((1, 5, 8), -1.0, device="cuda", dtype=dtype)
+    R.OptimizedRankLocalMaskedGather(src, si, rm, out3, 0)
+    for i in range(5):
+        assert torch.equal(out3[0, i], src[0, si[i]]) if rm[i] == 0 else (out3[0, i] == -1).all()
+    neg = -src.abs()  # masked scatter must not apply a ReLU (reference Q9)
+    out4 = torch.zeros(1, 8, 8, device="cuda", dtype=dtype)
+    R.RankLocalMaskedScatter(neg[:, :5], out4, di, rm, 0)
+    want4 = torch.zeros(8, 8, device="cuda")
+    for i in range(5):
+        if rm[i] == 0:
+            want4[di[i]] += neg[0, i].float()
+    assert torch.allclose(out4[0].float(), want4, rtol=2e-2, atol=2e-2) and (out4.float() <= 0).all()

@@ -1,0 +1,106 @@
+"""Halo gather / scatter micro-benchmark (parity: reference ``experiments/Benchmarks/TestNCCL.py:23-290``).
+
+``torchrun --nproc-per-node N experiments/Benchmarks/TestNCCL.py --message_size 128 --num_iters 1000 --log_dir logs``
+
+Protocol of the reference: all-pairs pattern, per-iteration CUDA-event times, first 10 iterations dropped, mean +- std;
+``.npy`` per rank.  Adds ``--sweep``: halo bandwidth sweep (rows x feature width) comparing the peer-memory pull engine with
+the NCCL all-to-all engine on identical splits; reports GB/s (max over ranks) and the fraction of the 770 GB/s per-direction
+NVLink peer-copy roofline (B200_PROFILING.md).
+"""
+import argparse
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from _common import cleanup, init_distributed  # noqa: E402
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from graph_utils import all_pairs_graph, halo_rows_graph  # noqa: E402
+
+
+def _time(fn, iters, dev):
+    ts = []
+    for _ in range(iters):
+        if dev.type == "cuda":
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        else:
+            import time
+
+            t0 = time.perf_counter()
+            fn()
+            ts.append((time.perf_counter() - t0) * 1e3)
+    return np.asarray(ts)
+
+
+def run(comm, graph, F, iters, dev, engine_name):
+    from dgraph_b200.parallel import HaloExchange, build_communication_pattern
+
+    rank, world = comm.get_rank(), comm.get_world_size()
+    pat = build_communication_pattern(graph.edge_list.to(dev), graph.partitioning.to(dev), rank, world)
+    dt = torch.bfloat16 if dev.type == "cuda" else torch.float32
+    x = torch.randn(pat.num_local_vertices, F, device=dev).to(dt).requires_grad_(True)
+    ex = HaloExchange(comm)
+    gather = _time(lambda: ex.augmented(x, pat), iters, dev)
+
+    def fwd_bwd():
+        a = ex.augmented(x, pat)
+        a.backward(torch.ones_like(a))
+
+    both = _time(fwd_bwd, iters, dev)
+    t = torch.tensor([gather[10:].mean(), both[10:].mean()], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    in_bytes = pat.num_halo_vertices * F * x.element_size()
+    out_bytes = int(pat.send_offset[-1]) * F * x.element_size()
+    b = torch.tensor([max(in_bytes, out_bytes)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(b, op=dist.ReduceOp.MAX)
+    return {"engine": engine_name, "F": F, "halo_rows": pat.num_halo_vertices, "gather_ms": float(t[0]),
+            "gather_scatter_ms": float(t[1]), "gather_GBps": float(b[0]) / float(t[0]) / 1e6,
+            "frac_of_770GBps": float(b[0]) / float(t[0]) / 1e6 / 770.0, "per_iter": gather}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--message_size", type=int, default=128)
+    ap.add_argument("--benchmark_cache", action="store_true")
+    ap.add_argument("--num_iters", type=int, default=1000)
+    ap.add_argument("--log_dir", type=str, default="logs")
+    ap.add_argument("--sweep", action="store_true")
+    ap.add_argument("--backend", type=str, default="nccl")
+    a = ap.parse_args()
+    comm, rank, world, dev = init_distributed(a.backend)
+    os.makedirs(a.log_dir, exist_ok=True)
+    name = type(comm.engine).__name__
+    results = []
+    if not a.sweep:
+        r = run(comm, all_pairs_graph(world), a.message_size, a.num_iters, dev, name)
+        np.save(os.path.join(a.log_dir, f"gather_times_{name}_rank{rank}.npy"), r.pop("per_iter"))
+        results.append(r)
+    else:
+        for rows in (1_000, 10_000, 100_000, 1_000_000):
+            for F in (64, 256, 768):
+                per_peer = max(rows // max(world - 1, 1), 1)
+                g = halo_rows_graph(world, max(per_peer * 2, 1024), per_peer)
+                r = run(comm, g, F, min(a.num_iters, 60), dev, name)
+                r.pop("per_iter")
+                results.append(r)
+    if rank == 0:
+        for r in results:
+            print(json.dumps(r), flush=True)
+        with open(os.path.join(a.log_dir, f"halo_bench_{name}_world{world}.json"), "w") as f:
+            json.dump(results, f)
+    cleanup(comm)
+
+
+if __name__ == "__main__":
+    main()

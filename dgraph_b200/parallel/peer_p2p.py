@@ -48,16 +48,13 @@ class PeerP2P:
         PeerP2P._count += 1
         t, off = PeerP2P._engine.slot_tensor(("p2p", name or PeerP2P._count), (int(numel),), dtype)
         t.zero_()
-        t._dgb_offset = off
         return t
 
     @staticmethod
     def clone_tensor(t: torch.Tensor, name: Optional[str] = None) -> torch.Tensor:
         s = PeerP2P.allocate_symmetric_memory(t.numel(), dtype=t.dtype, name=name)
         s.copy_(t.reshape(-1))
-        out = s.view(t.shape)
-        out._dgb_offset = s._dgb_offset
-        return out
+        return s.view(t.shape)
 
     @staticmethod
     def padded_clone_tensor(t: torch.Tensor, padded_numel: int, name: Optional[str] = None) -> torch.Tensor:
@@ -89,7 +86,7 @@ class PeerP2P:
         eng = PeerP2P._engine
         rb = symm_src.shape[-1] * symm_src.element_size()
         N.check(N.lib().dgb_gather_rows_peer(N.ptr(output), N.i64(rb), N.i64(rows.numel()), N.i32(rb),
-                                             N.ptr(eng.arena.ptr_table(symm_src._dgb_offset)), N.i64(rb),
+                                             N.ptr(eng.arena.ptr_table(symm_src.data_ptr() - eng.arena.base)), N.i64(rb),
                                              N.ptr(owners.to(torch.int32)), N.ptr(rows.to(torch.int32)), N.stream()),
                 "dgb_gather_rows_peer")
         N.count_launch()
@@ -101,7 +98,7 @@ class PeerP2P:
         eng = PeerP2P._engine
         F = symm_dst.shape[-1]
         N.check(N.lib().dgb_scatter_add_rows_peer_f32(N.ptr(values), N.i64(values.stride(0)), N.i64(rows.numel()), N.i32(F),
-                                                      N.ptr(eng.arena.ptr_table(symm_dst._dgb_offset)), N.i64(F),
+                                                      N.ptr(eng.arena.ptr_table(symm_dst.data_ptr() - eng.arena.base)), N.i64(F),
                                                       N.ptr(owners.to(torch.int32)), N.ptr(rows.to(torch.int32)), N.stream()),
                 "dgb_scatter_add_rows_peer_f32")
         N.count_launch()

@@ -164,6 +164,25 @@ class _PatternPeerInfo:
         self.n_bnd = int(self.bnd_row.numel())
 
 
+class _SlotGuard:
+    """Frees a ring entry when the autograd graph that needs it dies without ever running backward (forward-only loops with
+    ``requires_grad`` inputs would otherwise grow the ring on every call)."""
+
+    def __init__(self, engine, key, off):
+        self.engine, self.key, self.off = engine, key, off
+
+    def release(self):
+        if self.engine is not None:
+            self.engine.release_slot(self.key, self.off)
+            self.engine = None
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:  # noqa: BLE001 - interpreter shutdown
+            pass
+
+
 class _HaloAug(Function):
     """``aug = cat([x, halo(x)])`` through the symmetric arena; backward pull-reduces halo gradients on the owners."""
 
@@ -172,7 +191,7 @@ class _HaloAug(Function):
         info = engine.pattern_info(pat)
         F = x.shape[1]
         assert x.dim() == 2 and (F * x.element_size()) % 16 == 0, "feature rows must be multiples of 16 bytes"
-        aug, off = engine.slot_tensor(("halo_fwd", id(pat)), (info.max_aug, F), x.dtype, ring=True,
+        aug, off = engine.slot_tensor(("halo_fwd", info.uid), (info.max_aug, F), x.dtype, ring=True,
                                       track=torch.is_grad_enabled() and x.requires_grad)
         aug = aug[: info.n_nbr_local + info.n_halo]
         aug[: info.n_nbr_local].copy_(x)
@@ -183,18 +202,19 @@ class _HaloAug(Function):
                                       N.ptr(info.halo_row), N.stream()), "dgb_halo_pull")
         N.count_launch(2)
         engine.mark_read(off)
-        ctx.engine, ctx.pat, ctx.slot_key = engine, pat, (("halo_fwd", id(pat)), off)
+        ctx.engine, ctx.pat = engine, pat
+        ctx.slot_guard = _SlotGuard(engine, ("halo_fwd", info.uid), off)
         return aug
 
     @staticmethod
     def backward(ctx, g_aug):
         engine, pat = ctx.engine, ctx.pat
         info = engine.pattern_info(pat)
-        engine.release_slot(*ctx.slot_key)
+        ctx.slot_guard.release()
         F = g_aug.shape[1]
         g_aug = g_aug.contiguous()
         assert g_aug.dtype == torch.bfloat16, "halo gradient reduce kernel is bf16 (fp32 accumulate)"
-        gh, off = engine.slot_tensor(("halo_bwd", id(pat)), (info.max_halo, F), g_aug.dtype, ring=False)
+        gh, off = engine.slot_tensor(("halo_bwd", info.uid), (info.max_halo, F), g_aug.dtype, ring=False)
         gh[: info.n_halo].copy_(g_aug[info.n_nbr_local:])
         engine.barrier_on_stream()
         gx = g_aug[: info.n_nbr_local].clone()
@@ -213,7 +233,7 @@ class PeerMemoryEngine(TorchDistEngine):
         self.device = torch.device("cuda", torch.cuda.current_device())
         N.lib()
         self._epoch = 0
-        self._infos: Dict[int, _PatternPeerInfo] = {}
+        self._uid = 0
         self._rings: Dict[Tuple, List] = {}
         self._by_off: Dict[int, dict] = {}
         self._timeout_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
@@ -233,10 +253,14 @@ class PeerMemoryEngine(TorchDistEngine):
         return [o.tolist() for o in out]
 
     def pattern_info(self, pat) -> _PatternPeerInfo:
-        i = self._infos.get(id(pat))
-        if i is None:
+        """Per-pattern tables live on the pattern object itself (``id()`` values are recycled after garbage collection)."""
+        i = pat._cache.get("peer_info")
+        if i is None or i.engine_ref is not self:
             i = _PatternPeerInfo(self, pat)
-            self._infos[id(pat)] = i
+            i.engine_ref = self
+            self._uid += 1
+            i.uid = self._uid
+            pat._cache["peer_info"] = i
         return i
 
     # ---- symmetric slots -----------------------------------------------------------------------

@@ -85,9 +85,10 @@ class PeerP2P:
         ``nvshmemx_getmem_nbi_warp`` per row, ``nvshmem_comm_kernels.cuh:255-299``)."""
         eng = PeerP2P._engine
         rb = symm_src.shape[-1] * symm_src.element_size()
+        own32, row32 = owners.to(torch.int32).contiguous(), rows.to(torch.int32).contiguous()  # keep alive across the launch
         N.check(N.lib().dgb_gather_rows_peer(N.ptr(output), N.i64(rb), N.i64(rows.numel()), N.i32(rb),
                                              N.ptr(eng.arena.ptr_table(symm_src.data_ptr() - eng.arena.base)), N.i64(rb),
-                                             N.ptr(owners.to(torch.int32)), N.ptr(rows.to(torch.int32)), N.stream()),
+                                             N.ptr(own32), N.ptr(row32), N.stream()),
                 "dgb_gather_rows_peer")
         N.count_launch()
         return output
@@ -97,9 +98,10 @@ class PeerP2P:
         """``symm_dst@owners[i][rows[i], :] += values[i, :]`` (fp32 vector reductions on peer memory)."""
         eng = PeerP2P._engine
         F = symm_dst.shape[-1]
+        own32, row32 = owners.to(torch.int32).contiguous(), rows.to(torch.int32).contiguous()  # keep alive across the launch
         N.check(N.lib().dgb_scatter_add_rows_peer_f32(N.ptr(values), N.i64(values.stride(0)), N.i64(rows.numel()), N.i32(F),
                                                       N.ptr(eng.arena.ptr_table(symm_dst.data_ptr() - eng.arena.base)), N.i64(F),
-                                                      N.ptr(owners.to(torch.int32)), N.ptr(rows.to(torch.int32)), N.stream()),
+                                                      N.ptr(own32), N.ptr(row32), N.stream()),
                 "dgb_scatter_add_rows_peer_f32")
         N.count_launch()
         return symm_dst

@@ -29,7 +29,7 @@ def main():
     except Exception:
         pass
     shapes = [(2449029, 256, 104), (2449029, 512, 104), (2449029, 256, 256), (2449029, 512, 256), (2449029, 47, 256),
-              (655320, 128, 384), (655320, 512, 512), (8192, 8192, 8192)]
+              (655320, 128, 384), (655320, 512, 512), (3114720, 128, 384), (16384, 2048, 8192)]
     rows = []
     for M, N, K in shapes:
         a = torch.randn(M, K, device="cuda").bfloat16()

@@ -6,7 +6,8 @@
 //
 // Roles (320 threads): warp 0 = TMA producer (A and B k-blocks, 128-B swizzle), warp 1 = MMA issuer (one elected
 // lane, tcgen05.mma cta_group::1, M=128 x N=BLOCK_N x K=16), warps 2..9 = epilogue (tcgen05.ld 32x32b -> smem-staged
-// bias -> compile-time activation -> bf16/fp32 -> 16-byte global stores; two warps per TMEM lane quarter).  Two TMEM accumulator stages let the epilogue of tile i overlap
+// bias -> compile-time activation -> bf16/fp32 -> swizzled 32-row staging tile -> TMA store, double-buffered per warp;
+// two warps per TMEM lane quarter; direct register stores only when C is not 16-byte aligned).  Two TMEM accumulator stages let the epilogue of tile i overlap
 // the main loop of tile i+1; the smem ring has STAGES k-blocks in flight.  The gathered variant replaces the TMA
 // load of A by four producer warps that gather rows (local HBM or NVLink peer memory) into the same swizzled layout.
 #include "tc_common.cuh"
@@ -17,7 +18,7 @@ namespace dgb {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;  // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
-constexpr int MAX_N = 8192;  // bias for all N-tiles is staged in shared memory once per CTA
+constexpr int MAX_N = 2048;  // bias for all N-tiles is staged in shared memory once per CTA
 
 enum Act { ACT_NONE = 0, ACT_RELU = 1, ACT_SILU = 2 };
 
@@ -41,9 +42,10 @@ struct SmemLayout {
   static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
   static constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BLOCK_N >= 256) ? 4 : (BLOCK_N >= 128 ? 6 : 8);
+  static constexpr int STAGES = (BLOCK_N >= 256) ? 3 : (BLOCK_N >= 128 ? 4 : 6);
   static constexpr int BAR_BYTES = 256 + MAX_N * 4;  // mbarriers + tmem pointer, then the staged bias [MAX_N]
-  static constexpr int TOTAL = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // + alignment slack
+  static constexpr int STORE_BYTES = 8 * 2 * 4096;   // per epilogue warp: two 4-KB staging tiles for TMA stores
+  static constexpr int TOTAL = STAGES * STAGE_BYTES + STORE_BYTES + BAR_BYTES + 1024;  // + alignment slack
 };
 
 template <int ACT>
@@ -59,15 +61,16 @@ constexpr int GATHER_WARP0 = EPI_WARP0 + NUM_EPI_WARPS;  // warps 10..13 when GA
 constexpr int THREADS_DENSE = (EPI_WARP0 + NUM_EPI_WARPS) * 32;
 constexpr int THREADS_GATHER = THREADS_DENSE + 128;
 
-template <int BLOCK_N, bool OUT_F32, bool GATHER, int ACT>
+template <int BLOCK_N, bool OUT_F32, bool GATHER, int ACT, bool STORE_TMA>
 __global__ void __launch_bounds__(GATHER ? THREADS_GATHER : THREADS_DENSE, 1)
 gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                    const GemmParams p) {
+                    const __grid_constant__ CUtensorMap tmap_c, const GemmParams p) {
   using L = SmemLayout<BLOCK_N>;
   constexpr int STAGES = L::STAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* bar_base = smem + STAGES * L::STAGE_BYTES;
+  uint8_t* store_base = smem + STAGES * L::STAGE_BYTES;  // 1024-B aligned (stage sizes are multiples of 1024)
+  uint8_t* bar_base = store_base + L::STORE_BYTES;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(bar_base);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full = empty_bar + STAGES;
@@ -90,6 +93,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   if (warp == 0 && lane == 0) {
     if (!GATHER) tc::tma_prefetch_desc(&tmap_a);
     tc::tma_prefetch_desc(&tmap_b);
+    if (STORE_TMA) tc::tma_prefetch_desc(&tmap_c);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -171,9 +175,10 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     const int q = warp & 3;                      // TMEM lane quarter this warp may access
     const int half = (warp - EPI_WARP0) >> 2;    // which half of the tile's columns
     constexpr int COLS = BLOCK_N / 2;            // columns per epilogue warp
-    constexpr int CH = (COLS >= 64) ? 64 : 32;   // columns per TMEM round trip
+    constexpr int CH = OUT_F32 ? 32 : ((COLS >= 64) ? 64 : 32);  // columns per TMEM round trip (= one TMA store box)
     using OutT = typename std::conditional<OUT_F32, float, __nv_bfloat16>::type;
     int it = 0;
+    int sbuf = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int m0 = (tile / tiles_n) * BLOCK_M;
       const int nt = tile % tiles_n;
@@ -207,7 +212,33 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           v[t + 2] = apply_act<ACT>(__uint_as_float(r[t + 2]) + b4.z);
           v[t + 3] = apply_act<ACT>(__uint_as_float(r[t + 3]) + b4.w);
         }
-        if (row_ok) {
+        if (STORE_TMA) {
+          // stage the 32 x CH tile of this warp in shared memory (swizzled, conflict-free) and let TMA write full lines;
+          // rows >= M and columns >= N are clipped by the tensor map
+          constexpr int ROW_B = CH * (OUT_F32 ? 4 : 2);  // 128 bytes (SWIZZLE_128B box) or 64 bytes (unswizzled box)
+          uint8_t* st = store_base + ((warp - EPI_WARP0) * 2 + sbuf) * 4096;
+          if (lane == 0) tc::tma_store_wait_read1();  // the tile issued two chunks ago has been read out
+          __syncwarp();
+#pragma unroll
+          for (int t = 0; t < ROW_B / 16; ++t) {
+            uint4 w;
+            if (OUT_F32) {
+              const float* f = v + t * 4;
+              w = make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
+            } else {
+              w = pack8(v + t * 8);
+            }
+            const int off = (ROW_B == 128) ? (lane * 128 + ((t ^ (lane & 7)) << 4)) : (lane * 64 + (t << 4));
+            *reinterpret_cast<uint4*>(st + off) = w;
+          }
+          tc::fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tc::tma_store_2d(&tmap_c, st, n0 + half * COLS + c, m0 + q * 32);
+            tc::tma_store_commit();
+          }
+          sbuf ^= 1;
+        } else if (row_ok) {
           if (ncol >= CH && vec_ok) {
             if (OUT_F32) {
 #pragma unroll
@@ -232,6 +263,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       tc::tc_fence_before();
       tc::mbar_arrive(&tmem_empty[as]);
     }
+    if (STORE_TMA && lane == 0) tc::tma_store_wait_all();  // all bulk stores of this warp have landed before the CTA exits
   } else if (GATHER) {
     // ===================== gather producers (4 warps): A rows -> swizzled smem =====================
     const int gt = threadIdx.x - GATHER_WARP0 * 32;  // 0..127
@@ -281,10 +313,11 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   if (warp == 2) tc::tmem_dealloc(tmem_base, 2 * BLOCK_N);
 }
 
-template <int BLOCK_N, bool OUT_F32, bool GATHER, int ACT>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t stream) {
+template <int BLOCK_N, bool OUT_F32, bool GATHER, int ACT, bool STORE_TMA>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tcm, const GemmParams& p,
+                       cudaStream_t stream) {
   using L = SmemLayout<BLOCK_N>;
-  auto kern = gemm_bf16_tn_kernel<BLOCK_N, OUT_F32, GATHER, ACT>;
+  auto kern = gemm_bf16_tn_kernel<BLOCK_N, OUT_F32, GATHER, ACT, STORE_TMA>;
   static bool configured = false;
   if (!configured) {
     DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
@@ -295,21 +328,36 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   DGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const int tiles = ((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + BLOCK_N - 1) / BLOCK_N);
   const int grid = tiles < sms ? tiles : sms;
-  kern<<<grid, GATHER ? THREADS_GATHER : THREADS_DENSE, L::TOTAL, stream>>>(ta, tb, p);
+  kern<<<grid, GATHER ? THREADS_GATHER : THREADS_DENSE, L::TOTAL, stream>>>(ta, tb, tcm, p);
   DGB_CHECK_LAUNCH();
   return 0;
 }
 
+template <int BLOCK_N, bool OUT_F32, bool GATHER, int ACT>
+static int launch_store(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t s) {
+  // TMA store needs a 16-byte aligned base and row stride; otherwise fall back to direct (clipped) register stores
+  const int eb = OUT_F32 ? 4 : 2;
+  const bool tma_ok = ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0) && (((int64_t)p.ldc * eb) % 16 == 0);
+  if (tma_ok) {
+    constexpr int CH = OUT_F32 ? 32 : ((BLOCK_N / 2 >= 64) ? 64 : 32);
+    CUtensorMap tcm;
+    const int rc = make_tmap_2d(&tcm, p.C, (uint64_t)p.M, (uint64_t)p.N, (uint64_t)p.ldc, 32, CH, eb,
+                                (CH * eb == 128) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (rc == 0) return launch_gemm<BLOCK_N, OUT_F32, GATHER, ACT, true>(ta, tb, tcm, p, s);
+  }
+  return launch_gemm<BLOCK_N, OUT_F32, GATHER, ACT, false>(ta, tb, tb, p, s);
+}
+
 template <int BLOCK_N, bool GATHER>
 static int dispatch_act(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int out_f32, cudaStream_t s) {
-  if (out_f32) {  // fp32 output is only used for logits / loss inputs: no fused activation variants needed
-    if (p.act == ACT_NONE) return launch_gemm<BLOCK_N, true, GATHER, ACT_NONE>(ta, tb, p, s);
-    if (p.act == ACT_SILU) return launch_gemm<BLOCK_N, true, GATHER, ACT_SILU>(ta, tb, p, s);
-    return launch_gemm<BLOCK_N, true, GATHER, ACT_RELU>(ta, tb, p, s);
+  if (out_f32) {
+    if (p.act == ACT_NONE) return launch_store<BLOCK_N, true, GATHER, ACT_NONE>(ta, tb, p, s);
+    if (p.act == ACT_SILU) return launch_store<BLOCK_N, true, GATHER, ACT_SILU>(ta, tb, p, s);
+    return launch_store<BLOCK_N, true, GATHER, ACT_RELU>(ta, tb, p, s);
   }
-  if (p.act == ACT_NONE) return launch_gemm<BLOCK_N, false, GATHER, ACT_NONE>(ta, tb, p, s);
-  if (p.act == ACT_SILU) return launch_gemm<BLOCK_N, false, GATHER, ACT_SILU>(ta, tb, p, s);
-  return launch_gemm<BLOCK_N, false, GATHER, ACT_RELU>(ta, tb, p, s);
+  if (p.act == ACT_NONE) return launch_store<BLOCK_N, false, GATHER, ACT_NONE>(ta, tb, p, s);
+  if (p.act == ACT_SILU) return launch_store<BLOCK_N, false, GATHER, ACT_SILU>(ta, tb, p, s);
+  return launch_store<BLOCK_N, false, GATHER, ACT_RELU>(ta, tb, p, s);
 }
 
 template <bool GATHER>

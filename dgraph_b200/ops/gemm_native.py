@@ -24,6 +24,14 @@ def _as_bf16_rowmajor(t: torch.Tensor) -> torch.Tensor:
     return t
 
 
+def _alloc_out(M: int, Nn: int, dtype, device) -> torch.Tensor:
+    """Output with a 16-byte aligned row stride (lets the epilogue use TMA stores); returned as an ``[M, N]`` view."""
+    per16 = 16 // torch.empty((), dtype=dtype).element_size()
+    ld = (Nn + per16 - 1) // per16 * per16
+    buf = torch.empty((M, ld), dtype=dtype, device=device)
+    return buf if ld == Nn else buf[:, :Nn]
+
+
 def gemm_bf16_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, act=None,
                  out_dtype=torch.bfloat16, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``act(a @ b.T + bias)``; ``a [M, K]``, ``b [N, K]`` bf16.  Zero-padded extra K columns in either operand are fine."""
@@ -31,7 +39,7 @@ def gemm_bf16_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] 
     M, K = a.shape[0], min(a.shape[1], b.shape[1]) if a.shape[1] != b.shape[1] else a.shape[1]
     Nn = b.shape[0]
     if out is None:
-        out = torch.empty((M, Nn), dtype=out_dtype, device=a.device)
+        out = _alloc_out(M, Nn, out_dtype, a.device)
     assert out.stride(1) == 1 and out.dtype in (torch.bfloat16, torch.float32)
     bias_f = None if bias is None else bias.float().contiguous()
     N.check(N.lib().dgb_gemm_bf16_tn(N.ptr(a), N.i64(a.stride(0)), N.ptr(b), N.i64(b.stride(0)), N.ptr(out),
@@ -63,7 +71,7 @@ def gather_gemm_bf16(srcs: List[torch.Tensor], idxs: List[Optional[torch.Tensor]
     srcs = [_as_bf16_rowmajor(s) for s in srcs]
     idx32 = [None if i is None else (i if i.dtype == torch.int32 else i.to(torch.int32)).contiguous() for i in idxs]
     Nn = w_packed.shape[0]
-    out = torch.empty((M, Nn), dtype=out_dtype, device=w_packed.device)
+    out = _alloc_out(M, Nn, out_dtype, w_packed.device)
     bases = (ctypes.c_void_p * 3)(*[s.data_ptr() for s in srcs] + [0] * (3 - n))
     lds = (ctypes.c_int64 * 3)(*[s.stride(0) for s in srcs] + [0] * (3 - n))
     ips = (ctypes.c_void_p * 3)(*[(0 if i is None else i.data_ptr()) for i in idx32] + [0] * (3 - n))

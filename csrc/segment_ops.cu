@@ -96,8 +96,8 @@ __device__ __forceinline__ void seg_accumulate(const uint4& v, const uint4& v2, 
 }
 
 template <int MODE, int G, int NC, bool HALO>
-__global__ void __launch_bounds__(256) seg_reduce_kernel(const SegParams p) {
-  constexpr int UNROLL = (NC == 1 && MODE == SEG_SUM) ? 8 : 4;
+__global__ void __launch_bounds__(256, (NC == 1 && !HALO) ? (MODE == SEG_SUM ? 5 : 4) : 1) seg_reduce_kernel(const SegParams p) {
+  constexpr int UNROLL = 4;
   const int lane = threadIdx.x & 31;
   const int g = lane & (G - 1);
   const int sub = lane / G;

@@ -68,7 +68,14 @@ class _GatherLinear(Function):
         wb = weight.to(torch.bfloat16)
         dcat = gemm_bf16_tn(g, wb.t().contiguous())  # [M, sum(ks)]
         cat = torch.cat([s if i is None else s.index_select(0, i.long()) for s, i in zip(srcs, idxs)], dim=1)
-        dw = torch.matmul(g.t(), cat).float() if ctx.needs_input_grad[0] else None
+        dw = None
+        if ctx.needs_input_grad[0]:
+            from dgraph_b200.ops.gemm_native import gemm_bf16_nn_grad_w
+
+            if cat.shape[1] <= 256:
+                dw = gemm_bf16_nn_grad_w(g, cat)
+            else:  # wide concatenations: one split-K GEMM per 256-column slab
+                dw = torch.cat([gemm_bf16_nn_grad_w(g, cat[:, o:o + 256]) for o in range(0, cat.shape[1], 256)], dim=1)
         db = g.float().sum(0) if ctx.needs_input_grad[1] else None
         grads, o = [], 0
         for s, i, k in zip(srcs, idxs, ctx.ks):

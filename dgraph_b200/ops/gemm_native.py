@@ -86,9 +86,21 @@ def gather_gemm_bf16(srcs: List[torch.Tensor], idxs: List[Optional[torch.Tensor]
 
 
 def gemm_bf16_nn_grad_w(g: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
-    """Weight gradient ``g^T @ x`` (``[N, K]``; reduction over the huge row dimension).  Plain library GEMM (cuBLAS):
-    both operands are MN-major for this product; a split-K tcgen05 kernel is future work."""
-    return torch.matmul(g.t(), x[:, : x.shape[1]])
+    """Weight gradient ``g^T @ x`` -> fp32 ``[N1, N2]`` (reduction over the huge row dimension) with the split-K tcgen05
+    kernel (``csrc/gemm_wgrad_tcgen05.cu``: MN-major operands via TMA, TMEM accumulators, vector reductions into ``dW``).
+    Falls back to a library GEMM only for ``N2 > 256``."""
+    N1, N2 = g.shape[1], x.shape[1]
+    ok = (g.is_cuda and g.dtype == torch.bfloat16 and x.dtype == torch.bfloat16 and N2 <= 256 and g.shape[0] == x.shape[0]
+          and hasattr(N.lib(), "dgb_gemm_wgrad_bf16"))
+    if not ok:
+        return torch.matmul(g.t(), x).float()
+    g, x = _as_bf16_rowmajor(g), _as_bf16_rowmajor(x)
+    out = torch.zeros((N1, (N2 + 3) // 4 * 4), dtype=torch.float32, device=g.device)
+    N.check(N.lib().dgb_gemm_wgrad_bf16(N.ptr(g), N.i64(g.stride(0)), N.ptr(x), N.i64(x.stride(0)), N.ptr(out),
+                                        N.i64(out.stride(0)), N.i64(g.shape[0]), N.i32(N1), N.i32(N2), N.stream()),
+            "dgb_gemm_wgrad_bf16")
+    N.count_launch()
+    return out if out.shape[1] == N2 else out[:, :N2]
 
 
 def act_backward(g: torch.Tensor, y: torch.Tensor, act: str) -> torch.Tensor:

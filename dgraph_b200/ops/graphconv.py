@@ -2,7 +2,7 @@
 
 Forward  : one tcgen05 GEMM ``PQ = x_aug [W_i ; W_j]^T (+ b on the P half)`` -> one fused gather-add-ReLU-segment-sum.
 Backward : ``dP = g * cnt`` and ``dQ = masked CSC sum`` written straight into the two halves of one ``[n_aug, 2H]``
-           buffer -> one GEMM for ``dX`` (skipped when the input needs no gradient), one for ``dW``, one column-sum
+           buffer -> one GEMM for ``dX`` (skipped when the input needs no gradient), one split-K tcgen05 GEMM for ``dW``, one column-sum
            for ``db``.  No ``[E, *]`` tensor, no ``cat``/slice copies, no gradient-accumulation adds.
 
 Semantics: reference ``GraphConvLayer.forward`` (``experiments/OGB/GCN.py:34-67``).
@@ -13,7 +13,7 @@ import torch
 from torch.autograd import Function
 
 from dgraph_b200.ops import _native as N
-from dgraph_b200.ops.gemm_native import gemm_bf16_tn
+from dgraph_b200.ops.gemm_native import gemm_bf16_nn_grad_w, gemm_bf16_tn
 from dgraph_b200.ops.reduce import colsum
 from dgraph_b200.ops import segment as S
 
@@ -66,7 +66,7 @@ class _GraphConvFused(Function):
         if ctx.needs_input_grad[0]:
             dx = gemm_bf16_tn(dPQ, wcat.t().contiguous(), None, None)  # [n_aug, Fp]
         if ctx.needs_input_grad[1]:
-            dwcat = torch.matmul(dPQ.t(), x_aug).float()  # [2H, Fp]; plain library GEMM (reduction over rows)
+            dwcat = gemm_bf16_nn_grad_w(dPQ, x_aug)  # [2H, Fp] fp32: split-K tcgen05 kernel
             dw = torch.cat([dwcat[:H, :f_in], dwcat[H:, :f_in]], dim=1)
         if ctx.needs_input_grad[2]:
             db = colsum(dPQ[:n, :H])

@@ -92,3 +92,17 @@ def test_gather_gemm_matches_cat_linear(ks):
     cat = torch.cat([(s[:, :k] if i is None else s[i.long(), :k]) for s, i, k in zip(srcs, idxs, ks)], 1)
     yr = _ref(cat, w, bias, "silu")
     assert torch.allclose(y.float(), yr, rtol=2e-2, atol=5e-2), (y.float() - yr).abs().max().item()
+
+
+@pytest.mark.parametrize("M,N1,N2", [(1000, 128, 64), (5000, 512, 104), (70000, 256, 256), (333, 47, 8), (100000, 512, 256)])
+def test_wgrad_splitk_matches_fp32_reference(M, N1, N2):
+    from dgraph_b200.ops.gemm_native import gemm_bf16_nn_grad_w
+
+    torch.manual_seed(M)
+    big = torch.randn(M, N1 + 8, device="cuda").bfloat16()
+    g = big[:, :N1] if N1 % 8 == 0 else torch.randn(M, N1, device="cuda").bfloat16()
+    x = torch.randn(M, N2, device="cuda").bfloat16()
+    dw = gemm_bf16_nn_grad_w(g, x)
+    ref = g.float().t() @ x.float()
+    assert dw.shape == (N1, N2) and dw.dtype == torch.float32
+    assert torch.allclose(dw, ref, rtol=1e-2, atol=2e-2 * (M ** 0.5)), (dw - ref).abs().max().item()

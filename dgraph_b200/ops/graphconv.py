@@ -24,13 +24,18 @@ class _GraphConvFused(Function):
         H = weight.shape[0]
         Fp = x_aug.shape[1]
         dev = x_aug.device
+        n_aug = x_aug.shape[0]
+        # [W_i ; W_j] stacked along the output dimension, zero-padded to the (16-byte aligned) feature width
         wcat = torch.zeros((2 * H, Fp), dtype=torch.bfloat16, device=dev)
         wcat[:H, :f_in] = weight[:, :f_in]
         wcat[H:, :f_in] = weight[:, f_in:2 * f_in]
         bcat = torch.zeros(2 * H, dtype=torch.float32, device=dev)
         bcat[:H] = bias
-        n_aug = x_aug.shape[0]
-        PQ = gemm_bf16_tn(x_aug, wcat, bcat, None)
+        # local rows need P and Q (one GEMM, N = 2H); halo rows only Q (N = H) written into the same [n_aug, 2H] buffer
+        PQ = torch.empty((n_aug, 2 * H), dtype=torch.bfloat16, device=dev)
+        gemm_bf16_tn(x_aug[:n_local], wcat, bcat, None, out=PQ[:n_local])
+        if n_aug > n_local:
+            gemm_bf16_tn(x_aug[n_local:], wcat[H:], None, None, out=PQ[n_local:, H:])
         P, Q = PQ[:n_local, :H], PQ[:, H:]
         need_w = weight.requires_grad or x_aug.requires_grad
         out = torch.empty((n_local, H), dtype=torch.bfloat16, device=dev)
@@ -52,22 +57,27 @@ class _GraphConvFused(Function):
         g = g.contiguous()
         n_aug = x_aug.shape[0]
         dev = g.device
+        # [dP | dQ] for the local rows, dQ only for the halo rows (their P half is never read)
         dPQ = torch.empty((n_aug, 2 * H), dtype=torch.bfloat16, device=dev)
-        if n_aug > n:
-            dPQ[n:, :H].zero_()
         lib = N.lib()
         N.check(lib.dgb_mul_cnt(N.ptr(g), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(dPQ), N.i64(2 * H), N.i64(n), N.i32(H),
                                 N.stream()), "dgb_mul_cnt")
+        dQ = dPQ[:, H:]
         N.check(lib.dgb_seg_masked_sum(N.ptr(kp.colptr), N.ptr(kp.row), N.ptr(kp.csc_to_csr), N.ptr(mask), N.i64(n_aug),
-                                       N.i32(H), N.ptr(g), N.i64(H), N.ptr(dPQ[:, H:]), N.i64(2 * H), N.stream()),
+                                       N.i32(H), N.ptr(g), N.i64(H), N.ptr(dQ), N.i64(2 * H), N.stream()),
                 "dgb_seg_masked_sum")
         N.count_launch(2)
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
-            dx = gemm_bf16_tn(dPQ, wcat.t().contiguous(), None, None)  # [n_aug, Fp]
+            dx = torch.empty((n_aug, x_aug.shape[1]), dtype=torch.bfloat16, device=dev)
+            wt = wcat.t().contiguous()  # [Fp, 2H]
+            gemm_bf16_tn(dPQ[:n], wt, None, None, out=dx[:n])
+            if n_aug > n:
+                gemm_bf16_tn(dQ[n:], wt[:, H:], None, None, out=dx[n:])
         if ctx.needs_input_grad[1]:
-            dwcat = gemm_bf16_nn_grad_w(dPQ, x_aug)  # [2H, Fp] fp32: split-K tcgen05 kernel
-            dw = torch.cat([dwcat[:H, :f_in], dwcat[H:, :f_in]], dim=1)
+            dw_i = gemm_bf16_nn_grad_w(dPQ[:n, :H], x_aug[:n])  # [H, Fp] fp32, split-K tcgen05 kernel
+            dw_j = gemm_bf16_nn_grad_w(dQ, x_aug)
+            dw = torch.cat([dw_i[:, :f_in], dw_j[:, :f_in]], dim=1)
         if ctx.needs_input_grad[2]:
             db = colsum(dPQ[:n, :H])
         return dx, dw, db, None, None, None

@@ -22,6 +22,7 @@ import torch.nn.functional as F
 
 from dgraph_b200.ops.gather_linear import gather_linear
 from dgraph_b200.ops.gemm import linear
+from dgraph_b200.ops.norm import layer_norm_residual, silu
 from dgraph_b200.ops.segment import segment_sum
 from dgraph_b200.parallel.halo import HaloExchange
 from dgraph_b200.parallel.kernel_plan import GraphKernelPlan
@@ -99,8 +100,9 @@ class MeshGraphMLP(nn.Module):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         return self.forward_sources([x], [None])
 
-    def forward_sources(self, srcs, idxs) -> torch.Tensor:
-        """MLP applied to ``cat([srcs[k][idxs[k]] for k], 1)`` -- the gather and the concat happen inside the first GEMM."""
+    def forward_sources(self, srcs, idxs, residual=None, scatter_plans=None) -> torch.Tensor:
+        """MLP applied to ``cat([srcs[k][idxs[k]] for k], 1)`` -- the gather and the concat happen inside the first GEMM;
+        ``residual`` is added inside the fused LayerNorm kernel."""
         mods = list(self._model)
         first = mods[0]
         fused_silu = isinstance(mods[1], nn.SiLU)
@@ -113,17 +115,24 @@ class MeshGraphMLP(nn.Module):
                 parts.append(F.pad(w[:, o:o + k], (0, s.shape[1] - k)))
                 o += k
             w = torch.cat(parts, dim=1)
-        h = gather_linear(srcs, idxs, w, first.bias, act="silu" if fused_silu else None)
+        h = gather_linear(srcs, idxs, w, first.bias, act="silu" if fused_silu else None, scatter_plans=scatter_plans)
         i = 2 if fused_silu else 1
+        used_res = False
         while i < len(mods):
             m = mods[i]
             if isinstance(m, nn.Linear):
                 h = linear(h, m.weight.to(h.dtype), m.bias.to(h.dtype))
             elif isinstance(m, nn.LayerNorm):
-                h = F.layer_norm(h.float(), m.normalized_shape, m.weight.float(), m.bias.float(), m.eps).to(h.dtype)
+                last = i == len(mods) - 1
+                h = layer_norm_residual(h, m.weight, m.bias, m.eps, residual if last else None)
+                used_res = used_res or last
+            elif isinstance(m, nn.SiLU):
+                h = silu(h)
             else:
                 h = m(h)
             i += 1
+        if residual is not None and not used_res:
+            h = h + residual
         return h
 
 
@@ -156,7 +165,7 @@ class MeshNodeBlock(nn.Module):
         else:
             agg = torch.zeros((n, edge_features.shape[1]), dtype=edge_features.dtype, device=edge_features.device)
             agg = agg.index_add(0, src_indices.long(), edge_features)
-        return self.mesh_mlp.forward_sources([node_features, agg], [None, None]) + node_features
+        return self.mesh_mlp.forward_sources([node_features, agg], [None, None], residual=node_features)
 
 
 class MeshEdgeBlock(nn.Module):
@@ -169,7 +178,7 @@ class MeshEdgeBlock(nn.Module):
                                      num_hidden_layers)
 
     def forward(self, src_node_features, dst_node_features, edge_features, src_indices, dst_indices, src_rank_mapping=None,
-                dst_rank_mapping=None):
+                dst_rank_mapping=None, *, scatter_plans=None):
         """``src_node_features`` / ``dst_node_features`` are the matrices the indices refer to (already ``[local | halo]``
         for the side that crosses ranks).  With rank mappings the reference's gather API is used instead."""
         if src_rank_mapping is not None or dst_rank_mapping is not None:
@@ -177,7 +186,8 @@ class MeshEdgeBlock(nn.Module):
             d = self.comm.gather(dst_node_features, dst_indices, dst_rank_mapping)
             return self.mesh_mlp.forward_sources([s, d, edge_features], [None, None, None]) + edge_features
         return self.mesh_mlp.forward_sources([src_node_features, dst_node_features, edge_features],
-                                             [src_indices, dst_indices, None]) + edge_features
+                                             [src_indices, dst_indices, None], residual=edge_features,
+                                             scatter_plans=scatter_plans)
 
 
 class GraphCastEmbedder(nn.Module):
@@ -207,9 +217,10 @@ class GraphCastEncoder(nn.Module):
         self.grid_node_mlp = MeshGraphMLP(input_dim=h, output_dim=h)
 
     def forward(self, grid_node_features, mesh_node_features, grid2mesh_edge_features, grid2mesh_edge_indices_src,
-                grid2mesh_edge_indices_dst, *, grid_aug=None, agg_plan=None):
+                grid2mesh_edge_indices_dst, *, grid_aug=None, agg_plan=None, edge_scatter_plans=None):
         e = self.edge_mlp(grid_aug if grid_aug is not None else grid_node_features, mesh_node_features,
-                          grid2mesh_edge_features, grid2mesh_edge_indices_src, grid2mesh_edge_indices_dst)
+                          grid2mesh_edge_features, grid2mesh_edge_indices_src, grid2mesh_edge_indices_dst,
+                          scatter_plans=edge_scatter_plans)
         n = self.mesh_node_mlp(mesh_node_features, e, grid2mesh_edge_indices_dst, agg_plan=agg_plan)
         mesh_node_features = mesh_node_features + n
         grid_node_features = grid_node_features + self.grid_node_mlp(grid_node_features)
@@ -224,11 +235,12 @@ class GraphCastProcessor(nn.Module):
         self.node_processors = nn.ModuleList([MeshNodeBlock(h, h, h, comm, h) for _ in range(cfg.model.processor_layers)])
 
     def forward(self, embedded_mesh_features, embedded_mesh2mesh_edge_features, mesh2mesh_edge_indices_src,
-                mesh2mesh_edge_indices_dst, *, exchange=None, agg_plan=None):
+                mesh2mesh_edge_indices_dst, *, exchange=None, agg_plan=None, edge_scatter_plans=None):
         e, n = embedded_mesh2mesh_edge_features, embedded_mesh_features
         for edge_layer, node_layer in zip(self.edge_processors, self.node_processors):
             n_aug = exchange(n) if exchange is not None else n  # dst endpoints may live on other ranks
-            e = edge_layer(n, n_aug, e, mesh2mesh_edge_indices_src, mesh2mesh_edge_indices_dst)
+            e = edge_layer(n, n_aug, e, mesh2mesh_edge_indices_src, mesh2mesh_edge_indices_dst,
+                           scatter_plans=edge_scatter_plans)
             n = node_layer(n, e, mesh2mesh_edge_indices_src, agg_plan=agg_plan)
         return n, e
 
@@ -243,9 +255,10 @@ class GraphCastDecoder(nn.Module):
                                       num_hidden_layers=1)
 
     def forward(self, mesh2grid_edge_features, grid_node_features, mesh_node_features, mesh2grid_edge_indices_src,
-                mesh2grid_edge_indices_dst, *, mesh_aug=None, agg_plan=None):
+                mesh2grid_edge_indices_dst, *, mesh_aug=None, agg_plan=None, edge_scatter_plans=None):
         e = self.edge_mlp(mesh_aug if mesh_aug is not None else mesh_node_features, grid_node_features,
-                          mesh2grid_edge_features, mesh2grid_edge_indices_src, mesh2grid_edge_indices_dst)
+                          mesh2grid_edge_features, mesh2grid_edge_indices_src, mesh2grid_edge_indices_dst,
+                          scatter_plans=edge_scatter_plans)
         n = self.node_mlp(grid_node_features, e, mesh2grid_edge_indices_dst, agg_plan=agg_plan)
         return grid_node_features + n
 
@@ -272,15 +285,23 @@ class DGraphCast(nn.Module):
                                                        sg.grid2mesh_graph_edge_features.to(dt),
                                                        sg.mesh2grid_graph_edge_features.to(dt))
         n_mesh, n_grid = mesh.shape[0], grid.shape[0]
-        plan = lambda name, idx, n: _edge_plan(sg, name, idx, n) if hasattr(sg, "_plans") else None  # noqa: E731
+        use_plans = hasattr(sg, "_plans") and x_in.is_cuda and x_in.dtype == torch.bfloat16
+        plan = lambda name, idx, n: _edge_plan(sg, name, idx, n) if use_plans else None  # noqa: E731
+        grid_aug = halo(grid, pats.grid2mesh) if pats is not None else grid
         grid, mesh = self.encoder(grid, mesh, e_g2m, sg.grid2mesh_graph_src_indices, sg.grid2mesh_graph_dst_indices,
-                                  grid_aug=halo(grid, pats.grid2mesh) if pats is not None else None,
-                                  agg_plan=plan("g2m", sg.grid2mesh_graph_dst_indices, n_mesh))
+                                  grid_aug=grid_aug, agg_plan=plan("g2m", sg.grid2mesh_graph_dst_indices, n_mesh),
+                                  edge_scatter_plans=[plan("g2m:src", sg.grid2mesh_graph_src_indices, grid_aug.shape[0]),
+                                                      plan("g2m", sg.grid2mesh_graph_dst_indices, n_mesh), None] if use_plans else None)
+        n_mesh_aug = n_mesh + (pats.mesh.num_halo_vertices if pats is not None else 0)
         mesh, _ = self.processor(mesh, e_mm, sg.mesh_graph_src_indices, sg.mesh_graph_dst_indices,
                                  exchange=(lambda n: halo(n, pats.mesh)) if pats is not None else None,
-                                 agg_plan=plan("mesh", sg.mesh_graph_src_indices, n_mesh))
+                                 agg_plan=plan("mesh", sg.mesh_graph_src_indices, n_mesh),
+                                 edge_scatter_plans=[plan("mesh", sg.mesh_graph_src_indices, n_mesh),
+                                                     plan("mesh:dst", sg.mesh_graph_dst_indices, n_mesh_aug), None] if use_plans else None)
+        mesh_aug = halo(mesh, pats.mesh2grid) if pats is not None else mesh
         x = self.decoder(e_m2g, grid, mesh, sg.mesh2grid_graph_src_indices, sg.mesh2grid_graph_dst_indices,
-                         mesh_aug=halo(mesh, pats.mesh2grid) if pats is not None else None,
-                         agg_plan=plan("m2g", sg.mesh2grid_graph_dst_indices, n_grid))
+                         mesh_aug=mesh_aug, agg_plan=plan("m2g", sg.mesh2grid_graph_dst_indices, n_grid),
+                         edge_scatter_plans=[plan("m2g:src", sg.mesh2grid_graph_src_indices, mesh_aug.shape[0]),
+                                             plan("m2g", sg.mesh2grid_graph_dst_indices, n_grid), None] if use_plans else None)
         out = self.final_prediction(x)
         return x_in + out[:, : x_in.shape[1]].to(dt)

@@ -31,7 +31,7 @@ def gather_linear_ref(srcs: Sequence[torch.Tensor], idxs: Sequence[Optional[torc
 
 class _GatherLinear(Function):
     @staticmethod
-    def forward(ctx, weight, bias, act, n_src, *args):
+    def forward(ctx, weight, bias, act, n_src, scatter_plans, *args):
         from dgraph_b200.ops.gemm_native import gather_gemm_bf16, pack_segment_weight
 
         srcs, idxs = list(args[:n_src]), list(args[n_src:])
@@ -41,7 +41,7 @@ class _GatherLinear(Function):
             M = int(i.shape[0]) if i is not None else int(s.shape[0])
         wp = pack_segment_weight(weight, ks)
         pre = gather_gemm_bf16(srcs, idxs, wp, bias, M, ks, act=None)
-        ctx.act, ctx.n_src, ctx.ks = act, n_src, ks
+        ctx.act, ctx.n_src, ctx.ks, ctx.scatter_plans = act, n_src, ks, scatter_plans
         ctx.save_for_backward(weight, pre if act else None, *srcs, *[i for i in idxs if i is not None])
         ctx.idx_none = [i is None for i in idxs]
         if act == "silu":
@@ -61,8 +61,9 @@ class _GatherLinear(Function):
         idxs = [None if none else next(it) for none in ctx.idx_none]
         g = g.contiguous()
         if ctx.act == "silu":
-            sg = torch.sigmoid(pre.float())
-            g = (g.float() * (sg * (1 + pre.float() * (1 - sg)))).to(g.dtype)
+            from dgraph_b200.ops.norm import silu_backward
+
+            g = silu_backward(g, pre)
         elif ctx.act == "relu":
             g = g * (pre > 0).to(g.dtype)
         wb = weight.to(torch.bfloat16)
@@ -82,14 +83,23 @@ class _GatherLinear(Function):
             part = dcat[:, o:o + k]
             o += k
             if i is None:
-                grads.append(part.contiguous())
+                grads.append(part)
             else:
-                grads.append(torch.zeros_like(s).index_add_(0, i.long(), part))
-        return (dw, db, None, None, *grads, *([None] * len(idxs)))
+                sp = ctx.scatter_plans[len(grads)] if ctx.scatter_plans is not None else None
+                if sp is not None:  # atomic-free: CSR walk over (source row <- edge id) incidence
+                    from dgraph_b200.ops.segment import _native_seg_sum
+
+                    pc = part if (part.stride(1) == 1 and part.stride(0) % 8 == 0 and part.data_ptr() % 16 == 0) else part.contiguous()
+                    grads.append(_native_seg_sum(sp.rowptr, sp.col, sp.num_local, pc, None, False))
+                else:
+                    grads.append(torch.zeros_like(s).index_add_(0, i.long(), part))
+        return (dw, db, None, None, None, *grads, *([None] * len(idxs)))
 
 
 def gather_linear(srcs: List[torch.Tensor], idxs: List[Optional[torch.Tensor]], weight: torch.Tensor,
-                  bias: Optional[torch.Tensor], act: Optional[str] = None) -> torch.Tensor:
+                  bias: Optional[torch.Tensor], act: Optional[str] = None, scatter_plans=None) -> torch.Tensor:
+    """``scatter_plans[k]``: optional :class:`GraphKernelPlan` of the (row of ``srcs[k]`` <- edge id) incidence; when given, the
+    backward scatters that source's gradient with an atomic-free segment sum instead of ``index_add_``."""
     ok = (all(s.is_cuda and s.dtype == torch.bfloat16 and s.shape[1] % 8 == 0 for s in srcs) and 1 <= len(srcs) <= 3
           and N.available())
     if not ok:
@@ -97,4 +107,4 @@ def gather_linear(srcs: List[torch.Tensor], idxs: List[Optional[torch.Tensor]], 
             N.require_for(srcs[0])
         return gather_linear_ref(srcs, idxs, weight, bias, act)
     idx32 = [None if i is None else (i if i.dtype == torch.int32 else i.to(torch.int32)) for i in idxs]
-    return _GatherLinear.apply(weight, bias, act, len(srcs), *srcs, *idx32)
+    return _GatherLinear.apply(weight, bias, act, len(srcs), scatter_plans, *srcs, *idx32)

@@ -155,3 +155,34 @@ def test_rank_local_ops_match_python_loops(dtype):  # model: reference tests/tes
         if rm[i] == 0:
             want4[di[i]] += neg[0, i].float()
     assert torch.allclose(out4[0].float(), want4, rtol=2e-2, atol=2e-2) and (out4.float() <= 0).all()
+
+
+@pytest.mark.parametrize("C", [8, 128, 256, 512])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_fused_layernorm_residual_matches_torch(C, with_res):
+    from dgraph_b200.ops.norm import layer_norm_residual, silu
+
+    torch.manual_seed(C)
+    M = 3001
+    z = (torch.randn(M, C, device="cuda") * 2 + 0.5).bfloat16().requires_grad_(True)
+    res = torch.randn(M, C, device="cuda").bfloat16().requires_grad_(True) if with_res else None
+    gamma = (torch.rand(C, device="cuda") + 0.5).requires_grad_(True)
+    beta = torch.randn(C, device="cuda").requires_grad_(True)
+    y = layer_norm_residual(z, gamma, beta, 1e-5, res)
+    zf, gf, bf = z.detach().float().requires_grad_(True), gamma.detach().clone().requires_grad_(True), beta.detach().clone().requires_grad_(True)
+    rf = res.detach().float().requires_grad_(True) if with_res else None
+    yr = torch.nn.functional.layer_norm(zf, (C,), gf, bf, 1e-5) + (rf if with_res else 0)
+    assert torch.allclose(y.float(), yr, rtol=2e-2, atol=3e-2)
+    go = torch.randn_like(yr).bfloat16()
+    y.backward(go)
+    yr.backward(go.float())
+    assert torch.allclose(z.grad.float(), zf.grad, rtol=3e-2, atol=3e-2)
+    assert torch.allclose(gamma.grad, gf.grad, rtol=2e-2, atol=0.5)
+    assert torch.allclose(beta.grad, bf.grad, rtol=2e-2, atol=0.5)
+    if with_res:
+        assert torch.equal(res.grad, go)
+    p = torch.randn(M, C, device="cuda").bfloat16().requires_grad_(True)
+    pf = p.detach().float().requires_grad_(True)
+    silu(p).backward(go)
+    torch.nn.functional.silu(pf).backward(go.float())
+    assert torch.allclose(p.grad.float(), pf.grad, rtol=2e-2, atol=2e-2)

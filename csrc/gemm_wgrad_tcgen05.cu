@@ -22,10 +22,13 @@ struct WgSmem {
   static constexpr int TOTAL = STAGES * STAGE + 256 + 1024;
 };
 
-template <int BN2>
-__global__ void __launch_bounds__(192, 1)
+// GX: the rows of X are gathered (X[x_idx[m], :]) by four extra producer warps that write the MN-major swizzled panels
+// themselves -- the weight gradient of a gather-GEMM without materialising the gathered operand.
+template <int BN2, bool GX>
+__global__ void __launch_bounds__(GX ? 320 : 192, 1)
 gemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__ CUtensorMap tmap_x, float* __restrict__ dW,
-                  int64_t ldw, int N1, int N2, int64_t M, int kb_per_split) {
+                  int64_t ldw, int N1, int N2, int64_t M, int kb_per_split, const __nv_bfloat16* __restrict__ Xg, int64_t ldx,
+                  const int* __restrict__ x_idx) {
   using L = WgSmem<BN2>;
   constexpr int STAGES = L::STAGES;
   extern __shared__ uint8_t smem_raw[];
@@ -48,7 +51,7 @@ gemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      tc::mbar_init(&full_bar[s], 1);
+      tc::mbar_init(&full_bar[s], GX ? 129 : 1);
       tc::mbar_init(&empty_bar[s], 1);
     }
     tc::mbar_init(acc_full, 1);
@@ -72,12 +75,15 @@ gemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
           tc::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * L::STAGE;
           uint8_t* sb = sa + L::A_BYTES;
-          tc::mbar_expect_tx(&full_bar[stage], L::STAGE);
+          tc::mbar_expect_tx(&full_bar[stage], GX ? L::A_BYTES : L::STAGE);
           const int krow = (int)((kb0 + kb) * WG_BK);
 #pragma unroll
           for (int pnl = 0; pnl < 2; ++pnl) tc::tma_load_2d(sa + pnl * (WG_BK * 128), &tmap_g, &full_bar[stage], m0 + pnl * 64, krow);
+          if (!GX) {
 #pragma unroll
-          for (int pnl = 0; pnl < BN2 / 64; ++pnl) tc::tma_load_2d(sb + pnl * (WG_BK * 128), &tmap_x, &full_bar[stage], pnl * 64, krow);
+            for (int pnl = 0; pnl < BN2 / 64; ++pnl)
+              tc::tma_load_2d(sb + pnl * (WG_BK * 128), &tmap_x, &full_bar[stage], pnl * 64, krow);
+          }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -103,7 +109,43 @@ gemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
         }
         tc::umma_commit(acc_full);
       }
-    } else {
+    } else if (GX && warp >= 6) {
+      // gather producers: 128 threads fill the X panels of every stage (row kk of the stage = X[x_idx[krow + kk], :])
+      const int gt = threadIdx.x - 6 * 32;
+      const int chunk = gt & 7;  // 16-byte chunk inside a 128-byte panel row
+      const int rr = gt >> 3;    // rows rr + 16 * i
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int64_t krow = (kb0 + kb) * WG_BK;
+        int64_t roff[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int64_t m = krow + rr + 16 * i;
+          roff[i] = (m < M) ? (int64_t)__ldg(x_idx + m) * ldx : -1;
+        }
+        tc::mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sb = smem + stage * L::STAGE + L::A_BYTES;
+#pragma unroll
+        for (int pnl = 0; pnl < BN2 / 64; ++pnl) {
+          const int col = pnl * 64 + chunk * 8;
+          uint4 v[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            v[i] = make_uint4(0, 0, 0, 0);
+            if (roff[i] >= 0 && col < N2) v[i] = ldg_nc_v4(Xg + roff[i] + col);
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int kk = rr + 16 * i;
+            *reinterpret_cast<uint4*>(sb + pnl * (WG_BK * 128) + kk * 128 + ((chunk ^ (kk & 7)) << 4)) = v[i];
+          }
+        }
+        tc::fence_proxy_async_smem();
+        tc::mbar_arrive(&full_bar[stage]);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    } else if (warp >= 2 && warp < 6) {
       // epilogue: 4 warps, thread = one row of the 128 x BN2 accumulator
       const int q = warp & 3;
       tc::mbar_wait(acc_full, 0);
@@ -138,11 +180,11 @@ gemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
   if (warp == 2) tc::tmem_dealloc(tmem_base, BN2 < 32 ? 32 : BN2);
 }
 
-template <int BN2>
+template <int BN2, bool GX>
 static int launch_wgrad(const CUtensorMap& tg, const CUtensorMap& tx, float* dW, int64_t ldw, int N1, int N2, int64_t M,
-                        cudaStream_t s) {
+                        const void* X, int64_t ldx, const int* x_idx, cudaStream_t s) {
   using L = WgSmem<BN2>;
-  auto kern = gemm_wgrad_kernel<BN2>;
+  auto kern = gemm_wgrad_kernel<BN2, GX>;
   static bool configured = false;
   if (!configured) {
     DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
@@ -158,7 +200,8 @@ static int launch_wgrad(const CUtensorMap& tg, const CUtensorMap& tx, float* dW,
   if (splits > total_kb) splits = (int)total_kb;
   const int kb_per_split = (int)((total_kb + splits - 1) / splits);
   splits = (int)((total_kb + kb_per_split - 1) / kb_per_split);
-  kern<<<dim3(m_tiles, splits), 192, L::TOTAL, s>>>(tg, tx, dW, ldw, N1, N2, M, kb_per_split);
+  kern<<<dim3(m_tiles, splits), GX ? 320 : 192, L::TOTAL, s>>>(tg, tx, dW, ldw, N1, N2, M, kb_per_split,
+                                                               (const __nv_bfloat16*)X, ldx, x_idx);
   DGB_CHECK_LAUNCH();
   return 0;
 }
@@ -167,10 +210,11 @@ static int launch_wgrad(const CUtensorMap& tg, const CUtensorMap& tx, float* dW,
 
 using namespace dgb;
 
-// dW[N1, N2] (fp32, row stride ldw) += G[M, N1]^T @ X[M, N2]; G, X bf16 row-major (16-byte aligned bases, strides multiples
-// of 8 elements).  N2 <= 256.  dW must be initialised by the caller (zero for a plain gradient).
+// dW[N1, N2] (fp32, row stride ldw) += G[M, N1]^T @ X'[M, N2] with X' = X (x_idx null) or X'[m] = X[x_idx[m]] (gathered rows).
+// G, X bf16 row-major (16-byte aligned bases, strides multiples of 8 elements).  N2 <= 256.  dW must be initialised by the
+// caller (zero for a plain gradient).  `x_rows` = number of rows of X (only needed for the TMA map when x_idx is null).
 DGB_API int dgb_gemm_wgrad_bf16(const void* G, int64_t ldg, const void* X, int64_t ldx, float* dW, int64_t ldw, int64_t M,
-                                int N1, int N2, void* stream) {
+                                int N1, int N2, const int* x_idx, void* stream) {
   if (M <= 0 || N1 <= 0 || N2 <= 0) return 0;
   if (N2 > 256 || (ldg % 8) || (ldx % 8) || (reinterpret_cast<uintptr_t>(G) & 15) || (reinterpret_cast<uintptr_t>(X) & 15) ||
       M >= (int64_t(1) << 31))
@@ -178,10 +222,15 @@ DGB_API int dgb_gemm_wgrad_bf16(const void* G, int64_t ldg, const void* X, int64
   CUtensorMap tg, tx;
   int rc = make_tmap_2d(&tg, G, (uint64_t)M, (uint64_t)N1, (uint64_t)ldg, WG_BK, 64, 2, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (x_idx) {
+    if (N2 <= 64) return launch_wgrad<64, true>(tg, tg, dW, ldw, N1, N2, M, X, ldx, x_idx, s);
+    if (N2 <= 128) return launch_wgrad<128, true>(tg, tg, dW, ldw, N1, N2, M, X, ldx, x_idx, s);
+    return launch_wgrad<256, true>(tg, tg, dW, ldw, N1, N2, M, X, ldx, x_idx, s);
+  }
   rc = make_tmap_2d(&tx, X, (uint64_t)M, (uint64_t)N2, (uint64_t)ldx, WG_BK, 64, 2, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
-  cudaStream_t s = (cudaStream_t)stream;
-  if (N2 <= 64) return launch_wgrad<64>(tg, tx, dW, ldw, N1, N2, M, s);
-  if (N2 <= 128) return launch_wgrad<128>(tg, tx, dW, ldw, N1, N2, M, s);
-  return launch_wgrad<256>(tg, tx, dW, ldw, N1, N2, M, s);
+  if (N2 <= 64) return launch_wgrad<64, false>(tg, tx, dW, ldw, N1, N2, M, X, ldx, nullptr, s);
+  if (N2 <= 128) return launch_wgrad<128, false>(tg, tx, dW, ldw, N1, N2, M, X, ldx, nullptr, s);
+  return launch_wgrad<256, false>(tg, tx, dW, ldw, N1, N2, M, X, ldx, nullptr, s);
 }

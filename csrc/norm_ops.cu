@@ -22,7 +22,8 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const __nv_bfloat16* __rest
                                                      const __nv_bfloat16* __restrict__ res, int64_t ld_r,
                                                      const float* __restrict__ gamma, const float* __restrict__ beta,
                                                      __nv_bfloat16* __restrict__ y, int64_t ld_y, float* __restrict__ mean,
-                                                     float* __restrict__ rstd, int64_t M, int C, float eps) {
+                                                     float* __restrict__ rstd, int64_t M, int C, int Cv, float eps) {
+  // C = padded width (multiple of 8); Cv <= C = columns that take part in the normalisation (the rest is written as 0)
   const int lane = threadIdx.x & 31, g = lane & (G - 1), sub = lane / G;
   const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (sub * G));
   const int nchunk = C >> 3;
@@ -38,22 +39,26 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const __nv_bfloat16* __rest
     if (ch < nchunk) {
       unpack8(ldg_nc_v4(z + r * ld_z + ch * 8), x[c]);
 #pragma unroll
-      for (int t = 0; t < 8; ++t) s += x[c][t];
+      for (int t = 0; t < 8; ++t) {
+        if (ch * 8 + t >= Cv) x[c][t] = 0.f;
+        s += x[c][t];
+      }
     }
   }
-  const float mu = gsum<G>(s, gmask) / (float)C;
+  const float mu = gsum<G>(s, gmask) / (float)Cv;
   float v = 0.f;
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
-    if (g + c * G < nchunk) {
+    const int ch = g + c * G;
+    if (ch < nchunk) {
 #pragma unroll
       for (int t = 0; t < 8; ++t) {
-        const float d = x[c][t] - mu;
+        const float d = (ch * 8 + t < Cv) ? x[c][t] - mu : 0.f;
         v = fmaf(d, d, v);
       }
     }
   }
-  const float rs = rsqrtf(gsum<G>(v, gmask) / (float)C + eps);
+  const float rs = rsqrtf(gsum<G>(v, gmask) / (float)Cv + eps);
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
     const int ch = g + c * G;
@@ -62,8 +67,8 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const __nv_bfloat16* __rest
       if (res) unpack8(ldg_nc_v4(res + r * ld_r + ch * 8), rr);
 #pragma unroll
       for (int t = 0; t < 8; ++t) {
-        o[t] = (x[c][t] - mu) * rs * __ldg(gamma + ch * 8 + t) + __ldg(beta + ch * 8 + t);
-        if (res) o[t] += rr[t];
+        const int col = ch * 8 + t;
+        o[t] = (col < Cv) ? (x[c][t] - mu) * rs * __ldg(gamma + col) + __ldg(beta + col) + (res ? rr[t] : 0.f) : 0.f;
       }
       stg_v4(y + r * ld_y + ch * 8, pack8(o));
     }
@@ -80,7 +85,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const __nv_bfloat16* __rest
                                                      const __nv_bfloat16* __restrict__ z, int64_t ld_z,
                                                      const float* __restrict__ gamma, const float* __restrict__ mean,
                                                      const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dz,
-                                                     int64_t ld_dz, float* __restrict__ partial, int64_t M, int C) {
+                                                     int64_t ld_dz, float* __restrict__ partial, int64_t M, int C, int Cv) {
   extern __shared__ float sm[];  // [groups_per_block][2C]
   const int lane = threadIdx.x & 31, g = lane & (G - 1), sub = lane / G;
   const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (sub * G));
@@ -95,7 +100,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const __nv_bfloat16* __rest
     for (int t = 0; t < 8; ++t) {
       dgam[c][t] = 0.f;
       dbet[c][t] = 0.f;
-      gm[c][t] = (ch < nchunk) ? __ldg(gamma + ch * 8 + t) : 0.f;
+      gm[c][t] = (ch < nchunk && ch * 8 + t < Cv) ? __ldg(gamma + ch * 8 + t) : 0.f;
     }
   }
   for (int64_t r = (int64_t)blockIdx.x * groups_per_block + grp_in_block; r < M; r += (int64_t)gridDim.x * groups_per_block) {
@@ -111,7 +116,9 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const __nv_bfloat16* __rest
         unpack8(ldg_nc_v4(z + r * ld_z + ch * 8), b);
 #pragma unroll
         for (int t = 0; t < 8; ++t) {
-          xh[c][t] = (b[t] - mu) * rs;
+          const bool valid = ch * 8 + t < Cv;
+          if (!valid) a[t] = 0.f;
+          xh[c][t] = valid ? (b[t] - mu) * rs : 0.f;
           dgam[c][t] = fmaf(a[t], xh[c][t], dgam[c][t]);
           dbet[c][t] += a[t];
           gg[c][t] = a[t] * gm[c][t];
@@ -120,15 +127,15 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const __nv_bfloat16* __rest
         }
       }
     }
-    const float c1 = gsum<G>(s1, gmask) / (float)C;
-    const float c2 = gsum<G>(s2, gmask) / (float)C;
+    const float c1 = gsum<G>(s1, gmask) / (float)Cv;
+    const float c2 = gsum<G>(s2, gmask) / (float)Cv;
 #pragma unroll
     for (int c = 0; c < NC; ++c) {
       const int ch = g + c * G;
       if (ch < nchunk) {
         float o[8];
 #pragma unroll
-        for (int t = 0; t < 8; ++t) o[t] = rs * (gg[c][t] - c1 - xh[c][t] * c2);
+        for (int t = 0; t < 8; ++t) o[t] = (ch * 8 + t < Cv) ? rs * (gg[c][t] - c1 - xh[c][t] * c2) : 0.f;
         stg_v4(dz + r * ld_dz + ch * 8, pack8(o));
       }
     }
@@ -199,18 +206,21 @@ using namespace dgb;
   } while (0)
 
 // y = LayerNorm(z; gamma, beta, eps) (+ res).  z, res, y bf16 [M, C] (C multiple of 8, <= 1024); gamma, beta fp32 [C];
-// mean, rstd fp32 [M] (saved for backward).  res may be null.
+// mean, rstd fp32 [M] (saved for backward).  res may be null.  Only the first C_valid columns are normalised (statistics
+// over C_valid columns); columns [C_valid, C) are zero padding and are written as 0 (e.g. GraphCast's 73-wide output).
 DGB_API int dgb_layernorm_fwd(const void* z, int64_t ld_z, const void* res, int64_t ld_r, const float* gamma, const float* beta,
-                              void* y, int64_t ld_y, float* mean, float* rstd, int64_t M, int C, float eps, void* stream) {
+                              void* y, int64_t ld_y, float* mean, float* rstd, int64_t M, int C, int C_valid, float eps,
+                              void* stream) {
   if (M == 0) return 0;
-  if (C % 8 || C > 1024 || ld_z % 8 || ld_y % 8 || (res && ld_r % 8)) return (int)cudaErrorInvalidValue;
+  if (C % 8 || C > 1024 || C_valid < 1 || C_valid > C || ld_z % 8 || ld_y % 8 || (res && ld_r % 8))
+    return (int)cudaErrorInvalidValue;
   cudaStream_t s = (cudaStream_t)stream;
 #define DGB_LNF(G, NC)                                                                                              \
   do {                                                                                                              \
     const int64_t rows_per_block = 8 * (32 / (G));                                                                  \
     ln_fwd_kernel<G, NC><<<(unsigned)((M + rows_per_block - 1) / rows_per_block), 256, 0, s>>>(                      \
         (const __nv_bfloat16*)z, ld_z, (const __nv_bfloat16*)res, ld_r, gamma, beta, (__nv_bfloat16*)y, ld_y, mean, \
-        rstd, M, C, eps);                                                                                           \
+        rstd, M, C, C_valid, eps);                                                                                  \
   } while (0)
   DGB_LN_DISPATCH(DGB_LNF);
 #undef DGB_LNF
@@ -224,7 +234,8 @@ DGB_API int64_t dgb_layernorm_bwd_scratch_bytes(int64_t M, int C) { return (int6
 // `scratch` holds dgb_layernorm_bwd_scratch_bytes(M, C) bytes.
 DGB_API int dgb_layernorm_bwd(const void* gy, int64_t ld_g, const void* z, int64_t ld_z, const float* gamma, const float* mean,
                               const float* rstd, void* dz, int64_t ld_dz, float* scratch, float* dgamma_dbeta, int64_t M,
-                              int C, void* stream) {
+                              int C, int C_valid, void* stream) {
+  if (C_valid < 1 || C_valid > C) return (int)cudaErrorInvalidValue;
   if (C % 8 || C > 512 || ld_g % 8 || ld_z % 8 || ld_dz % 8) return (int)cudaErrorInvalidValue;  // smem: 8 groups x 2C floats
   cudaStream_t s = (cudaStream_t)stream;
   if (M == 0) {
@@ -236,7 +247,7 @@ DGB_API int dgb_layernorm_bwd(const void* gy, int64_t ld_g, const void* z, int64
   do {                                                                                                               \
     const size_t smem = (size_t)8 * (32 / (G)) * 2 * C * sizeof(float);                                              \
     ln_bwd_kernel<G, NC><<<nb, 256, smem, s>>>((const __nv_bfloat16*)gy, ld_g, (const __nv_bfloat16*)z, ld_z, gamma,  \
-                                              mean, rstd, (__nv_bfloat16*)dz, ld_dz, scratch, M, C);                 \
+                                              mean, rstd, (__nv_bfloat16*)dz, ld_dz, scratch, M, C, C_valid);        \
   } while (0)
   DGB_LN_DISPATCH(DGB_LNB);
 #undef DGB_LNB

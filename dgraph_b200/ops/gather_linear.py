@@ -68,16 +68,24 @@ class _GatherLinear(Function):
             g = g * (pre > 0).to(g.dtype)
         wb = weight.to(torch.bfloat16)
         dcat = gemm_bf16_tn(g, wb.t().contiguous())  # [M, sum(ks)]
-        cat = torch.cat([s if i is None else s.index_select(0, i.long()) for s, i in zip(srcs, idxs)], dim=1)
         dw = None
         if ctx.needs_input_grad[0]:
+            # per-source split-K weight gradients; gathered sources are gathered inside the kernel (no [M, K] temporaries)
             from dgraph_b200.ops.gemm_native import gemm_bf16_nn_grad_w
 
-            if cat.shape[1] <= 256:
-                dw = gemm_bf16_nn_grad_w(g, cat)
-            else:  # wide concatenations: one split-K GEMM per 256-column slab
-                dw = torch.cat([gemm_bf16_nn_grad_w(g, cat[:, o:o + 256]) for o in range(0, cat.shape[1], 256)], dim=1)
-        db = g.float().sum(0) if ctx.needs_input_grad[1] else None
+            parts = []
+            for s_, i_ in zip(srcs, idxs):
+                k = s_.shape[1]
+                if k <= 256:
+                    parts.append(gemm_bf16_nn_grad_w(g, s_, i_))
+                else:
+                    parts.append(torch.cat([gemm_bf16_nn_grad_w(g, s_[:, o:o + 256], i_) for o in range(0, k, 256)], dim=1))
+            dw = torch.cat(parts, dim=1) if len(parts) > 1 else parts[0]
+        db = None
+        if ctx.needs_input_grad[1]:
+            from dgraph_b200.ops.reduce import colsum
+
+            db = colsum(g)
         grads, o = [], 0
         for s, i, k in zip(srcs, idxs, ctx.ks):
             part = dcat[:, o:o + k]

@@ -85,19 +85,23 @@ def gather_gemm_bf16(srcs: List[torch.Tensor], idxs: List[Optional[torch.Tensor]
     return out
 
 
-def gemm_bf16_nn_grad_w(g: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
-    """Weight gradient ``g^T @ x`` -> fp32 ``[N1, N2]`` (reduction over the huge row dimension) with the split-K tcgen05
+def gemm_bf16_nn_grad_w(g: torch.Tensor, x: torch.Tensor, x_idx: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Weight gradient ``g^T @ x`` (``x`` optionally row-gathered by ``x_idx`` inside the kernel) -> fp32 ``[N1, N2]``
+    (reduction over the huge row dimension) with the split-K tcgen05
     kernel (``csrc/gemm_wgrad_tcgen05.cu``: MN-major operands via TMA, TMEM accumulators, vector reductions into ``dW``).
     Falls back to a library GEMM only for ``N2 > 256``."""
     N1, N2 = g.shape[1], x.shape[1]
-    ok = (g.is_cuda and g.dtype == torch.bfloat16 and x.dtype == torch.bfloat16 and N2 <= 256 and g.shape[0] == x.shape[0]
+    rows_ok = g.shape[0] == (x.shape[0] if x_idx is None else x_idx.shape[0])
+    ok = (g.is_cuda and g.dtype == torch.bfloat16 and x.dtype == torch.bfloat16 and N2 <= 256 and rows_ok
           and hasattr(N.lib(), "dgb_gemm_wgrad_bf16"))
     if not ok:
-        return torch.matmul(g.t(), x).float()
+        return torch.matmul(g.t(), x if x_idx is None else x.index_select(0, x_idx.long())).float()
     g, x = _as_bf16_rowmajor(g), _as_bf16_rowmajor(x)
+    idx32 = None if x_idx is None else (x_idx if x_idx.dtype == torch.int32 else x_idx.to(torch.int32)).contiguous()
     out = torch.zeros((N1, (N2 + 3) // 4 * 4), dtype=torch.float32, device=g.device)
     N.check(N.lib().dgb_gemm_wgrad_bf16(N.ptr(g), N.i64(g.stride(0)), N.ptr(x), N.i64(x.stride(0)), N.ptr(out),
-                                        N.i64(out.stride(0)), N.i64(g.shape[0]), N.i32(N1), N.i32(N2), N.stream()),
+                                        N.i64(out.stride(0)), N.i64(g.shape[0]), N.i32(N1), N.i32(N2), N.ptr(idx32),
+                                        N.stream()),
             "dgb_gemm_wgrad_bf16")
     N.count_launch()
     return out if out.shape[1] == N2 else out[:, :N2]

@@ -20,25 +20,29 @@ def layer_norm_residual_ref(z, gamma, beta, eps, residual=None):
 
 class _LNRes(Function):
     @staticmethod
-    def forward(ctx, z, gamma, beta, eps, residual):
-        M, C = z.shape
+    def forward(ctx, z, gamma, beta, eps, residual, c_valid):
+        M, C = z.shape  # C is the padded width (multiple of 8)
         y = torch.empty((M, C), dtype=torch.bfloat16, device=z.device)
         mean = torch.empty(M, dtype=torch.float32, device=z.device)
         rstd = torch.empty(M, dtype=torch.float32, device=z.device)
-        gf, bf = gamma.float().contiguous(), beta.float().contiguous()
+        gf = torch.zeros(C, dtype=torch.float32, device=z.device)
+        bf = torch.zeros(C, dtype=torch.float32, device=z.device)
+        gf[:c_valid] = gamma
+        bf[:c_valid] = beta
         N.check(N.lib().dgb_layernorm_fwd(N.ptr(z), N.i64(z.stride(0)), N.ptr(residual),
                                           N.i64(0 if residual is None else residual.stride(0)), N.ptr(gf), N.ptr(bf), N.ptr(y),
-                                          N.i64(C), N.ptr(mean), N.ptr(rstd), N.i64(M), N.i32(C), N.f32(eps), N.stream()),
-                "dgb_layernorm_fwd")
+                                          N.i64(C), N.ptr(mean), N.ptr(rstd), N.i64(M), N.i32(C), N.i32(c_valid), N.f32(eps),
+                                          N.stream()), "dgb_layernorm_fwd")
         N.count_launch()
         ctx.save_for_backward(z, gf, mean, rstd)
-        ctx.has_res = residual is not None
+        ctx.has_res, ctx.c_valid = residual is not None, c_valid
         return y
 
     @staticmethod
     def backward(ctx, gy):
         z, gf, mean, rstd = ctx.saved_tensors
         M, C = z.shape
+        cv = ctx.c_valid
         gy = gy.contiguous()
         dz = torch.empty_like(gy)
         lib = N.lib()
@@ -47,21 +51,28 @@ class _LNRes(Function):
         scratch = torch.empty(max(nb // 4, 1), dtype=torch.float32, device=gy.device)
         dgb = torch.empty(2 * C, dtype=torch.float32, device=gy.device)
         N.check(lib.dgb_layernorm_bwd(N.ptr(gy), N.i64(C), N.ptr(z), N.i64(z.stride(0)), N.ptr(gf), N.ptr(mean), N.ptr(rstd),
-                                      N.ptr(dz), N.i64(C), N.ptr(scratch), N.ptr(dgb), N.i64(M), N.i32(C), N.stream()),
+                                      N.ptr(dz), N.i64(C), N.ptr(scratch), N.ptr(dgb), N.i64(M), N.i32(C), N.i32(cv), N.stream()),
                 "dgb_layernorm_bwd")
         N.count_launch(2)
-        return dz, dgb[:C], dgb[C:], None, (gy if ctx.has_res else None)
+        return dz, dgb[:cv], dgb[C:C + cv], None, (gy if ctx.has_res else None), None
 
 
 def layer_norm_residual(z: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5,
                         residual: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """``LayerNorm(z) * gamma + beta (+ residual)`` over the last dimension of a 2-D tensor."""
+    """``LayerNorm(z) * gamma + beta (+ residual)`` over the last dimension of a 2-D tensor.  Widths that are not a multiple of
+    8 (GraphCast's 73 output channels) run on a zero-padded copy with the statistics restricted to the valid columns."""
     C = z.shape[-1]
-    if z.is_cuda and z.dtype == torch.bfloat16 and z.dim() == 2 and C % 8 == 0 and C <= 512 and z.stride(1) == 1 \
-            and z.stride(0) % 8 == 0 and N.available():
+    Cp = (C + 7) // 8 * 8
+    if z.is_cuda and z.dtype == torch.bfloat16 and z.dim() == 2 and Cp <= 512 and N.available():
+        if Cp != C:
+            zp = F.pad(z, (0, Cp - C))
+            rp = None if residual is None else F.pad(residual.to(torch.bfloat16), (0, Cp - C))
+            return _LNRes.apply(zp, gamma, beta, float(eps), rp, C)[:, :C]
+        if z.stride(1) != 1 or z.stride(0) % 8:
+            z = z.contiguous()
         if residual is not None and (residual.dtype != torch.bfloat16 or residual.stride(-1) != 1 or residual.stride(0) % 8):
             residual = residual.to(torch.bfloat16).contiguous()
-        return _LNRes.apply(z, gamma, beta, float(eps), residual)
+        return _LNRes.apply(z, gamma, beta, float(eps), residual, C)
     if z.is_cuda:
         N.require_for(z)
     return layer_norm_residual_ref(z, gamma, beta, eps, residual)

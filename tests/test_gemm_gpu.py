@@ -106,3 +106,16 @@ def test_wgrad_splitk_matches_fp32_reference(M, N1, N2):
     ref = g.float().t() @ x.float()
     assert dw.shape == (N1, N2) and dw.dtype == torch.float32
     assert torch.allclose(dw, ref, rtol=1e-2, atol=2e-2 * (M ** 0.5)), (dw - ref).abs().max().item()
+
+
+@pytest.mark.parametrize("M,N1,N2,V", [(5000, 128, 128, 700), (70001, 128, 104, 3000), (999, 256, 256, 50)])
+def test_wgrad_with_gathered_rows_matches_reference(M, N1, N2, V):
+    from dgraph_b200.ops.gemm_native import gemm_bf16_nn_grad_w
+
+    torch.manual_seed(M)
+    g = torch.randn(M, N1, device="cuda").bfloat16()
+    x = torch.randn(V, N2, device="cuda").bfloat16()
+    idx = torch.randint(0, V, (M,), device="cuda", dtype=torch.int32)
+    dw = gemm_bf16_nn_grad_w(g, x, idx)
+    ref = g.float().t() @ x.float()[idx.long()]
+    assert torch.allclose(dw, ref, rtol=1e-2, atol=2e-2 * (M ** 0.5)), (dw - ref).abs().max().item()

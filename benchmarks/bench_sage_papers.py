@@ -43,12 +43,13 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--hidden", type=int, default=256)
+    ap.add_argument("--cut", type=float, default=0.05, help="fraction of edges whose neighbour is drawn uniformly (long range)")
     a = ap.parse_args()
     comm, rank, world, dev = init_distributed("nccl")
     V0, E0, F, C = SHAPES["ogbn-papers100M"]
     V, E = int(V0 * a.scale), int(E0 * a.scale)
     t0 = time.time()
-    edges = shard_edges(V, E, rank, world, dev)
+    edges = shard_edges(V, E, rank, world, dev, cut=a.cut)
     offsets = torch.tensor([V * r // world for r in range(world + 1)])
     pat = build_communication_pattern_from_shard(edges, offsets, rank, world)
     del edges
@@ -91,7 +92,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     if rank == 0:
         print(json.dumps({"model": "GraphSAGE 2 layers hidden %d" % a.hidden, "graph": f"papers100M-shaped V={V} E~{E} F={F}",
-                          "n_gpus": world, "ms_per_epoch": float(t[0]), "edges_per_s": E / (float(t[0]) * 1e-3),
+                          "cut": a.cut, "n_gpus": world, "ms_per_epoch": float(t[0]), "edges_per_s": E / (float(t[0]) * 1e-3),
                           "max_halo_rows": int(t[1]), "max_local_edges": int(t[2]), "setup_s": round(setup_s, 1),
                           "loss": float(loss.detach()), "engine": type(comm.engine).__name__,
                           "mem_GB": round(torch.cuda.max_memory_allocated() / 2 ** 30, 1) if dev.type == "cuda" else None}),

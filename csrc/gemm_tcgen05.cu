@@ -35,6 +35,12 @@ struct GemmParams {
   int64_t seg_ld[3];
   int seg_kblocks[3];  // k-blocks (of 64) per segment; weights are laid out segment after segment, each padded to 64
   int seg_k[3];        // true K of the segment (columns beyond are zero-filled)
+  // optional peer addressing per segment: gathered row j >= seg_nlocal[s] lives on another GPU, in the same matrix at
+  // peer_base[halo_owner[j - nlocal]] + halo_row[j - nlocal] * ld  (NVLink pull inside the GEMM's producer warps)
+  const __nv_bfloat16* const* seg_peer[3];
+  const int* seg_halo_owner[3];
+  const int* seg_halo_row[3];
+  int64_t seg_nlocal[3];
 };
 
 template <int BLOCK_N>
@@ -274,17 +280,22 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m0 = (tile / tiles_n) * BLOCK_M;
       for (int s = 0; s < p.n_seg; ++s) {
-        int64_t rowoff[8];
+        const __nv_bfloat16* rowptr[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const int m = m0 + r0 + 16 * i;
+          rowptr[i] = nullptr;
           if (m < p.M) {
             const int j = p.seg_idx[s] ? __ldg(p.seg_idx[s] + m) : m;
-            rowoff[i] = (int64_t)j * p.seg_ld[s];
-          } else {
-            rowoff[i] = -1;
+            if (p.seg_peer[s] && j >= p.seg_nlocal[s]) {
+              const int h = j - (int)p.seg_nlocal[s];
+              rowptr[i] = p.seg_peer[s][__ldg(p.seg_halo_owner[s] + h)] + (int64_t)__ldg(p.seg_halo_row[s] + h) * p.seg_ld[s];
+            } else {
+              rowptr[i] = p.seg_base[s] + (int64_t)j * p.seg_ld[s];
+            }
           }
         }
+        const bool remote_ok = p.seg_peer[s] != nullptr;  // peer rows were written by another GPU: coherent loads
         for (int kb = 0; kb < p.seg_kblocks[s]; ++kb) {
           tc::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * L::STAGE_BYTES;
@@ -293,7 +304,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             v[i] = make_uint4(0, 0, 0, 0);
-            if (rowoff[i] >= 0 && k < p.seg_k[s]) v[i] = ldg_nc_v4(p.seg_base[s] + rowoff[i] + k);
+            if (rowptr[i] != nullptr && k < p.seg_k[s]) v[i] = remote_ok ? ldg_v4(rowptr[i] + k) : ldg_nc_v4(rowptr[i] + k);
           }
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
@@ -413,6 +424,41 @@ DGB_API int dgb_gather_gemm_bf16(int n_seg, const void* const* seg_base, const i
     p.seg_idx[s] = seg_idx[s];
     p.seg_k[s] = seg_k[s];
     p.seg_kblocks[s] = (seg_k[s] + BLOCK_K - 1) / BLOCK_K;
+    ktot += p.seg_kblocks[s] * BLOCK_K;
+  }
+  p.K = ktot;
+  const int bn = pick_block_n(N);
+  CUtensorMap tb;
+  int rc = make_tmap_bf16_2d(&tb, W, (uint64_t)N, (uint64_t)ktot, (uint64_t)ldw, bn, BLOCK_K);
+  if (rc) return rc;
+  return dispatch_gemm<true>(tb, tb, p, out_f32, bn, (cudaStream_t)stream);
+}
+
+// Gather-GEMM whose gathered rows may live on other GPUs (F1: halo gather fused into the first edge/node MLP GEMM).
+// Same as dgb_gather_gemm_bf16; for every segment s with seg_peer[s] != null, gathered row j >= seg_nlocal[s] is read from
+// seg_peer[s][halo_owner[s][j - nlocal]] + halo_row[s][j - nlocal] * seg_ld[s] -- a plain 16-byte load on an NVLink-mapped
+// peer pointer issued by the producer warps that assemble the tcgen05 A tile.  The caller orders the exchange (barrier).
+DGB_API int dgb_gather_gemm_peer_bf16(int n_seg, const void* const* seg_base, const int64_t* seg_ld, const int* const* seg_idx,
+                                      const int* seg_k, const void* const* const* seg_peer, const int* const* seg_halo_owner,
+                                      const int* const* seg_halo_row, const int64_t* seg_nlocal, const void* W, int64_t ldw,
+                                      void* C, int64_t ldc, int M, int N, const float* bias, int act, int out_f32,
+                                      void* stream) {
+  if (M <= 0 || N <= 0) return 0;
+  if (n_seg < 1 || n_seg > 3 || (ldw % 8) || N > MAX_N) return (int)cudaErrorInvalidValue;
+  GemmParams p{};
+  p.M = M; p.N = N; p.bias = bias; p.C = C; p.ldc = ldc; p.act = act; p.n_seg = n_seg;
+  int ktot = 0;
+  for (int s = 0; s < n_seg; ++s) {
+    if ((seg_ld[s] % 8) || (seg_k[s] % 8) || (reinterpret_cast<uintptr_t>(seg_base[s]) & 15)) return (int)cudaErrorInvalidValue;
+    p.seg_base[s] = (const __nv_bfloat16*)seg_base[s];
+    p.seg_ld[s] = seg_ld[s];
+    p.seg_idx[s] = seg_idx[s];
+    p.seg_k[s] = seg_k[s];
+    p.seg_kblocks[s] = (seg_k[s] + BLOCK_K - 1) / BLOCK_K;
+    p.seg_peer[s] = seg_peer ? (const __nv_bfloat16* const*)seg_peer[s] : nullptr;
+    p.seg_halo_owner[s] = seg_halo_owner ? seg_halo_owner[s] : nullptr;
+    p.seg_halo_row[s] = seg_halo_row ? seg_halo_row[s] : nullptr;
+    p.seg_nlocal[s] = seg_nlocal ? seg_nlocal[s] : 0;
     ktot += p.seg_kblocks[s] * BLOCK_K;
   }
   p.K = ktot;

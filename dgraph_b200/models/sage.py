@@ -5,6 +5,8 @@ pull of the neighbour rows, ONE bf16 CSR mean-aggregation kernel (``ops.segment_
 gather-GEMM over the two un-concatenated sources ``[x_local | agg]``."""
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.nn as nn
 
@@ -19,8 +21,9 @@ class SAGEConv(nn.Module):
         super().__init__()
         self.lin = nn.Linear(2 * in_channels, out_channels)  # columns [W_self | W_nbr]
 
-    def forward(self, x_aug: torch.Tensor, kp: GraphKernelPlan, num_local: int, act=None):
-        agg = segment_mean(x_aug, kp)
+    def forward(self, x_aug: torch.Tensor, kp: GraphKernelPlan, num_local: int, act=None, agg: torch.Tensor = None):
+        if agg is None:
+            agg = segment_mean(x_aug, kp)
         x_loc = x_aug[:num_local]
         k = self.lin.in_features // 2
         w = self.lin.weight
@@ -46,6 +49,12 @@ class CommAwareSAGE(nn.Module):
             x = x.to(self.compute_dtype)
         n = x.shape[0]
         kp = comm_pattern.kernel_plan(x.device)
+        engine = getattr(self.comm, "engine", None)
+        fused_pull = (os.environ.get("DGRAPH_B200_FUSED_PULL", "0") == "1" and hasattr(engine, "aggregate_pull")
+                      and x.is_cuda and x.dtype == torch.bfloat16)
         for conv in self.convs:
-            x = conv(self.halo_exchanger.augmented(x, comm_pattern), kp, n, act="relu")
+            if fused_pull:  # remote neighbour rows are read inside the aggregation kernel; no halo buffer at all
+                x = conv(x, kp, n, act="relu", agg=engine.aggregate_pull(x, comm_pattern, mean=True))
+            else:
+                x = conv(self.halo_exchanger.augmented(x, comm_pattern), kp, n, act="relu")
         return linear(x, self.fc.weight.to(x.dtype), self.fc.bias.to(x.dtype))

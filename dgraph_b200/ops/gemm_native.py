@@ -63,7 +63,7 @@ def pack_segment_weight(w: torch.Tensor, seg_k: Sequence[int]) -> torch.Tensor:
 
 def gather_gemm_bf16(srcs: List[torch.Tensor], idxs: List[Optional[torch.Tensor]], w_packed: torch.Tensor,
                      bias: Optional[torch.Tensor], M: int, seg_k: Sequence[int], act=None,
-                     out_dtype=torch.bfloat16) -> torch.Tensor:
+                     out_dtype=torch.bfloat16, peers: Optional[List[Optional[tuple]]] = None) -> torch.Tensor:
     """``act(cat([srcs[s][idxs[s]] for s], 1) @ W.T + bias)`` with the gather and the concat done inside the GEMM's
     producer warps (F1b).  ``idxs[s] is None`` means row ``m`` of ``srcs[s]`` (per-edge features)."""
     n = len(srcs)
@@ -77,6 +77,20 @@ def gather_gemm_bf16(srcs: List[torch.Tensor], idxs: List[Optional[torch.Tensor]
     ips = (ctypes.c_void_p * 3)(*[(0 if i is None else i.data_ptr()) for i in idx32] + [0] * (3 - n))
     ks = (ctypes.c_int * 3)(*[int(k) for k in seg_k] + [0] * (3 - n))
     bias_f = None if bias is None else bias.float().contiguous()
+    if peers is not None and any(p is not None for p in peers):
+        # peers[s] = (ptr_table int64 [W], halo_owner int32 [n_halo], halo_row int32 [n_halo], n_local): gathered rows
+        # >= n_local of segment s are pulled from the owner GPU inside the producer warps (NVLink loads)
+        pt = (ctypes.c_void_p * 3)(*[(0 if p is None else p[0].data_ptr()) for p in peers] + [0] * (3 - n))
+        ho = (ctypes.c_void_p * 3)(*[(0 if p is None else p[1].data_ptr()) for p in peers] + [0] * (3 - n))
+        hr = (ctypes.c_void_p * 3)(*[(0 if p is None else p[2].data_ptr()) for p in peers] + [0] * (3 - n))
+        nl = (ctypes.c_int64 * 3)(*[(0 if p is None else int(p[3])) for p in peers] + [0] * (3 - n))
+        N.check(N.lib().dgb_gather_gemm_peer_bf16(N.i32(n), bases, lds, ips, ks, pt, ho, hr, nl, N.ptr(w_packed),
+                                                  N.i64(w_packed.stride(0)), N.ptr(out), N.i64(out.stride(0)), N.i32(M),
+                                                  N.i32(Nn), N.ptr(bias_f), N.i32(_ACT[act]),
+                                                  N.i32(1 if out_dtype == torch.float32 else 0), N.stream()),
+                "dgb_gather_gemm_peer_bf16")
+        N.count_launch()
+        return out
     N.check(N.lib().dgb_gather_gemm_bf16(N.i32(n), bases, lds, ips, ks, N.ptr(w_packed), N.i64(w_packed.stride(0)),
                                          N.ptr(out), N.i64(out.stride(0)), N.i32(M), N.i32(Nn), N.ptr(bias_f),
                                          N.i32(_ACT[act]), N.i32(1 if out_dtype == torch.float32 else 0), N.stream()),

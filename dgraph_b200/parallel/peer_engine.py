@@ -183,6 +183,56 @@ class _SlotGuard:
             pass
 
 
+def _halo_grad_reduce(engine, pat, g_aug):
+    """Backward of any halo read: gradients of halo rows are published in a symmetric slot and pull-reduced by the owners."""
+    info = engine.pattern_info(pat)
+    F = g_aug.shape[1]
+    g_aug = g_aug.contiguous()
+    assert g_aug.dtype == torch.bfloat16, "halo gradient reduce kernel is bf16 (fp32 accumulate)"
+    gh, off = engine.slot_tensor(("halo_bwd", info.uid), (info.max_halo, F), g_aug.dtype, ring=False)
+    gh[: info.n_halo].copy_(g_aug[info.n_nbr_local:])
+    engine.barrier_on_stream()
+    gx = g_aug[: info.n_nbr_local].clone()
+    N.check(N.lib().dgb_halo_grad_reduce(N.ptr(gx), N.i64(F), N.ptr(g_aug), N.i64(F), N.i32(F), N.i64(info.n_bnd),
+                                         N.ptr(info.bnd_row), N.ptr(info.bnd_ptr), N.ptr(info.src_rank),
+                                         N.ptr(info.src_row), N.ptr(engine.arena.ptr_table(off)), N.i64(F),
+                                         N.stream()), "dgb_halo_grad_reduce")
+    N.count_launch(2)
+    engine.mark_read(off)  # the next writer of this slot inserts a barrier only if none happened in between
+    return gx
+
+
+class _FusedPullAggregate(Function):
+    """``out[i] = (1/deg) sum_{j in N(i)} x[j]`` where remote neighbour rows are read **directly from the owner GPU's matrix**
+    inside the aggregation kernel (no halo buffer, no exchange kernel): publish + barrier + ONE segment kernel."""
+
+    @staticmethod
+    def forward(ctx, x, engine, pat, kp, mean):
+        info = engine.pattern_info(pat)
+        F = x.shape[1]
+        pub, off = engine.slot_tensor(("pub", info.uid), (max(info.nbr_local_all), F), x.dtype, ring=False)
+        pub[: info.n_nbr_local].copy_(x)
+        engine.barrier_on_stream()
+        out = torch.empty((kp.num_local, F), dtype=torch.bfloat16, device=x.device)
+        N.check(N.lib().dgb_seg_sum(N.ptr(kp.rowptr), N.ptr(kp.col), N.i64(kp.num_local), N.i32(F), N.ptr(pub), N.i64(F),
+                                    N.ptr(None), N.i32(1 if mean else 0), N.ptr(out), N.i64(F), N.i64(info.n_nbr_local),
+                                    N.ptr(engine.arena.ptr_table(off)), N.ptr(info.halo_owner), N.ptr(info.halo_row), N.i64(F),
+                                    N.stream()), "dgb_seg_sum(halo pull)")
+        N.count_launch(2)
+        engine.mark_read(off)
+        ctx.engine, ctx.pat, ctx.kp, ctx.mean = engine, pat, kp, mean
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        from dgraph_b200.ops.segment import _mean_bwd_weights, _native_seg_sum
+
+        kp = ctx.kp
+        w = _mean_bwd_weights(kp) if ctx.mean else None
+        g_aug = _native_seg_sum(kp.colptr, kp.row, kp.num_aug, g.contiguous(), w, False)
+        return _halo_grad_reduce(ctx.engine, ctx.pat, g_aug), None, None, None, None
+
+
 class _HaloAug(Function):
     """``aug = cat([x, halo(x)])`` through the symmetric arena; backward pull-reduces halo gradients on the owners."""
 
@@ -209,22 +259,8 @@ class _HaloAug(Function):
     @staticmethod
     def backward(ctx, g_aug):
         engine, pat = ctx.engine, ctx.pat
-        info = engine.pattern_info(pat)
         ctx.slot_guard.release()
-        F = g_aug.shape[1]
-        g_aug = g_aug.contiguous()
-        assert g_aug.dtype == torch.bfloat16, "halo gradient reduce kernel is bf16 (fp32 accumulate)"
-        gh, off = engine.slot_tensor(("halo_bwd", info.uid), (info.max_halo, F), g_aug.dtype, ring=False)
-        gh[: info.n_halo].copy_(g_aug[info.n_nbr_local:])
-        engine.barrier_on_stream()
-        gx = g_aug[: info.n_nbr_local].clone()
-        N.check(N.lib().dgb_halo_grad_reduce(N.ptr(gx), N.i64(F), N.ptr(g_aug), N.i64(F), N.i32(F), N.i64(info.n_bnd),
-                                             N.ptr(info.bnd_row), N.ptr(info.bnd_ptr), N.ptr(info.src_rank),
-                                             N.ptr(info.src_row), N.ptr(engine.arena.ptr_table(off)), N.i64(F),
-                                             N.stream()), "dgb_halo_grad_reduce")
-        N.count_launch(2)
-        engine.mark_read(off)  # the next writer of this slot inserts a barrier only if none happened in between
-        return gx, None, None
+        return _halo_grad_reduce(engine, pat, g_aug), None, None
 
 
 class PeerMemoryEngine(TorchDistEngine):
@@ -340,6 +376,25 @@ class PeerMemoryEngine(TorchDistEngine):
             return x.new_zeros((0, x.shape[1]))
         info = self.pattern_info(pat)
         return self.halo_exchange_aug(x, pat)[info.n_nbr_local:]
+
+    def aggregate_pull(self, x: torch.Tensor, pat, mean: bool = True) -> torch.Tensor:
+        """Neighbourhood sum / mean with remote rows pulled inside the aggregation kernel (F1a + F7 fused)."""
+        kp = pat.kernel_plan(x.device)
+        if self._world == 1:
+            from dgraph_b200.ops.segment import segment_sum
+
+            return segment_sum(x, kp, mean=mean)
+        return _FusedPullAggregate.apply(x, self, pat, kp, mean)
+
+    def publish(self, x: torch.Tensor, pat, tag: str = "pubx"):
+        """Copy ``x`` into a symmetric slot and order it for the peers; returns ``(peer pointer table, halo_owner, halo_row,
+        n_local)`` -- the ``peers`` entry that ``ops.gemm_native.gather_gemm_bf16`` needs to pull remote rows itself."""
+        info = self.pattern_info(pat)
+        pub, off = self.slot_tensor((tag, info.uid), (max(info.nbr_local_all), x.shape[1]), x.dtype, ring=False)
+        pub[: info.n_nbr_local].copy_(x)
+        self.barrier_on_stream()
+        self.mark_read(off)
+        return pub[: info.n_nbr_local], (self.arena.ptr_table(off), info.halo_owner, info.halo_row, info.n_nbr_local)
 
     # ---- fused gradient all-reduce + Adam ----------------------------------------------------------
     def symmetric_flat(self, key: str, numel: int, dtype=torch.float32) -> Tuple[torch.Tensor, int]:

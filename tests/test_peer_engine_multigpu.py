@@ -53,6 +53,32 @@ def _worker(rank, W, port, e, part, xg, yg, state, ret):
     full = sum(allw)
     ok = ok and torch.allclose(x.grad.float()[:, 0], full[gids], rtol=2e-2, atol=2e-2)
 
+    # fused pull aggregation (remote rows read inside the segment kernel) == aggregation over the materialised halo
+    from dgraph_b200.ops.segment import segment_mean
+
+    xa = xg.to(dev)[gids].bfloat16().requires_grad_(True)
+    xb = xg.to(dev)[gids].bfloat16().requires_grad_(True)
+    a1 = comm.engine.aggregate_pull(xa, pat, mean=True)
+    a2 = segment_mean(ex.augmented(xb, pat), pat.kernel_plan(dev))
+    ok = ok and torch.equal(a1, a2)
+    gsel = torch.randn_like(a1)
+    a1.backward(gsel)
+    a2.backward(gsel)
+    ok = ok and torch.allclose(xa.grad.float(), xb.grad.float(), rtol=2e-2, atol=2e-2)
+    # gather-GEMM with peer rows: the producer warps pull remote rows themselves
+    from dgraph_b200.ops.gemm_native import gather_gemm_bf16, pack_segment_weight
+
+    Fw = xa.shape[1]
+    wq = (torch.randn(64, 2 * Fw, device=dev) * 0.1).bfloat16()
+    wpk = pack_segment_weight(wq, [Fw, Fw])
+    with torch.no_grad():
+        aug_ref = ex.augmented(xb.detach(), pat)
+        srci, dsti = pat.local_edge_list[:, 0].int().contiguous(), pat.local_edge_list[:, 1].int().contiguous()
+        ref_out = gather_gemm_bf16([aug_ref, aug_ref], [srci, dsti], wpk, None, int(srci.numel()), [Fw, Fw])
+        pubx, peer = comm.engine.publish(xb.detach(), pat)
+        got_out = gather_gemm_bf16([pubx, pubx], [srci, dsti], wpk, None, int(srci.numel()), [Fw, Fw], peers=[None, peer])
+    ok = ok and torch.equal(got_out, ref_out)
+
     # 3 training steps must match the single-process run on the whole graph
     torch.manual_seed(0)
     model = CommAwareGCN(xg.shape[1], 64, 5, ex, comm, compute_dtype=torch.bfloat16).to(dev)

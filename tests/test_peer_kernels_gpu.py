@@ -101,3 +101,46 @@ def test_adam_allreduce_and_allreduce_sum_emulated():
     for r in range(W):
         assert torch.allclose(ps[r], ref_p.detach(), atol=1e-5)
         assert torch.equal(ps[r], ps[0])  # replicas stay bit-identical
+
+
+@pytest.mark.parametrize("W", [2, 3])
+def test_fused_pull_kernels_emulated(W):
+    """Segment-mean with in-kernel halo pulls and the gather-GEMM with peer rows == the same ops on a materialised [local | halo]
+    matrix (ranks emulated as buffers of one process)."""
+    from dgraph_b200.ops import _native as N
+    from dgraph_b200.ops.gemm_native import gather_gemm_bf16, pack_segment_weight
+    from dgraph_b200.ops.segment import _native_seg_sum
+    from dgraph_b200.parallel import build_all_patterns
+    from dgraph_b200.parallel.peer_engine import _PatternPeerInfo
+
+    torch.manual_seed(0)
+    V, F, H = 400, 64, 128
+    e = random_graph(V, 7, seed=W + 5, symmetric=False)
+    part = partition(V, W, "random")
+    pats = build_all_patterns(e, part, W)
+    counts = [[p.num_local_vertices, p.num_halo_vertices, int(p.send_offset[-1])] for p in pats]
+    infos = [_PatternPeerInfo(_FakeEngine(r, W, counts), pats[r]) for r in range(W)]
+    xg = torch.randn(V, F, device="cuda").bfloat16()
+    nmax = max(c[0] for c in counts)
+    pubs = [torch.zeros(nmax, F, device="cuda", dtype=torch.bfloat16) for _ in range(W)]
+    for r in range(W):
+        pubs[r][: counts[r][0]] = xg[pats[r].local_vertices_global.cuda()]
+    table = torch.tensor([p.data_ptr() for p in pubs], dtype=torch.int64, device="cuda")
+    w = (torch.randn(H, 2 * F, device="cuda") * 0.1).bfloat16()
+    wp = pack_segment_weight(w, [F, F])
+    for r in range(W):
+        i, pat = infos[r], pats[r]
+        kp = pat.kernel_plan("cuda")
+        aug = xg[torch.cat([pat.local_vertices_global, pat.halo_vertices_global]).cuda()].contiguous()
+        want = _native_seg_sum(kp.rowptr, kp.col, kp.num_local, aug, None, True)
+        got = _native_seg_sum(kp.rowptr, kp.col, kp.num_local, pubs[r], None, True,
+                              halo=(table, i.halo_owner, i.halo_row, i.n_nbr_local, F))
+        assert torch.equal(got, want)
+        # gather-GEMM over cat([x[src], x_aug[dst]]): dst rows beyond n_local are pulled from the owner
+        src = pat.local_edge_list[:, 0].cuda().int()
+        dst = pat.local_edge_list[:, 1].cuda().int()
+        E = int(src.numel())
+        ref = gather_gemm_bf16([aug, aug], [src, dst], wp, None, E, [F, F], act="silu")
+        out = gather_gemm_bf16([pubs[r], pubs[r]], [src, dst], wp, None, E, [F, F], act="silu",
+                               peers=[None, (table, i.halo_owner, i.halo_row, i.n_nbr_local)])
+        assert torch.equal(out, ref)

@@ -55,13 +55,17 @@ template <int G>
 __global__ void __launch_bounds__(256) halo_pull_kernel(uint8_t* __restrict__ dst, int64_t ld_dst_bytes, int64_t n_halo,
                                                         int row_bytes, const uint8_t* const* __restrict__ peer_base,
                                                         int64_t ld_peer_bytes, const int* __restrict__ halo_owner,
-                                                        const int* __restrict__ halo_row) {
+                                                        const int* __restrict__ halo_row, int64_t rot) {
+  // Halo rows are stored owner-major; every rank starts `rot` rows in (the segment of owner rank+1), so at any moment the
+  // ranks read from different owners instead of all hitting owner 0 first (NVLink incast).
   const int lane = threadIdx.x & 31;
   const int g = lane & (G - 1);
   const int64_t grp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
   const int64_t ngrp = ((int64_t)gridDim.x * blockDim.x) / G;
   const int chunks = row_bytes >> 4;
-  for (int64_t h = grp; h < n_halo; h += ngrp) {
+  for (int64_t h0 = grp; h0 < n_halo; h0 += ngrp) {
+    int64_t h = h0 + rot;
+    if (h >= n_halo) h -= n_halo;
     const uint8_t* src = peer_base[halo_owner[h]] + (int64_t)halo_row[h] * ld_peer_bytes;
     uint8_t* out = dst + h * ld_dst_bytes;
     for (int c = g; c < chunks; c += G) stg_v4(out + (c << 4), ldg_v4(src + (c << 4)));
@@ -260,8 +264,9 @@ DGB_API int dgb_peer_barrier(void* const* pads, int rank, int world, unsigned ep
 static int pick_group(int chunks) { return chunks <= 4 ? 4 : (chunks <= 8 ? 8 : (chunks <= 16 ? 16 : 32)); }
 
 DGB_API int dgb_halo_pull(void* dst, int64_t ld_dst_bytes, int64_t n_halo, int row_bytes, const void* const* peer_base,
-                          int64_t ld_peer_bytes, const int* halo_owner, const int* halo_row, void* stream) {
+                          int64_t ld_peer_bytes, const int* halo_owner, const int* halo_row, int64_t rot, void* stream) {
   if (n_halo == 0) return 0;
+  if (rot < 0 || rot >= n_halo) rot = 0;
   if ((row_bytes & 15) || (ld_dst_bytes & 15) || (ld_peer_bytes & 15)) return (int)cudaErrorInvalidValue;
   const int G = pick_group(row_bytes >> 4);
   const int64_t groups_per_block = 256 / G;
@@ -271,7 +276,7 @@ DGB_API int dgb_halo_pull(void* dst, int64_t ld_dst_bytes, int64_t n_halo, int r
 #define DGB_HP(GG)                                                                                                   \
   halo_pull_kernel<GG><<<(unsigned)blocks, 256, 0, s>>>((uint8_t*)dst, ld_dst_bytes, n_halo, row_bytes,              \
                                                        (const uint8_t* const*)peer_base, ld_peer_bytes, halo_owner, \
-                                                       halo_row)
+                                                       halo_row, rot)
   if (G == 4) DGB_HP(4); else if (G == 8) DGB_HP(8); else if (G == 16) DGB_HP(16); else DGB_HP(32);
 #undef DGB_HP
   DGB_CHECK_LAUNCH();

@@ -132,6 +132,10 @@ class _PatternPeerInfo:
         self.n_halo = pat.num_halo_vertices
         self.halo_owner = pat.halo_owner.to(dev, torch.int32).contiguous()
         self.halo_row = pat.halo_remote_row.to(dev, torch.int32).contiguous()
+        # start pulling at the segment of owner (rank + 1) % W: staggers the ranks over the owners (no incast on owner 0)
+        self.rot = int(pat.recv_offset[(r + 1) % W]) if W > 1 else 0
+        if self.rot >= max(self.n_halo, 1):
+            self.rot = 0
         counts = engine.all_gather_ints([self.n_nbr_local, self.n_halo, int(pat.send_offset[-1])])
         self.nbr_local_all = [c[0] for c in counts]
         self.max_aug = max(c[0] + c[1] for c in counts)
@@ -249,7 +253,7 @@ class _HaloAug(Function):
         rb = F * x.element_size()
         N.check(N.lib().dgb_halo_pull(N.ptr(aug[info.n_nbr_local:]), N.i64(rb), N.i64(info.n_halo), N.i32(rb),
                                       N.ptr(engine.arena.ptr_table(off)), N.i64(rb), N.ptr(info.halo_owner),
-                                      N.ptr(info.halo_row), N.stream()), "dgb_halo_pull")
+                                      N.ptr(info.halo_row), N.i64(info.rot), N.stream()), "dgb_halo_pull")
         N.count_launch(2)
         engine.mark_read(off)
         ctx.engine, ctx.pat = engine, pat

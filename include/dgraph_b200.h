@@ -81,7 +81,7 @@ int dgb_enable_peer_access(int peer);
 int dgb_peer_barrier(void* const* pads, int rank, int world, unsigned epoch, int* timeout_flag, long long max_spin,
                      void* stream);
 int dgb_halo_pull(void* dst, int64_t ld_dst_bytes, int64_t n_halo, int row_bytes, const void* const* peer_base,
-                  int64_t ld_peer_bytes, const int* halo_owner, const int* halo_row, void* stream);
+                  int64_t ld_peer_bytes, const int* halo_owner, const int* halo_row, int64_t rot, void* stream);
 int dgb_gather_rows_peer(void* out, int64_t ld_out_bytes, int64_t n, int row_bytes, const void* const* peer_base,
                          int64_t ld_peer_bytes, const int* owner, const int* row, void* stream);
 int dgb_halo_grad_reduce(void* gx, int64_t ld_gx, const void* g_local, int64_t ld_gl, int H, int64_t n_bnd,

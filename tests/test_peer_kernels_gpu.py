@@ -50,7 +50,7 @@ def test_halo_pull_and_grad_reduce_emulated(W, F):
     for r in range(W):  # phase 2: every rank pulls its halo
         i = infos[r]
         N.check(N.lib().dgb_halo_pull(N.ptr(slots[r][i.n_nbr_local:]), N.i64(rb), N.i64(i.n_halo), N.i32(rb), N.ptr(table),
-                                      N.i64(rb), N.ptr(i.halo_owner), N.ptr(i.halo_row), N.stream()), "pull")
+                                      N.i64(rb), N.ptr(i.halo_owner), N.ptr(i.halo_row), N.i64(i.rot), N.stream()), "pull")
     for r in range(W):
         want = xg[torch.cat([pats[r].local_vertices_global, pats[r].halo_vertices_global]).cuda()]
         assert torch.equal(slots[r][: want.shape[0]], want)

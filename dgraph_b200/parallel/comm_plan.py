@@ -39,14 +39,18 @@ class NCCLGraphCommPlan:
     boundary_edge_splits: List[int]
     boundary_vertex_idx: torch.Tensor
     boundary_vertex_splits: List[int]
+    # extras for the peer-memory engine (not in the reference): owner rank and row inside the owner's matrix, per edge
+    edge_owner: Optional[torch.Tensor] = None
+    edge_owner_row: Optional[torch.Tensor] = None
     _cache: Dict[str, Any] = field(default_factory=dict, repr=False, compare=False)
 
     _TENSORS = ("local_edge_idx", "local_vertex_idx", "boundary_edge_idx", "boundary_edge_buffer_map",
-                "boundary_vertex_idx")
+                "boundary_vertex_idx", "edge_owner", "edge_owner_row")
 
     def to(self, device) -> "NCCLGraphCommPlan":
         for n in self._TENSORS:
-            setattr(self, n, getattr(self, n).to(device))
+            if getattr(self, n) is not None:
+                setattr(self, n, getattr(self, n).to(device))
         self._cache.clear()
         return self
 
@@ -203,6 +207,8 @@ def plan_from_requests(
         boundary_edge_splits=[int(x) for x in edge_splits],
         boundary_vertex_idx=recv_rows.to(dev),
         boundary_vertex_splits=[int(x) for x in vertex_splits],
+        edge_owner=owner.to(torch.int32),
+        edge_owner_row=owner_row.to(torch.int32),
     )
 
 

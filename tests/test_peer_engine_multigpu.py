@@ -79,6 +79,32 @@ def _worker(rank, W, port, e, part, xg, yg, state, ret):
         got_out = gather_gemm_bf16([pubx, pubx], [srci, dsti], wpk, None, int(srci.numel()), [Fw, Fw], peers=[None, peer])
     ok = ok and torch.equal(got_out, ref_out)
 
+    # CommPlan gather / scatter over peer memory (pull kernels) vs the global oracle, forward and backward
+    from dgraph_b200.parallel.comm_plan import COO_to_NCCLCommPlan
+
+    V = xg.shape[0]
+    offp = torch.tensor([V * r // W for r in range(W + 1)])
+    ed = e.to(dev)
+    minee = torch.nonzero((ed[:, 0] >= offp[rank]) & (ed[:, 0] < offp[rank + 1]), as_tuple=True)[0]
+    plan = COO_to_NCCLCommPlan(rank, W, ed[:, 1], minee, offp.to(dev))
+    xp = xg.to(dev)[offp[rank]:offp[rank + 1]].bfloat16().unsqueeze(0).requires_grad_(True)
+    gat = comm.gather(xp, comm_plan=plan)
+    ok = ok and torch.equal(gat[0], xg.to(dev).bfloat16()[ed[minee, 1]])
+    wts = (torch.arange(gat.shape[1], device=dev) % 5 + 1).bfloat16().view(1, -1, 1)
+    (gat * wts).sum().backward()
+    contrib = torch.zeros(V, device=dev)
+    contrib.index_add_(0, ed[minee, 1], wts.view(-1).float())
+    allc = [torch.zeros(V, device=dev) for _ in range(W)]
+    dist.all_gather(allc, contrib)
+    ok = ok and torch.allclose(xp.grad[0, :, 0].float(), sum(allc)[offp[rank]:offp[rank + 1]], rtol=2e-2, atol=0.5)
+    ef = torch.ones(1, int(minee.numel()), 8, device=dev, dtype=torch.bfloat16)
+    sc = comm.scatter(ef, comm_plan=plan)
+    deg = torch.zeros(V, device=dev)
+    deg.index_add_(0, ed[minee, 1], torch.ones(minee.numel(), device=dev))
+    alld = [torch.zeros(V, device=dev) for _ in range(W)]
+    dist.all_gather(alld, deg)
+    ok = ok and torch.allclose(sc[0, :, 0].float(), sum(alld)[offp[rank]:offp[rank + 1]], rtol=2e-2, atol=0.5)
+
     # 3 training steps must match the single-process run on the whole graph
     torch.manual_seed(0)
     model = CommAwareGCN(xg.shape[1], 64, 5, ex, comm, compute_dtype=torch.bfloat16).to(dev)

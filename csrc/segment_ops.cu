@@ -43,6 +43,11 @@ struct SegParams {
   // read by SEG_MASKED_SUM through slot_map (slot of the *forward* walk for each slot of this walk)
   unsigned char* mask;
   const int* slot_map;
+  // SEG_MASKED_SUM only: rows r < dp_rows additionally produce dP[r,:] = src[r,:] * cnt[r,:] (the gradient of the per-row
+  // operand of the forward kernel) in the same pass, so no separate elementwise kernel re-reads dOut
+  __nv_bfloat16* dp_out;
+  int64_t ld_dp;
+  int64_t dp_rows;
   // halo pull: rows >= n_local of `src` live on peers
   int64_t n_local;
   const __nv_bfloat16* const* peer_base;  // [W] base pointer of the same matrix on every rank
@@ -199,6 +204,16 @@ __global__ void __launch_bounds__(256, (NC == 1 && !HALO) ? (MODE == SEG_SUM ? 5
         for (int t = 0; t < 8; ++t) acc[c][t] *= scale;
       }
       stg_cs_v4(p.out + r * p.ld_out + colo, pack8(acc[c]));
+      if (MODE == SEG_MASKED_SUM && p.dp_out && r < p.dp_rows) {
+        float gr[8];
+        unpack8(ldg_nc_v4(reinterpret_cast<const char*>(p.src) + (uint64_t)r * p.ld_src_b + colo * 2), gr);
+        const uint4 cv = ldg_nc_v4(p.cnt + r * p.ld_cnt + colo);
+        gr[0] *= (float)(cv.x & 0xffff); gr[1] *= (float)(cv.x >> 16);
+        gr[2] *= (float)(cv.y & 0xffff); gr[3] *= (float)(cv.y >> 16);
+        gr[4] *= (float)(cv.z & 0xffff); gr[5] *= (float)(cv.z >> 16);
+        gr[6] *= (float)(cv.w & 0xffff); gr[7] *= (float)(cv.w >> 16);
+        stg_cs_v4(p.dp_out + r * p.ld_dp + colo, pack8(gr));
+      }
       if (MODE == SEG_ADD_RELU && p.cnt) {
         uint4 cv = make_uint4(cn2[c][0], cn2[c][1], cn2[c][2], cn2[c][3]);
         stg_cs_v4(p.cnt + r * p.ld_cnt + colo, cv);
@@ -311,15 +326,21 @@ DGB_API int dgb_seg_add_relu_bwd(const int* colptr, const int* row, int64_t n_au
 }
 
 // dQ[j,:] = sum_{k in CSC seg j} mask[slot_map[k]] ? dOut[row[k],:] : 0, with the ReLU bit masks the forward kernel saved
-// (one byte per edge slot and 8-column chunk): one row gather per edge instead of two, no recomputation.
+// (one byte per edge slot and 8-column chunk): one row gather per edge instead of two, no recomputation.  When dP is given,
+// rows j < dp_rows also write dP[j,:] = dOut[j,:] * cnt[j,:] in the same pass.
 DGB_API int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slot_map, const unsigned char* mask,
-                               int64_t n_aug, int H, const void* dOut, int64_t ld_g, void* dQ, int64_t ld_dq, void* stream) {
-  if (H % 8 || ld_g % 8 || ld_dq % 8 || !fits32(ld_g * 2)) return (int)cudaErrorInvalidValue;
+                               int64_t n_aug, int H, const void* dOut, int64_t ld_g, void* dQ, int64_t ld_dq,
+                               const unsigned short* cnt, int64_t ld_cnt, void* dP, int64_t ld_dp, int64_t dp_rows,
+                               void* stream) {
+  if (H % 8 || ld_g % 8 || ld_dq % 8 || !fits32(ld_g * 2) || (dP && (ld_dp % 8 || ld_cnt % 8 || !cnt)))
+    return (int)cudaErrorInvalidValue;
   SegParams p{};
   p.ptr = colptr; p.idx = row; p.n_rows = n_aug; p.H = H;
   p.src = (const __nv_bfloat16*)dOut; p.ld_src_b = (uint32_t)(ld_g * 2);
   p.mask = const_cast<unsigned char*>(mask); p.slot_map = slot_map;
   p.out = (__nv_bfloat16*)dQ; p.ld_out = ld_dq;
+  p.cnt = const_cast<unsigned short*>(cnt); p.ld_cnt = ld_cnt;
+  p.dp_out = (__nv_bfloat16*)dP; p.ld_dp = ld_dp; p.dp_rows = dP ? dp_rows : 0;
   return launch_seg<SEG_MASKED_SUM, false>(p, (cudaStream_t)stream);
 }
 

@@ -60,13 +60,13 @@ class _GraphConvFused(Function):
         # [dP | dQ] for the local rows, dQ only for the halo rows (their P half is never read)
         dPQ = torch.empty((n_aug, 2 * H), dtype=torch.bfloat16, device=dev)
         lib = N.lib()
-        N.check(lib.dgb_mul_cnt(N.ptr(g), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(dPQ), N.i64(2 * H), N.i64(n), N.i32(H),
-                                N.stream()), "dgb_mul_cnt")
         dQ = dPQ[:, H:]
+        # one CSC walk writes dQ (masked sums) for all rows and dP = g * cnt for the local rows
         N.check(lib.dgb_seg_masked_sum(N.ptr(kp.colptr), N.ptr(kp.row), N.ptr(kp.csc_to_csr), N.ptr(mask), N.i64(n_aug),
-                                       N.i32(H), N.ptr(g), N.i64(H), N.ptr(dQ), N.i64(2 * H), N.stream()),
+                                       N.i32(H), N.ptr(g), N.i64(H), N.ptr(dQ), N.i64(2 * H), N.ptr(cnt), N.i64(H),
+                                       N.ptr(dPQ), N.i64(2 * H), N.i64(n), N.stream()),
                 "dgb_seg_masked_sum")
-        N.count_launch(2)
+        N.count_launch(1)
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty((n_aug, x_aug.shape[1]), dtype=torch.bfloat16, device=dev)

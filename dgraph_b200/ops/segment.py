@@ -159,7 +159,8 @@ class _GraphConvAgg(Function):
             dQ = torch.empty((kp.num_aug, H), dtype=torch.bfloat16, device=g.device)
             N.check(N.lib().dgb_seg_masked_sum(
                 N.ptr(kp.colptr), N.ptr(kp.row), N.ptr(kp.csc_to_csr), N.ptr(mask), N.i64(kp.num_aug), N.i32(H), N.ptr(g),
-                N.i64(H), N.ptr(dQ), N.i64(H), N.stream()), "dgb_seg_masked_sum")
+                N.i64(H), N.ptr(dQ), N.i64(H), N.ptr(None), N.i64(0), N.ptr(None), N.i64(0), N.i64(0), N.stream()),
+                "dgb_seg_masked_sum")
             N.count_launch()
         elif ctx.needs_input_grad[1]:
             dQ = torch.empty((kp.num_aug, H), dtype=torch.bfloat16, device=g.device)

@@ -33,6 +33,12 @@ def _make_engine(backend: str, **kwargs):
         return LocalEngine()
     use_cuda = torch.cuda.is_available()
     forced = os.environ.get("DGRAPH_B200_ENGINE", "").lower()
+    rpg = kwargs.get("ranks_per_graph", -1)
+    if rpg not in (-1, None):
+        import torch.distributed as dist
+
+        if dist.is_available() and dist.is_initialized() and 0 < int(rpg) < dist.get_world_size():
+            return _make_hybrid_engine(int(rpg), use_cuda, **kwargs)
     if backend == "gloo" or not use_cuda:
         return TorchDistEngine(dist_backend="gloo", **kwargs)
     if backend == "torch" or forced == "torch":
@@ -40,6 +46,28 @@ def _make_engine(backend: str, **kwargs):
     from dgraph_b200.parallel.peer_engine import PeerMemoryEngine
 
     return PeerMemoryEngine(**kwargs)
+
+
+def _make_hybrid_engine(rpg: int, use_cuda: bool, **kwargs):
+    """Hybrid data-parallel x graph-partition layout (SURVEY §2.5): the world is cut into ``world / ranks_per_graph`` replicas;
+    each replica partitions one graph over its ``ranks_per_graph`` ranks.  Halo exchanges / plan collectives run inside the
+    replica's process group, gradient all-reduces over the whole world.  (The reference only does the rank arithmetic,
+    ``NCCLBackendEngine.py:56-64``; no sub-groups are ever created there.)"""
+    import torch.distributed as dist
+
+    from dgraph_b200.parallel.collective_engine import TorchDistEngine
+
+    world, rank = dist.get_world_size(), dist.get_rank()
+    assert world % rpg == 0, "world size must be a multiple of ranks_per_graph"
+    mine = None
+    for g in range(world // rpg):  # every rank creates every group, in the same order
+        grp = dist.new_group(list(range(g * rpg, (g + 1) * rpg)))
+        if rank // rpg == g:
+            mine = grp
+    kw = {k: v for k, v in kwargs.items() if k != "ranks_per_graph"}
+    eng = TorchDistEngine(dist_backend="nccl" if use_cuda else "gloo", group=mine, ranks_per_graph=rpg, **kw)
+    eng.replica_id, eng.num_replicas, eng.global_rank, eng.global_world = rank // rpg, world // rpg, rank, world
+    return eng
 
 
 class Communicator(CommunicatorBase):
@@ -105,9 +133,26 @@ class Communicator(CommunicatorBase):
         return self.__backend_engine.put(send_buffer, recv_buffer, send_offsets, recv_offsets,
                                          remote_offsets=remote_offsets)
 
-    def all_reduce(self, tensor: torch.Tensor, op: str = "sum") -> torch.Tensor:
-        """In-place all-reduce across the communicator (used by distributed BatchNorm / loss normalisation)."""
-        return self.__backend_engine.all_reduce(tensor, op)
+    def all_reduce(self, tensor: torch.Tensor, op: str = "sum", scope: str = "graph") -> torch.Tensor:
+        """In-place all-reduce.  ``scope="graph"``: the ranks that share one graph (distributed BatchNorm, loss normalisation);
+        ``scope="world"``: every rank (data-parallel gradient sums in the hybrid DP x graph-partition layout)."""
+        eng = self.__backend_engine
+        if scope == "world" and getattr(eng, "num_replicas", 1) > 1:
+            import torch.distributed as dist
+
+            dist.all_reduce(tensor, op={"sum": dist.ReduceOp.SUM, "max": dist.ReduceOp.MAX, "min": dist.ReduceOp.MIN}[op])
+            return tensor
+        return eng.all_reduce(tensor, op)
+
+    def get_global_world_size(self) -> int:
+        return getattr(self.__backend_engine, "global_world", self.get_world_size())
+
+    def get_replica_id(self) -> int:
+        """Index of the graph replica this rank works on (0 when the whole world shares one graph)."""
+        return getattr(self.__backend_engine, "replica_id", 0)
+
+    def get_num_replicas(self) -> int:
+        return getattr(self.__backend_engine, "num_replicas", 1)
 
     def barrier(self) -> None:
         self.__check_init()

@@ -58,6 +58,10 @@ class FusedAdam(torch.optim.Optimizer):
             o += s
         self._params = ps
 
+    def _global_world(self) -> int:
+        c = self.comm
+        return c.get_global_world_size() if hasattr(c, "get_global_world_size") else c.get_world_size()
+
     # gradients live in the flat buffer: zeroing is one memset and the views stay attached
     def zero_grad(self, set_to_none: bool = False):
         self.flat_g.zero_()
@@ -67,8 +71,8 @@ class FusedAdam(torch.optim.Optimizer):
 
     def sync_grads(self):
         """Data-parallel all-reduce of the flat gradient (SUM); averaging is folded into the Adam kernel."""
-        if self.comm is not None and self.comm.get_world_size() > 1:
-            self.comm.all_reduce(self.flat_g)
+        if self.comm is not None and self._global_world() > 1:
+            self.comm.all_reduce(self.flat_g, scope="world") if hasattr(self.comm, "get_num_replicas") else self.comm.all_reduce(self.flat_g)
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -79,7 +83,7 @@ class FusedAdam(torch.optim.Optimizer):
                 p.grad = self.flat_g[o:o + n].view(p.shape)
         self._step += 1
         g = self.param_groups[0]
-        W = self.comm.get_world_size() if (self.comm is not None and self.grad_average) else 1
+        W = self._global_world() if (self.comm is not None and self.grad_average) else 1
         lr, (b1, b2), eps, wd = g["lr"], g["betas"], g["eps"], g["weight_decay"]
         if self._peer is not None:  # ONE kernel: sum of all ranks' gradients over NVLink + Adam
             self._peer.adam_allreduce(self.flat_p, self._g_off, self.flat_m, self.flat_v, self.flat_p.numel(), lr, b1,

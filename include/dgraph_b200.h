@@ -51,6 +51,45 @@ int dgb_gather_gemm_bf16(int n_seg, const void* const* seg_base, const int64_t* 
                          const int* seg_k, const void* W, int64_t ldw, void* C, int64_t ldc, int M, int N, const float* bias,
                          int act, int out_f32, void* stream);
 
+/* Gather-GEMM whose gathered rows may live on other GPUs: rows j >= seg_nlocal[s] of segment s are read from
+ * seg_peer[s][halo_owner[s][j - nlocal]] + halo_row[s][j - nlocal] * seg_ld[s] by the producer warps (NVLink loads inside the
+ * tcgen05 GEMM).  Reference: NVSHMEM gather + index + cat + nn.Linear (experiments/GraphCast/layers.py:205-216). */
+int dgb_gather_gemm_peer_bf16(int n_seg, const void* const* seg_base, const int64_t* seg_ld, const int* const* seg_idx,
+                              const int* seg_k, const void* const* const* seg_peer, const int* const* seg_halo_owner,
+                              const int* const* seg_halo_row, const int64_t* seg_nlocal, const void* W, int64_t ldw, void* C,
+                              int64_t ldc, int M, int N, const float* bias, int act, int out_f32, void* stream);
+/* Split-K weight gradient dW[N1,N2] (fp32) += G[M,N1]^T @ X'[M,N2], X' = X or X[x_idx] (rows gathered inside the kernel);
+ * csrc/gemm_wgrad_tcgen05.cu.  Reference: autograd of nn.Linear -> cuBLAS. */
+int dgb_gemm_wgrad_bf16(const void* G, int64_t ldg, const void* X, int64_t ldx, float* dW, int64_t ldw, int64_t M, int N1,
+                        int N2, const int* x_idx, void* stream);
+
+/* ---- segment softmax + attention-weighted aggregation (csrc/softmax_ops.cu) ------------------------------------------
+ * Reference: GAT attention chain, experiments/OGB-LSC/RGAT.py:147-165,191-202 (5 all-to-alls per layer). */
+int dgb_seg_softmax_fwd(const int* rowptr, const int* col, int64_t n_dst, int C, float slope, const float* s_i, const float* s_j,
+                        const void* h_j, int64_t ld_h, void* out, int64_t ld_out, float* row_max, float* row_den, void* stream);
+int dgb_seg_softmax_bwd(const int* rowptr, const int* col, const int* colptr, const int* row, const int* slot_map, int64_t n_dst,
+                        int64_t n_src, int C, float slope, const float* s_i, const float* s_j, const void* h_j, int64_t ld_h,
+                        const void* out, int64_t ld_out, const float* row_max, const float* row_den, const void* g, int64_t ld_g,
+                        float* dscore, float* ds_i, float* ds_j, void* dh, int64_t ld_dh, void* stream);
+
+/* ---- fused LayerNorm (+ residual) and SiLU gradient (csrc/norm_ops.cu) ------------------------------------------------
+ * Reference: nn.LayerNorm / nn.SiLU / residual adds of MeshGraphMLP and the mesh blocks (experiments/GraphCast/layers.py:52-63,
+ * 142, 215).  Only the first C_valid columns are normalised; columns [C_valid, C) are zero padding. */
+int dgb_layernorm_fwd(const void* z, int64_t ld_z, const void* res, int64_t ld_r, const float* gamma, const float* beta, void* y,
+                      int64_t ld_y, float* mean, float* rstd, int64_t M, int C, int C_valid, float eps, void* stream);
+int64_t dgb_layernorm_bwd_scratch_bytes(int64_t M, int C);
+int dgb_layernorm_bwd(const void* gy, int64_t ld_g, const void* z, int64_t ld_z, const float* gamma, const float* mean,
+                      const float* rstd, void* dz, int64_t ld_dz, float* scratch, float* dgamma_dbeta, int64_t M, int C,
+                      int C_valid, void* stream);
+int dgb_silu_bwd(const void* g, const void* pre, void* out, int64_t n, void* stream);
+
+/* ---- rank-local masked row copy / accumulate (csrc/rank_local.cu) -----------------------------------------------------
+ * Reference: torch_local.{local_masked_gather, local_masked_scatter, local_masked_scatter_gather,
+ * local_masked_scatter_add_gather} (DGraph/distributed/csrc/torch_local_kernels.cu:28-254).  mode 0 = set, 1 = add. */
+int dgb_rows_indexed(void* out, int64_t ld_out_bytes, const void* src, int64_t ld_src_bytes, const int64_t* dst_idx,
+                     const int64_t* src_idx, const int64_t* placement, int rank, int64_t n, int row_bytes, int elem_bytes,
+                     int mode, void* stream);
+
 /* ---- column reductions (csrc/reduce_ops.cu) ---------------------------------------------------------------------------
  * Reference: statistics of DistributedBatchNorm1D (experiments/OGB-LSC/distributed_layers.py:22-74); ATen sum(0) for bias
  * gradients.  Two-phase and deterministic; the caller provides the scratch buffer. */
@@ -85,6 +124,9 @@ int dgb_halo_pull(void* dst, int64_t ld_dst_bytes, int64_t n_halo, int row_bytes
                   int64_t ld_peer_bytes, const int* halo_owner, const int* halo_row, int64_t rot, void* stream);
 int dgb_gather_rows_peer(void* out, int64_t ld_out_bytes, int64_t n, int row_bytes, const void* const* peer_base,
                          int64_t ld_peer_bytes, const int* owner, const int* row, void* stream);
+/* peer[owner[i]][row[i], :] += src[i, :] (fp32 vector reductions on NVLink-mapped memory): NVSHMEMP2P::dist_put */
+int dgb_scatter_add_rows_peer_f32(const float* src, int64_t ld_src, int64_t n, int F, void* const* peer_base, int64_t ld_peer,
+                                  const int* owner, const int* row, void* stream);
 int dgb_halo_grad_reduce(void* gx, int64_t ld_gx, const void* g_local, int64_t ld_gl, int H, int64_t n_bnd,
                          const int* bnd_row, const int* bnd_ptr, const int* src_rank, const int* src_row,
                          const void* const* peer_base, int64_t ld_peer, void* stream);

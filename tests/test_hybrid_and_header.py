@@ -1,0 +1,78 @@
+"""Hybrid DP x graph-partition layout over gloo (4 processes, ranks_per_graph=2); C header / source sync; sampler."""
+import glob
+import os
+import re
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from tests._graphs import random_graph, partition
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_header_declares_every_entry_point():
+    src = set()
+    for f in glob.glob(os.path.join(ROOT, "csrc", "*.cu")):
+        src |= set(re.findall(r"^DGB_API\s+[\w\s\*]+?\b(dgb_\w+)\s*\(", open(f).read(), flags=re.M))
+    hdr = set(re.findall(r"\b(dgb_\w+)\s*\(", open(os.path.join(ROOT, "include", "dgraph_b200.h")).read()))
+    assert src and not (src - hdr), f"missing from include/dgraph_b200.h: {sorted(src - hdr)}"
+
+
+def test_sampler_gives_replicas_disjoint_samples():
+    from dgraph_b200.utils.dist_utils import CommAwareDistributedSampler, SingleProcessDummyCommunicator
+
+    ds = list(range(10))
+    a = list(CommAwareDistributedSampler(ds, num_replicas=2, replica_id=0, shuffle=False))
+    b = list(CommAwareDistributedSampler(ds, num_replicas=2, replica_id=1, shuffle=False))
+    assert a == [0, 2, 4, 6, 8] and b == [1, 3, 5, 7, 9]
+    c = SingleProcessDummyCommunicator()
+    assert c.get_world_size() == 1 and c.get_num_replicas() == 1
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, W, port, e, xg, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(W))
+    dist.init_process_group("gloo", rank=rank, world_size=W)
+    from dgraph_b200 import Communicator
+    from dgraph_b200.parallel import HaloExchange, build_communication_pattern
+
+    Communicator._is_initialized = False
+    comm = Communicator.init_process_group("nccl", ranks_per_graph=2)
+    ok = comm.get_world_size() == 2 and comm.get_global_world_size() == 4 and comm.get_num_replicas() == 2
+    ok = ok and comm.get_replica_id() == rank // 2 and comm.get_rank() == rank % 2
+    part = partition(xg.shape[0], 2, "random")
+    pat = build_communication_pattern(e, part, comm.get_rank(), 2)
+    scale = float(comm.get_replica_id() + 1)  # every replica works on its own sample
+    x = xg[pat.local_vertices_global] * scale
+    halo = HaloExchange(comm)(x, pat)
+    ok = ok and torch.allclose(halo, xg[pat.halo_vertices_global] * scale)
+    t = torch.ones(1, dtype=torch.float64)
+    comm.all_reduce(t)  # graph scope: 2 ranks
+    u = torch.ones(1, dtype=torch.float64)
+    comm.all_reduce(u, scope="world")
+    ok = ok and float(t) == 2.0 and float(u) == 4.0
+    ret[rank] = bool(ok)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(240)
+def test_hybrid_dp_graph_partition_gloo():
+    W = 4
+    e = random_graph(40, 5, seed=1, symmetric=False)
+    xg = torch.randn(40, 3, dtype=torch.float64)
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker, args=(W, _free_port(), e, xg, ret), nprocs=W, join=True)
+    assert all(ret[r] for r in range(W))

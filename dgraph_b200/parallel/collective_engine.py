@@ -12,6 +12,8 @@ from __future__ import annotations
 import threading
 from typing import Dict, List, Optional, Sequence, Tuple
 
+import weakref
+
 import torch
 import torch.distributed as dist
 
@@ -103,9 +105,14 @@ class CollectiveEngine(BackendEngine):
         else:
             assert output_size is not None, "scatter needs output_size (rows of the local output)"
             n_rows_local = int(output_size)
-        key = (kind, idx.data_ptr(), idx.numel(), None if rank_mappings is None else rank_mappings.data_ptr(), n_rows_local)
-        if key in self._legacy_plans:
-            return self._legacy_plans[key]
+        # Keyed on tensor identity + in-place version (not on the data pointer, which the allocator recycles): a hit needs
+        # the very same index tensor object, unmodified, so every rank of an SPMD program hits or misses together.
+        key = (kind, id(idx), idx._version, None if rank_mappings is None else (id(rank_mappings), rank_mappings._version),
+               n_rows_local)
+        hit = self._legacy_plans.get(key)
+        if hit is not None and hit[0]() is idx and (rank_mappings is None or hit[1]() is rank_mappings):
+            return hit[2]
+        idx_in, rm_in = idx, rank_mappings
         if rank_mappings is None:
             owner = torch.div(idx, n_rows_local, rounding_mode="floor").clamp_(max=W - 1)
             mine = torch.ones_like(idx, dtype=torch.bool)
@@ -118,7 +125,11 @@ class CollectiveEngine(BackendEngine):
         if not bool(mine.all()):
             idx, owner = idx[mine], owner[mine]
         plan = plan_from_requests(r, W, owner, idx % n_rows_local, n_rows_local, self.exchange_ids)
-        self._legacy_plans[key] = plan
+        if len(self._legacy_plans) >= 256:  # drop entries whose tensors died; bounded either way
+            self._legacy_plans = {k: v for k, v in self._legacy_plans.items() if v[0]() is not None}
+            if len(self._legacy_plans) >= 256:
+                self._legacy_plans.clear()
+        self._legacy_plans[key] = (weakref.ref(idx_in), None if rm_in is None else weakref.ref(rm_in), plan)
         return plan
 
 

@@ -97,7 +97,15 @@ def f32(v) -> ctypes.c_float:
     return ctypes.c_float(float(v))
 
 
+# Observers called as ``hook(what)`` after every successful native launch (tracing: ``utils/tracing.KernelTrace``;
+# sync-checking: ``utils/debug.enable_sync_checks``).  Empty on the hot path.
+_post_launch_hooks: list = []
+
+
 def check(code: int, what: str):
+    if code == 0 and _post_launch_hooks:
+        for h in tuple(_post_launch_hooks):
+            h(what)
     if code != 0:
         name = ""
         try:

@@ -87,7 +87,7 @@ class GraphKernelPlan:
         nl = pattern.num_neighbor_local_vertices
         if nl is None:
             nl = pattern.num_local_vertices
-        return GraphKernelPlan.from_edges(
+        plan = GraphKernelPlan.from_edges(
             pattern.local_edge_list,
             pattern.num_local_vertices,
             nl + pattern.num_halo_vertices,
@@ -97,3 +97,9 @@ class GraphKernelPlan:
             halo_remote_row=pattern.halo_remote_row,
             send_local_idx=pattern.send_local_idx,
         )
+        from dgraph_b200.utils import debug
+
+        if debug.validate_enabled():  # DGRAPH_B200_VALIDATE=1: range-check every index the kernels will dereference
+            debug.validate_pattern(pattern)
+            debug.validate_kernel_plan(plan)
+        return plan

@@ -9,6 +9,7 @@ by default.  On CPU tensors it falls back to ``time.perf_counter``.
 from __future__ import annotations
 
 import json
+import os
 import time
 from typing import Dict, List, Optional
 
@@ -53,6 +54,8 @@ class TimingReport:
     def start(name: str):
         TimingReport._barrier()
         if torch.cuda.is_available():
+            if os.environ.get("DGRAPH_B200_NVTX", "0") == "1":
+                torch.cuda.nvtx.range_push(name)
             ev = torch.cuda.Event(enable_timing=True)
             ev.record()
             TimingReport._open[name] = ev
@@ -67,6 +70,8 @@ class TimingReport:
         if torch.cuda.is_available():
             ev = torch.cuda.Event(enable_timing=True)
             ev.record()
+            if os.environ.get("DGRAPH_B200_NVTX", "0") == "1":
+                torch.cuda.nvtx.range_pop()
             torch.cuda.synchronize()
             ms = st.elapsed_time(ev)
         else:

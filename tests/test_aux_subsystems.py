@@ -1,0 +1,78 @@
+"""Tracing hooks, plan validators, watchdog / heartbeat / health check (all CPU)."""
+import json
+import time
+
+import pytest
+import torch
+
+from dgraph_b200.ops import _native as N
+from dgraph_b200.parallel import build_communication_pattern
+from dgraph_b200.parallel.kernel_plan import GraphKernelPlan
+from dgraph_b200.utils import debug, tracing, watchdog
+from tests._graphs import random_graph, partition
+
+
+def test_kernel_trace_records_launch_hooks(tmp_path):
+    with tracing.KernelTrace() as tr:
+        N.check(0, "dgb_fake_a")
+        N.check(0, "dgb_fake_b")
+        N.check(0, "dgb_fake_a")
+    assert [r["name"] for r in tr.records] == ["dgb_fake_a", "dgb_fake_b", "dgb_fake_a"]
+    assert tr.summary()["dgb_fake_a"]["launches"] == 2
+    assert not N._post_launch_hooks
+    p = tmp_path / "t.json"
+    tr.to_chrome_trace(str(p))
+    assert len(json.load(open(p))["traceEvents"]) == 3
+    with tracing.nvtx_range("x"):
+        pass
+    assert "aten::add" in tracing.profile_step(lambda: torch.ones(4) + 1)
+
+
+def test_plan_validators_accept_good_and_reject_corrupt():
+    e = random_graph(30, 4, seed=3, symmetric=True)
+    part = partition(30, 3, "random")
+    for r in range(3):
+        pat = build_communication_pattern(e, part, r, 3)
+        debug.validate_pattern(pat)
+        kp = pat.kernel_plan("cpu")
+        debug.validate_kernel_plan(kp)
+    bad = GraphKernelPlan.from_edges(torch.tensor([[0, 1], [1, 0], [1, 2]]), 2, 3, device="cpu")
+    debug.validate_kernel_plan(bad)
+    bad.col = bad.col.clone()
+    bad.col[0] = 7
+    with pytest.raises(AssertionError, match="csr.col"):
+        debug.validate_kernel_plan(bad)
+    pat.send_local_idx = pat.send_local_idx.clone()
+    if pat.send_local_idx.numel():
+        pat.send_local_idx[0] = pat.num_local_vertices + 5
+        with pytest.raises(AssertionError):
+            debug.validate_pattern(pat)
+    with pytest.raises(FloatingPointError, match="w"):
+        debug.check_finite([("w", torch.tensor([1.0, float("nan")])), ("v", torch.ones(2))])
+
+
+def test_watchdog_fires_only_without_beats():
+    fired = []
+    with watchdog.StepWatchdog(0.3, on_timeout=fired.append, poll_s=0.05) as wd:
+        for _ in range(8):
+            time.sleep(0.05)
+            wd.beat()
+        assert not fired
+        time.sleep(0.6)
+    assert fired and wd.fired
+
+
+def test_heartbeat_and_health_check(tmp_path, monkeypatch):
+    hb0, hb1 = watchdog.Heartbeat(str(tmp_path), 0, 2), watchdog.Heartbeat(str(tmp_path), 1, 2)
+    hb0.beat(5)
+    assert hb0.stale(60.0) == [1]
+    hb1.beat(5)
+    assert hb0.stale(60.0) == [] and hb1.read(0)[0] == 5
+    from dgraph_b200.utils.dist_utils import SingleProcessDummyCommunicator
+
+    comm = SingleProcessDummyCommunicator()
+    assert watchdog.health_check(comm, torch.tensor(1.0))
+    assert not watchdog.health_check(comm, torch.tensor(float("inf")))
+    monkeypatch.setenv("DGRAPH_B200_FAULT_INJECT", "nan:rank=0:step=2")
+    assert torch.isfinite(watchdog.inject_fault(0, 1, torch.tensor(1.0)))
+    assert torch.isnan(watchdog.inject_fault(0, 2, torch.tensor(1.0)))

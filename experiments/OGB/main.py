@@ -18,7 +18,12 @@ import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
 from dgraph_b200.utils.cli import run_cli  # noqa: E402
+from dgraph_b200.utils.tracing import KernelTrace  # noqa: E402
+from dgraph_b200.utils.watchdog import StepWatchdog, health_check, inject_fault  # noqa: E402
 from utils import calculate_accuracy, dist_print_ephemeral, make_experiment_log, safe_plot, write_experiment_log  # noqa: E402
+
+
+_OPTS = {"watchdog_s": 0.0, "health_every": 0, "trace": ""}
 
 
 def _run_experiment(dataset, comm, lr, epochs, log_prefix, hidden_dims, num_classes, device, rank, save="", resume=""):
@@ -44,8 +49,14 @@ def _run_experiment(dataset, comm, lr, epochs, log_prefix, hidden_dims, num_clas
     for n in ("training_loss", "validation_loss", "validation_accuracy"):
         make_experiment_log(f"{log_prefix}_{n}.log", rank)
     best = -1.0
+    wd = StepWatchdog(_OPTS["watchdog_s"]).start() if _OPTS["watchdog_s"] > 0 else None
     for epoch in range(start, start + epochs):
         model.train()
+        if wd is not None:
+            wd.beat()
+        trace = KernelTrace(cuda_events=True) if (_OPTS["trace"] and epoch == start + 1 and rank == 0) else None
+        if trace is not None:
+            trace.__enter__()
         comm.barrier()
         if device.type == "cuda":
             torch.cuda.synchronize()
@@ -63,6 +74,15 @@ def _run_experiment(dataset, comm, lr, epochs, log_prefix, hidden_dims, num_clas
             e1.record()
             torch.cuda.synchronize()
             times.append(e0.elapsed_time(e1))
+        if trace is not None:
+            trace.__exit__(None, None, None)
+            trace.to_chrome_trace(_OPTS["trace"])
+            print("\n" + "\n".join(f"{k:40s} x{v['launches']:3d} {v['gpu_ms']:8.3f} ms" for k, v in trace.summary().items()))
+        loss = inject_fault(rank, epoch, loss)
+        if _OPTS["health_every"] > 0 and (epoch + 1) % _OPTS["health_every"] == 0 and not health_check(comm, loss):
+            if save:
+                save_checkpoint(save + ".emergency", model, opt, step=epoch, rank=rank)
+            raise RuntimeError(f"health check failed at epoch {epoch} (non-finite loss or barrier timeout on some rank)")
         tr_loss.append(float(loss.detach()))
         dist_print_ephemeral(f"Epoch {epoch:4d} | loss: {tr_loss[-1]:.4f} | {times[-1] if times else 0:.1f} ms", rank)
         write_experiment_log(str(tr_loss[-1]), f"{log_prefix}_training_loss.log", rank)
@@ -77,6 +97,8 @@ def _run_experiment(dataset, comm, lr, epochs, log_prefix, hidden_dims, num_clas
         if save and va_acc[-1] > best:
             best = va_acc[-1]
             save_checkpoint(save, model, opt, step=epoch + 1, rank=rank)
+    if wd is not None:
+        wd.stop()
     model.eval()
     with torch.no_grad():
         to = model(x, pat)[masks["test_mask"]].float()
@@ -99,7 +121,12 @@ def _run_experiment(dataset, comm, lr, epochs, log_prefix, hidden_dims, num_clas
 
 def main(backend: str = "nccl", dataset: str = "arxiv", epochs: int = 10, lr: float = 0.001, runs: int = 1,
          hidden_dims: int = 256, log_dir: str = "logs", node_rank_placement_file: str = "", root_dir: str = "data",
-         scale: float = 1.0, save: str = "", resume: str = "", timing_report: bool = True):
+         scale: float = 1.0, save: str = "", resume: str = "", timing_report: bool = True, watchdog_s: float = 0.0,
+         health_every: int = 0, trace: str = ""):
+    """Reference flags (``experiments/OGB/main.py:235-362``) plus: ``scale`` (synthetic graph size), ``save`` / ``resume``
+    (best-validation checkpoint), ``watchdog_s`` (abort the rank after that many seconds without an epoch), ``health_every``
+    (all-rank NaN / timeout check every N epochs), ``trace`` (write a chrome trace of epoch 1's native kernel launches)."""
+    _OPTS.update(watchdog_s=float(watchdog_s), health_every=int(health_every), trace=trace)
     from dgraph_b200.data.ogbn_datasets import DGraphOGBDataset
     from dgraph_b200.utils import TimingReport
 

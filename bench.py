@@ -44,6 +44,8 @@ def parse_args():
     ap.add_argument("--lr", type=float, default=1e-3)
     ap.add_argument("--engine", default=None, help="override DGRAPH_B200_ENGINE (torch | peer)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cuda-graph", action="store_true",
+                    help="1 GPU only: capture the whole step (fwd+loss+bwd+Adam) in a CUDA graph and replay it")
     ap.add_argument("--cpu", action="store_true", help="CPU/gloo plumbing run (tiny graphs only)")
     return ap.parse_args()
 
@@ -163,16 +165,29 @@ def run_ours(args):
 
     torch.manual_seed(0)
     model = CommAwareGCN(F_in, args.hidden, g.num_classes, HaloExchange(comm), comm, compute_dtype=cdt).to(dev)
-    opt = FusedAdam(model.parameters(), lr=args.lr, comm=comm)
+    use_graph = bool(args.cuda_graph) and world == 1 and not args.cpu
+    opt = FusedAdam(model.parameters(), lr=args.lr, comm=comm, capturable=use_graph)
     loss_fn = torch.nn.CrossEntropyLoss()
+
+    def forward_loss(x_dev, y_dev):
+        out = model(x_dev, pat)
+        return loss_fn(out.index_select(0, train_idx).float(), y_dev.index_select(0, train_idx))
 
     def step(x_dev, y_dev):
         opt.zero_grad()
-        out = model(x_dev, pat)
-        loss = loss_fn(out.index_select(0, train_idx).float(), y_dev.index_select(0, train_idx))
+        loss = forward_loss(x_dev, y_dev)
         loss.backward()
         opt.step()
         return loss
+
+    if use_graph:  # same work per step, replayed with one cudaGraphLaunch (utils/cuda_graph.py)
+        from dgraph_b200.utils.cuda_graph import GraphedTrainStep
+
+        eager_step = step
+        graphed = GraphedTrainStep(forward_loss, opt, (xh.to(dev), yh.to(dev)), warmup=2)
+
+        def step(x_dev, y_dev):  # noqa: F811
+            return graphed(x_dev, y_dev).clone()
 
     def sync():
         if world > 1:
@@ -270,7 +285,7 @@ def run_ours(args):
                        "partition": f"contiguous blocks, cut_fraction={args.cut}", "hidden": args.hidden,
                        "l2": "inputs larger than L2 (edge structure + features >> 126 MB)",
                        "engine": type(comm.engine).__name__, "scale": args.scale,
-                       "gemm": os.environ.get("DGRAPH_B200_GEMM", "tcgen05")},
+                       "gemm": os.environ.get("DGRAPH_B200_GEMM", "tcgen05"), "cuda_graph": use_graph},
             "e2e": e2e, "gpu_launches": n_launch, "clocks": clocks, "final_loss": final_loss,
             "loss_first": float(losses[0].detach()),
         }

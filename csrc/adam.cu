@@ -14,9 +14,15 @@ struct AdamArgs {
 
 __global__ void __launch_bounds__(256) adam_flat_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                         float* __restrict__ m, float* __restrict__ v,
-                                                        __nv_bfloat16* __restrict__ p_bf16, int64_t n, AdamArgs a) {
+                                                        __nv_bfloat16* __restrict__ p_bf16, int64_t n, AdamArgs a,
+                                                        const float* __restrict__ dev_state) {
   const int64_t i4 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i4 >= n) return;
+  if (dev_state) {  // capturable mode: learning rate and bias corrections live in device memory (see adam_tick_kernel)
+    a.lr = dev_state[0];
+    a.bias_c1 = dev_state[1];
+    a.bias_c2 = dev_state[2];
+  }
   const float inv_c1 = 1.f / a.bias_c1;
   const float inv_sqrt_c2 = rsqrtf(a.bias_c2);
   if (i4 + 4 <= n) {
@@ -56,6 +62,15 @@ __global__ void __launch_bounds__(256) adam_flat_kernel(float* __restrict__ p, c
   }
 }
 
+// Capturable mode: advances the device-resident step counter and refreshes the bias corrections, so a CUDA graph that
+// contains the optimizer step replays with the right `t` (kernel arguments are frozen at capture time).
+__global__ void adam_tick_kernel(int* __restrict__ step, float* __restrict__ dev_state, float beta1, float beta2) {
+  const int t = *step + 1;
+  *step = t;
+  dev_state[1] = 1.f - powf(beta1, (float)t);
+  dev_state[2] = 1.f - powf(beta2, (float)t);
+}
+
 }  // namespace dgb
 
 // One Adam step over flat fp32 arrays of n elements (16-byte aligned).  `step` >= 1.  p_bf16 may be null.
@@ -67,7 +82,25 @@ DGB_API int dgb_adam_flat(float* p, const float* g, float* m, float* v, void* p_
                   1.f - powf(beta2, (float)step)};
   const int64_t threads = (n + 3) / 4;
   dgb::adam_flat_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      p, g, m, v, (__nv_bfloat16*)p_bf16, n, a);
+      p, g, m, v, (__nv_bfloat16*)p_bf16, n, a, nullptr);
+  DGB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Same step with the step counter (`step_dev`, int32) and `dev_state` = {lr, 1-beta1^t, 1-beta2^t, unused} in device memory:
+// two launches (tick + update), no host-side value that changes from step to step -> safe to capture once and replay.
+// The caller writes dev_state[0] (learning rate) with a device-side fill outside the captured region.
+DGB_API int dgb_adam_flat_capturable(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n, float beta1,
+                                     float beta2, float eps, float weight_decay, float grad_scale, int* step_dev,
+                                     float* dev_state, void* stream) {
+  if (n == 0) return 0;
+  if (!step_dev || !dev_state) return (int)cudaErrorInvalidValue;
+  dgb::adam_tick_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_dev, dev_state, beta1, beta2);
+  DGB_CHECK_LAUNCH();
+  dgb::AdamArgs a{0.f, beta1, beta2, eps, weight_decay, grad_scale, 1.f, 1.f};
+  const int64_t threads = (n + 3) / 4;
+  dgb::adam_flat_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      p, g, m, v, (__nv_bfloat16*)p_bf16, n, a, dev_state);
   DGB_CHECK_LAUNCH();
   return 0;
 }

@@ -22,13 +22,14 @@ from dgraph_b200.ops import _native as N
 
 class FusedAdam(torch.optim.Optimizer):
     def __init__(self, params: Iterable, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
-                 weight_decay: float = 0.0, comm=None, grad_average: bool = True):
+                 weight_decay: float = 0.0, comm=None, grad_average: bool = True, capturable: bool = False):
         defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
         super().__init__(params, defaults)
         assert len(self.param_groups) == 1, "FusedAdam keeps one flat arena (single param group)"
         self.comm = comm
         self.grad_average = grad_average
         self._step = 0
+        self.capturable = capturable  # step counter / lr in device memory: the step can live inside a CUDA graph
         ps = [p for p in self.param_groups[0]["params"] if p.requires_grad]
         assert all(p.dtype == torch.float32 for p in ps), "master parameters are fp32"
         dev = ps[0].device
@@ -47,6 +48,12 @@ class FusedAdam(torch.optim.Optimizer):
             self.flat_g = torch.zeros(total, dtype=torch.float32, device=dev)
         self.flat_m = torch.zeros(total, dtype=torch.float32, device=dev)
         self.flat_v = torch.zeros(total, dtype=torch.float32, device=dev)
+        if capturable:
+            assert dev.type == "cuda", "capturable FusedAdam is a CUDA-graph feature"
+            self._dev_step = torch.zeros(1, dtype=torch.int32, device=dev)
+            self._dev_state = torch.zeros(4, dtype=torch.float32, device=dev)
+            self._dev_lr = None
+            self.sync_hyper()
         self._views = []
         o = 0
         for p, s in zip(ps, sizes):
@@ -57,6 +64,14 @@ class FusedAdam(torch.optim.Optimizer):
             self._views.append((p, o, n))
             o += s
         self._params = ps
+
+    def sync_hyper(self):
+        """Capturable mode: push the (possibly scheduler-updated) learning rate to device memory.  Call it outside the
+        captured region, before each replay; a no-op when the value did not change."""
+        lr = float(self.param_groups[0]["lr"])
+        if self._dev_lr != lr:
+            self._dev_state[0:1].fill_(lr)
+            self._dev_lr = lr
 
     def _global_world(self) -> int:
         c = self.comm
@@ -85,6 +100,18 @@ class FusedAdam(torch.optim.Optimizer):
         g = self.param_groups[0]
         W = self._global_world() if (self.comm is not None and self.grad_average) else 1
         lr, (b1, b2), eps, wd = g["lr"], g["betas"], g["eps"], g["weight_decay"]
+        if self.capturable:
+            assert self._peer is None, "capturable mode is single-engine (no peer-memory fused all-reduce yet)"
+            self.sync_grads()
+            if not torch.cuda.is_current_stream_capturing():
+                self.sync_hyper()
+            N.check(N.lib().dgb_adam_flat_capturable(N.ptr(self.flat_p), N.ptr(self.flat_g), N.ptr(self.flat_m),
+                                                     N.ptr(self.flat_v), N.ptr(None), N.i64(self.flat_p.numel()),
+                                                     N.f32(b1), N.f32(b2), N.f32(eps), N.f32(wd), N.f32(1.0 / W),
+                                                     N.ptr(self._dev_step), N.ptr(self._dev_state), N.stream()),
+                    "dgb_adam_flat_capturable")
+            N.count_launch(2)
+            return loss
         if self._peer is not None:  # ONE kernel: sum of all ranks' gradients over NVLink + Adam
             self._peer.adam_allreduce(self.flat_p, self._g_off, self.flat_m, self.flat_v, self.flat_p.numel(), lr, b1,
                                       b2, eps, wd, 1.0 / W, self._step)
@@ -107,6 +134,8 @@ class FusedAdam(torch.optim.Optimizer):
     # -- torch.optim.Adam-compatible checkpoint format ---------------------------------------------
     def state_dict(self):
         state = {}
+        if self.capturable:  # the device counter is the truth once graphs replay without the host
+            self._step = int(self._dev_step.item())
         for i, (p, o, n) in enumerate(self._views):
             state[i] = {"step": torch.tensor(float(self._step)),
                         "exp_avg": self.flat_m[o:o + n].view(p.shape).clone(),
@@ -126,3 +155,6 @@ class FusedAdam(torch.optim.Optimizer):
         for k, v in sd["param_groups"][0].items():
             if k != "params":
                 self.param_groups[0][k] = v
+        if self.capturable:
+            self._dev_step.fill_(self._step)
+            self.sync_hyper()

@@ -108,6 +108,12 @@ int dgb_colsum_bf16_noalloc(const void* x, int64_t ld, int64_t M, int N, int wit
 int dgb_adam_flat(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n, float lr, float beta1, float beta2,
                   float eps, float weight_decay, float grad_scale, int step, void* stream);
 
+/* Capturable Adam: step counter (int32) and {lr, 1-beta1^t, 1-beta2^t, -} (4 floats) live in device memory, so the two
+ * launches (tick + update) can sit inside a CUDA graph that is replayed every step (reference: torch.optim.Adam only). */
+DGB_API int dgb_adam_flat_capturable(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n, float beta1,
+                                     float beta2, float eps, float weight_decay, float grad_scale, int* step_dev,
+                                     float* dev_state, void* stream);
+
 /* ---- peer-memory runtime and kernels (csrc/peer.cu) ---------------------------------------------------------------------
  * Reference: NVSHMEMP2P::{AllocateSymmetricMemory, dist_get, dist_put, barrier} (DGraph/distributed/csrc/
  * torch_nvshmem_p2p.cu:96-376) and NCCLBackendEngine.put (DGraph/distributed/nccl/NCCLBackendEngine.py:281-306).

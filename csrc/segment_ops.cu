@@ -68,25 +68,44 @@ __device__ __forceinline__ const char* src_row(const SegParams& p, const char* s
   return src_lane + (uint64_t)(uint32_t)j * p.ld_src_b;  // one IMAD.WIDE.U32
 }
 
+// SEG_ADD_RELU on packed bf16 pairs (two columns per 32-bit lane word): HADD2 + HMNMX2 + HSET2 replace per-column
+// FADD / FSETP / predicated count + mask updates (9 -> ~5 instructions per column-edge; ncu: the scalar version was
+// issue-bound at 69 % SM throughput).  The message m = P[i] + Q[j] is rounded to bf16 before the ReLU -- exactly what a bf16
+// Linear -> ReLU produces -- and still accumulated in fp32; the sign of the rounded sum equals the sign of the exact sum, so
+// the saved mask is unchanged.
+//   cnt trick: mk is 0xFFFF per active half.  word -= mk adds 1 to the low count and (hi_active - lo_active) to the high one;
+//   the caller repairs the high half once per row with word += word << 16.
+__device__ __forceinline__ void add_relu_pair(uint32_t q2, uint32_t p2, float& a_lo, float& a_hi, uint32_t& cn, uint32_t& mout,
+                                              uint32_t bitc) {
+  const __nv_bfloat162 zero = __floats2bfloat162_rn(0.f, 0.f);
+  const __nv_bfloat162 s = __hadd2(*reinterpret_cast<const __nv_bfloat162*>(&p2), *reinterpret_cast<const __nv_bfloat162*>(&q2));
+  const uint32_t mk = __hgt2_mask(s, zero);
+  const __nv_bfloat162 r = __hmax2(s, zero);
+  const uint32_t rb = *reinterpret_cast<const uint32_t*>(&r);
+  a_lo += __uint_as_float(rb << 16);
+  a_hi += __uint_as_float(rb & 0xffff0000u);
+  cn -= mk;
+  mout |= mk & bitc;
+}
+
 // One edge worth of work for one lane chunk (8 columns).
 template <int MODE>
-__device__ __forceinline__ void seg_accumulate(const uint4& v, const uint4& v2, const float* rop, float w, uint32_t mbyte,
-                                               float* acc, uint32_t* cn2, uint32_t& mout) {
+__device__ __forceinline__ void seg_accumulate(const uint4& v, const uint4& v2, const float* rop, const uint4& rop2, float w,
+                                               uint32_t mbyte, float* acc, uint32_t* cn2, uint32_t& mout) {
+  if (MODE == SEG_ADD_RELU) {
+    uint32_t m = 0;
+    add_relu_pair(v.x, rop2.x, acc[0], acc[1], cn2[0], m, 0x00020001u);
+    add_relu_pair(v.y, rop2.y, acc[2], acc[3], cn2[1], m, 0x00080004u);
+    add_relu_pair(v.z, rop2.z, acc[4], acc[5], cn2[2], m, 0x00200010u);
+    add_relu_pair(v.w, rop2.w, acc[6], acc[7], cn2[3], m, 0x00800040u);
+    mout = m | (m >> 16);  // only the low byte is stored
+    return;
+  }
   float f[8];
   unpack8(v, f);
   if (MODE == SEG_SUM) {
 #pragma unroll
     for (int t = 0; t < 8; ++t) acc[t] = fmaf(w, f[t], acc[t]);
-  } else if (MODE == SEG_ADD_RELU) {
-#pragma unroll
-    for (int t = 0; t < 8; ++t) {
-      const float m = rop[t] + f[t];
-      if (m > 0.f) {  // predicated: FADD + IADD + LOP3
-        acc[t] += m;
-        cn2[t >> 1] += (t & 1) ? 0x10000u : 1u;
-        mout |= (1u << t);
-      }
-    }
   } else if (MODE == SEG_ADD_RELU_BWD) {  // f = dOut[i], f2 = P[i], rop = Q[j]
     float f2[8];
     unpack8(v2, f2);
@@ -100,39 +119,42 @@ __device__ __forceinline__ void seg_accumulate(const uint4& v, const uint4& v2, 
   }
 }
 
-template <int MODE, int G, int NC, bool HALO>
-__global__ void __launch_bounds__(256, (NC == 1 && !HALO) ? (MODE == SEG_SUM ? 5 : 4) : 1) seg_reduce_kernel(const SegParams p) {
+// One output row (segment) handled by a group of G lanes.  FULL: the row has exactly G*NC 8-column chunks, so every lane
+// owns valid columns and the chunk count is a compile-time constant (no per-edge column predicates, immediate offsets for
+// the mask bytes).  AUX (SEG_ADD_RELU only): the ReLU bit mask is written.  Both are block-uniform run-time facts that the
+// kernel turns into template arguments once, outside the edge loop (ncu/SASS: the per-edge null check of p.mask cost two
+// uniform compares, a constant reload and two R2UR per edge because it evicted the L2-policy descriptor).
+template <int MODE, int G, int NC, bool HALO, bool FULL, bool AUX>
+__device__ __forceinline__ void seg_row(const SegParams& p, const int64_t r, const int g, const unsigned gmask) {
   constexpr int UNROLL = 4;
-  const int lane = threadIdx.x & 31;
-  const int g = lane & (G - 1);
-  const int sub = lane / G;
-  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const int64_t r = warp * (32 / G) + sub;
-  if (r >= p.n_rows) return;
-  const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (sub * G));
-  const int nchunk = p.H >> 3;  // 8-column chunks per row
+  const int nchunk = FULL ? (G * NC) : (p.H >> 3);  // 8-column chunks per row
   const uint64_t pol_keep = l2_policy_evict_last();
   const uint64_t pol_stream = l2_policy_evict_first();
 
   float acc[NC][8];
   float rop[NC][8];
+  uint4 rop2[NC];  // SEG_ADD_RELU: the row operand stays packed (bf16x2)
   uint32_t cn2[NC][4];
   bool colok[NC];
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
     const int ch = g + c * G;
-    colok[c] = ch < nchunk;
+    colok[c] = FULL ? true : (ch < nchunk);
 #pragma unroll
     for (int t = 0; t < 8; ++t) { acc[c][t] = 0.f; rop[c][t] = 0.f; }
 #pragma unroll
     for (int t = 0; t < 4; ++t) cn2[c][t] = 0;
-    if ((MODE == SEG_ADD_RELU || MODE == SEG_ADD_RELU_BWD) && colok[c])
-      unpack8(ldg_hint_v4(p.rowop + r * p.ld_rowop + ch * 8, pol_stream), rop[c]);
+    rop2[c] = make_uint4(0, 0, 0, 0);
+    if (MODE == SEG_ADD_RELU && colok[c]) rop2[c] = ldg_hint_v4(p.rowop + r * p.ld_rowop + ch * 8, pol_stream);
+    if (MODE == SEG_ADD_RELU_BWD && colok[c]) unpack8(ldg_hint_v4(p.rowop + r * p.ld_rowop + ch * 8, pol_stream), rop[c]);
   }
   const char* src_lane = reinterpret_cast<const char*>(p.src) + g * 16;
   const char* src2_lane = reinterpret_cast<const char*>(p.src2) + g * 16;
 
   const int beg = p.ptr[r], end = p.ptr[r + 1];
+  // SEG_ADD_RELU + AUX: running pointer to this lane's mask byte of the current edge slot
+  unsigned char* mp = (MODE == SEG_ADD_RELU && AUX) ? p.mask + (int64_t)beg * nchunk + g : nullptr;
+  const unsigned char* mask_lane = (MODE == SEG_MASKED_SUM) ? p.mask + g : nullptr;
   for (int base = beg; base < end; base += G) {
     const int n = min(G, end - base);
     int my_j = 0, my_s = 0;
@@ -158,7 +180,7 @@ __global__ void __launch_bounds__(256, (NC == 1 && !HALO) ? (MODE == SEG_SUM ? 5
           if (colok[c]) {
             v[u][c] = HALO ? ldg_v4(row + c * G * 16) : ldg_hint_v4(row + c * G * 16, pol_keep);
             if (MODE == SEG_ADD_RELU_BWD) v2[u][c] = ldg_nc_v4(src2_lane + (uint64_t)(uint32_t)j * p.ld_src2_b + c * G * 16);
-            if (MODE == SEG_MASKED_SUM) mb[u][c] = __ldg(p.mask + (int64_t)sl * nchunk + g + c * G);
+            if (MODE == SEG_MASKED_SUM) mb[u][c] = __ldg(mask_lane + (int64_t)sl * nchunk + c * G);
           }
         }
       }
@@ -168,11 +190,12 @@ __global__ void __launch_bounds__(256, (NC == 1 && !HALO) ? (MODE == SEG_SUM ? 5
         for (int c = 0; c < NC; ++c) {
           if (colok[c]) {
             uint32_t mout = 0;
-            seg_accumulate<MODE>(v[u][c], v2[u][c], rop[c], w[u], mb[u][c], acc[c], cn2[c], mout);
-            if (MODE == SEG_ADD_RELU && p.mask) stg_cs_u8(p.mask + (int64_t)(base + t0 + u) * nchunk + g + c * G, mout);
+            seg_accumulate<MODE>(v[u][c], v2[u][c], rop[c], rop2[c], w[u], mb[u][c], acc[c], cn2[c], mout);
+            if (MODE == SEG_ADD_RELU && AUX) stg_cs_u8(mp + u * nchunk + c * G, mout);
           }
         }
       }
+      if (MODE == SEG_ADD_RELU && AUX) mp += UNROLL * nchunk;
     }
     for (; t0 < n; ++t0) {  // tail
       const int j = __shfl_sync(gmask, my_j, t0, G);
@@ -186,11 +209,12 @@ __global__ void __launch_bounds__(256, (NC == 1 && !HALO) ? (MODE == SEG_SUM ? 5
           uint4 v2 = make_uint4(0, 0, 0, 0);
           uint32_t mb = 0, mout = 0;
           if (MODE == SEG_ADD_RELU_BWD) v2 = ldg_nc_v4(src2_lane + (uint64_t)(uint32_t)j * p.ld_src2_b + c * G * 16);
-          if (MODE == SEG_MASKED_SUM) mb = __ldg(p.mask + (int64_t)sl * nchunk + g + c * G);
-          seg_accumulate<MODE>(v, v2, rop[c], w, mb, acc[c], cn2[c], mout);
-          if (MODE == SEG_ADD_RELU && p.mask) stg_cs_u8(p.mask + (int64_t)(base + t0) * nchunk + g + c * G, mout);
+          if (MODE == SEG_MASKED_SUM) mb = __ldg(mask_lane + (int64_t)sl * nchunk + c * G);
+          seg_accumulate<MODE>(v, v2, rop[c], rop2[c], w, mb, acc[c], cn2[c], mout);
+          if (MODE == SEG_ADD_RELU && AUX) stg_cs_u8(mp + c * G, mout);
         }
       }
+      if (MODE == SEG_ADD_RELU && AUX) mp += nchunk;
     }
   }
 
@@ -215,10 +239,37 @@ __global__ void __launch_bounds__(256, (NC == 1 && !HALO) ? (MODE == SEG_SUM ? 5
         stg_cs_v4(p.dp_out + r * p.ld_dp + colo, pack8(gr));
       }
       if (MODE == SEG_ADD_RELU && p.cnt) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t) cn2[c][t] += cn2[c][t] << 16;  // repair the high halves (see add_relu_pair)
         uint4 cv = make_uint4(cn2[c][0], cn2[c][1], cn2[c][2], cn2[c][3]);
         stg_cs_v4(p.cnt + r * p.ld_cnt + colo, cv);
       }
     }
+  }
+}
+
+template <int MODE, int G, int NC, bool HALO>
+__global__ void __launch_bounds__(256, (NC == 1 && !HALO) ? (MODE == SEG_SUM ? 5 : 4) : 1) seg_reduce_kernel(const SegParams p) {
+  const int lane = threadIdx.x & 31;
+  const int g = lane & (G - 1);
+  const int sub = lane / G;
+  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t r = warp * (32 / G) + sub;
+  if (r >= p.n_rows) return;
+  const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (sub * G));
+  const bool full = (p.H >> 3) == G * NC;
+  if (MODE == SEG_ADD_RELU) {
+    const bool aux = p.mask != nullptr;
+    if (full) {
+      if (aux) seg_row<MODE, G, NC, HALO, true, true>(p, r, g, gmask);
+      else seg_row<MODE, G, NC, HALO, true, false>(p, r, g, gmask);
+    } else {
+      if (aux) seg_row<MODE, G, NC, HALO, false, true>(p, r, g, gmask);
+      else seg_row<MODE, G, NC, HALO, false, false>(p, r, g, gmask);
+    }
+  } else {
+    if (full) seg_row<MODE, G, NC, HALO, true, false>(p, r, g, gmask);
+    else seg_row<MODE, G, NC, HALO, false, false>(p, r, g, gmask);
   }
 }
 

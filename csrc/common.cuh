@@ -56,6 +56,12 @@ __device__ __forceinline__ uint4 ldg_hint_v4(const void* p, uint64_t pol) {
                : "l"(p), "l"(pol));
   return r;
 }
+__device__ __forceinline__ uint32_t ldg_stream_u8(const void* p) {  // read-once byte stream: do not keep it in L1
+  uint32_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.u8 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+
 __device__ __forceinline__ void stg_cs_u8(void* p, uint32_t v) {
   asm volatile("st.global.cs.u8 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }

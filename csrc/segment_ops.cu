@@ -10,6 +10,8 @@
 // Neighbour indices are loaded coalesced and broadcast with shuffles; UNROLL independent 16-byte row loads
 // are in flight per lane.  When HALO is set, neighbour rows >= n_local are read *directly from the owner
 // GPU's matrix* through NVLink peer pointers (pull), so no halo buffer is materialised.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace dgb {
@@ -54,6 +56,7 @@ struct SegParams {
   const int* halo_owner;                  // [n_halo]
   const int* halo_row;                    // [n_halo] row inside the owner's matrix
   uint32_t ld_peer_b;
+  int rows_per_group;  // consecutive rows per lane group (set by launch_seg)
 };
 
 template <bool HALO>
@@ -121,15 +124,55 @@ __device__ __forceinline__ void seg_accumulate(const uint4& v, const uint4& v2, 
 
 // One output row (segment) handled by a group of G lanes.  FULL: the row has exactly G*NC 8-column chunks, so every lane
 // owns valid columns and the chunk count is a compile-time constant (no per-edge column predicates, immediate offsets for
-// the mask bytes).  AUX (SEG_ADD_RELU only): the ReLU bit mask is written.  Both are block-uniform run-time facts that the
+// the mask bytes).  AUX: how the ReLU bit mask is addressed -- 0 = not used, 1 = rows in this walk's slot order (running
+// pointer, streaming), 2 = rows through p.slot_map (one extra index load + shuffle per edge).  SEG_ADD_RELU writes the mask,
+// SEG_MASKED_SUM reads it; exactly one of the two walks can be sequential, the other one pays the random 32-byte accesses
+// (writes are fire-and-forget, reads stall: see DESIGN.md).  FULL and AUX are block-uniform run-time facts that the
 // kernel turns into template arguments once, outside the edge loop (ncu/SASS: the per-edge null check of p.mask cost two
 // uniform compares, a constant reload and two R2UR per edge because it evicted the L2-policy descriptor).
-template <int MODE, int G, int NC, bool HALO, bool FULL, bool AUX>
-__device__ __forceinline__ void seg_row(const SegParams& p, const int64_t r, const int g, const unsigned gmask) {
+//
+// The lane group walks rows r, r + stride, ... < r_end and software-pipelines the dependent index loads -- while row r is being
+// reduced, the segment bounds of row r + 2*stride and the first G neighbour indices of row r + stride are already in flight.
+// Without this every row (25 edges on average for the products graph) pays three serialised memory latencies
+// (ptr -> idx -> gather) before its first useful instruction.  The kernel gives each group a short run of CONSECUTIVE rows
+// (p.rows_per_group) and keeps the grid non-persistent: a grid-strided persistent variant was measured 35 % slower because the
+// hardware block scheduler otherwise keeps all SMs inside one compact window of rows, which is what makes the evict_last L2
+// policy on the gathered rows pay.
+template <int MODE, int G, int NC, bool HALO, bool FULL, int AUX>
+__device__ __forceinline__ void seg_rows(const SegParams& p, int r, const int stride, const int n_rows, const int g,
+                                         const unsigned gmask) {
   constexpr int UNROLL = 4;
+  constexpr bool USES_MASK = (MODE == SEG_ADD_RELU && AUX != 0) || MODE == SEG_MASKED_SUM;
+  constexpr bool MAPPED = USES_MASK && AUX == 2;
   const int nchunk = FULL ? (G * NC) : (p.H >> 3);  // 8-column chunks per row
   const uint64_t pol_keep = l2_policy_evict_last();
   const uint64_t pol_stream = l2_policy_evict_first();
+
+  // pipeline registers: current row (beg, end, first-group indices) and the bounds of the next one
+  int beg = p.ptr[r], end = p.ptr[r + 1];
+  int cur_j = 0, cur_s = 0;
+  float cur_w = 1.f;
+  if (g < min(G, end - beg)) {
+    cur_j = p.idx[beg + g];
+    if (MODE == SEG_SUM && p.slot_w) cur_w = p.slot_w[beg + g];
+    if (MAPPED) cur_s = p.slot_map[beg + g];
+  }
+  int rn = r + stride;
+  int nbeg = 0, nend = 0;
+  if (rn < n_rows) { nbeg = p.ptr[rn]; nend = p.ptr[rn + 1]; }
+
+  while (true) {
+  // ---- issue the prefetches for the following rows (consumed after this row's reduction) ----
+  int nxt_j = 0, nxt_s = 0;
+  float nxt_w = 1.f;
+  if (g < min(G, nend - nbeg)) {
+    nxt_j = p.idx[nbeg + g];
+    if (MODE == SEG_SUM && p.slot_w) nxt_w = p.slot_w[nbeg + g];
+    if (MAPPED) nxt_s = p.slot_map[nbeg + g];
+  }
+  const int rnn = rn + stride;
+  int nnbeg = 0, nnend = 0;
+  if (rnn < n_rows) { nnbeg = p.ptr[rnn]; nnend = p.ptr[rnn + 1]; }
 
   float acc[NC][8];
   float rop[NC][8];
@@ -145,42 +188,47 @@ __device__ __forceinline__ void seg_row(const SegParams& p, const int64_t r, con
 #pragma unroll
     for (int t = 0; t < 4; ++t) cn2[c][t] = 0;
     rop2[c] = make_uint4(0, 0, 0, 0);
-    if (MODE == SEG_ADD_RELU && colok[c]) rop2[c] = ldg_hint_v4(p.rowop + r * p.ld_rowop + ch * 8, pol_stream);
-    if (MODE == SEG_ADD_RELU_BWD && colok[c]) unpack8(ldg_hint_v4(p.rowop + r * p.ld_rowop + ch * 8, pol_stream), rop[c]);
+    if (MODE == SEG_ADD_RELU && colok[c]) rop2[c] = ldg_hint_v4(p.rowop + (int64_t)r * p.ld_rowop + ch * 8, pol_stream);
+    if (MODE == SEG_ADD_RELU_BWD && colok[c])
+      unpack8(ldg_hint_v4(p.rowop + (int64_t)r * p.ld_rowop + ch * 8, pol_stream), rop[c]);
   }
   const char* src_lane = reinterpret_cast<const char*>(p.src) + g * 16;
   const char* src2_lane = reinterpret_cast<const char*>(p.src2) + g * 16;
 
-  const int beg = p.ptr[r], end = p.ptr[r + 1];
   // SEG_ADD_RELU + AUX: running pointer to this lane's mask byte of the current edge slot
-  unsigned char* mp = (MODE == SEG_ADD_RELU && AUX) ? p.mask + (int64_t)beg * nchunk + g : nullptr;
-  const unsigned char* mask_lane = (MODE == SEG_MASKED_SUM) ? p.mask + g : nullptr;
+  unsigned char* mp = (USES_MASK && !MAPPED) ? p.mask + (int64_t)beg * nchunk + g : nullptr;  // running pointer
+  unsigned char* mask_lane = MAPPED ? p.mask + g : nullptr;
   for (int base = beg; base < end; base += G) {
     const int n = min(G, end - base);
-    int my_j = 0, my_s = 0;
-    float my_w = 1.f;
-    if (g < n) {
-      my_j = p.idx[base + g];
-      if (MODE == SEG_SUM && p.slot_w) my_w = p.slot_w[base + g];
-      if (MODE == SEG_MASKED_SUM) my_s = p.slot_map[base + g];
+    int my_j = cur_j, my_s = cur_s;  // first group: prefetched while the previous row was reduced
+    float my_w = cur_w;
+    if (base != beg) {
+      my_j = 0; my_s = 0; my_w = 1.f;
+      if (g < n) {
+        my_j = p.idx[base + g];
+        if (MODE == SEG_SUM && p.slot_w) my_w = p.slot_w[base + g];
+        if (MAPPED) my_s = p.slot_map[base + g];
+      }
     }
     int t0 = 0;
     for (; t0 + UNROLL <= n; t0 += UNROLL) {  // full groups: no per-edge predication
       uint4 v[UNROLL][NC], v2[UNROLL][NC];
       uint32_t mb[UNROLL][NC];
       float w[UNROLL];
+      int sl[UNROLL];
 #pragma unroll
       for (int u = 0; u < UNROLL; ++u) {
         const int j = __shfl_sync(gmask, my_j, t0 + u, G);
         if (MODE == SEG_SUM) w[u] = __shfl_sync(gmask, my_w, t0 + u, G); else w[u] = 1.f;
-        const int sl = (MODE == SEG_MASKED_SUM) ? __shfl_sync(gmask, my_s, t0 + u, G) : 0;
+        sl[u] = MAPPED ? __shfl_sync(gmask, my_s, t0 + u, G) : 0;
         const char* row = src_row<HALO>(p, src_lane, g * 16, j);
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
           if (colok[c]) {
             v[u][c] = HALO ? ldg_v4(row + c * G * 16) : ldg_hint_v4(row + c * G * 16, pol_keep);
             if (MODE == SEG_ADD_RELU_BWD) v2[u][c] = ldg_nc_v4(src2_lane + (uint64_t)(uint32_t)j * p.ld_src2_b + c * G * 16);
-            if (MODE == SEG_MASKED_SUM) mb[u][c] = __ldg(mask_lane + (int64_t)sl * nchunk + c * G);
+            if (MODE == SEG_MASKED_SUM)
+              mb[u][c] = MAPPED ? __ldg(mask_lane + (int64_t)sl[u] * nchunk + c * G) : ldg_stream_u8(mp + u * nchunk + c * G);
           }
         }
       }
@@ -191,16 +239,17 @@ __device__ __forceinline__ void seg_row(const SegParams& p, const int64_t r, con
           if (colok[c]) {
             uint32_t mout = 0;
             seg_accumulate<MODE>(v[u][c], v2[u][c], rop[c], rop2[c], w[u], mb[u][c], acc[c], cn2[c], mout);
-            if (MODE == SEG_ADD_RELU && AUX) stg_cs_u8(mp + u * nchunk + c * G, mout);
+            if (MODE == SEG_ADD_RELU && AUX == 1) stg_cs_u8(mp + u * nchunk + c * G, mout);
+            if (MODE == SEG_ADD_RELU && AUX == 2) stg_cs_u8(mask_lane + (int64_t)sl[u] * nchunk + c * G, mout);
           }
         }
       }
-      if (MODE == SEG_ADD_RELU && AUX) mp += UNROLL * nchunk;
+      if (USES_MASK && !MAPPED) mp += UNROLL * nchunk;
     }
     for (; t0 < n; ++t0) {  // tail
       const int j = __shfl_sync(gmask, my_j, t0, G);
       const float w = (MODE == SEG_SUM) ? __shfl_sync(gmask, my_w, t0, G) : 1.f;
-      const int sl = (MODE == SEG_MASKED_SUM) ? __shfl_sync(gmask, my_s, t0, G) : 0;
+      const int sl = MAPPED ? __shfl_sync(gmask, my_s, t0, G) : 0;
       const char* row = src_row<HALO>(p, src_lane, g * 16, j);
 #pragma unroll
       for (int c = 0; c < NC; ++c) {
@@ -209,12 +258,13 @@ __device__ __forceinline__ void seg_row(const SegParams& p, const int64_t r, con
           uint4 v2 = make_uint4(0, 0, 0, 0);
           uint32_t mb = 0, mout = 0;
           if (MODE == SEG_ADD_RELU_BWD) v2 = ldg_nc_v4(src2_lane + (uint64_t)(uint32_t)j * p.ld_src2_b + c * G * 16);
-          if (MODE == SEG_MASKED_SUM) mb = __ldg(mask_lane + (int64_t)sl * nchunk + c * G);
+          if (MODE == SEG_MASKED_SUM) mb = MAPPED ? __ldg(mask_lane + (int64_t)sl * nchunk + c * G) : ldg_stream_u8(mp + c * G);
           seg_accumulate<MODE>(v, v2, rop[c], rop2[c], w, mb, acc[c], cn2[c], mout);
-          if (MODE == SEG_ADD_RELU && AUX) stg_cs_u8(mp + c * G, mout);
+          if (MODE == SEG_ADD_RELU && AUX == 1) stg_cs_u8(mp + c * G, mout);
+          if (MODE == SEG_ADD_RELU && AUX == 2) stg_cs_u8(mask_lane + (int64_t)sl * nchunk + c * G, mout);
         }
       }
-      if (MODE == SEG_ADD_RELU && AUX) mp += nchunk;
+      if (USES_MASK && !MAPPED) mp += nchunk;
     }
   }
 
@@ -227,25 +277,32 @@ __device__ __forceinline__ void seg_row(const SegParams& p, const int64_t r, con
 #pragma unroll
         for (int t = 0; t < 8; ++t) acc[c][t] *= scale;
       }
-      stg_cs_v4(p.out + r * p.ld_out + colo, pack8(acc[c]));
+      stg_cs_v4(p.out + (int64_t)r * p.ld_out + colo, pack8(acc[c]));
       if (MODE == SEG_MASKED_SUM && p.dp_out && r < p.dp_rows) {
         float gr[8];
         unpack8(ldg_nc_v4(reinterpret_cast<const char*>(p.src) + (uint64_t)r * p.ld_src_b + colo * 2), gr);
-        const uint4 cv = ldg_nc_v4(p.cnt + r * p.ld_cnt + colo);
+        const uint4 cv = ldg_nc_v4(p.cnt + (int64_t)r * p.ld_cnt + colo);
         gr[0] *= (float)(cv.x & 0xffff); gr[1] *= (float)(cv.x >> 16);
         gr[2] *= (float)(cv.y & 0xffff); gr[3] *= (float)(cv.y >> 16);
         gr[4] *= (float)(cv.z & 0xffff); gr[5] *= (float)(cv.z >> 16);
         gr[6] *= (float)(cv.w & 0xffff); gr[7] *= (float)(cv.w >> 16);
-        stg_cs_v4(p.dp_out + r * p.ld_dp + colo, pack8(gr));
+        stg_cs_v4(p.dp_out + (int64_t)r * p.ld_dp + colo, pack8(gr));
       }
       if (MODE == SEG_ADD_RELU && p.cnt) {
 #pragma unroll
         for (int t = 0; t < 4; ++t) cn2[c][t] += cn2[c][t] << 16;  // repair the high halves (see add_relu_pair)
         uint4 cv = make_uint4(cn2[c][0], cn2[c][1], cn2[c][2], cn2[c][3]);
-        stg_cs_v4(p.cnt + r * p.ld_cnt + colo, cv);
+        stg_cs_v4(p.cnt + (int64_t)r * p.ld_cnt + colo, cv);
       }
     }
   }
+
+  // ---- rotate the pipeline ----
+  if (rn >= n_rows) break;
+  r = rn; beg = nbeg; end = nend;
+  cur_j = nxt_j; cur_s = nxt_s; cur_w = nxt_w;
+  rn = rnn; nbeg = nnbeg; nend = nnend;
+  }  // while rows
 }
 
 template <int MODE, int G, int NC, bool HALO>
@@ -253,23 +310,27 @@ __global__ void __launch_bounds__(256, (NC == 1 && !HALO) ? (MODE == SEG_SUM ? 5
   const int lane = threadIdx.x & 31;
   const int g = lane & (G - 1);
   const int sub = lane / G;
-  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const int64_t r = warp * (32 / G) + sub;
+  const int warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int r = (warp * (32 / G) + sub) * p.rows_per_group;  // first of this group's consecutive rows
+  const int stride = 1;
   if (r >= p.n_rows) return;
+  const int r_end = min(r + p.rows_per_group, (int)p.n_rows);
   const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (sub * G));
   const bool full = (p.H >> 3) == G * NC;
-  if (MODE == SEG_ADD_RELU) {
-    const bool aux = p.mask != nullptr;
+  if (MODE == SEG_ADD_RELU || MODE == SEG_MASKED_SUM) {
+    const int aux = p.mask == nullptr ? 0 : (p.slot_map ? 2 : 1);
     if (full) {
-      if (aux) seg_row<MODE, G, NC, HALO, true, true>(p, r, g, gmask);
-      else seg_row<MODE, G, NC, HALO, true, false>(p, r, g, gmask);
+      if (aux == 2) seg_rows<MODE, G, NC, HALO, true, 2>(p, r, stride, r_end, g, gmask);
+      else if (aux == 1) seg_rows<MODE, G, NC, HALO, true, 1>(p, r, stride, r_end, g, gmask);
+      else if (MODE == SEG_ADD_RELU) seg_rows<MODE, G, NC, HALO, true, 0>(p, r, stride, r_end, g, gmask);
     } else {
-      if (aux) seg_row<MODE, G, NC, HALO, false, true>(p, r, g, gmask);
-      else seg_row<MODE, G, NC, HALO, false, false>(p, r, g, gmask);
+      if (aux == 2) seg_rows<MODE, G, NC, HALO, false, 2>(p, r, stride, r_end, g, gmask);
+      else if (aux == 1) seg_rows<MODE, G, NC, HALO, false, 1>(p, r, stride, r_end, g, gmask);
+      else if (MODE == SEG_ADD_RELU) seg_rows<MODE, G, NC, HALO, false, 0>(p, r, stride, r_end, g, gmask);
     }
   } else {
-    if (full) seg_row<MODE, G, NC, HALO, true, false>(p, r, g, gmask);
-    else seg_row<MODE, G, NC, HALO, false, false>(p, r, g, gmask);
+    if (full) seg_rows<MODE, G, NC, HALO, true, 0>(p, r, stride, r_end, g, gmask);
+    else seg_rows<MODE, G, NC, HALO, false, 0>(p, r, stride, r_end, g, gmask);
   }
 }
 
@@ -278,11 +339,20 @@ static int launch_seg(const SegParams& p, cudaStream_t s) {
   if (p.n_rows == 0) return 0;
   const int chunks = p.H / 8;
   const int warps_per_block = 8;
+  if (p.n_rows >= (int64_t)1 << 31) return (int)cudaErrorInvalidValue;
+  static int rows_per_group = 0;
+  if (rows_per_group == 0) {
+    const char* e = getenv("DGRAPH_B200_SEG_ROWS");
+    rows_per_group = e ? atoi(e) : 8;
+    if (rows_per_group < 1 || rows_per_group > 64) rows_per_group = 8;
+  }
+  SegParams q = p;
+  q.rows_per_group = rows_per_group;
 #define DGB_LAUNCH(G, NC)                                                                 \
   do {                                                                                    \
-    const int64_t rows_per_block = (int64_t)warps_per_block * (32 / (G));                 \
+    const int64_t rows_per_block = (int64_t)warps_per_block * (32 / (G)) * rows_per_group; \
     const int64_t blocks = (p.n_rows + rows_per_block - 1) / rows_per_block;              \
-    seg_reduce_kernel<MODE, G, NC, HALO><<<(unsigned)blocks, warps_per_block * 32, 0, s>>>(p); \
+    seg_reduce_kernel<MODE, G, NC, HALO><<<(unsigned)blocks, warps_per_block * 32, 0, s>>>(q); \
   } while (0)
   if (chunks <= 4) DGB_LAUNCH(4, 1);
   else if (chunks <= 8) DGB_LAUNCH(8, 1);
@@ -342,10 +412,13 @@ DGB_API int dgb_seg_sum(const int* ptr, const int* idx, int64_t n_rows, int H, c
 }
 
 // out[r,:] = sum_{k in seg r} relu(P[r,:] + Q[idx[k],:]);   cnt[r,c] = #active edges (optional)
-DGB_API int dgb_seg_add_relu_fwd(const int* ptr, const int* idx, int64_t n_rows, int H, const void* P, int64_t ld_p,
-                                 const void* Q, int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt,
-                                 int64_t ld_cnt, unsigned char* mask, int64_t n_local, const void* const* peer_base,
-                                 const int* halo_owner, const int* halo_row, int64_t ld_peer, void* stream) {
+// mask_slot_map (optional): mask row of edge slot k is mask_slot_map[k] instead of k -- pass the CSR->CSC slot permutation so
+// that the backward CSC walk (dgb_seg_masked_sum with slot_map = null) streams the mask rows sequentially.
+DGB_API int dgb_seg_add_relu_fwd_mapped(const int* ptr, const int* idx, int64_t n_rows, int H, const void* P, int64_t ld_p,
+                                        const void* Q, int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt,
+                                        int64_t ld_cnt, unsigned char* mask, const int* mask_slot_map, int64_t n_local,
+                                        const void* const* peer_base, const int* halo_owner, const int* halo_row,
+                                        int64_t ld_peer, void* stream) {
   if (H % 8 || ld_p % 8 || ld_q % 8 || ld_out % 8 || (cnt && ld_cnt % 8) || !aligned16(P) || !aligned16(Q) ||
       !aligned16(out))
     return (int)cudaErrorInvalidValue;
@@ -355,10 +428,19 @@ DGB_API int dgb_seg_add_relu_fwd(const int* ptr, const int* idx, int64_t n_rows,
   p.src = (const __nv_bfloat16*)Q; p.ld_src_b = (uint32_t)(ld_q * 2);
   p.rowop = (const __nv_bfloat16*)P; p.ld_rowop = ld_p;
   p.out = (__nv_bfloat16*)out; p.ld_out = ld_out; p.cnt = cnt; p.ld_cnt = ld_cnt; p.mask = mask;
+  p.slot_map = mask ? mask_slot_map : nullptr;
   p.n_local = n_local; p.peer_base = (const __nv_bfloat16* const*)peer_base;
   p.halo_owner = halo_owner; p.halo_row = halo_row; p.ld_peer_b = (uint32_t)(ld_peer * 2);
   return peer_base ? launch_seg<SEG_ADD_RELU, true>(p, (cudaStream_t)stream)
                    : launch_seg<SEG_ADD_RELU, false>(p, (cudaStream_t)stream);
+}
+
+DGB_API int dgb_seg_add_relu_fwd(const int* ptr, const int* idx, int64_t n_rows, int H, const void* P, int64_t ld_p,
+                                 const void* Q, int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt,
+                                 int64_t ld_cnt, unsigned char* mask, int64_t n_local, const void* const* peer_base,
+                                 const int* halo_owner, const int* halo_row, int64_t ld_peer, void* stream) {
+  return dgb_seg_add_relu_fwd_mapped(ptr, idx, n_rows, H, P, ld_p, Q, ld_q, out, ld_out, cnt, ld_cnt, mask, nullptr, n_local,
+                                     peer_base, halo_owner, halo_row, ld_peer, stream);
 }
 
 // dQ[j,:] = sum_{k in CSC seg j} (P[row[k],:] + Q[j,:] > 0) ? dOut[row[k],:] : 0       (transposed walk)
@@ -377,13 +459,14 @@ DGB_API int dgb_seg_add_relu_bwd(const int* colptr, const int* row, int64_t n_au
 }
 
 // dQ[j,:] = sum_{k in CSC seg j} mask[slot_map[k]] ? dOut[row[k],:] : 0, with the ReLU bit masks the forward kernel saved
-// (one byte per edge slot and 8-column chunk): one row gather per edge instead of two, no recomputation.  When dP is given,
+// (one byte per edge slot and 8-column chunk): one row gather per edge instead of two, no recomputation.  slot_map = null
+// means the mask rows are already in this walk's slot order (forward used dgb_seg_add_relu_fwd_mapped).  When dP is given,
 // rows j < dp_rows also write dP[j,:] = dOut[j,:] * cnt[j,:] in the same pass.
 DGB_API int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slot_map, const unsigned char* mask,
                                int64_t n_aug, int H, const void* dOut, int64_t ld_g, void* dQ, int64_t ld_dq,
                                const unsigned short* cnt, int64_t ld_cnt, void* dP, int64_t ld_dp, int64_t dp_rows,
                                void* stream) {
-  if (H % 8 || ld_g % 8 || ld_dq % 8 || !fits32(ld_g * 2) || (dP && (ld_dp % 8 || ld_cnt % 8 || !cnt)))
+  if (H % 8 || ld_g % 8 || ld_dq % 8 || !fits32(ld_g * 2) || !mask || (dP && (ld_dp % 8 || ld_cnt % 8 || !cnt)))
     return (int)cudaErrorInvalidValue;
   SegParams p{};
   p.ptr = colptr; p.idx = row; p.n_rows = n_aug; p.H = H;

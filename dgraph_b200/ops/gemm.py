@@ -15,6 +15,7 @@ import torch.nn.functional as F
 from torch.autograd import Function
 
 from dgraph_b200.ops import _native as N
+from dgraph_b200.ops import _sparsity
 
 _ACT = {None: 0, "none": 0, "relu": 1, "silu": 2}
 
@@ -59,6 +60,23 @@ class _LinearTC(Function):
         from dgraph_b200.ops.gemm_native import gemm_bf16_nn_grad_w, act_backward
 
         x, w, y = ctx.saved_tensors
+        hint = _sparsity.take(g) if ctx.act in (None, "none") else None
+        if hint is not None:  # g is zero outside rows `idx`: work on the compact rows only (bit-identical results)
+            idx, gcp = hint  # compact rows, possibly with zero padding columns up to a 16-byte row
+            gc = gcp[:, :w.shape[0]]
+            dx = dw = db = None
+            if ctx.needs_input_grad[0]:
+                dx_sel = gemm_tn(gcp, w.t().contiguous())
+                dx = torch.zeros((x.shape[0], w.shape[1]), dtype=dx_sel.dtype, device=g.device)
+                dx.index_copy_(0, idx, dx_sel)
+                _sparsity.put(dx, idx, dx_sel)
+            if ctx.needs_input_grad[1]:
+                dw = gemm_bf16_nn_grad_w(gc, x, x_idx=idx)
+            if ctx.has_bias and ctx.needs_input_grad[2]:
+                from dgraph_b200.ops.reduce import colsum
+
+                db = colsum(gcp)[:w.shape[0]]
+            return dx, dw, db, None
         g = g.contiguous()
         if ctx.act not in (None, "none"):
             g = act_backward(g, y, ctx.act)

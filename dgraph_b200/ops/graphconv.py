@@ -16,6 +16,7 @@ from dgraph_b200.ops import _native as N
 from dgraph_b200.ops.gemm_native import gemm_bf16_nn_grad_w, gemm_bf16_tn
 from dgraph_b200.ops.reduce import colsum
 from dgraph_b200.ops import segment as S
+from dgraph_b200.ops import _sparsity
 
 
 class _GraphConvFused(Function):
@@ -41,10 +42,12 @@ class _GraphConvFused(Function):
         out = torch.empty((n_local, H), dtype=torch.bfloat16, device=dev)
         cnt = torch.empty((n_local, H), dtype=torch.uint16, device=dev) if need_w else None
         mask = torch.empty((kp.num_edges, H // 8), dtype=torch.uint8, device=dev) if need_w else None
-        N.check(N.lib().dgb_seg_add_relu_fwd(
+        smap = kp.csr_to_csc() if (mask is not None and S.MASK_IN_CSC_ORDER) else None
+        N.check(N.lib().dgb_seg_add_relu_fwd_mapped(
             N.ptr(kp.rowptr), N.ptr(kp.col), N.i64(n_local), N.i32(H), N.ptr(P), N.i64(2 * H), N.ptr(Q), N.i64(2 * H),
-            N.ptr(out), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(mask), N.i64(n_aug), N.ptr(None), N.ptr(None), N.ptr(None),
-            N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
+            N.ptr(out), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(mask), N.ptr(smap), N.i64(n_aug), N.ptr(None), N.ptr(None),
+            N.ptr(None), N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
+        ctx.mask_csc = smap is not None
         N.count_launch()
         ctx.save_for_backward(x_aug, wcat, cnt, mask)
         ctx.kp, ctx.n_local, ctx.f_in, ctx.H = kp, n_local, f_in, H
@@ -54,7 +57,12 @@ class _GraphConvFused(Function):
     def backward(ctx, g):
         x_aug, wcat, cnt, mask = ctx.saved_tensors
         kp, n, f_in, H = ctx.kp, ctx.n_local, ctx.f_in, ctx.H
+        hint = _sparsity.take(g)
+        if ctx.mask_csc:
+            hint = None  # the restricted walk addresses the mask through csc_to_csr
         g = g.contiguous()
+        # g zero outside rows `idx` (loss over the labelled vertices): walk only the edges that start there
+        colptr, row, slot_map = (kp.colptr, kp.row, kp.csc_to_csr) if hint is None else kp.restricted_csc(hint[0])
         n_aug = x_aug.shape[0]
         dev = g.device
         # [dP | dQ] for the local rows, dQ only for the halo rows (their P half is never read)
@@ -62,7 +70,8 @@ class _GraphConvFused(Function):
         lib = N.lib()
         dQ = dPQ[:, H:]
         # one CSC walk writes dQ (masked sums) for all rows and dP = g * cnt for the local rows
-        N.check(lib.dgb_seg_masked_sum(N.ptr(kp.colptr), N.ptr(kp.row), N.ptr(kp.csc_to_csr), N.ptr(mask), N.i64(n_aug),
+        N.check(lib.dgb_seg_masked_sum(N.ptr(colptr), N.ptr(row), N.ptr(None if ctx.mask_csc else slot_map), N.ptr(mask),
+                                       N.i64(n_aug),
                                        N.i32(H), N.ptr(g), N.i64(H), N.ptr(dQ), N.i64(2 * H), N.ptr(cnt), N.i64(H),
                                        N.ptr(dPQ), N.i64(2 * H), N.i64(n), N.stream()),
                 "dgb_seg_masked_sum")

@@ -24,6 +24,11 @@ from dgraph_b200.parallel.kernel_plan import GraphKernelPlan
 
 # Save 1 bit per (edge, column) in the forward so the backward gathers one row per edge instead of two (E * H / 8 bytes).
 SAVE_RELU_MASK = os.environ.get("DGRAPH_B200_RELU_MASK", "1") == "1"
+# Where the random 32-byte mask accesses go: "csc" = the forward kernel scatters its mask rows to the CSC slot and the backward
+# walk streams them; "csr" (default) = forward streams, backward gathers through csc_to_csr.  Measured on the products-shaped
+# graph (B200): csr 4.09 ms forward + 4.38 ms backward, csc 4.75 + 4.26 -- the scattered byte stores cost the issue-bound forward
+# kernel more than the streamed reads save the latency-bound backward kernel.
+MASK_IN_CSC_ORDER = os.environ.get("DGRAPH_B200_MASK_ORDER", "csr") == "csc"
 
 
 # ------------------------------------------------------------------------------------------------
@@ -127,10 +132,12 @@ class _GraphConvAgg(Function):
         cnt = torch.empty((n, H), dtype=torch.uint16, device=P.device) if need_p else None
         # ReLU bit masks (1 byte per edge and 8 columns = E * H / 8 bytes) let backward gather ONE row per edge
         mask = torch.empty((kp.num_edges, H // 8), dtype=torch.uint8, device=P.device) if (need_q and SAVE_RELU_MASK) else None
-        N.check(N.lib().dgb_seg_add_relu_fwd(
+        smap = kp.csr_to_csc() if (mask is not None and MASK_IN_CSC_ORDER) else None
+        N.check(N.lib().dgb_seg_add_relu_fwd_mapped(
             N.ptr(kp.rowptr), N.ptr(kp.col), N.i64(n), N.i32(H), N.ptr(P), N.i64(_ld(P)), N.ptr(Qaug), N.i64(_ld(Qaug)),
-            N.ptr(out), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(mask), N.i64(Qaug.shape[0]), N.ptr(None), N.ptr(None),
-            N.ptr(None), N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
+            N.ptr(out), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(mask), N.ptr(smap), N.i64(Qaug.shape[0]), N.ptr(None),
+            N.ptr(None), N.ptr(None), N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
+        ctx.mask_csc = smap is not None
         N.count_launch()
         if mask is not None:
             ctx.save_for_backward(cnt, mask)
@@ -158,7 +165,8 @@ class _GraphConvAgg(Function):
         if ctx.needs_input_grad[1] and ctx.has_mask:
             dQ = torch.empty((kp.num_aug, H), dtype=torch.bfloat16, device=g.device)
             N.check(N.lib().dgb_seg_masked_sum(
-                N.ptr(kp.colptr), N.ptr(kp.row), N.ptr(kp.csc_to_csr), N.ptr(mask), N.i64(kp.num_aug), N.i32(H), N.ptr(g),
+                N.ptr(kp.colptr), N.ptr(kp.row), N.ptr(None if ctx.mask_csc else kp.csc_to_csr), N.ptr(mask),
+                N.i64(kp.num_aug), N.i32(H), N.ptr(g),
                 N.i64(H), N.ptr(dQ), N.i64(H), N.ptr(None), N.i64(0), N.ptr(None), N.i64(0), N.i64(0), N.stream()),
                 "dgb_seg_masked_sum")
             N.count_launch()

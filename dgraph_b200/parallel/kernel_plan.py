@@ -40,6 +40,38 @@ class GraphKernelPlan:
     def num_aug(self) -> int:
         return self.num_nbr_local + self.num_halo
 
+    def csr_to_csc(self) -> torch.Tensor:
+        """CSC slot of each CSR slot (inverse of ``csc_to_csr``), built on first use.  The forward add-ReLU kernel writes its
+        ReLU bit masks at the CSC slot so that the backward CSC walk reads them as one sequential stream."""
+        t = getattr(self, "_csr_to_csc", None)
+        if t is None or t.device != self.csc_to_csr.device:
+            t = torch.empty_like(self.csc_to_csr)
+            t[self.csc_to_csr.long()] = torch.arange(self.csc_to_csr.numel(), device=t.device, dtype=t.dtype)
+            self._csr_to_csc = t
+        return t
+
+    def restricted_csc(self, rows: torch.Tensor):
+        """CSC structure restricted to the edges whose *row* (central vertex) is in ``rows``: ``(colptr, row, csc_to_csr)``.
+        Used by the backward of the last message-passing layer when the incoming gradient is zero outside ``rows`` (the
+        labelled vertices).  Built once per index tensor and cached."""
+        cache = self.__dict__.setdefault("_restricted", {})
+        key = (rows.data_ptr(), rows.numel(), rows._version)
+        hit = cache.get(key)
+        if hit is not None:
+            return hit
+        dev = self.row.device
+        member = torch.zeros(self.num_local + 1, dtype=torch.bool, device=dev)
+        member[rows.to(dev).long()] = True
+        keep = member[self.row.long()]
+        pref = torch.zeros(self.row.numel() + 1, dtype=torch.long, device=dev)
+        torch.cumsum(keep, 0, out=pref[1:])
+        colptr = pref[self.colptr.long()].to(self.colptr.dtype)
+        out = (colptr, self.row[keep].contiguous(), self.csc_to_csr[keep].contiguous())
+        if len(cache) >= 4:
+            cache.clear()
+        cache[key] = out
+        return out
+
     @staticmethod
     def from_edges(edge_list: torch.Tensor, num_local: int, num_aug: int, device=None, num_nbr_local=None,
                    halo_owner=None, halo_remote_row=None, send_local_idx=None) -> "GraphKernelPlan":

@@ -34,6 +34,14 @@ int dgb_seg_add_relu_fwd(const int* ptr, const int* idx, int64_t n_rows, int H, 
                          int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt, int64_t ld_cnt, unsigned char* mask,
                          int64_t n_local, const void* const* peer_base, const int* halo_owner, const int* halo_row,
                          int64_t ld_peer, void* stream);
+
+/* Same, with the mask row of edge slot k at mask_slot_map[k] (null = k): lets the backward walk stream the mask.  The
+ * reference has no saved-activation-mask mechanism at all (it re-materialises [E, 2F] edge tensors, GCN.py:43-65). */
+int dgb_seg_add_relu_fwd_mapped(const int* ptr, const int* idx, int64_t n_rows, int H, const void* P, int64_t ld_p,
+                                        const void* Q, int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt,
+                                        int64_t ld_cnt, unsigned char* mask, const int* mask_slot_map, int64_t n_local,
+                                        const void* const* peer_base, const int* halo_owner, const int* halo_row,
+                                        int64_t ld_peer, void* stream);
 int dgb_seg_add_relu_bwd(const int* colptr, const int* row, int64_t n_aug, int H, const void* dOut, int64_t ld_g,
                          const void* P, int64_t ld_p, const void* Q, int64_t ld_q, void* dQ, int64_t ld_dq, void* stream);
 int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slot_map, const unsigned char* mask, int64_t n_aug,
@@ -110,7 +118,7 @@ int dgb_adam_flat(float* p, const float* g, float* m, float* v, void* p_bf16, in
 
 /* Capturable Adam: step counter (int32) and {lr, 1-beta1^t, 1-beta2^t, -} (4 floats) live in device memory, so the two
  * launches (tick + update) can sit inside a CUDA graph that is replayed every step (reference: torch.optim.Adam only). */
-DGB_API int dgb_adam_flat_capturable(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n, float beta1,
+int dgb_adam_flat_capturable(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n, float beta1,
                                      float beta2, float eps, float weight_decay, float grad_scale, int* step_dev,
                                      float* dev_state, void* stream);
 
@@ -139,6 +147,13 @@ int dgb_halo_grad_reduce(void* gx, int64_t ld_gx, const void* g_local, int64_t l
 int dgb_adam_allreduce(float* p, const void* const* peer_g, int world, float* m, float* v, float* g_out, int64_t n, float lr,
                        float beta1, float beta2, float eps, float weight_decay, float grad_scale, int step, void* stream);
 int dgb_allreduce_sum_f32(float* out, const void* const* peer, int world, int64_t n, void* stream);
+
+/* ---- fused masked cross-entropy (csrc/loss_ops.cu); reference: ATen chain in experiments/OGB/main.py:115,140-148 ---- */
+int dgb_masked_ce_fwd(const void* logits, int64_t ld, int is_f32, const int64_t* labels, const int64_t* idx,
+                              int64_t n_sel, int C, float* loss_sum, float* lse, void* stream);
+int dgb_masked_ce_bwd(const void* logits, int64_t ld, int is_f32, const int64_t* labels, const int64_t* idx,
+                              int64_t n_sel, int C, const float* lse, const float* gout, void* dsel, int64_t ld_o,
+                              void* stream);
 
 #ifdef __cplusplus
 }

@@ -20,6 +20,13 @@ def test_header_declares_every_entry_point():
         src |= set(re.findall(r"^DGB_API\s+[\w\s\*]+?\b(dgb_\w+)\s*\(", open(f).read(), flags=re.M))
     hdr = set(re.findall(r"\b(dgb_\w+)\s*\(", open(os.path.join(ROOT, "include", "dgraph_b200.h")).read()))
     assert src and not (src - hdr), f"missing from include/dgraph_b200.h: {sorted(src - hdr)}"
+    import shutil
+    import subprocess
+
+    if shutil.which("gcc"):  # the header is plain C (ctypes / dlopen users): it must compile on its own
+        r = subprocess.run(["gcc", "-fsyntax-only", "-x", "c", os.path.join(ROOT, "include", "dgraph_b200.h")],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr[:2000]
 
 
 def test_sampler_gives_replicas_disjoint_samples():

@@ -19,8 +19,13 @@ namespace dgb {
 enum SegMode { SEG_SUM = 0, SEG_ADD_RELU = 1, SEG_ADD_RELU_BWD = 2, SEG_MASKED_SUM = 3 };
 
 struct SegParams {
-  // CSR (or CSC) structure: segment r covers slots [ptr[r], ptr[r+1]) of idx
+  // CSR (or CSC) structure: segment r covers slots [ptr[r], ptr_end[r]) of idx (ptr_end = ptr + 1 for a whole segment; other
+  // arrays let a launch walk only a sub-range of every segment, e.g. the local-neighbour or the halo-neighbour part)
   const int* ptr;
+  const int* ptr_end;
+  // SEG_ADD_RELU: add to the existing out / cnt rows instead of overwriting them (second pass over the halo neighbours);
+  // rows whose range is empty are left untouched
+  int accumulate;
   const int* idx;
   int64_t n_rows;
   int H;  // columns (bf16), multiple of 8
@@ -149,7 +154,7 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, int r, const int st
   const uint64_t pol_stream = l2_policy_evict_first();
 
   // pipeline registers: current row (beg, end, first-group indices) and the bounds of the next one
-  int beg = p.ptr[r], end = p.ptr[r + 1];
+  int beg = p.ptr[r], end = p.ptr_end[r];
   int cur_j = 0, cur_s = 0;
   float cur_w = 1.f;
   if (g < min(G, end - beg)) {
@@ -159,7 +164,7 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, int r, const int st
   }
   int rn = r + stride;
   int nbeg = 0, nend = 0;
-  if (rn < n_rows) { nbeg = p.ptr[rn]; nend = p.ptr[rn + 1]; }
+  if (rn < n_rows) { nbeg = p.ptr[rn]; nend = p.ptr_end[rn]; }
 
   while (true) {
   // ---- issue the prefetches for the following rows (consumed after this row's reduction) ----
@@ -172,8 +177,10 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, int r, const int st
   }
   const int rnn = rn + stride;
   int nnbeg = 0, nnend = 0;
-  if (rnn < n_rows) { nnbeg = p.ptr[rnn]; nnend = p.ptr[rnn + 1]; }
+  if (rnn < n_rows) { nnbeg = p.ptr[rnn]; nnend = p.ptr_end[rnn]; }
 
+  const bool accum = (MODE == SEG_ADD_RELU) && p.accumulate != 0;
+  if (!(accum && beg == end)) {  // an accumulate pass leaves rows without edges in its range untouched
   float acc[NC][8];
   float rop[NC][8];
   uint4 rop2[NC];  // SEG_ADD_RELU: the row operand stays packed (bf16x2)
@@ -188,6 +195,14 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, int r, const int st
 #pragma unroll
     for (int t = 0; t < 4; ++t) cn2[c][t] = 0;
     rop2[c] = make_uint4(0, 0, 0, 0);
+    if (accum && colok[c]) {  // continue from the first pass: out row back to fp32, counters back to the borrow-free form
+      unpack8(ldg_v4(p.out + (int64_t)r * p.ld_out + ch * 8), acc[c]);
+      if (p.cnt) {
+        const uint4 cv = ldg_v4(p.cnt + (int64_t)r * p.ld_cnt + ch * 8);
+        cn2[c][0] = cv.x - (cv.x << 16); cn2[c][1] = cv.y - (cv.y << 16);
+        cn2[c][2] = cv.z - (cv.z << 16); cn2[c][3] = cv.w - (cv.w << 16);
+      }
+    }
     if (MODE == SEG_ADD_RELU && colok[c]) rop2[c] = ldg_hint_v4(p.rowop + (int64_t)r * p.ld_rowop + ch * 8, pol_stream);
     if (MODE == SEG_ADD_RELU_BWD && colok[c])
       unpack8(ldg_hint_v4(p.rowop + (int64_t)r * p.ld_rowop + ch * 8, pol_stream), rop[c]);
@@ -297,6 +312,8 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, int r, const int st
     }
   }
 
+  }  // !(accum && empty range)
+
   // ---- rotate the pipeline ----
   if (rn >= n_rows) break;
   r = rn; beg = nbeg; end = nend;
@@ -348,6 +365,7 @@ static int launch_seg(const SegParams& p, cudaStream_t s) {
   }
   SegParams q = p;
   q.rows_per_group = rows_per_group;
+  if (q.ptr_end == nullptr) q.ptr_end = q.ptr + 1;
 #define DGB_LAUNCH(G, NC)                                                                 \
   do {                                                                                    \
     const int64_t rows_per_block = (int64_t)warps_per_block * (32 / (G)) * rows_per_group; \
@@ -414,16 +432,20 @@ DGB_API int dgb_seg_sum(const int* ptr, const int* idx, int64_t n_rows, int H, c
 // out[r,:] = sum_{k in seg r} relu(P[r,:] + Q[idx[k],:]);   cnt[r,c] = #active edges (optional)
 // mask_slot_map (optional): mask row of edge slot k is mask_slot_map[k] instead of k -- pass the CSR->CSC slot permutation so
 // that the backward CSC walk (dgb_seg_masked_sum with slot_map = null) streams the mask rows sequentially.
-DGB_API int dgb_seg_add_relu_fwd_mapped(const int* ptr, const int* idx, int64_t n_rows, int H, const void* P, int64_t ld_p,
-                                        const void* Q, int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt,
-                                        int64_t ld_cnt, unsigned char* mask, const int* mask_slot_map, int64_t n_local,
-                                        const void* const* peer_base, const int* halo_owner, const int* halo_row,
-                                        int64_t ld_peer, void* stream) {
+// ptr_end (optional, null = ptr + 1) and accumulate: walk only slots [ptr[r], ptr_end[r]) of every row and, with accumulate = 1,
+// add to the out / cnt rows an earlier launch produced.  Two launches -- local-neighbour part while the halo rows are still
+// in flight over NVLink, halo-neighbour part afterwards -- give the same result as one launch over the whole rows (up to one
+// extra bf16 rounding of out).
+DGB_API int dgb_seg_add_relu_fwd_ex(const int* ptr, const int* ptr_end, const int* idx, int64_t n_rows, int H, const void* P,
+                                    int64_t ld_p, const void* Q, int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt,
+                                    int64_t ld_cnt, unsigned char* mask, const int* mask_slot_map, int accumulate,
+                                    int64_t n_local, const void* const* peer_base, const int* halo_owner,
+                                    const int* halo_row, int64_t ld_peer, void* stream) {
   if (H % 8 || ld_p % 8 || ld_q % 8 || ld_out % 8 || (cnt && ld_cnt % 8) || !aligned16(P) || !aligned16(Q) ||
       !aligned16(out))
     return (int)cudaErrorInvalidValue;
   SegParams p{};
-  p.ptr = ptr; p.idx = idx; p.n_rows = n_rows; p.H = H;
+  p.ptr = ptr; p.ptr_end = ptr_end; p.accumulate = accumulate; p.idx = idx; p.n_rows = n_rows; p.H = H;
   if (!fits32(ld_q * 2) || !fits32(ld_peer * 2)) return (int)cudaErrorInvalidValue;
   p.src = (const __nv_bfloat16*)Q; p.ld_src_b = (uint32_t)(ld_q * 2);
   p.rowop = (const __nv_bfloat16*)P; p.ld_rowop = ld_p;
@@ -439,8 +461,8 @@ DGB_API int dgb_seg_add_relu_fwd(const int* ptr, const int* idx, int64_t n_rows,
                                  const void* Q, int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt,
                                  int64_t ld_cnt, unsigned char* mask, int64_t n_local, const void* const* peer_base,
                                  const int* halo_owner, const int* halo_row, int64_t ld_peer, void* stream) {
-  return dgb_seg_add_relu_fwd_mapped(ptr, idx, n_rows, H, P, ld_p, Q, ld_q, out, ld_out, cnt, ld_cnt, mask, nullptr, n_local,
-                                     peer_base, halo_owner, halo_row, ld_peer, stream);
+  return dgb_seg_add_relu_fwd_ex(ptr, nullptr, idx, n_rows, H, P, ld_p, Q, ld_q, out, ld_out, cnt, ld_cnt, mask, nullptr, 0,
+                                 n_local, peer_base, halo_owner, halo_row, ld_peer, stream);
 }
 
 // dQ[j,:] = sum_{k in CSC seg j} (P[row[k],:] + Q[j,:] > 0) ? dOut[row[k],:] : 0       (transposed walk)

@@ -32,9 +32,21 @@ class GraphConvLayer(nn.Module):
         self.act = nn.ReLU(inplace=True)
         self.fused = fused
 
+    @staticmethod
+    def _wait_halo(x):
+        """A buffer from ``HaloExchange.augmented(defer=True)`` may still be receiving its halo rows: every path that does not
+        overlap with the transfer itself (``ops/graphconv.py`` does) waits here before the first read."""
+        if x.is_cuda:
+            from dgraph_b200.ops import _pending
+
+            ev = _pending.take(x)
+            if ev is not None:
+                torch.cuda.current_stream().wait_event(ev)
+
     def forward(self, x, edge_index, num_local_nodes, edge_features=None, kernel_plan: Optional[GraphKernelPlan] = None):
         if self.fused and edge_features is None:
             return self._forward_fused(x, edge_index, num_local_nodes, kernel_plan)
+        self._wait_halo(x)
         src, dst = edge_index[:, 0], edge_index[:, 1]
         F_in = (self.conv.weight.shape[1] - (0 if edge_features is None else edge_features.shape[1])) // 2
         x = x[:, :F_in]
@@ -54,6 +66,7 @@ class GraphConvLayer(nn.Module):
             from dgraph_b200.ops.graphconv import graphconv_fused
 
             return graphconv_fused(x, self.conv.weight, self.conv.bias, kp, num_local_nodes, F_in)
+        self._wait_halo(x)
         W = self.conv.weight.to(x.dtype)
         w_i, w_j = W[:, :F_in], W[:, F_in:2 * F_in]
         pad = x.shape[1] - F_in  # features may arrive zero-padded to a 16-byte row (e.g. 100 -> 104 columns)
@@ -87,12 +100,13 @@ class CommAwareGCN(nn.Module):
             x = x.to(self.compute_dtype)
         kp = comm_pattern.kernel_plan(x.device) if self.conv1.fused else None
         edges = comm_pattern.local_edge_list
+        defer = self.conv1.fused  # the fused layer overlaps its local work with the in-flight halo rows (ops/_pending.py)
         with TimingReport("feature-exchange-1"):
-            aug = self.halo_exchanger.augmented(x, comm_pattern)
+            aug = self.halo_exchanger.augmented(x, comm_pattern, defer=defer)
         with TimingReport("process-1"):
             x = self.conv1(aug, edges, n, kernel_plan=kp)
         with TimingReport("feature-exchange-2"):
-            aug = self.halo_exchanger.augmented(x, comm_pattern)
+            aug = self.halo_exchanger.augmented(x, comm_pattern, defer=defer)
         with TimingReport("process-2"):
             x = self.conv2(aug, edges, n, kernel_plan=kp)
         with TimingReport("final-fc"):

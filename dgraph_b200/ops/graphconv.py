@@ -17,6 +17,7 @@ from dgraph_b200.ops.gemm_native import gemm_bf16_nn_grad_w, gemm_bf16_tn
 from dgraph_b200.ops.reduce import colsum
 from dgraph_b200.ops import segment as S
 from dgraph_b200.ops import _sparsity
+from dgraph_b200.ops import _pending
 
 
 class _GraphConvFused(Function):
@@ -34,21 +35,37 @@ class _GraphConvFused(Function):
         bcat[:H] = bias
         # local rows need P and Q (one GEMM, N = 2H); halo rows only Q (N = H) written into the same [n_aug, 2H] buffer
         PQ = torch.empty((n_aug, 2 * H), dtype=torch.bfloat16, device=dev)
+        pull_done = _pending.take(x_aug)  # halo rows still arriving over NVLink (HaloExchange.augmented(defer=True))
         gemm_bf16_tn(x_aug[:n_local], wcat, bcat, None, out=PQ[:n_local])
-        if n_aug > n_local:
-            gemm_bf16_tn(x_aug[n_local:], wcat[H:], None, None, out=PQ[n_local:, H:])
         P, Q = PQ[:n_local, :H], PQ[:, H:]
         need_w = weight.requires_grad or x_aug.requires_grad
         out = torch.empty((n_local, H), dtype=torch.bfloat16, device=dev)
         cnt = torch.empty((n_local, H), dtype=torch.uint16, device=dev) if need_w else None
         mask = torch.empty((kp.num_edges, H // 8), dtype=torch.uint8, device=dev) if need_w else None
         smap = kp.csr_to_csc() if (mask is not None and S.MASK_IN_CSC_ORDER) else None
-        N.check(N.lib().dgb_seg_add_relu_fwd_mapped(
-            N.ptr(kp.rowptr), N.ptr(kp.col), N.i64(n_local), N.i32(H), N.ptr(P), N.i64(2 * H), N.ptr(Q), N.i64(2 * H),
-            N.ptr(out), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(mask), N.ptr(smap), N.i64(n_aug), N.ptr(None), N.ptr(None),
-            N.ptr(None), N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
+
+        def aggregate(ptr, ptr_end, accumulate):
+            N.check(N.lib().dgb_seg_add_relu_fwd_ex(
+                N.ptr(ptr), N.ptr(ptr_end), N.ptr(kp.col), N.i64(n_local), N.i32(H), N.ptr(P), N.i64(2 * H), N.ptr(Q),
+                N.i64(2 * H), N.ptr(out), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(mask), N.ptr(smap), N.i32(accumulate),
+                N.i64(n_aug), N.ptr(None), N.ptr(None), N.ptr(None), N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
+            N.count_launch()
+
+        split = pull_done is not None and n_aug > n_local and kp.num_nbr_local == n_local
+        if split:
+            # pass 1 touches only local neighbours (Q rows < n_local) and overlaps the pull; pass 2 adds the halo neighbours
+            mid = kp.rowmid()
+            aggregate(kp.rowptr, mid, 0)
+            torch.cuda.current_stream().wait_event(pull_done)
+            gemm_bf16_tn(x_aug[n_local:], wcat[H:], None, None, out=PQ[n_local:, H:])
+            aggregate(mid, kp.rowptr[1:], 1)
+        else:
+            if pull_done is not None:
+                torch.cuda.current_stream().wait_event(pull_done)
+            if n_aug > n_local:
+                gemm_bf16_tn(x_aug[n_local:], wcat[H:], None, None, out=PQ[n_local:, H:])
+            aggregate(kp.rowptr, None, 0)
         ctx.mask_csc = smap is not None
-        N.count_launch()
         ctx.save_for_backward(x_aug, wcat, cnt, mask)
         ctx.kp, ctx.n_local, ctx.f_in, ctx.H = kp, n_local, f_in, H
         return out

@@ -133,10 +133,10 @@ class _GraphConvAgg(Function):
         # ReLU bit masks (1 byte per edge and 8 columns = E * H / 8 bytes) let backward gather ONE row per edge
         mask = torch.empty((kp.num_edges, H // 8), dtype=torch.uint8, device=P.device) if (need_q and SAVE_RELU_MASK) else None
         smap = kp.csr_to_csc() if (mask is not None and MASK_IN_CSC_ORDER) else None
-        N.check(N.lib().dgb_seg_add_relu_fwd_mapped(
-            N.ptr(kp.rowptr), N.ptr(kp.col), N.i64(n), N.i32(H), N.ptr(P), N.i64(_ld(P)), N.ptr(Qaug), N.i64(_ld(Qaug)),
-            N.ptr(out), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(mask), N.ptr(smap), N.i64(Qaug.shape[0]), N.ptr(None),
-            N.ptr(None), N.ptr(None), N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
+        N.check(N.lib().dgb_seg_add_relu_fwd_ex(
+            N.ptr(kp.rowptr), N.ptr(None), N.ptr(kp.col), N.i64(n), N.i32(H), N.ptr(P), N.i64(_ld(P)), N.ptr(Qaug),
+            N.i64(_ld(Qaug)), N.ptr(out), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(mask), N.ptr(smap), N.i32(0),
+            N.i64(Qaug.shape[0]), N.ptr(None), N.ptr(None), N.ptr(None), N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
         ctx.mask_csc = smap is not None
         N.count_launch()
         if mask is not None:

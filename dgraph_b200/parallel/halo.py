@@ -56,12 +56,12 @@ class HaloExchange:
               and x_local.dtype == torch.bfloat16 and x_local.dim() == 2 and (x_local.shape[1] * 2) % 16 == 0)
         return engine if ok else None
 
-    def augmented(self, x_local: torch.Tensor, comm_pattern: CommunicationPattern) -> torch.Tensor:
+    def augmented(self, x_local: torch.Tensor, comm_pattern: CommunicationPattern, defer: bool = False) -> torch.Tensor:
         """``cat([x_local, halo])`` -- on the peer-memory engine this is one symmetric buffer filled by ONE pull
         kernel (no ``cat`` copy); elsewhere it is the reference's exchange followed by ``torch.cat``."""
         engine = self._fused_engine(x_local)
         if engine is not None:
-            return engine.halo_exchange_aug(x_local, comm_pattern)
+            return engine.halo_exchange_aug(x_local, comm_pattern, defer=defer)
         if comm_pattern.world_size == 1 and comm_pattern.num_halo_vertices == 0:
             return x_local
         return torch.cat([x_local, self(x_local, comm_pattern)], dim=0)

@@ -50,6 +50,19 @@ class GraphKernelPlan:
             self._csr_to_csc = t
         return t
 
+    def rowmid(self) -> torch.Tensor:
+        """First halo-neighbour slot of every CSR row (rows are neighbour-sorted, local neighbours first): the local part of
+        row r is ``[rowptr[r], rowmid[r])``, the halo part ``[rowmid[r], rowptr[r+1])``."""
+        t = getattr(self, "_rowmid", None)
+        if t is None or t.device != self.col.device:
+            is_local = (self.col < self.num_nbr_local).to(torch.long)
+            pref = torch.zeros(self.col.numel() + 1, dtype=torch.long, device=self.col.device)
+            torch.cumsum(is_local, 0, out=pref[1:])
+            rp = self.rowptr.long()
+            t = (rp[:-1] + (pref[rp[1:]] - pref[rp[:-1]])).to(self.rowptr.dtype).contiguous()
+            self._rowmid = t
+        return t
+
     def restricted_csc(self, rows: torch.Tensor):
         """CSC structure restricted to the edges whose *row* (central vertex) is in ``rows``: ``(colptr, row, csc_to_csr)``.
         Used by the backward of the last message-passing layer when the incoming gradient is zero outside ``rows`` (the

@@ -27,6 +27,7 @@ import torch.distributed as dist
 from torch.autograd import Function
 
 from dgraph_b200.ops import _native as N
+from dgraph_b200.ops import _pending
 from dgraph_b200.parallel.collective_engine import TorchDistEngine
 
 _ALIGN = 256
@@ -356,7 +357,7 @@ class _HaloAug(Function):
     """``aug = cat([x, halo(x)])`` through the symmetric arena; backward pull-reduces halo gradients on the owners."""
 
     @staticmethod
-    def forward(ctx, x, engine, pat):
+    def forward(ctx, x, engine, pat, defer=False):
         info = engine.pattern_info(pat)
         F = x.shape[1]
         assert x.dim() == 2 and (F * x.element_size()) % 16 == 0, "feature rows must be multiples of 16 bytes"
@@ -366,9 +367,24 @@ class _HaloAug(Function):
         aug[: info.n_nbr_local].copy_(x)
         engine.barrier_on_stream()
         rb = F * x.element_size()
-        N.check(N.lib().dgb_halo_pull(N.ptr(aug[info.n_nbr_local:]), N.i64(rb), N.i64(info.n_halo), N.i32(rb),
-                                      N.ptr(engine.arena.ptr_table(off)), N.i64(rb), N.ptr(info.halo_owner),
-                                      N.ptr(info.halo_row), N.i64(info.rot), N.stream()), "dgb_halo_pull")
+
+        def pull():
+            N.check(N.lib().dgb_halo_pull(N.ptr(aug[info.n_nbr_local:]), N.i64(rb), N.i64(info.n_halo), N.i32(rb),
+                                          N.ptr(engine.arena.ptr_table(off)), N.i64(rb), N.ptr(info.halo_owner),
+                                          N.ptr(info.halo_row), N.i64(info.rot), N.stream()), "dgb_halo_pull")
+
+        if defer and info.n_halo > 0:
+            # pull on the side stream, ordered after the barrier; the consumer overlaps local work with it (ops/_pending.py)
+            main = torch.cuda.current_stream()
+            side = engine.side_stream()
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                pull()
+                ev = torch.cuda.Event()
+                ev.record(side)
+            _pending.put(aug, ev)
+        else:
+            pull()
         N.count_launch(2)
         engine.mark_read(off)
         ctx.engine, ctx.pat = engine, pat
@@ -379,7 +395,7 @@ class _HaloAug(Function):
     def backward(ctx, g_aug):
         engine, pat = ctx.engine, ctx.pat
         ctx.slot_guard.release()
-        return _halo_grad_reduce(engine, pat, g_aug), None, None
+        return _halo_grad_reduce(engine, pat, g_aug), None, None, None
 
 
 class PeerMemoryEngine(TorchDistEngine):
@@ -501,6 +517,7 @@ class PeerMemoryEngine(TorchDistEngine):
         """All ranks' streams have reached this point (epoch-flag barrier kernel; no host synchronisation)."""
         if self._world == 1:
             return
+        _pending.wait_all()  # no rank may run ahead of a pull that still reads its peers' slots
         self._epoch += 1
         N.check(N.lib().dgb_peer_barrier(N.ptr(self.arena.pad_table), N.i32(self._rank), N.i32(self._world),
                                          ctypes.c_uint(self._epoch & 0xFFFFFFFF), N.ptr(self._timeout_flag),
@@ -512,11 +529,18 @@ class PeerMemoryEngine(TorchDistEngine):
             raise RuntimeError("peer barrier timed out (a rank did not arrive)")
 
     # ---- fused halo exchange ---------------------------------------------------------------------
-    def halo_exchange_aug(self, x: torch.Tensor, pat) -> torch.Tensor:
-        """``cat([x, halo])`` as one symmetric buffer (rows ``[0, n_local)`` = ``x``)."""
+    def side_stream(self) -> "torch.cuda.Stream":
+        s = getattr(self, "_side_stream", None)
+        if s is None:
+            s = self._side_stream = torch.cuda.Stream(device=self.device)
+        return s
+
+    def halo_exchange_aug(self, x: torch.Tensor, pat, defer: bool = False) -> torch.Tensor:
+        """``cat([x, halo])`` as one symmetric buffer (rows ``[0, n_local)`` = ``x``).  ``defer=True``: the halo rows arrive
+        on a side stream; hand the buffer only to a consumer that waits for ``ops._pending.take(buffer)``."""
         if self._world == 1:
             return x
-        return _HaloAug.apply(x, self, pat)
+        return _HaloAug.apply(x, self, pat, bool(defer) and os.environ.get("DGRAPH_B200_OVERLAP", "1") == "1")
 
     def halo_exchange(self, x: torch.Tensor, pat) -> torch.Tensor:
         if self._world == 1:

@@ -35,13 +35,15 @@ int dgb_seg_add_relu_fwd(const int* ptr, const int* idx, int64_t n_rows, int H, 
                          int64_t n_local, const void* const* peer_base, const int* halo_owner, const int* halo_row,
                          int64_t ld_peer, void* stream);
 
-/* Same, with the mask row of edge slot k at mask_slot_map[k] (null = k): lets the backward walk stream the mask.  The
- * reference has no saved-activation-mask mechanism at all (it re-materialises [E, 2F] edge tensors, GCN.py:43-65). */
-int dgb_seg_add_relu_fwd_mapped(const int* ptr, const int* idx, int64_t n_rows, int H, const void* P, int64_t ld_p,
-                                        const void* Q, int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt,
-                                        int64_t ld_cnt, unsigned char* mask, const int* mask_slot_map, int64_t n_local,
-                                        const void* const* peer_base, const int* halo_owner, const int* halo_row,
-                                        int64_t ld_peer, void* stream);
+/* Extended form: mask row of edge slot k at mask_slot_map[k] (null = k); ptr_end (null = ptr + 1) restricts every row to
+ * slots [ptr[r], ptr_end[r]); accumulate = 1 adds to the out / cnt rows of an earlier launch (local-neighbour pass overlapped
+ * with the NVLink halo pull, halo-neighbour pass afterwards).  No counterpart in the reference (GCN.py:43-65 materialises
+ * [E, 2F] edge tensors). */
+int dgb_seg_add_relu_fwd_ex(const int* ptr, const int* ptr_end, const int* idx, int64_t n_rows, int H, const void* P,
+                            int64_t ld_p, const void* Q, int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt,
+                            int64_t ld_cnt, unsigned char* mask, const int* mask_slot_map, int accumulate, int64_t n_local,
+                            const void* const* peer_base, const int* halo_owner, const int* halo_row, int64_t ld_peer,
+                            void* stream);
 int dgb_seg_add_relu_bwd(const int* colptr, const int* row, int64_t n_aug, int H, const void* dOut, int64_t ld_g,
                          const void* P, int64_t ld_p, const void* Q, int64_t ld_q, void* dQ, int64_t ld_dq, void* stream);
 int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slot_map, const unsigned char* mask, int64_t n_aug,

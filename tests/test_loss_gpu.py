@@ -61,3 +61,39 @@ def test_row_sparse_backward_is_exact():
         d = (p1.grad - p2.grad).norm() / (p2.grad.norm() + 1e-12)
         assert d < 2e-2, (n1, float(d))
     comm.destroy()
+
+
+def test_split_aggregation_matches_single_pass():
+    """Local-neighbour pass + accumulate pass over the halo neighbours (the overlap path of the peer-memory engine, driven here
+    by a dummy event on one GPU) == one pass over whole rows, forward and backward."""
+    from dgraph_b200.ops import _pending
+    from dgraph_b200.ops.graphconv import graphconv_fused
+    from dgraph_b200.parallel.kernel_plan import GraphKernelPlan
+
+    torch.manual_seed(0)
+    dev = torch.device("cuda")
+    n_local, n_halo, F, H = 3000, 1700, 40, 64
+    E = 40000
+    src = torch.randint(0, n_local, (E,), device=dev)
+    dst = torch.randint(0, n_local + n_halo, (E,), device=dev)
+    dst[:50] = n_local + torch.arange(50, device=dev)  # a few rows with only halo neighbours / only local ones exist anyway
+    e = torch.unique(torch.stack([src, dst], 1), dim=0)
+    kp = GraphKernelPlan.from_edges(e, n_local, n_local + n_halo, device=dev, num_nbr_local=n_local)
+    mid = kp.rowmid()
+    assert bool(((kp.rowptr[:-1] <= mid) & (mid <= kp.rowptr[1:])).all())
+    x = torch.randn(n_local + n_halo, F, device=dev).to(torch.bfloat16)
+    w = (torch.randn(H, 2 * F, device=dev) * 0.2).requires_grad_(True)
+    b = torch.randn(H, device=dev).requires_grad_(True)
+    res = []
+    for split in (False, True):
+        xa = x.clone().requires_grad_(True)
+        if split:
+            ev = torch.cuda.Event()
+            ev.record()
+            _pending.put(xa, ev)
+        out = graphconv_fused(xa, w, b, kp, n_local, F)
+        assert _pending.take(xa) is None
+        gw, gb, gx = torch.autograd.grad((out.float() ** 2).sum(), [w, b, xa])
+        res.append((out.float(), gw, gb, gx.float()))
+    for a, c in zip(res[0], res[1]):
+        assert (a - c).norm() <= 1e-2 * c.norm() + 1e-6

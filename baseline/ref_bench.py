@@ -21,9 +21,15 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 REF = os.path.join(HERE, "_ref")
 
 
+def _json_out():
+    import builtins
+
+    return getattr(builtins, "_DGB_JSON_OUT", sys.stdout)  # bench.py keeps the real stdout here (native noise -> stderr)
+
+
 def _unavailable(why: str):
     if int(os.environ.get("RANK", "0")) == 0:
-        print(json.dumps({"impl": "reference", "unavailable": why[:400]}), flush=True)
+        print(json.dumps({"impl": "reference", "unavailable": why[:400]}), file=_json_out(), flush=True)
 
 
 def run(args):
@@ -146,7 +152,7 @@ def run(args):
                            "partition": f"contiguous blocks, cut_fraction={args.cut}",
                            "l2": "inputs larger than L2"},
                 "e2e": e2e, "gpu_launches": 0, "clocks": clocks, "final_loss": float(losses[-1].detach()),
-            }), flush=True)
+            }), file=_json_out(), flush=True)
     except torch.OutOfMemoryError as e:
         _unavailable(f"reference ran out of device memory at {world} GPU(s) on this graph (fp32 [E,2F] edge intermediates): "
                      f"{str(e)[:160]}")

@@ -28,6 +28,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+_JSON_OUT = sys.stdout
 BASELINE_VALUE = None  # BASELINE.md publishes no number for this metric (``published: {}``)
 
 
@@ -293,7 +294,7 @@ def run_ours(args):
             "e2e": e2e, "gpu_launches": n_launch, "clocks": clocks, "final_loss": final_loss,
             "loss_first": float(losses[0].detach()),
         }
-        print(json.dumps(out), flush=True)
+        print(json.dumps(out), file=_JSON_OUT, flush=True)
     comm.destroy()
     if world > 1:
         dist.barrier()
@@ -302,13 +303,22 @@ def run_ours(args):
 
 def main():
     args = parse_args()
+    # stdout carries exactly ONE line (the JSON): anything native libraries print there (NCCL's version banner under
+    # NCCL_DEBUG=VERSION, for instance) is routed to stderr for the whole run.
+    global _JSON_OUT
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    import builtins
+
+    builtins._DGB_JSON_OUT = _JSON_OUT  # baseline/ref_bench.py prints its line through the same descriptor
     if args.impl == "reference":
         sys.path.insert(0, os.path.join(ROOT, "baseline"))
         try:
             import ref_bench
         except Exception as e:  # noqa: BLE001
             if int(os.environ.get("RANK", "0")) == 0:
-                print(json.dumps({"impl": "reference", "unavailable": f"reference harness import failed: {e!r}"[:300]}))
+                print(json.dumps({"impl": "reference", "unavailable": f"reference harness import failed: {e!r}"[:300]}),
+                      file=_JSON_OUT, flush=True)
             return
         ref_bench.run(args)
         return

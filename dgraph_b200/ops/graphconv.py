@@ -9,6 +9,8 @@ Semantics: reference ``GraphConvLayer.forward`` (``experiments/OGB/GCN.py:34-67`
 """
 from __future__ import annotations
 
+import os
+
 import torch
 from torch.autograd import Function
 
@@ -51,7 +53,11 @@ class _GraphConvFused(Function):
                 N.i64(n_aug), N.ptr(None), N.ptr(None), N.ptr(None), N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
             N.count_launch()
 
-        split = pull_done is not None and n_aug > n_local and kp.num_nbr_local == n_local
+        # DGRAPH_B200_OVERLAP (opt-in, default "0" = pull on the main stream): "gemm" overlaps only the local-row GEMM above with
+        # the pull (measured: no gain at 2 GPUs, 13.08 vs 13.10 ms/epoch -- both sides are HBM-bound); "split" also splits the
+        # aggregation (measured slower at 2 GPUs, 14.4 ms: the second pass re-reads P / out / cnt of almost every row).
+        split = (pull_done is not None and n_aug > n_local and kp.num_nbr_local == n_local
+                 and os.environ.get("DGRAPH_B200_OVERLAP", "0") == "split")
         if split:
             # pass 1 touches only local neighbours (Q rows < n_local) and overlaps the pull; pass 2 adds the halo neighbours
             mid = kp.rowmid()

@@ -540,7 +540,7 @@ class PeerMemoryEngine(TorchDistEngine):
         on a side stream; hand the buffer only to a consumer that waits for ``ops._pending.take(buffer)``."""
         if self._world == 1:
             return x
-        return _HaloAug.apply(x, self, pat, bool(defer) and os.environ.get("DGRAPH_B200_OVERLAP", "1") == "1")
+        return _HaloAug.apply(x, self, pat, bool(defer) and os.environ.get("DGRAPH_B200_OVERLAP", "0") != "0")
 
     def halo_exchange(self, x: torch.Tensor, pat) -> torch.Tensor:
         if self._world == 1:

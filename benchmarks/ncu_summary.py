@@ -34,7 +34,7 @@ def main(rep, out):
                 vals.append("-")
         key = name
         seen[key] = seen.get(key, 0) + 1
-        if seen[key] <= 2:
+        if seen[key] <= 4:
             lines.append(f"| `{name}` | " + " | ".join(vals) + " |")
     open(out, "w").write("\n".join(lines) + "\n")
     print("\n".join(lines))

@@ -18,9 +18,10 @@ from dgraph_b200.ops import _sparsity
 
 
 def masked_cross_entropy_ref(logits: torch.Tensor, labels: torch.Tensor, idx: Optional[torch.Tensor]) -> torch.Tensor:
+    up = (lambda t: t) if logits.dtype == torch.float64 else (lambda t: t.float())
     if idx is None:
-        return F.cross_entropy(logits.float(), labels.reshape(-1))
-    return F.cross_entropy(logits.index_select(0, idx).float(), labels.reshape(-1).index_select(0, idx))
+        return F.cross_entropy(up(logits), labels.reshape(-1))
+    return F.cross_entropy(up(logits.index_select(0, idx)), labels.reshape(-1).index_select(0, idx))
 
 
 class _MaskedCE(Function):

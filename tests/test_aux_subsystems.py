@@ -76,3 +76,48 @@ def test_heartbeat_and_health_check(tmp_path, monkeypatch):
     monkeypatch.setenv("DGRAPH_B200_FAULT_INJECT", "nan:rank=0:step=2")
     assert torch.isfinite(watchdog.inject_fault(0, 1, torch.tensor(1.0)))
     assert torch.isnan(watchdog.inject_fault(0, 2, torch.tensor(1.0)))
+
+
+def test_rowmid_and_restricted_csc_match_brute_force():
+    torch.manual_seed(0)
+    n_local, n_halo, E = 40, 25, 400
+    e = torch.unique(torch.stack([torch.randint(0, n_local, (E,)), torch.randint(0, n_local + n_halo, (E,))], 1), dim=0)
+    kp = GraphKernelPlan.from_edges(e, n_local, n_local + n_halo, device="cpu", num_nbr_local=n_local)
+    mid = kp.rowmid()
+    for r in range(n_local):
+        cols = kp.col[kp.rowptr[r]:kp.rowptr[r + 1]]
+        assert bool((cols[: mid[r] - kp.rowptr[r]] < n_local).all()) and bool((cols[mid[r] - kp.rowptr[r]:] >= n_local).all())
+    rows = torch.arange(0, n_local, 3)
+    colptr, row, smap = kp.restricted_csc(rows)
+    assert kp.restricted_csc(rows)[0] is colptr  # cached per index tensor
+    member = set(rows.tolist())
+    for j in range(n_local + n_halo):
+        full = [(int(kp.row[k]), int(kp.csc_to_csr[k])) for k in range(kp.colptr[j], kp.colptr[j + 1])]
+        want = [(i, s) for i, s in full if i in member]
+        got = [(int(row[k]), int(smap[k])) for k in range(colptr[j], colptr[j + 1])]
+        assert got == want
+    inv = kp.csr_to_csc()
+    assert torch.equal(inv[kp.csc_to_csr.long()].long(), torch.arange(kp.num_edges))
+
+
+def test_sparsity_hint_is_one_shot_and_identity_checked():
+    from dgraph_b200.ops import _sparsity
+    from dgraph_b200.ops.loss import masked_cross_entropy, masked_cross_entropy_ref
+
+    g = torch.zeros(6, 3)
+    idx = torch.tensor([1, 4])
+    _sparsity.put(g, idx, torch.ones(2, 3))
+    assert _sparsity.take(torch.zeros(6, 3)) is None  # another tensor: no match, and the slot is consumed
+    assert _sparsity.take(g) is None
+    _sparsity.put(g, idx, torch.ones(2, 3))
+    g.add_(1.0)  # modified after the note was left: stale
+    assert _sparsity.take(g) is None
+    _sparsity.put(g, idx, torch.ones(2, 3))
+    got = _sparsity.take(g)
+    assert got is not None and got[0] is idx
+    logits = torch.randn(9, 4, dtype=torch.float64, requires_grad=True)
+    y = torch.randint(0, 4, (9,))
+    sel = torch.tensor([0, 3, 8])
+    a = masked_cross_entropy(logits, y, sel)  # CPU: reference path
+    assert torch.allclose(a, masked_cross_entropy_ref(logits, y, sel))
+    assert torch.allclose(masked_cross_entropy(logits, y), torch.nn.functional.cross_entropy(logits, y))

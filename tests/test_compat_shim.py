@@ -39,3 +39,39 @@ def test_communicator_contract():
     assert c.alloc_buffer((2, 3), torch.float32, "cpu").shape == (2, 3)
     c.destroy()
     assert Communicator._is_initialized is False
+
+
+def test_entry_points_keep_the_reference_flags():
+    """every CLI flag of the reference entry points is still accepted (extra flags are additions)."""
+    import importlib.util
+    import inspect
+    import os
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    want = {
+        "experiments/OGB/main.py": ["backend", "dataset", "epochs", "lr", "runs", "hidden_dims", "log_dir",
+                                    "node_rank_placement_file", "root_dir"],
+        "experiments/OGB-LSC/main.py": ["comm_type", "dataset", "num_papers", "num_authors", "num_institutions",
+                                        "optimized_graph_structure", "paper_rank_mapping_file", "author_rank_mapping_file",
+                                        "institution_rank_mapping_file", "data_dir"],
+        "experiments/GraphCast/train_graphcast.py": ["batch_size", "is_distributed", "test_run", "use_synthetic_data",
+                                                     "benchmark", "backend", "procs_per_graph"],
+    }
+    saved_path, saved_mods = list(sys.path), set(sys.modules)
+    try:
+        for i, (rel, flags) in enumerate(want.items()):
+            path = os.path.join(root, rel)
+            for m in ("utils", "config", "Trainer", "_common"):  # the experiment folders reuse these short module names
+                sys.modules.pop(m, None)
+            sys.path[:0] = [os.path.dirname(path), os.path.join(root, "experiments")]
+            spec = importlib.util.spec_from_file_location(f"_entry_{i}", path)
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            params = inspect.signature(mod.main).parameters
+            assert not [f for f in flags if f not in params], (rel, [f for f in flags if f not in params])
+    finally:
+        sys.path[:] = saved_path
+        for m in set(sys.modules) - saved_mods:
+            if m in ("utils", "config", "Trainer", "_common", "GCN", "RGAT"):
+                sys.modules.pop(m, None)

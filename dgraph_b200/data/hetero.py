@@ -168,13 +168,93 @@ class SyntheticHeterogeneousDataset(DistributedHeteroGraphDataset):
                          num_classes, comm=comm, split=split, cache_dir=cache_dir)
 
 
-class DGraph_MAG240M_Dataset(DistributedHeteroGraphDataset):
-    """Real OGB-LSC MAG240M (``MAG240M_dataset.py:116-340``); needs the ``ogb`` package and the downloaded dataset."""
+def _edges_touching(ei, src_range, dst_range, chunk: int = 1 << 26) -> torch.Tensor:
+    """Rows ``[E', 2]`` of a (memory-mapped) ``[2, E]`` edge index whose source lies in ``src_range`` or whose destination lies
+    in ``dst_range`` -- everything one rank's plans can depend on -- read in chunks so the 1.3 B-edge citation list is never
+    resident as a whole."""
+    import numpy as np
 
-    def __init__(self, rank, world_size, data_dir="data/MAG240M", comm=None, **kw):
-        try:
-            from ogb.lsc import MAG240MDataset  # noqa: F401
-        except ImportError as e:
-            raise RuntimeError("MAG240M needs the `ogb` package and a local copy of the dataset (no network access here); "
-                               "use SyntheticHeterogeneousDataset for MAG240M-shaped runs") from e
-        raise NotImplementedError("MAG240M ingestion requires the dataset on disk")
+    (slo, shi), (dlo, dhi) = src_range, dst_range
+    keep = []
+    E = int(ei.shape[1])
+    for o in range(0, E, chunk):
+        blk = np.asarray(ei[:, o:o + chunk])
+        m = ((blk[0] >= slo) & (blk[0] < shi)) | ((blk[1] >= dlo) & (blk[1] < dhi))
+        if m.any():
+            keep.append(torch.from_numpy(np.ascontiguousarray(blk[:, m].T).astype(np.int64)))
+    return torch.cat(keep, 0) if keep else torch.zeros(0, 2, dtype=torch.long)
+
+
+class DGraph_MAG240M_Dataset(DistributedHeteroGraphDataset):
+    """Real OGB-LSC MAG240M from the processed files on disk (``MAG240M_dataset.py:116-340``), without the ``ogb`` package:
+    ``data/ogb_raw.MAG240MFiles`` memory-maps ``<data_dir>/mag240m_kddcup2021/processed``.
+
+    Every rank keeps its contiguous block of each node type and only the edges that touch it.  Paper features are this rank's
+    rows of ``paper/node_feat.npy``; author / institution features follow ``features``: ``"mean"`` = average of the written
+    papers' / affiliated authors' features (what the reference computes with ``torch_sparse``), ``"random"`` = unit normal of
+    the same width (what the reference currently trains with: ``randn(..., 1)``, ``MAG240M_dataset.py:150-170``)."""
+
+    def __init__(self, rank, world_size, data_dir="data/MAG240M", comm=None, features: str = "random", feature_dim: int = 0,
+                 cache_dir: Optional[str] = None, dtype=torch.float32, seed: int = 0, **kw):
+        from dgraph_b200.data.ogb_raw import MAG240MFiles, find_mag240m
+
+        if find_mag240m(data_dir) is None:
+            raise RuntimeError(f"no processed MAG240M files under {data_dir} (expected mag240m_kddcup2021/processed/...); there is "
+                               "no network access here -- use SyntheticHeterogeneousDataset for MAG240M-shaped runs")
+        f = MAG240MFiles(data_dir)
+        n = [f.num_papers, f.num_authors, f.num_institutions]
+        offs = [node_offsets(k, world_size) for k in n]
+        rng = [(int(o[rank]), int(o[rank + 1])) for o in offs]
+        cites = _edges_touching(f.edge_index("cites"), rng[0], rng[0])
+        writes = _edges_touching(f.edge_index("writes"), rng[1], rng[0])  # author -> paper
+        affil = _edges_touching(f.edge_index("affiliated_with"), rng[1], rng[2])  # author -> institution
+        edges = [cites, writes.flip(1), writes, affil, affil.flip(1)]  # order of RELATIONS
+        g = torch.Generator().manual_seed(seed + rank)
+        if f.paper_feat is not None and features == "mean":
+            F = int(f.paper_feat.shape[1])
+            paper = f.paper_feat_rows(*rng[0], dtype=dtype)
+
+            def mean_of(dst_lo, dst_hi, e, fetch):  # e: [E, 2] (dst-type id, src-type id); rows of the source via fetch(ids)
+                sel = e[(e[:, 0] >= dst_lo) & (e[:, 0] < dst_hi)]
+                out = torch.zeros(dst_hi - dst_lo, F, dtype=torch.float32)
+                cnt = torch.zeros(dst_hi - dst_lo, dtype=torch.float32)
+                if sel.numel():
+                    out.index_add_(0, sel[:, 0] - dst_lo, fetch(sel[:, 1]).float())
+                    cnt.index_add_(0, sel[:, 0] - dst_lo, torch.ones(sel.shape[0]))
+                return out / cnt.clamp_(min=1).unsqueeze(1)
+
+            def fetch_paper(ids):
+                import numpy as np
+
+                u, inv = torch.unique(ids, return_inverse=True)  # sorted unique ids: monotone reads from the memory map
+                rows = torch.from_numpy(np.asarray(f.paper_feat[u.numpy()]).astype("float32"))
+                return rows[inv]
+
+            author = mean_of(*rng[1], writes, fetch_paper)
+
+            def fetch_author(ids):  # authors of other ranks: recompute their mean from the papers they wrote
+                import numpy as np
+
+                u, inv = torch.unique(ids, return_inverse=True)
+                w = np.asarray(f.edge_index("writes"))
+                m = np.isin(w[0], u.numpy())
+                ee = torch.from_numpy(np.ascontiguousarray(w[:, m].T).astype("int64"))
+                pos = torch.searchsorted(u, ee[:, 0].contiguous())
+                out = torch.zeros(u.numel(), F)
+                cnt = torch.zeros(u.numel())
+                if ee.numel():
+                    out.index_add_(0, pos, fetch_paper(ee[:, 1]))
+                    cnt.index_add_(0, pos, torch.ones(ee.shape[0]))
+                return (out / cnt.clamp_(min=1).unsqueeze(1))[inv]
+
+            inst = mean_of(*rng[2], affil.flip(1), fetch_author)
+            feats = [paper, author.to(dtype), inst.to(dtype)]
+        else:
+            F = feature_dim or (int(f.paper_feat.shape[1]) if f.paper_feat is not None else 1)
+            feats = [f.paper_feat_rows(*rng[0], dtype=dtype) if (f.paper_feat is not None and not feature_dim)
+                     else torch.randn(rng[0][1] - rng[0][0], F, generator=g).to(dtype)]
+            feats += [torch.randn(hi - lo, F, generator=g).to(dtype) for lo, hi in rng[1:]]
+        labels = f.labels()[rng[0][0]:rng[0][1]].contiguous()
+        sp = f.split()
+        split = {"train": sp["train"], "valid": sp.get("valid", sp.get("val")), "test": sp.get("test-dev", sp.get("test"))}
+        super().__init__(rank, world_size, n, feats, edges, labels, f.num_classes, comm=comm, split=split, cache_dir=cache_dir)

@@ -1,7 +1,8 @@
 """OGB node-property datasets, distributed (parity: reference ``DGraph/data/ogbn_datasets.py:25-148`` and
 ``experiments/OGB/ogb_comm_dataset.py:54-145``).
 
-``ogb`` is not installed and there is no network, so when the real dataset cannot be loaded a synthetic graph of the same
+Real data: if the OGB raw files are on disk (``<root>/ogbn_products/raw/*.csv.gz`` + ``split/``), ``data/ogb_raw.py`` parses them
+directly; else the ``ogb`` package is tried; ``ogb`` is not installed here and there is no network, so otherwise a synthetic graph of the same
 shape (``dgraph_b200.data.synthetic.SHAPES``) is generated instead -- every other step (rank-0-first preprocessing with
 barriers, ``torch.save`` cache at ``{dir}/{dname}_graph_data_{W}.pt``, ``__getitem__`` layout) follows the reference."""
 from __future__ import annotations
@@ -21,6 +22,12 @@ num_classes = {"ogbn-arxiv": 40, "ogbn-proteins": 112, "ogbn-papers100M": 172, "
 
 
 def _load_raw(dname: str, root: str, scale: float = 1.0, seed: int = 0):
+    from dgraph_b200.data import ogb_raw
+
+    if ogb_raw.find_ogbn(dname, root) is not None:  # the files are on disk: parse them ourselves, no `ogb` package needed
+        g, y, split = ogb_raw.load_ogbn_raw(dname, root)
+        g = {"node_feat": g["node_feat"], "edge_index": g["edge_index"], "num_nodes": g["num_nodes"]}
+        return g, y, split, False
     try:
         from ogb.nodeproppred import NodePropPredDataset  # type: ignore
 

@@ -79,13 +79,41 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     return LIB
 
 
+HOST_LIB = OUT_DIR / "libdgraph_b200_host.so"
+
+
+def build_host(force: bool = False) -> Path:
+    """Host-only C++ runtime pieces (``csrc/host/*.cpp``: the multilevel graph partitioner) -> ``libdgraph_b200_host.so``.
+    Separate from the CUDA library so that a host-code change never triggers an nvcc rebuild."""
+    srcs = sorted((CSRC / "host").glob("*.cpp"))
+    if not srcs:
+        raise RuntimeError("no host sources")
+    stamp = OUT_DIR / ".build_stamp_host"
+    h = hashlib.sha1()
+    for p in srcs:
+        h.update(p.read_bytes())
+    digest = h.hexdigest()
+    if not force and HOST_LIB.exists() and stamp.exists() and stamp.read_text().strip() == digest:
+        return HOST_LIB
+    OUT_DIR.mkdir(parents=True, exist_ok=True)
+    cxx = os.environ.get("CXX") or shutil.which("g++") or shutil.which("c++")
+    if not cxx:
+        raise RuntimeError("no C++ compiler found")
+    cmd = [cxx, "-O3", "-std=c++17", "-shared", "-fPIC", "-fvisibility=hidden", "-o", str(HOST_LIB), *map(str, srcs)]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"host build failed:\n{r.stderr[-4000:]}")
+    stamp.write_text(digest)
+    return HOST_LIB
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     a = ap.parse_args()
     try:
-        print("BUILD OK", build(a.force, a.verbose))
+        print("BUILD OK", build(a.force, a.verbose), build_host(a.force))
     except Exception as e:  # noqa: BLE001
         print(str(e)[:3000])
         print("BUILD FAILED")

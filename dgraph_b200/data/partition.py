@@ -63,3 +63,39 @@ def bfs_blocks(edge_list: torch.Tensor, num_nodes: int, world_size: int, refine_
 
 def edge_cut_fraction(edge_list: torch.Tensor, part: torch.Tensor) -> float:
     return float((part[edge_list[:, 0]] != part[edge_list[:, 1]]).float().mean())
+
+
+def multilevel(edge_list: torch.Tensor, num_nodes: int, world_size: int, imbalance: float = 1.03, refine_iters: int = 8,
+               seed: int = 0, vertex_weights: torch.Tensor = None) -> torch.Tensor:
+    """Multilevel k-way partition (heavy-edge matching, region growing, greedy boundary refinement) by the native host
+    library ``csrc/host/partition.cpp`` -- the role of ``metis.part_graph`` in the reference's preprocessing
+    (``experiments/OGB/preprocess.py:15-29``).  ``edge_list`` ``[E, 2]`` in any direction; it is symmetrised here.
+    Falls back to :func:`bfs_blocks` when no C++ compiler is available."""
+    import ctypes
+
+    if world_size == 1 or num_nodes == 0:
+        return torch.zeros(num_nodes, dtype=torch.long)
+    try:
+        from dgraph_b200.build import build_host
+
+        lib = ctypes.CDLL(str(build_host()))
+    except Exception:  # noqa: BLE001 - no compiler: keep working with the PyTorch partitioner
+        return bfs_blocks(edge_list, num_nodes, world_size)
+    e = edge_list.detach().cpu().long()
+    e = e[e[:, 0] != e[:, 1]]
+    both = torch.cat([e, e.flip(1)], 0)
+    key = torch.unique(both[:, 0] * num_nodes + both[:, 1])  # sorted: CSR order, duplicates merged
+    src, dst = key // num_nodes, (key % num_nodes).to(torch.int32)
+    rowptr = torch.zeros(num_nodes + 1, dtype=torch.int64)
+    rowptr[1:] = torch.bincount(src, minlength=num_nodes).cumsum(0)
+    dst = dst.contiguous()
+    vw = None if vertex_weights is None else vertex_weights.detach().cpu().to(torch.int64).contiguous()
+    out = torch.empty(num_nodes, dtype=torch.int32)
+    fn = lib.dgb_partition_kway
+    fn.restype = ctypes.c_int64
+    cut = fn(ctypes.c_int64(num_nodes), ctypes.c_void_p(rowptr.data_ptr()), ctypes.c_void_p(dst.data_ptr()),
+             ctypes.c_void_p(0 if vw is None else vw.data_ptr()), ctypes.c_int(world_size), ctypes.c_double(imbalance),
+             ctypes.c_int(refine_iters), ctypes.c_uint64(seed), ctypes.c_void_p(out.data_ptr()))
+    if cut < 0:
+        raise RuntimeError("dgb_partition_kway rejected its arguments")
+    return out.long()

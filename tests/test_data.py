@@ -50,3 +50,34 @@ def test_partitioners_balanced_and_bfs_cuts_less_than_hash():
 def test_split_helpers():
     assert largest_split(10, 4) == 3
     assert [split_per_rank(10, r, 4) for r in range(4)] == [(0, 3), (3, 6), (6, 9), (9, 10)]
+
+
+def test_native_multilevel_partitioner_quality_balance_determinism():
+    """csrc/host/partition.cpp (the METIS role): balanced parts, far fewer cut edges than hashing, better than the BFS blocks on a
+    shuffled 2-D grid, reproducible for a seed, vertex weights respected."""
+    from dgraph_b200.data.partition import bfs_blocks, edge_cut_fraction, hashed, multilevel
+
+    n = 60
+    V = n * n
+    idx = torch.arange(V).view(n, n)
+    e = torch.cat([torch.stack([idx[:, :-1].reshape(-1), idx[:, 1:].reshape(-1)], 1),
+                   torch.stack([idx[:-1].reshape(-1), idx[1:].reshape(-1)], 1)])
+    perm = torch.randperm(V, generator=torch.Generator().manual_seed(0))
+    e = perm[e]  # vertex ids carry no locality
+    for W in (2, 4, 8):
+        p = multilevel(e, V, W, imbalance=1.03)
+        sizes = torch.bincount(p, minlength=W)
+        assert int(p.min()) >= 0 and int(p.max()) == W - 1
+        assert float(sizes.max()) <= 1.03 * (V / W) + 2
+        cut = edge_cut_fraction(e, p)
+        assert cut < 0.25 * edge_cut_fraction(e, hashed(V, W))
+        assert cut <= edge_cut_fraction(e, bfs_blocks(e, V, W)) + 1e-9
+        assert torch.equal(p, multilevel(e, V, W, imbalance=1.03))
+    assert multilevel(e, V, 1).sum() == 0
+    w = torch.ones(V, dtype=torch.long)
+    w[: V // 10] = 10  # a few heavy vertices: parts are balanced by weight, not by count
+    p = multilevel(e, V, 4, vertex_weights=w)
+    pw = torch.zeros(4, dtype=torch.long).index_add_(0, p, w)
+    assert float(pw.max()) <= 1.05 * float(w.sum()) / 4 + 10
+    # isolated vertices and an empty edge list are fine
+    assert multilevel(torch.zeros(0, 2, dtype=torch.long), 10, 3).numel() == 10

@@ -216,9 +216,16 @@ class DistributedGraphCastGraph:
 class DistributedGraphCastGraphGenerator:
     """Builds the global graph once and shards it (``graphcast_graph.py:162-437``)."""
 
-    def __init__(self, lat_lon: Tuple[int, int] = (721, 1440), mesh_level: int = 6, multi: bool = True):
-        self.lat_lon, self.mesh_level, self.multi = lat_lon, mesh_level, multi
+    def __init__(self, lat_lon: Tuple[int, int] = (721, 1440), mesh_level: int = 6, multi: bool = True,
+                 placement: str = "bands"):
+        """``placement``: ``"bands"`` = contiguous latitude bands (no graph partitioner needed); ``"multilevel"`` = the mesh is cut
+        by the native multilevel partitioner (the reference's METIS step, ``data_utils/preprocess.py:14-30``) with every mesh
+        vertex weighted by the grid vertices it feeds, and each grid vertex follows the majority of its mesh2grid sources
+        (the reference derives the grid placement from the bipartite edges as well, ``graphcast_graph.py:85-159``)."""
+        assert placement in ("bands", "multilevel")
+        self.lat_lon, self.mesh_level, self.multi, self.placement = lat_lon, mesh_level, multi, placement
         self._global: Optional[GraphCastGraph] = None
+        self._placements = {}
 
     def global_graph(self) -> GraphCastGraph:
         if self._global is not None:
@@ -240,14 +247,28 @@ class DistributedGraphCastGraphGenerator:
         return self._global
 
     def placements(self, world_size: int) -> Tuple[torch.Tensor, torch.Tensor]:
-        """``(grid_placement [V_grid], mesh_placement [V_mesh])``: contiguous latitude bands."""
+        """``(grid_placement [V_grid], mesh_placement [V_mesh])``."""
+        if world_size in self._placements:
+            return self._placements[world_size]
         g = self.global_graph()
+        if self.placement == "multilevel" and world_size > 1:
+            from dgraph_b200.data.partition import multilevel
+
+            m2g = g.mesh2grid_edges  # [E, 2] = (mesh source, grid destination)
+            w = 1 + torch.bincount(m2g[:, 0], minlength=g.num_mesh)
+            mesh_pl = multilevel(g.mesh_edges, g.num_mesh, world_size, vertex_weights=w)
+            votes = torch.zeros(g.num_grid, world_size, dtype=torch.long)
+            votes.index_put_((m2g[:, 1], mesh_pl[m2g[:, 0]]), torch.ones(m2g.shape[0], dtype=torch.long), accumulate=True)
+            grid_pl = votes.argmax(1)
+            self._placements[world_size] = (grid_pl, mesh_pl)
+            return grid_pl, mesh_pl
         n_lat, n_lon = self.lat_lon
         row_rank = (torch.arange(n_lat) * world_size // n_lat).clamp(max=world_size - 1)
         grid_pl = row_rank.repeat_interleave(n_lon)
         mlat, _ = xyz2sph(g.mesh_xyz)
         lat_row = np.clip(np.round((90.0 - np.rad2deg(mlat)) / 180.0 * (n_lat - 1)), 0, n_lat - 1).astype(np.int64)
         mesh_pl = row_rank[torch.from_numpy(lat_row)]
+        self._placements[world_size] = (grid_pl, mesh_pl)
         return grid_pl, mesh_pl
 
     def shard(self, rank: int, world_size: int) -> DistributedGraphCastGraph:

@@ -14,8 +14,8 @@ from dgraph_b200.data.graphcast_graph import DistributedGraphCastGraphGenerator 
 from dgraph_b200.utils.cli import run_cli  # noqa: E402
 
 
-def main(world_size: int = 4, mesh_level: int = 6, lat: int = 721, lon: int = 1440, out_dir: str = "graphcast_cache"):
-    gen = DistributedGraphCastGraphGenerator((lat, lon), mesh_level)
+def main(world_size: int = 4, mesh_level: int = 6, lat: int = 721, lon: int = 1440, out_dir: str = "graphcast_cache", placement: str = "multilevel"):
+    gen = DistributedGraphCastGraphGenerator((lat, lon), mesh_level, placement=placement)
     g = gen.global_graph()
     grid_pl, mesh_pl = gen.placements(world_size)
     os.makedirs(out_dir, exist_ok=True)

@@ -25,7 +25,7 @@ def loss_fn(pred, target, ranks_per_sample, world):
 
 def main(batch_size: int = 1, is_distributed: bool = False, test_run: bool = False, use_synthetic_data: bool = True,
          benchmark: bool = False, backend: str = "single", procs_per_graph: int = 2, iters: int = 10, mesh_level: int = 6,
-         lat: int = 721, lon: int = 1440, hidden_dim: int = 128, save_dir: str = "", resume: str = ""):
+         lat: int = 721, lon: int = 1440, hidden_dim: int = 128, save_dir: str = "", resume: str = "", placement: str = "bands"):
     from dgraph_b200.data.graphcast_graph import DistributedGraphCastGraphGenerator, SyntheticWeatherDataset
     from dgraph_b200.models.graphcast import Config, DGraphCast
     from dgraph_b200.optim import FusedAdam
@@ -39,7 +39,7 @@ def main(batch_size: int = 1, is_distributed: bool = False, test_run: bool = Fal
         mesh_level, lat, lon, iters = min(mesh_level, 3), min(lat, 46), min(lon, 90), min(iters, 3)
     cfg.model.mesh_level, cfg.model.hidden_dim, cfg.data.latlon_res = mesh_level, hidden_dim, (lat, lon)
     cdt = torch.bfloat16 if dev.type == "cuda" else torch.float32
-    gen = DistributedGraphCastGraphGenerator(cfg.data.latlon_res, cfg.model.mesh_level, cfg.model.multimesh)
+    gen = DistributedGraphCastGraphGenerator(cfg.data.latlon_res, cfg.model.mesh_level, cfg.model.multimesh, placement=placement)
     sg = gen.shard(rank, world).to(dev, cdt)
     data = SyntheticWeatherDataset(cfg.model.input_grid_dim, cfg.data.latlon_res, num_samples=max(iters, 2),
                                    grid_rows=sg.grid_rows_global.cpu())

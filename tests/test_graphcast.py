@@ -33,11 +33,11 @@ def _cfg():
     return c
 
 
-@pytest.mark.parametrize("W", [2, 3])
-def test_distributed_graphcast_matches_single_process(W):
+@pytest.mark.parametrize("W,placement", [(2, "bands"), (3, "bands"), (3, "multilevel")])
+def test_distributed_graphcast_matches_single_process(W, placement):
     torch.manual_seed(0)
     cfg = _cfg()
-    gen = DistributedGraphCastGraphGenerator(cfg.data.latlon_res, cfg.model.mesh_level)
+    gen = DistributedGraphCastGraphGenerator(cfg.data.latlon_res, cfg.model.mesh_level, placement=placement)
     ref = DGraphCast(cfg, comm=None).double()
     state = {k: v.clone() for k, v in ref.state_dict().items()}
     x_full = SyntheticWeatherDataset(5, cfg.data.latlon_res, dtype=torch.float64)[0]["invar"]

@@ -33,14 +33,19 @@ def main(batch_size: int = 1, is_distributed: bool = False, test_run: bool = Fal
 
     assert backend in ("single", "nccl", "nvshmem", "mpi")
     assert batch_size == 1, "full-graph training: one sample per step (as the reference)"
-    comm, rank, world, dev = init_distributed("nccl" if backend == "single" else backend)
+    world_env = int(os.environ.get("WORLD_SIZE", "1"))
+    hybrid = is_distributed and 0 < procs_per_graph < world_env and world_env % procs_per_graph == 0
+    # hybrid data-parallel x graph-partition: `procs_per_graph` ranks share one sample's graph, replicas take different samples
+    comm, rank, world, dev = init_distributed("nccl" if backend == "single" else backend,
+                                              **({"ranks_per_graph": procs_per_graph} if hybrid else {}))
+    g_rank, g_world = comm.get_rank(), comm.get_world_size()
     cfg = Config()
     if test_run:
         mesh_level, lat, lon, iters = min(mesh_level, 3), min(lat, 46), min(lon, 90), min(iters, 3)
     cfg.model.mesh_level, cfg.model.hidden_dim, cfg.data.latlon_res = mesh_level, hidden_dim, (lat, lon)
     cdt = torch.bfloat16 if dev.type == "cuda" else torch.float32
     gen = DistributedGraphCastGraphGenerator(cfg.data.latlon_res, cfg.model.mesh_level, cfg.model.multimesh, placement=placement)
-    sg = gen.shard(rank, world).to(dev, cdt)
+    sg = gen.shard(g_rank, g_world).to(dev, cdt)
     data = SyntheticWeatherDataset(cfg.model.input_grid_dim, cfg.data.latlon_res, num_samples=max(iters, 2),
                                    grid_rows=sg.grid_rows_global.cpu())
     torch.manual_seed(0)
@@ -53,14 +58,18 @@ def main(batch_size: int = 1, is_distributed: bool = False, test_run: bool = Fal
         torch.optim.lr_scheduler.LambdaLR(opt, lambda _e: tc.lr_step3 / tc.lr)],
         milestones=[tc.num_iters_step1, tc.num_iters_step1 + tc.num_iters_step2])
     start = load_checkpoint(resume, model, opt, sched, map_location=dev) if resume else 0
+    from dgraph_b200.utils.dist_utils import CommAwareDistributedSampler
+
+    sampler = CommAwareDistributedSampler(data, comm, shuffle=False)  # every rank of a replica sees the same sample
+    order = list(sampler)
     times = []
     for it in range(start, start + iters):
-        item = data[it % len(data)]
+        item = data[order[it % len(order)]]
         x, y = item["invar"].to(dev, cdt), item["outvar"].to(dev, cdt)
         comm.barrier()
         t0 = time.perf_counter()
         opt.zero_grad()
-        loss = loss_fn(model(x, sg), y, world, world)
+        loss = loss_fn(model(x, sg), y, world, world)  # factor 1: FusedAdam already averages over the whole world
         loss.backward()
         opt.step()
         sched.step()

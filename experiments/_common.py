@@ -7,7 +7,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
-def init_distributed(backend: str = "nccl"):
+def init_distributed(backend: str = "nccl", **comm_kwargs):
     """Returns ``(comm, rank, world, device)``.  Single process -> ``single`` engine; CPU-only box -> gloo."""
     import torch
     import torch.distributed as dist
@@ -27,8 +27,8 @@ def init_distributed(backend: str = "nccl"):
         dist.init_process_group("nccl" if cuda else "gloo", rank=rank, world_size=world,
                                 **({"device_id": dev} if cuda else {}))
     Communicator._is_initialized = False
-    comm = Communicator.init_process_group("single" if world == 1 else backend)
-    return comm, rank, world, dev
+    comm = Communicator.init_process_group("single" if world == 1 else backend, **(comm_kwargs if world > 1 else {}))
+    return comm, rank, world, dev  # rank / world are GLOBAL; comm.get_rank() / get_world_size() are per graph replica
 
 
 def cleanup(comm):

@@ -19,14 +19,16 @@ import torch
 
 ENABLED = os.environ.get("DGRAPH_B200_ROW_SPARSITY", "1") == "1"
 STATS = {"put": 0, "hit": 0, "miss": 0}
-_slot = None  # (data_ptr, shape, dtype, version, idx, compact)
+# (tensor, version at put time, idx, compact).  The tensor itself is kept alive: while the note exists its memory cannot be handed
+# to another tensor, so "same address + same shape / dtype + unchanged version" really means "the very data the note describes".
+_slot = None
 
 
 def put(t: torch.Tensor, idx: torch.Tensor, compact: torch.Tensor) -> None:
     global _slot
     if not ENABLED:
         return
-    _slot = (t.data_ptr(), tuple(t.shape), t.dtype, t._version, idx, compact)
+    _slot = (t, t._version, idx, compact)
     STATS["put"] += 1
 
 
@@ -36,9 +38,11 @@ def take(t: torch.Tensor) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
     s, _slot = _slot, None
     if s is None:
         return None
-    if ENABLED and s[0] == t.data_ptr() and s[1] == tuple(t.shape) and s[2] == t.dtype and s[3] == t._version:
+    ref = s[0]
+    if (ENABLED and ref.data_ptr() == t.data_ptr() and ref.shape == t.shape and ref.dtype == t.dtype
+            and ref.stride() == t.stride() and t._version == s[1] and ref._version == s[1]):
         STATS["hit"] += 1
-        return s[4], s[5]
+        return s[2], s[3]
     STATS["miss"] += 1
     return None
 

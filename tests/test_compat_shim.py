@@ -75,3 +75,48 @@ def test_entry_points_keep_the_reference_flags():
         for m in set(sys.modules) - saved_mods:
             if m in ("utils", "config", "Trainer", "_common", "GCN", "RGAT"):
                 sys.modules.pop(m, None)
+
+
+def test_torch_local_module_matches_reference_semantics():
+    """Same cases as the reference's ``tests/test_local_kernels.py:19-154`` (CPU formulation here; the CUDA kernel behind the
+    same functions is covered by ``test_peer_kernels_gpu.py`` / ``test_segment_ops_gpu.py``)."""
+    import torch
+    from DGraph.torch_local import (local_masked_gather, local_masked_scatter, local_masked_scatter_add_gather,
+                                    local_masked_scatter_gather)
+    import DGraph.torch_nvshmem_p2p as nv
+
+    assert all(hasattr(nv.NVSHMEMP2P, n) for n in ("init", "finalize", "dist_put", "dist_get", "allocate_symmetric_memory",
+                                                   "register_memory", "deregister_memory", "clone_tensor",
+                                                   "padded_clone_tensor", "barrier", "barrier_stream"))
+    torch.manual_seed(0)
+    src = torch.randn(1, 4, 4)
+    idx = torch.tensor([0, 0, 2, 1, 1, 2, 3, 3])
+    rm = torch.tensor([0, 0, 1, 0, 0, 1, 1, 1])
+    out = torch.zeros(1, 8, 4)
+    local_masked_gather(src, idx, rm, out, 1, 4, 4, 8, 0)
+    want = torch.zeros(1, 8, 4)
+    for j in range(8):
+        if rm[j] == 0:
+            want[0, j] = src[0, idx[j]]
+    assert torch.equal(out, want)
+    vals = torch.randn(1, 8, 4)
+    acc = torch.zeros(1, 4, 4)
+    local_masked_scatter(vals, idx, rm, acc, 1, 8, 4, 4, 1)
+    want = torch.zeros(1, 4, 4)
+    for j in range(8):
+        if rm[j] == 1:
+            want[0, idx[j]] += vals[0, j]
+    assert torch.allclose(acc, want)
+    src8 = torch.randn(1, 8, 4)
+    out = torch.zeros(1, 8, 4)
+    local_masked_scatter_gather(src8, torch.tensor([0, 3, 2, 1]), torch.tensor([1, 3, 5, 7]), out, 1, 4, 4, 8)
+    want = torch.zeros(1, 8, 4)
+    for s, d in zip([0, 3, 2, 1], [1, 3, 5, 7]):
+        want[0, d] = src8[0, s]
+    assert torch.equal(out, want)
+    out = torch.zeros(1, 8, 4)
+    local_masked_scatter_add_gather(src8, torch.tensor([0, 3, 2, 1, 3]), torch.tensor([1, 3, 5, 7, 3]), out, 1, 5, 4, 8)
+    want = torch.zeros(1, 8, 4)
+    for s, d in zip([0, 3, 2, 1, 3], [1, 3, 5, 7, 3]):
+        want[0, d] += src8[0, s]
+    assert torch.allclose(out, want)

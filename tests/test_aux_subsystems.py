@@ -121,3 +121,32 @@ def test_sparsity_hint_is_one_shot_and_identity_checked():
     a = masked_cross_entropy(logits, y, sel)  # CPU: reference path
     assert torch.allclose(a, masked_cross_entropy_ref(logits, y, sel))
     assert torch.allclose(masked_cross_entropy(logits, y), torch.nn.functional.cross_entropy(logits, y))
+
+
+def test_packed_counter_arithmetic_of_the_aggregation_kernel():
+    """Host re-statement of the borrow-free packed counters in ``csrc/segment_ops.cu`` (``add_relu_pair``): per edge the kernel
+    does ``word -= mask`` with 0xFFFF per active 16-bit half, repairs the high half once per row with ``word += word << 16``,
+    and an accumulate pass resumes from stored counts with ``word - (word << 16)``."""
+    import random
+
+    M = 0xFFFFFFFF
+    rnd = random.Random(0)
+    for _ in range(200):
+        n1, n2 = rnd.randrange(0, 300), rnd.randrange(0, 300)
+        acts = [(rnd.random() < 0.6, rnd.random() < 0.3) for _ in range(n1 + n2)]
+
+        def run(word, seq):
+            for lo, hi in seq:
+                mk = (0xFFFF if lo else 0) | (0xFFFF0000 if hi else 0)
+                word = (word - mk) & M
+            return word
+
+        def repair(word):
+            return (word + (word << 16)) & M
+
+        one = repair(run(0, acts))
+        lo_true, hi_true = sum(a for a, _ in acts), sum(b for _, b in acts)
+        assert one == ((hi_true << 16) | lo_true)
+        first = repair(run(0, acts[:n1]))  # pass 1 stores true counts ...
+        resumed = (first - (first << 16)) & M  # ... pass 2 converts them back before continuing
+        assert repair(run(resumed, acts[n1:])) == one

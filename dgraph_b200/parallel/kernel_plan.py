@@ -67,11 +67,13 @@ class GraphKernelPlan:
         """CSC structure restricted to the edges whose *row* (central vertex) is in ``rows``: ``(colptr, row, csc_to_csr)``.
         Used by the backward of the last message-passing layer when the incoming gradient is zero outside ``rows`` (the
         labelled vertices).  Built once per index tensor and cached."""
+        # The cache keeps the index tensor alive: as long as an entry exists its memory cannot be recycled for another index
+        # tensor, so "same address, same length, version unchanged since the entry was made" means "same contents".
         cache = self.__dict__.setdefault("_restricted", {})
-        key = (rows.data_ptr(), rows.numel(), rows._version)
+        key = (rows.data_ptr(), rows.numel())
         hit = cache.get(key)
-        if hit is not None:
-            return hit
+        if hit is not None and hit[0]._version == hit[1] == rows._version and hit[0].device == rows.device:
+            return hit[2]
         dev = self.row.device
         member = torch.zeros(self.num_local + 1, dtype=torch.bool, device=dev)
         member[rows.to(dev).long()] = True
@@ -82,7 +84,7 @@ class GraphKernelPlan:
         out = (colptr, self.row[keep].contiguous(), self.csc_to_csr[keep].contiguous())
         if len(cache) >= 4:
             cache.clear()
-        cache[key] = out
+        cache[key] = (rows, rows._version, out)
         return out
 
     @staticmethod

@@ -96,6 +96,9 @@ def test_rowmid_and_restricted_csc_match_brute_force():
         want = [(i, s) for i, s in full if i in member]
         got = [(int(row[k]), int(smap[k])) for k in range(colptr[j], colptr[j + 1])]
         assert got == want
+    rows[0] = 1  # modified in place: the cached plan must not be served for the new contents
+    colptr2, row2, _ = kp.restricted_csc(rows)
+    assert colptr2 is not colptr and set(row2.tolist()) <= set(rows.tolist()) and 0 not in set(row2.tolist())
     inv = kp.csr_to_csc()
     assert torch.equal(inv[kp.csc_to_csr.long()].long(), torch.arange(kp.num_edges))
 

@@ -247,6 +247,23 @@ void rebalance(const Graph& g, int k, int64_t max_pw, std::vector<int32_t>& part
   }
 }
 
+// ew[e] = 1 + |N(v) & N(u)| for every edge (v, u): edges inside a dense neighbourhood become heavy, long-range "small-world"
+// shortcuts (no common neighbours) stay light.  Heavy-edge matching then contracts along the locality of the graph instead of
+// gluing far-apart vertices together, which is what keeps unit-weight matching from finding good cuts on such graphs.
+void triangle_weights(Graph& g) {
+  std::vector<int32_t> stamp(g.n, -1);
+  for (int32_t v = 0; v < g.n; ++v) {
+    for (int64_t e = g.ptr[v]; e < g.ptr[v + 1]; ++e) stamp[g.adj[e]] = v;
+    for (int64_t e = g.ptr[v]; e < g.ptr[v + 1]; ++e) {
+      const int32_t u = g.adj[e];
+      int64_t common = 0;
+      const int64_t b = g.ptr[u], en = std::min<int64_t>(g.ptr[u + 1], b + 256);  // cap the scan of hub neighbours
+      for (int64_t f = b; f < en; ++f) common += (stamp[g.adj[f]] == v);
+      g.ew[e] = 1 + common;
+    }
+  }
+}
+
 int64_t edge_cut(const Graph& g, const std::vector<int32_t>& part) {
   int64_t cut = 0;
   for (int64_t v = 0; v < g.n; ++v)
@@ -258,11 +275,13 @@ int64_t edge_cut(const Graph& g, const std::vector<int32_t>& part) {
 }  // namespace
 
 // n vertices; CSR of the undirected graph (rowptr int64 [n+1], col int32); optional vertex weights (null = 1);
-// k parts; imbalance = allowed max part weight / ideal (e.g. 1.03); part_out int32 [n].  Returns the edge cut (>= 0) or -1.
+// k parts; imbalance = allowed max part weight / ideal (e.g. 1.03); use_triangle_weights: coarsen along common-neighbour-weighted
+// edges (see triangle_weights); part_out int32 [n].  Returns the number of cut edges (>= 0) or -1.
 extern "C" __attribute__((visibility("default"))) int64_t dgb_partition_kway(int64_t n, const int64_t* rowptr,
                                                                               const int32_t* col, const int64_t* vweights,
                                                                               int k, double imbalance, int refine_iters,
-                                                                              uint64_t seed, int32_t* part_out) {
+                                                                              int use_triangle_weights, uint64_t seed,
+                                                                              int32_t* part_out) {
   if (n < 0 || k < 1 || !rowptr || !part_out || (n > 0 && rowptr[n] > 0 && !col)) return -1;
   if (k == 1 || n == 0) {
     if (n > 0) std::memset(part_out, 0, sizeof(int32_t) * (size_t)n);
@@ -277,6 +296,7 @@ extern "C" __attribute__((visibility("default"))) int64_t dgb_partition_kway(int
     g.adj.assign(col, col + rowptr[n]);
     g.ew.assign((size_t)rowptr[n], 1);
     if (vweights) g.vw.assign(vweights, vweights + n); else g.vw.assign(n, 1);
+    if (use_triangle_weights) triangle_weights(g);
   }
   const int64_t total = std::accumulate(levels[0].vw.begin(), levels[0].vw.end(), (int64_t)0);
   const int64_t ideal = (total + k - 1) / k;
@@ -323,6 +343,15 @@ extern "C" __attribute__((visibility("default"))) int64_t dgb_partition_kway(int
       for (int64_t v = 0; v < levels[lvl - 1].n; ++v) fine[v] = part[cmap[v]];
       part.swap(fine);
     }
+  }
+  if (use_triangle_weights) {  // the real objective is the number of cut edges: finish with unit weights on the input graph
+    Graph& g = levels[0];
+    std::fill(g.ew.begin(), g.ew.end(), 1);
+    std::vector<int64_t> pw(k, 0);
+    for (int64_t v = 0; v < g.n; ++v) pw[part[v]] += g.vw[v];
+    for (int it = 0; it < refine_iters; ++it)
+      if (refine_pass(g, k, max_pw, rng, part, pw) == 0) break;
+    rebalance(g, k, max_pw, part, pw);
   }
   std::memcpy(part_out, part.data(), sizeof(int32_t) * (size_t)n);
   return edge_cut(levels[0], part);

@@ -66,7 +66,7 @@ def edge_cut_fraction(edge_list: torch.Tensor, part: torch.Tensor) -> float:
 
 
 def multilevel(edge_list: torch.Tensor, num_nodes: int, world_size: int, imbalance: float = 1.03, refine_iters: int = 8,
-               seed: int = 0, vertex_weights: torch.Tensor = None) -> torch.Tensor:
+               seed: int = 0, vertex_weights: torch.Tensor = None, triangle_weights: bool = True) -> torch.Tensor:
     """Multilevel k-way partition (heavy-edge matching, region growing, greedy boundary refinement) by the native host
     library ``csrc/host/partition.cpp`` -- the role of ``metis.part_graph`` in the reference's preprocessing
     (``experiments/OGB/preprocess.py:15-29``).  ``edge_list`` ``[E, 2]`` in any direction; it is symmetrised here.
@@ -95,7 +95,8 @@ def multilevel(edge_list: torch.Tensor, num_nodes: int, world_size: int, imbalan
     fn.restype = ctypes.c_int64
     cut = fn(ctypes.c_int64(num_nodes), ctypes.c_void_p(rowptr.data_ptr()), ctypes.c_void_p(dst.data_ptr()),
              ctypes.c_void_p(0 if vw is None else vw.data_ptr()), ctypes.c_int(world_size), ctypes.c_double(imbalance),
-             ctypes.c_int(refine_iters), ctypes.c_uint64(seed), ctypes.c_void_p(out.data_ptr()))
+             ctypes.c_int(refine_iters), ctypes.c_int(1 if triangle_weights else 0), ctypes.c_uint64(seed),
+             ctypes.c_void_p(out.data_ptr()))
     if cut < 0:
         raise RuntimeError("dgb_partition_kway rejected its arguments")
     return out.long()

@@ -153,3 +153,51 @@ def test_packed_counter_arithmetic_of_the_aggregation_kernel():
         first = repair(run(0, acts[:n1]))  # pass 1 stores true counts ...
         resumed = (first - (first << 16)) & M  # ... pass 2 converts them back before continuing
         assert repair(run(resumed, acts[n1:])) == one
+
+
+def test_symmetric_slot_rings_bookkeeping():
+    """Host-side slot logic of the peer-memory engine with a fake arena (no GPU): rings grow on demand, tracked entries stay
+    reserved until released, and re-using a slot that peers read in the current epoch inserts a barrier first."""
+    from dgraph_b200.parallel.peer_engine import PeerMemoryEngine
+
+    class FakeArena:
+        def __init__(self):
+            self.slots, self.top = {}, 0
+
+        def slot(self, name, nbytes):
+            if name not in self.slots:
+                self.slots[name] = self.top
+                self.top += (nbytes + 255) // 256 * 256
+            return self.slots[name]
+
+        def tensor(self, off, shape, dtype):
+            return torch.empty(shape, dtype=dtype)
+
+    eng = object.__new__(PeerMemoryEngine)
+    eng._world, eng._rank, eng._epoch, eng._rings, eng._by_off, eng.arena = 2, 0, 0, {}, {}, FakeArena()
+    barriers = []
+
+    def fake_barrier():
+        eng._epoch += 1
+        barriers.append(eng._epoch)
+
+    eng.barrier_on_stream = fake_barrier
+    t1, o1 = eng.slot_tensor("halo", (4, 8), torch.float32, ring=True, track=True)
+    t2, o2 = eng.slot_tensor("halo", (4, 8), torch.float32, ring=True, track=True)
+    assert o1 != o2 and t1.shape == (4, 8)  # first entry is saved for backward -> a second one is added
+    eng.release_slot("halo", o1)
+    _, o3 = eng.slot_tensor("halo", (4, 8), torch.float32, ring=True, track=True)
+    assert o3 == o1  # released entry is re-used, the ring does not grow
+    eng.new_step()
+    _, o4 = eng.slot_tensor("halo", (4, 8), torch.float32, ring=True, track=False)
+    assert o4 == o1 and not barriers
+    eng.mark_read(o4)  # peers read it after the latest barrier ...
+    _, o5 = eng.slot_tensor("halo", (4, 8), torch.float32, ring=True, track=False)
+    assert o5 == o1 and barriers == [1]  # ... so overwriting it needs one more barrier, exactly once
+    _, o6 = eng.slot_tensor("halo", (4, 8), torch.float32, ring=True, track=False)
+    assert barriers == [1]
+    _, p1 = eng.slot_tensor("plain", (16,), torch.bfloat16)
+    _, p2 = eng.slot_tensor("plain", (16,), torch.bfloat16)
+    assert p1 == p2 and p1 not in (o1, o2)  # non-ring keys are one persistent buffer
+    _, q = eng.slot_tensor("halo", (8, 8), torch.float32, ring=True)
+    assert q not in (o1, o2)  # another shape under the same key gets its own ring

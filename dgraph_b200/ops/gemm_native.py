@@ -1,6 +1,8 @@
 """Launch wrappers for ``csrc/gemm_tcgen05.cu`` (tcgen05 / TMEM / TMA GEMM and gather-GEMM)."""
 from __future__ import annotations
 
+import os
+
 import ctypes
 from typing import List, Optional, Sequence
 
@@ -24,6 +26,9 @@ def _as_bf16_rowmajor(t: torch.Tensor) -> torch.Tensor:
     return t
 
 
+_BRES = os.environ.get("DGRAPH_B200_GEMM_BRES", "0") == "1"  # opt-in, not yet validated on hardware
+
+
 def _alloc_out(M: int, Nn: int, dtype, device) -> torch.Tensor:
     """Output with a 16-byte aligned row stride (lets the epilogue use TMA stores); returned as an ``[M, N]`` view."""
     per16 = 16 // torch.empty((), dtype=dtype).element_size()
@@ -42,6 +47,15 @@ def gemm_bf16_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] 
         out = _alloc_out(M, Nn, out_dtype, a.device)
     assert out.stride(1) == 1 and out.dtype in (torch.bfloat16, torch.float32)
     bias_f = None if bias is None else bias.float().contiguous()
+    if _BRES and out.dtype == torch.bfloat16:
+        # experimental B-resident variant for small K (csrc/gemm_bres_tcgen05.cu); 801 = shape not supported -> default kernel
+        rc = N.lib().dgb_gemm_bf16_tn_bres(N.ptr(a), N.i64(a.stride(0)), N.ptr(b), N.i64(b.stride(0)), N.ptr(out),
+                                           N.i64(out.stride(0)), N.i32(M), N.i32(Nn), N.i32(K), N.ptr(bias_f),
+                                           N.i32(_ACT[act]), N.stream())
+        if rc != 801:
+            N.check(rc, "dgb_gemm_bf16_tn_bres")
+            N.count_launch()
+            return out
     N.check(N.lib().dgb_gemm_bf16_tn(N.ptr(a), N.i64(a.stride(0)), N.ptr(b), N.i64(b.stride(0)), N.ptr(out),
                                      N.i64(out.stride(0)), N.i32(M), N.i32(Nn), N.i32(K), N.ptr(bias_f),
                                      N.i32(_ACT[act]), N.i32(1 if out.dtype == torch.float32 else 0), N.stream()),

@@ -157,6 +157,11 @@ int dgb_masked_ce_bwd(const void* logits, int64_t ld, int is_f32, const int64_t*
                               int64_t n_sel, int C, const float* lse, const float* gout, void* dsel, int64_t ld_o,
                               void* stream);
 
+/* Experimental: the same GEMM with the B operand resident in shared memory (small K).  Returns 801 (cudaErrorNotSupported) when
+ * the shape does not fit; opt-in through DGRAPH_B200_GEMM_BRES=1, not yet validated on hardware.  No counterpart in the reference. */
+int dgb_gemm_bf16_tn_bres(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N, int K,
+                          const float* bias, int act, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

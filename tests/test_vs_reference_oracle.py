@@ -101,3 +101,60 @@ def test_reference_gcn_model_runs_unmodified_on_this_framework():
         assert torch.allclose(y_ref, y_ours, atol=1e-9) and torch.allclose(g_ref, g_ours, atol=1e-8)
         assert torch.allclose(y_ours, single[1][1][0][rows], atol=1e-9)
         assert torch.allclose(g_ours, single[1][1][1], atol=1e-8)
+
+
+def test_reference_gat_layer_runs_unmodified_on_this_framework():
+    """The reference's ``CommAwareGAT`` (``experiments/OGB-LSC/RGAT.py``, loaded by path) drives ``comm.gather / scatter`` with
+    ``comm_plan=`` through this repository's ``DGraph`` package on a 3-rank emulated world; with shared weights it must agree
+    with ``dgraph_b200.models.rgat.CommAwareGAT`` (forward and parameter gradients)."""
+    import sys
+
+    d = "/root/reference/experiments/OGB-LSC"
+    if not os.path.exists(os.path.join(d, "RGAT.py")):
+        pytest.skip("reference tree not available")
+    saved = list(sys.path)
+    mods = set(sys.modules)
+    try:
+        sys.path.insert(0, d)  # its sibling modules (distributed_layers, CacheGenerator)
+        spec = importlib.util.spec_from_file_location("_ref_RGAT", os.path.join(d, "RGAT.py"))
+        ref = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(ref)
+    finally:
+        sys.path[:] = saved
+        for m in set(sys.modules) - mods:
+            if m in ("distributed_layers", "CacheGenerator", "config"):
+                sys.modules.pop(m, None)
+
+    from dgraph_b200.models.rgat import CommAwareGAT
+    from dgraph_b200.parallel.comm_plan import COO_to_NCCLEdgeConditionedCommPlan
+    from dgraph_b200.parallel.emulator import run_world
+
+    W, V, F, H = 3, 36, 5, 8
+    e = random_graph(V, 4, seed=7, symmetric=False)
+    off = torch.tensor([V * r // W for r in range(W + 1)])
+    xg = torch.randn(V, F, dtype=torch.float64, generator=torch.Generator().manual_seed(0))
+    torch.manual_seed(3)
+    proto = ref.CommAwareGAT(F, H, None, residual=True).double()
+    state = {k: v.clone() for k, v in proto.state_dict().items()}
+
+    def job(comm):
+        r = comm.get_rank()
+        src, dst = e[:, 0], e[:, 1]
+        mine = torch.nonzero((src >= off[r]) & (src < off[r + 1]), as_tuple=True)[0]
+        # edges live with their source; messages flow source -> destination (the layer's "dest" plan indexes dst)
+        plan = COO_to_NCCLEdgeConditionedCommPlan(r, W, dst, src, mine, off, None, exchange=comm.engine.exchange_ids)
+        x = xg[off[r]:off[r + 1]].unsqueeze(0)
+        res = []
+        for cls in (ref.CommAwareGAT, CommAwareGAT):
+            m = cls(F, H, comm, residual=True).double()
+            m.load_state_dict(state)
+            y = m(x, comm_plan=plan)
+            (y ** 2).sum().backward()
+            g = torch.cat([p.grad.reshape(-1) for p in m.parameters()])
+            comm.all_reduce(g)
+            res.append((y.detach(), g))
+        return res
+
+    for (y_ref, g_ref), (y_ours, g_ours) in run_world(W, job):
+        assert y_ref.shape == y_ours.shape
+        assert torch.allclose(y_ref, y_ours, atol=1e-9) and torch.allclose(g_ref, g_ours, atol=1e-8)

@@ -1,11 +1,49 @@
-"""Reference file name (``experiments/GraphCast/dataset.py:24-226``)."""
+"""Reference file name (``experiments/GraphCast/dataset.py:24-226``).
+
+``SyntheticWeatherDataset`` here takes the reference's constructor arguments (``channels`` as a list, ``num_samples_per_year``,
+``num_steps``, optional ``mesh_vertex_placement``, ``device``, ``grid_size``, ``mesh_level``, ``rank`` / ``world_size`` /
+``ranks_per_graph``, free keyword arguments) and offers ``get_static_graph()``; the fields and the graph come from
+``dgraph_b200.data.graphcast_graph``."""
 import os
 import sys
+from typing import Any, List, Optional, Sequence, Tuple, Union
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import _common  # noqa: F401,E402
 
+import torch  # noqa: E402
+
 from dgraph_b200.data.graphcast_graph import (DistributedGraphCastGraph, DistributedGraphCastGraphGenerator,  # noqa: F401,E402
-                                              SyntheticWeatherDataset)
+                                              SyntheticWeatherDataset as _Fields)
 
 __all__ = ["SyntheticWeatherDataset", "DistributedGraphCastGraphGenerator", "DistributedGraphCastGraph"]
+
+
+class SyntheticWeatherDataset(torch.utils.data.Dataset):
+    def __init__(self, channels: Union[int, Sequence[int]], num_samples_per_year: int, num_steps: int = 1,
+                 mesh_vertex_placement: Optional[torch.Tensor] = None, device: Union[str, torch.device] = "cpu",
+                 grid_size: Tuple[int, int] = (721, 1440), base_temp: float = 15, amplitude: float = 10, noise_level: float = 2,
+                 mesh_level: int = 6, rank: int = 0, world_size: int = 1, ranks_per_graph: int = 1, **kwargs: Any):
+        self.num_channels = channels if isinstance(channels, int) else len(channels)
+        self.num_days, self.num_steps, self.device = int(num_samples_per_year), int(num_steps), torch.device(device)
+        self.grid_size, self.mesh_level = tuple(grid_size), mesh_level
+        self.rank, self.world_size, self.ranks_per_graph = rank, world_size, max(int(ranks_per_graph), 1)
+        self.extra_args = kwargs
+        # ranks of one replica share a graph; `mesh_vertex_placement` (a METIS-style placement file in the reference) selects
+        # the partitioner-based placement, otherwise latitude bands are used
+        placement = "multilevel" if mesh_vertex_placement is not None else "bands"
+        self._gen = DistributedGraphCastGraphGenerator(self.grid_size, mesh_level, placement=placement)
+        g_rank, g_world = rank % self.ranks_per_graph, self.ranks_per_graph if world_size > 1 else 1
+        self._graph = self._gen.shard(g_rank, g_world).to(self.device, torch.float32)
+        self._fields = _Fields(self.num_channels, self.grid_size, num_samples=self.num_days,
+                               grid_rows=self._graph.grid_rows_global.cpu())
+
+    def get_static_graph(self) -> DistributedGraphCastGraph:
+        return self._graph
+
+    def __len__(self) -> int:
+        return self.num_days
+
+    def __getitem__(self, idx: int):
+        item = self._fields[idx]
+        return {"invar": item["invar"].to(self.device), "outvar": item["outvar"].to(self.device)}

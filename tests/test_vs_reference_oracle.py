@@ -182,3 +182,20 @@ def test_reference_single_process_test_files_pass_against_this_package(tmp_path)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
     assert "passed" in tail and "failed" not in tail and "error" not in tail, tail
     assert int(tail.split(" passed")[0].split()[-1]) >= 39, tail
+
+
+@pytest.mark.gpu
+@pytest.mark.xfail(strict=False, reason="added after the round's GPU budget was spent: first hardware run decides (XPASS expected)")
+def test_reference_local_kernel_tests_pass_against_this_package_gpu(tmp_path):
+    """The reference's ``tests/test_local_kernels.py`` (its 1-GPU test of the ``torch_local`` extension), unmodified, with
+    ``DGraph.torch_local`` resolving to this repository's launchers (``csrc/rank_local.cu``)."""
+    import subprocess
+    import sys
+
+    f = "/root/reference/tests/test_local_kernels.py"
+    if not os.path.exists(f):
+        pytest.skip("reference tree not available")
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    r = subprocess.run([sys.executable, "-m", "pytest", f, "-q", "-p", "no:cacheprovider", "--rootdir", str(tmp_path)],
+                       capture_output=True, text=True, cwd=str(tmp_path), env=env, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]

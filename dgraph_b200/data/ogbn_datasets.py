@@ -70,14 +70,23 @@ class DGraphOGBDataset:
     """Halo-plan flavour used by the GCN trainer: ``ds[0] -> (local_feats, local_labels, comm_pattern)``."""
 
     def __init__(self, dname: str, comm, root_dir: str = "data", node_rank_placement: Optional[torch.Tensor] = None,
-                 scale: float = 1.0, seed: int = 0, device="cpu"):
+                 scale: float = 1.0, seed: int = 0, device="cpu", partition: str = "contiguous"):
+        """``partition`` (used when no placement tensor is given): ``"contiguous"`` blocks of vertex ids, ``"multilevel"`` = the
+        native multilevel partitioner (deterministic, so every rank computes the same placement), ``"round_robin"`` = the
+        reference's default (``ogb_comm_dataset.py:54-90``)."""
         self.comm, self.rank, self.world = comm, comm.get_rank(), comm.get_world_size()
         name = {"arxiv": "ogbn-arxiv", "products": "ogbn-products"}.get(dname, dname)
         g, y, split, self.synthetic = _load_raw(name, root_dir, scale, seed)
         self.num_classes = num_classes.get(name, int(y.max()) + 1)
         V = int(g["num_nodes"])
         edges = torch.as_tensor(g["edge_index"]).t().contiguous().long().to(device)
-        if node_rank_placement is None:
+        if node_rank_placement is None and partition == "multilevel" and self.world > 1:
+            from dgraph_b200.data.partition import multilevel
+
+            node_rank_placement = multilevel(edges.cpu(), V, self.world)
+        elif node_rank_placement is None and partition == "round_robin":
+            node_rank_placement = torch.arange(V) % self.world
+        elif node_rank_placement is None:
             # rank-contiguous blocks: what a METIS + renumber pass yields (the reference defaults to round robin)
             node_rank_placement = (torch.arange(V) * self.world // V).clamp(max=self.world - 1)
         part = node_rank_placement.to(device)

@@ -124,7 +124,7 @@ def _run_experiment(dataset, comm, lr, epochs, log_prefix, hidden_dims, num_clas
 def main(backend: str = "nccl", dataset: str = "arxiv", epochs: int = 10, lr: float = 0.001, runs: int = 1,
          hidden_dims: int = 256, log_dir: str = "logs", node_rank_placement_file: str = "", root_dir: str = "data",
          scale: float = 1.0, save: str = "", resume: str = "", timing_report: bool = True, watchdog_s: float = 0.0,
-         health_every: int = 0, trace: str = ""):
+         health_every: int = 0, trace: str = "", partition: str = "contiguous"):
     """Reference flags (``experiments/OGB/main.py:235-362``) plus: ``scale`` (synthetic graph size), ``save`` / ``resume``
     (best-validation checkpoint), ``watchdog_s`` (abort the rank after that many seconds without an epoch), ``health_every``
     (all-rank NaN / timeout check every N epochs), ``trace`` (write a chrome trace of epoch 1's native kernel launches)."""
@@ -136,7 +136,7 @@ def main(backend: str = "nccl", dataset: str = "arxiv", epochs: int = 10, lr: fl
     comm, rank, world, dev = init_distributed(backend)
     TimingReport.init(comm, enabled=timing_report)
     placement = torch.load(node_rank_placement_file, weights_only=False) if node_rank_placement_file else None
-    ds = DGraphOGBDataset(dataset, comm, root_dir, placement, scale=scale, device=dev)
+    ds = DGraphOGBDataset(dataset, comm, root_dir, placement, scale=scale, device=dev, partition=partition)
     if rank == 0:
         print(f"{dataset}{' (synthetic stand-in)' if ds.synthetic else ''}: V={ds.num_nodes} E={ds.num_edges} world={world}")
     os.makedirs(log_dir, exist_ok=True)

@@ -221,6 +221,83 @@ int64_t refine_pass(const Graph& g, int k, int64_t max_pw, std::mt19937_64& rng,
   return moves;
 }
 
+// Fiduccia-Mattheyses style pass with hill climbing: repeatedly apply the best available boundary move (also when its gain is
+// negative), lock the moved vertex, remember the best prefix of the move sequence and roll back everything after it.  This is
+// what gets the greedy refinement above out of its local minima (a straight boundary often needs a few zero / negative moves
+// before a whole bump can be shaved off).  Lazy priority queue: stale entries are recognised by a per-vertex stamp.
+int64_t fm_pass(const Graph& g, int k, int64_t max_pw, std::vector<int32_t>& part, std::vector<int64_t>& pw) {
+  struct Entry { int64_t gain; int32_t v, to; uint32_t stamp; };
+  struct Less { bool operator()(const Entry& a, const Entry& b) const { return a.gain < b.gain; } };
+  std::priority_queue<Entry, std::vector<Entry>, Less> pq;
+  std::vector<uint32_t> stamp(g.n, 0);
+  std::vector<char> locked(g.n, 0);
+  std::vector<int64_t> conn(k, 0);
+  std::vector<int32_t> touched;
+  auto best_move = [&](int32_t v, int64_t& gain, int32_t& to) -> bool {
+    const int32_t pv = part[v];
+    touched.clear();
+    for (int64_t e = g.ptr[v]; e < g.ptr[v + 1]; ++e) {
+      const int32_t pu = part[g.adj[e]];
+      if (conn[pu] == 0) touched.push_back(pu);
+      conn[pu] += g.ew[e];
+    }
+    to = -1;
+    gain = 0;
+    for (int32_t p : touched) {
+      if (p == pv || pw[p] + g.vw[v] > max_pw) continue;
+      const int64_t gn = conn[p] - conn[pv];
+      if (to < 0 || gn > gain) { to = p; gain = gn; }
+    }
+    for (int32_t p : touched) conn[p] = 0;
+    return to >= 0;
+  };
+  for (int32_t v = 0; v < g.n; ++v) {
+    int64_t gain;
+    int32_t to;
+    if (best_move(v, gain, to)) pq.push({gain, v, to, 0});
+  }
+  struct Move { int32_t v, from, to; };
+  std::vector<Move> moves;
+  int64_t cur = 0, best = 0;
+  size_t best_len = 0;
+  const size_t patience = 64 + (size_t)g.n / 200;
+  while (!pq.empty() && moves.size() - best_len < patience) {
+    const Entry e = pq.top();
+    pq.pop();
+    if (locked[e.v] || e.stamp != stamp[e.v]) continue;
+    int64_t gain;
+    int32_t to;
+    if (!best_move(e.v, gain, to)) continue;
+    if (gain != e.gain || to != e.to) {  // neighbourhood changed since the entry was made: re-queue with the fresh gain
+      pq.push({gain, e.v, to, stamp[e.v]});
+      continue;
+    }
+    const int32_t from = part[e.v];
+    part[e.v] = to;
+    pw[from] -= g.vw[e.v];
+    pw[to] += g.vw[e.v];
+    locked[e.v] = 1;
+    moves.push_back({e.v, from, to});
+    cur += gain;
+    if (cur > best) { best = cur; best_len = moves.size(); }
+    for (int64_t f = g.ptr[e.v]; f < g.ptr[e.v + 1]; ++f) {
+      const int32_t u = g.adj[f];
+      if (locked[u]) continue;
+      ++stamp[u];
+      int64_t gu;
+      int32_t tu;
+      if (best_move(u, gu, tu)) pq.push({gu, u, tu, stamp[u]});
+    }
+  }
+  for (size_t i = moves.size(); i > best_len; --i) {  // roll back the tail after the best prefix
+    const Move& m = moves[i - 1];
+    part[m.v] = m.from;
+    pw[m.to] -= g.vw[m.v];
+    pw[m.from] += g.vw[m.v];
+  }
+  return best;
+}
+
 // Moves vertices out of overweight parts (cheapest cut increase first come, first served) until every part fits.
 void rebalance(const Graph& g, int k, int64_t max_pw, std::vector<int32_t>& part, std::vector<int64_t>& pw) {
   std::vector<int64_t> conn(k, 0);
@@ -336,6 +413,8 @@ extern "C" __attribute__((visibility("default"))) int64_t dgb_partition_kway(int
     rebalance(g, k, max_pw, part, pw);
     for (int it = 0; it < refine_iters; ++it)
       if (refine_pass(g, k, max_pw, rng, part, pw) == 0) break;
+    for (int it = 0; it < 4; ++it)
+      if (fm_pass(g, k, max_pw, part, pw) <= 0) break;
     rebalance(g, k, max_pw, part, pw);
     if (lvl > 0) {  // project onto the finer graph
       const std::vector<int32_t>& cmap = cmaps[lvl - 1];
@@ -351,6 +430,8 @@ extern "C" __attribute__((visibility("default"))) int64_t dgb_partition_kway(int
     for (int64_t v = 0; v < g.n; ++v) pw[part[v]] += g.vw[v];
     for (int it = 0; it < refine_iters; ++it)
       if (refine_pass(g, k, max_pw, rng, part, pw) == 0) break;
+    for (int it = 0; it < 4; ++it)
+      if (fm_pass(g, k, max_pw, part, pw) <= 0) break;
     rebalance(g, k, max_pw, part, pw);
   }
   std::memcpy(part_out, part.data(), sizeof(int32_t) * (size_t)n);

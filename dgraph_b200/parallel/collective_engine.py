@@ -107,12 +107,13 @@ class CollectiveEngine(BackendEngine):
             n_rows_local = int(output_size)
         # Keyed on tensor identity + in-place version (not on the data pointer, which the allocator recycles): a hit needs
         # the very same index tensor object, unmodified, so every rank of an SPMD program hits or misses together.
-        key = (kind, id(idx), idx._version, None if rank_mappings is None else (id(rank_mappings), rank_mappings._version),
-               n_rows_local)
+        # (The caller's tensor is the key, not the reshaped / cast view derived from it above -- that is a new object per call.)
+        key = (kind, id(indices), indices._version,
+               None if rank_mappings is None else (id(rank_mappings), rank_mappings._version), n_rows_local)
         hit = self._legacy_plans.get(key)
-        if hit is not None and hit[0]() is idx and (rank_mappings is None or hit[1]() is rank_mappings):
+        if hit is not None and hit[0]() is indices and (rank_mappings is None or hit[1]() is rank_mappings):
             return hit[2]
-        idx_in, rm_in = idx, rank_mappings
+        idx_in, rm_in = indices, rank_mappings
         if rank_mappings is None:
             owner = torch.div(idx, n_rows_local, rounding_mode="floor").clamp_(max=W - 1)
             mine = torch.ones_like(idx, dtype=torch.bool)

@@ -85,3 +85,27 @@ def test_plan_to_and_reverse():
     assert p.source_graph_plan.num_local_edges == e.shape[0]
     single = COO_to_NCCLCommPlan(0, 1, e[:, 1], torch.arange(e.shape[0]), off)
     assert single.local_edge_idx.numel() == e.shape[0]
+
+
+def test_legacy_plan_is_cached_per_index_tensor():
+    """The ``indices + rank_mappings`` API builds its plan (two collectives) once per index tensor object, not once per call."""
+    W, n = 2, 6
+    e = random_graph(W * n, 3, seed=5)
+    xg = torch.randn(W * n, 2, dtype=torch.float64)
+    idx = e[:, 1].unsqueeze(0)
+    rm = torch.stack([e[:, 0] // n, e[:, 1] // n])
+
+    def job(comm):
+        x = xg[comm.get_rank() * n:(comm.get_rank() + 1) * n].unsqueeze(0)
+        comm.gather(x, idx, rm)
+        n1 = len(comm.engine._legacy_plans)
+        p1 = next(iter(comm.engine._legacy_plans.values()))[2]
+        comm.gather(x, idx, rm)
+        comm.gather(x, idx, rm)
+        same = next(iter(comm.engine._legacy_plans.values()))[2] is p1
+        idx2 = idx.clone()
+        comm.gather(x, idx2, rm)
+        return n1, len(comm.engine._legacy_plans), same
+
+    for n1, n2, same in run_world(W, job):
+        assert n1 == 1 and n2 == 2 and same

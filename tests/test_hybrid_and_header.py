@@ -83,3 +83,54 @@ def test_hybrid_dp_graph_partition_gloo():
     ret = mgr.dict()
     mp.spawn(_worker, args=(W, _free_port(), e, xg, ret), nprocs=W, join=True)
     assert all(ret[r] for r in range(W))
+
+
+def _train_worker(rank, W, port, e, xs, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(W))
+    dist.init_process_group("gloo", rank=rank, world_size=W)
+    from dgraph_b200 import Communicator
+    from dgraph_b200.models.gcn import CommAwareGCN
+    from dgraph_b200.optim import FusedAdam
+    from dgraph_b200.parallel import HaloExchange, build_communication_pattern
+
+    Communicator._is_initialized = False
+    comm = Communicator.init_process_group("nccl", ranks_per_graph=2)
+    V = xs[0].shape[0]
+    part = partition(V, 2, "contiguous")
+    pat = build_communication_pattern(e, part, comm.get_rank(), 2)
+    torch.manual_seed(0)
+    model = CommAwareGCN(xs[0].shape[1], 8, 3, HaloExchange(comm), comm)
+    opt = FusedAdam([p for p in model.parameters()], lr=1e-2, comm=comm)
+    x = xs[comm.get_replica_id()][pat.local_vertices_global]  # every replica trains on its own sample
+    opt.zero_grad()
+    (model(x, pat) ** 2).sum().backward()
+    opt.sync_grads()  # SUM over all four ranks: two graph partitions x two replicas
+    ret[rank] = opt.flat_g.clone()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(240)
+def test_hybrid_gradients_equal_sum_over_samples_and_partitions():
+    from dgraph_b200 import Communicator
+    from dgraph_b200.models.gcn import CommAwareGCN
+    from dgraph_b200.optim import FusedAdam
+    from dgraph_b200.parallel import HaloExchange, build_communication_pattern
+    from dgraph_b200.utils.dist_utils import SingleProcessDummyCommunicator
+
+    V = 30
+    e = random_graph(V, 4, seed=2, symmetric=True)
+    xs = [torch.randn(V, 4, generator=torch.Generator().manual_seed(s)) for s in (10, 11)]
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_train_worker, args=(4, _free_port(), e, xs, ret), nprocs=4, join=True)
+    comm = SingleProcessDummyCommunicator()
+    pat = build_communication_pattern(e, torch.zeros(V, dtype=torch.long), 0, 1)
+    torch.manual_seed(0)
+    model = CommAwareGCN(4, 8, 3, HaloExchange(comm), comm)
+    opt = FusedAdam([p for p in model.parameters()], lr=1e-2)
+    opt.zero_grad()
+    for x in xs:  # gradients accumulate over the two samples
+        (model(x, pat) ** 2).sum().backward()
+    for r in range(4):
+        assert torch.allclose(ret[r], opt.flat_g, rtol=1e-4, atol=1e-4 * float(opt.flat_g.abs().max())), r

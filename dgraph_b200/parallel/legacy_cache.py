@@ -141,5 +141,18 @@ def torch_alltoallv_with_comm_map(send_tensor: torch.Tensor, send_splits: List[i
     for k in recv_splits:
         shape[dim] = k
         recv.append(torch.empty(shape, dtype=send_tensor.dtype, device=send_tensor.device))
-    dist.all_to_all(recv, send)
+    if dist.get_backend() == "gloo":  # gloo has no list all-to-all: one send / receive pair per peer instead
+        me = dist.get_rank()
+        recv[me].copy_(send[me])
+        ops = []
+        for r in range(dist.get_world_size()):
+            if r != me and send[r].numel():
+                ops.append(dist.P2POp(dist.isend, send[r], r))
+            if r != me and recv[r].numel():
+                ops.append(dist.P2POp(dist.irecv, recv[r], r))
+        if ops:
+            for req in dist.batch_isend_irecv(ops):
+                req.wait()
+    else:
+        dist.all_to_all(recv, send)
     return torch.cat(recv, dim=dim)

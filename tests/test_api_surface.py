@@ -1,0 +1,147 @@
+"""Less travelled parts of the public API: ``Communicator.put`` contract, rank slices, global scalars, legacy caches and
+all-to-all-v helpers, rank-local aggregation, hetero dataset accessors, TimingReport, the cached OGB wrapper."""
+import os
+import socket
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from dgraph_b200.parallel.emulator import run_world
+from tests._graphs import random_graph
+
+
+def test_put_contract_and_slices_and_global_val():
+    """``put``: chunk i of the send buffer (rows ``send_offsets[i]:send_offsets[i+1]``) lands in rank i's receive buffer at
+    ``recv_offsets[me]`` (``Engine.py:67-86``)."""
+    from dgraph_b200.nn.dist_bn import GetGlobalVal
+
+    W = 3
+    counts = torch.tensor([[0, 2, 1], [3, 0, 2], [1, 1, 0]])  # counts[a, b] rows from a to b
+
+    def job(comm):
+        r = comm.get_rank()
+        send_off = torch.cat([torch.zeros(1, dtype=torch.long), counts[r].cumsum(0)])
+        recv_off = torch.cat([torch.zeros(1, dtype=torch.long), counts[:, r].cumsum(0)])
+        send = torch.stack([torch.full((2,), 100.0 * r + 10 * d + k) for d in range(W) for k in range(int(counts[r, d]))]) \
+            if int(send_off[-1]) else torch.zeros(0, 2)
+        recv = comm.alloc_buffer((int(recv_off[-1]), 2), torch.float32, "cpu")
+        comm.put(send, recv, send_off, recv_off)
+        t = torch.arange(12.0).view(2, 6)
+        return recv, comm.get_local_rank_slice(t, dim=1), GetGlobalVal(r + 1, comm, device="cpu")
+
+    for r, (recv, sl, total) in enumerate(run_world(W, job)):
+        want = [100.0 * s + 10 * r + k for s in range(W) for k in range(int(counts[s, r]))]
+        assert recv[:, 0].tolist() == want
+        assert torch.equal(sl, torch.arange(12.0).view(2, 6)[:, 2 * r:2 * r + 2]) and total == 6.0
+
+
+def test_rank_local_aggregate_and_hetero_accessors():
+    from dgraph_b200.data.hetero import RELATIONS, SyntheticHeterogeneousDataset
+    from dgraph_b200.parallel.rank_local import LocalAggregateWithRemapping, RankLocalRenumberingWithMapping
+
+    data = torch.arange(10.0).view(1, 5, 2)
+    idx = torch.tensor([7, 3, 7, 9, 3])
+    summed, uniq = LocalAggregateWithRemapping(data, idx, 2)
+    assert uniq.tolist() == [3, 7, 9] and summed.shape == (1, 3, 2)
+    assert torch.equal(summed[0], torch.stack([data[0, 1] + data[0, 4], data[0, 0] + data[0, 2], data[0, 3]]))
+    renum, uniq2, ranks = RankLocalRenumberingWithMapping(idx, torch.tensor([1, 0, 1, 2, 0]))
+    assert renum.tolist() == [1, 0, 1, 2, 0] and uniq2.tolist() == [3, 7, 9] and ranks.tolist() == [0, 1, 2]
+    ds = SyntheticHeterogeneousDataset(1, 2, num_papers=64, num_authors=32, num_institutions=4, num_features=6)
+    assert ds.num_relations == len(RELATIONS) == 5 and ds.num_features == 6
+    lo, hi = ds.local_range(0)
+    assert ds.features[0].shape == (hi - lo, 6) and ds.labels.shape == (hi - lo,)
+    m = ds.get_mask("train")
+    assert bool(((m >= 0) & (m < hi - lo)).all()) and ds.get_target("train").shape == m.shape
+    ds.add_batch_dimension()
+    assert ds.features[0].shape == (1, hi - lo, 6)
+    ds.prepare_plans(fused=True, reference_layout=False)
+    assert len(ds.patterns) == 5 and ds.patterns[0].num_local_vertices == hi - lo
+
+
+def test_timing_report_scopes_and_dump(tmp_path):
+    from dgraph_b200.utils import TimingReport
+    from dgraph_b200.utils.dist_utils import SingleProcessDummyCommunicator
+
+    TimingReport.init(SingleProcessDummyCommunicator())
+    with TimingReport("a"):
+        torch.ones(10).sum()
+    TimingReport.start("b")
+    TimingReport.stop("b")
+    TimingReport.add_time("c", 1.5)
+    t = TimingReport.get_timers()
+    assert set(t) == {"a", "b", "c"} and t["c"] == [1.5] and all(v[0] >= 0 for v in t.values())
+    TimingReport.dump(str(tmp_path / "t.json"))
+    assert os.path.getsize(tmp_path / "t.json") > 10
+    TimingReport.enabled = False
+    with TimingReport("off"):
+        pass
+    assert "off" not in TimingReport.get_timers()
+    TimingReport.reset()
+
+
+def test_distributed_ogb_wrapper_caches_and_slices(tmp_path):
+    from dgraph_b200.data.ogbn_datasets import DistributedOGBWrapper
+
+    def job(comm):
+        ds = DistributedOGBWrapper("tiny", comm, dir_name=str(tmp_path))
+        feats, edges, rank_maps, labels = ds[0]
+        return feats.shape, edges.shape, rank_maps.shape, labels.shape, ds.graph_obj.get_nodes_per_rank()
+
+    res = run_world(2, job)
+    assert os.path.exists(tmp_path / "tiny_graph_data_2.pt")  # written once by rank 0, loaded by everyone
+    total = 0
+    for r, (fs, es, rs, ls, per_rank) in enumerate(res):
+        assert fs[0] == ls[0] == int(per_rank[r]) and es[0] == 2 and rs == (2, es[1])
+        total += fs[0]
+    assert total == 10_000
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _a2av_worker(rank, W, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(W))
+    dist.init_process_group("gloo", rank=rank, world_size=W)
+    from dgraph_b200.parallel.legacy_cache import (NCCLGatherCacheGenerator, NCCLScatterCacheGenerator, _nccl_alltoall_v,
+                                                   _nccl_alltoallv_with_dict, torch_alltoallv_with_comm_map)
+
+    # rank r sends (r + 1) rows to the other rank and keeps 1
+    send_counts = [1, rank + 1] if rank == 0 else [rank + 1, 1]
+    recv_counts = [1, 2] if rank == 0 else [1, 1]
+    send = torch.arange(sum(send_counts) * 2, dtype=torch.float32).view(1, -1, 2) + 100 * rank
+    recv = torch.zeros(1, sum(recv_counts), 2)
+    _nccl_alltoall_v(send, recv, None, None, None, None, rank, W, send_counts, recv_counts)
+    got_v = recv.clone()
+    other = 1 - rank
+    d = _nccl_alltoallv_with_dict({other: torch.full((3,), float(rank))}, {other: torch.zeros(3)}, rank, W)
+    cat = torch_alltoallv_with_comm_map(send, send_counts, recv_counts, dim=1)
+    # legacy caches: 8 vertices, 4 per rank; every rank owns the edges whose source it owns
+    e = torch.tensor([[0, 5], [1, 2], [2, 7], [3, 4], [4, 1], [5, 6], [6, 0], [7, 3]])
+    place, dest = e[:, 0] // 4, e[:, 1] // 4
+    gc = NCCLGatherCacheGenerator(e[:, 1], place, dest, 4, rank, W)
+    sc = NCCLScatterCacheGenerator(e[:, 1], place, dest, 4, rank, W)
+    ret[rank] = (got_v, d[other], cat, gc.gather_send_comm_vector, gc.gather_recv_comm_vector, sc.scatter_send_comm_vector,
+                 sc.scatter_recv_comm_vector)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_legacy_alltoallv_helpers_and_caches_gloo():
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_a2av_worker, args=(2, _free_port(), ret), nprocs=2, join=True)
+    r0, r1 = ret[0], ret[1]
+    # rank 0 receives rank 1's first two rows into its second segment; rank 1 receives rank 0's rows 1..2 into its first segment
+    assert torch.equal(r0[0][0, 1:], torch.tensor([[100., 101.], [102., 103.]]))
+    assert torch.equal(r1[0][0, :1], torch.tensor([[2., 3.]]))
+    assert r0[1].tolist() == [1.0] * 3 and r1[1].tolist() == [0.0] * 3
+    assert r0[2].shape == (1, 3, 2) and r1[2].shape == (1, 2, 2)
+    # what one rank sends for a gather is what the other receives, and scatter is the mirror image
+    assert r0[3][1] == r1[4][0] and r1[3][0] == r0[4][1]
+    assert r0[5] == r0[4] and r0[6] == r0[3]

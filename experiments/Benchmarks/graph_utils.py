@@ -7,24 +7,22 @@ import torch
 
 
 @dataclass
-class GatherGraphData:
+class PatternBenchGraph:
+    """Edge list + placement for the halo-plan flavour of the benchmarks (``TestNCCL.py --sweep``)."""
     edge_list: torch.Tensor  # [E, 2] global (central, neighbour)
     partitioning: torch.Tensor  # [V]
     num_vertices: int
 
 
-ScatterGraphData = GatherGraphData
-
-
-def all_pairs_graph(world_size: int, verts_per_rank: int = 1) -> GatherGraphData:
+def all_pairs_graph(world_size: int, verts_per_rank: int = 1) -> PatternBenchGraph:
     V = world_size * verts_per_rank
     part = torch.arange(V) // verts_per_rank
     u, v = torch.meshgrid(torch.arange(V), torch.arange(V), indexing="ij")
     m = part[u] != part[v]
-    return GatherGraphData(torch.stack([u[m], v[m]], 1), part, V)
+    return PatternBenchGraph(torch.stack([u[m], v[m]], 1), part, V)
 
 
-def halo_rows_graph(world_size: int, local_rows: int, halo_rows_per_peer: int, seed: int = 0) -> GatherGraphData:
+def halo_rows_graph(world_size: int, local_rows: int, halo_rows_per_peer: int, seed: int = 0) -> PatternBenchGraph:
     """Every rank pulls ``halo_rows_per_peer`` distinct rows from every other rank (one edge per pulled row)."""
     V = world_size * local_rows
     part = torch.arange(V) // local_rows
@@ -37,4 +35,75 @@ def halo_rows_graph(world_size: int, local_rows: int, halo_rows_per_peer: int, s
             nb = torch.randperm(local_rows, generator=g)[:halo_rows_per_peer] + q * local_rows
             ce = torch.randint(0, local_rows, (nb.numel(),), generator=g) + r * local_rows
             es.append(torch.stack([ce, nb], 1))
-    return GatherGraphData(torch.cat(es), part, V)
+    return PatternBenchGraph(torch.cat(es), part, V)
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+# The reference's data holders and generators for the vector-addressed (legacy API) benchmarks: one vertex per rank, one edge from
+# every rank to every other rank ("all pairs").  Tensors follow the layouts of `comm.gather(x, indices, rank_mappings)` /
+# `comm.scatter(x, indices, rank_mappings, output_size)`.
+# ---------------------------------------------------------------------------------------------------------------------------
+@dataclass
+class GatherGraphData:
+    vertex_data: torch.Tensor          # [W, F]: row r is the vertex owned by rank r
+    vertex_rank_mapping: torch.Tensor  # [W]
+    edge_rank_placement: torch.Tensor  # [1, E]: rank that holds each edge
+    edge_src_rank: torch.Tensor        # [1, E]: rank that owns the vertex each edge reads
+    edge_indices: torch.Tensor         # [1, E]: global vertex id each edge reads
+
+
+@dataclass
+class ScatterGraphData:
+    vertex_data: torch.Tensor          # [1, E, F]: one row per edge
+    data_rank_mapping: torch.Tensor    # [1, E]
+    edge_rank_placement: torch.Tensor  # [1, E]
+    edge_dest_rank: torch.Tensor       # [1, E]: rank that owns the vertex each edge adds to
+    edge_indices: torch.Tensor         # [1, E]: global vertex id each edge adds to
+    num_local_vertices: int
+
+
+def _all_pairs(world_size: int, ranks_per_node=None, intra_node_only=False):
+    assert ranks_per_node is not None or not intra_node_only, "ranks_per_node must be provided if intra_node_only is True"
+    holder, target = [], []
+    for i in range(world_size):
+        for j in range(world_size):
+            if i == j or (intra_node_only and i // ranks_per_node != j // ranks_per_node):
+                continue
+            holder.append(i)
+            target.append(j)
+    return torch.tensor(holder, dtype=torch.long).unsqueeze(0), torch.tensor(target, dtype=torch.long).unsqueeze(0)
+
+
+def get_nccl_gather_benchmark_data(sample_size, world_size, device, ranks_per_node=None, intra_node_only=False):
+    g = torch.Generator().manual_seed(0)
+    holder, target = _all_pairs(world_size, ranks_per_node, intra_node_only)
+    return GatherGraphData(vertex_data=torch.randn(world_size, sample_size, generator=g).to(device),
+                           vertex_rank_mapping=torch.arange(world_size, device=device),
+                           edge_rank_placement=holder.to(device), edge_src_rank=target.to(device),
+                           edge_indices=target.clone().to(device))
+
+
+def get_nccl_scatter_benchmark_data(sample_size, world_size, device, ranks_per_node=None, intra_node_only=False):
+    g = torch.Generator().manual_seed(0)
+    holder, target = _all_pairs(world_size, ranks_per_node, intra_node_only)
+    E = holder.shape[1]
+    return ScatterGraphData(vertex_data=torch.randn(1, E, sample_size, generator=g).to(device),
+                            data_rank_mapping=holder.clone().to(device), edge_rank_placement=holder.to(device),
+                            edge_dest_rank=target.to(device), edge_indices=target.clone().to(device), num_local_vertices=1)
+
+
+def get_nvshmem_gather_benchmark_data(sample_size, world_size, device, ranks_per_node=None, intra_node_only=False, **_):
+    """Same pattern; the one-sided engine takes the same tensors here (no separate symmetric-heap staging is needed)."""
+    return get_nccl_gather_benchmark_data(sample_size, world_size, device, ranks_per_node, intra_node_only)
+
+
+def get_nvshmem_scatter_benchmark_data(sample_size, world_size, device, ranks_per_node=None, intra_node_only=False, **_):
+    return get_nccl_scatter_benchmark_data(sample_size, world_size, device, ranks_per_node, intra_node_only)
+
+
+def safe_create_dir(directory, rank):
+    """Rank 0 creates the directory (no error when it exists)."""
+    import os
+
+    if rank == 0:
+        os.makedirs(directory, exist_ok=True)

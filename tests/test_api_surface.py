@@ -145,3 +145,35 @@ def test_legacy_alltoallv_helpers_and_caches_gloo():
     # what one rank sends for a gather is what the other receives, and scatter is the mirror image
     assert r0[3][1] == r1[4][0] and r1[3][0] == r0[4][1]
     assert r0[5] == r0[4] and r0[6] == r0[3]
+
+
+def test_benchmark_graph_utils_all_pairs_through_legacy_api():
+    """The reference's benchmark data generators (``experiments/Benchmarks/graph_utils.py``) drive the legacy gather / scatter
+    API: with one vertex per rank every rank gathers the vertices of all other ranks, and scattering the edge rows back sums, per
+    vertex, the rows of all edges that point at it."""
+    import importlib.util
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("_bench_graph_utils", os.path.join(root, "experiments", "Benchmarks", "graph_utils.py"))
+    gu = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gu)
+    W, F = 4, 3
+    gd = gu.get_nccl_gather_benchmark_data(F, W, "cpu")
+    sd = gu.get_nccl_scatter_benchmark_data(F, W, "cpu")
+    assert gd.edge_indices.shape == (1, W * (W - 1)) and sd.vertex_data.shape == (1, W * (W - 1), F)
+
+    def job(comm):
+        r = comm.get_rank()
+        x = gd.vertex_data[r:r + 1].unsqueeze(0)  # [1, 1, F]: this rank's vertex
+        rm = torch.cat([gd.edge_rank_placement, gd.edge_src_rank], 0)
+        got = comm.gather(x, gd.edge_indices, rm)  # rows for the edges held by this rank
+        mine = sd.edge_rank_placement[0] == r
+        back = comm.scatter(sd.vertex_data[:, mine], sd.edge_indices, torch.cat([sd.edge_rank_placement, sd.edge_dest_rank], 0),
+                            sd.num_local_vertices)
+        return got[0], back[0]
+
+    for r, (got, back) in enumerate(run_world(W, job)):
+        others = [j for j in range(W) if j != r]
+        assert torch.allclose(got, gd.vertex_data[others])
+        to_me = sd.edge_indices[0] == r
+        assert torch.allclose(back[0], sd.vertex_data[0, to_me].sum(0))

@@ -20,7 +20,8 @@ import numpy as np  # noqa: E402
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
-from graph_utils import all_pairs_graph, halo_rows_graph  # noqa: E402
+from graph_utils import (all_pairs_graph, get_nccl_gather_benchmark_data, get_nccl_scatter_benchmark_data,  # noqa: E402
+                         halo_rows_graph)
 
 
 def _time(fn, iters, dev):
@@ -70,6 +71,34 @@ def run(comm, graph, F, iters, dev, engine_name):
             "frac_of_770GBps": float(b[0]) / float(t[0]) / 1e6 / 770.0, "per_iter": gather}
 
 
+def run_legacy(comm, F, iters, dev, use_cache):
+    """The reference's own protocol: all-pairs pattern (one vertex per rank), vector-addressed ``comm.gather`` /
+    ``comm.scatter`` with ``indices + rank_mappings``, per-iteration times.  ``use_cache=False`` drops the cached plan before
+    every call, i.e. pays the two metadata collectives each time (the reference's "no cache" arm)."""
+    rank, world = comm.get_rank(), comm.get_world_size()
+    gd = get_nccl_gather_benchmark_data(F, world, dev)
+    sd = get_nccl_scatter_benchmark_data(F, world, dev)
+    x = gd.vertex_data[rank:rank + 1].unsqueeze(0).contiguous()
+    g_map = torch.cat([gd.edge_rank_placement, gd.edge_src_rank], 0)
+    s_map = torch.cat([sd.edge_rank_placement, sd.edge_dest_rank], 0)
+    mine = sd.edge_rank_placement[0] == rank
+    vals = sd.vertex_data[:, mine].contiguous()
+
+    def drop():
+        if not use_cache and hasattr(comm.engine, "_legacy_plans"):
+            comm.engine._legacy_plans.clear()
+
+    def gather():
+        drop()
+        comm.gather(x, gd.edge_indices, g_map)
+
+    def scatter():
+        drop()
+        comm.scatter(vals, sd.edge_indices, s_map, sd.num_local_vertices)
+
+    return _time(gather, iters, dev), _time(scatter, iters, dev)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--message_size", type=int, default=128)
@@ -83,6 +112,15 @@ def main():
     os.makedirs(a.log_dir, exist_ok=True)
     name = type(comm.engine).__name__
     results = []
+    if not a.sweep and world > 1:  # the reference's legacy-API arm (with the plan cache, and without it on --benchmark_cache)
+        for cached in ([True, False] if a.benchmark_cache else [True]):
+            g_t, s_t = run_legacy(comm, a.message_size, min(a.num_iters, 1000), dev, cached)
+            tag = "cache" if cached else "nocache"
+            np.save(os.path.join(a.log_dir, f"legacy_gather_{tag}_{name}_rank{rank}.npy"), g_t)
+            np.save(os.path.join(a.log_dir, f"legacy_scatter_{tag}_{name}_rank{rank}.npy"), s_t)
+            results.append({"engine": name, "api": f"legacy ({tag})", "F": a.message_size,
+                            "gather_ms": float(g_t[10:].mean()) if len(g_t) > 10 else float(g_t.mean()),
+                            "scatter_ms": float(s_t[10:].mean()) if len(s_t) > 10 else float(s_t.mean())})
     if not a.sweep:
         r = run(comm, all_pairs_graph(world), a.message_size, a.num_iters, dev, name)
         np.save(os.path.join(a.log_dir, f"gather_times_{name}_rank{rank}.npy"), r.pop("per_iter"))

@@ -212,6 +212,32 @@ def plan_from_requests(
     )
 
 
+def offline_exchange(global_edge_owner_key: torch.Tensor, global_vertex_ids: torch.Tensor, key_offset: torch.Tensor,
+                     vertex_offset: torch.Tensor, rank: int, world_size: int) -> Callable:
+    """An ``exchange`` callable that needs no process group: with the *global* edge arrays at hand, what every other rank will
+    ask ``rank`` for can be computed locally.  ``global_edge_owner_key`` decides which rank holds an edge (its source vertex with
+    ``key_offset``), ``global_vertex_ids`` is the endpoint the plan indexes (partitioned by ``vertex_offset``).  Lets one process
+    pre-build and store the plans of all ranks (``experiments/OGB/GenerateCache.py``)."""
+    dev = global_vertex_ids.device
+    koff, voff = key_offset.to(dev).long(), vertex_offset.to(dev).long()
+    holder = torch.bucketize(global_edge_owner_key.to(dev).long(), koff, right=True) - 1
+    ids = global_vertex_ids.to(dev).long()
+    wanted = (ids >= voff[rank]) & (ids < voff[rank + 1]) & (holder != rank)  # edges of other ranks that read my vertices
+
+    def exchange(_ids, _send_splits):
+        rows, splits = [], []
+        for q in range(world_size):
+            if q == rank:
+                splits.append(0)
+                continue
+            u = torch.unique(ids[wanted & (holder == q)]) - voff[rank]  # sorted: the order fast_2D_unique gives the requester
+            rows.append(u)
+            splits.append(int(u.numel()))
+        return (torch.cat(rows) if rows else torch.empty(0, dtype=torch.long, device=dev)), splits
+
+    return exchange
+
+
 def COO_to_NCCLEdgeConditionedCommPlan(
     rank: int,
     world_size: int,

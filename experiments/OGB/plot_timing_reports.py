@@ -6,6 +6,39 @@ import re
 import sys
 
 
+def plot_stacked_bar_from_dicts(data, x_ticks=None, plot_filename="stacked_bar_plot.png", title="Stacked Bar Plot"):
+    """One stacked bar per dictionary of ``data``: keys are timing scopes, values lists of per-epoch milliseconds, segment height
+    = mean of the list (scopes ``cache_generation_time`` and ``pre-processing`` are left out, as in the reference).  Returns the
+    per-bar means; draws the figure when matplotlib is importable."""
+    if not data:
+        print("Input data is empty. Cannot generate a plot.")
+        return None
+    skip = {"cache_generation_time", "pre-processing"}
+    keys = [k for k in data[0] if k not in skip]
+    means = [{k: (sum(d[k]) / len(d[k]) if d.get(k) else 0.0) for k in keys} for d in data]
+    ticks = [str(t) for t in (x_ticks if x_ticks is not None else range(len(data)))]
+    try:
+        import matplotlib
+
+        matplotlib.use("Agg")
+        import matplotlib.pyplot as plt
+    except ImportError:
+        return means
+    plt.figure()
+    bottom = [0.0] * len(data)
+    for k in keys:
+        vals = [m[k] for m in means]
+        plt.bar(ticks, vals, bottom=bottom, label=k.replace("_", " "))
+        bottom = [b + v for b, v in zip(bottom, vals)]
+    plt.ylabel("ms / epoch")
+    plt.xlabel("ranks")
+    plt.title(title)
+    plt.legend()
+    plt.savefig(plot_filename)
+    plt.close()
+    return means
+
+
 def main(log_dir="logs", dataset="products"):
     rows = {}
     for f in sorted(glob.glob(f"{log_dir}/{dataset}_timing_report_world*.json")):

@@ -46,3 +46,26 @@ def safe_plot(x, ys, labels, title, path):
     plt.savefig(path)
     plt.close()
     return True
+
+
+def cleanup():
+    """Tear down the default process group if there is one (reference ``utils.py:7-9``)."""
+    import torch.distributed as dist
+
+    if dist.is_available() and dist.is_initialized():
+        dist.destroy_process_group()
+
+
+def safe_create_dir(directory, rank):
+    if rank == 0:
+        os.makedirs(directory, exist_ok=True)
+
+
+def visualize_trajectories(trajectories, title, figsave, rank):
+    """Rank 0 plots mean +- std over runs of a per-epoch metric (``[runs, epochs]``) and saves the figure."""
+    if rank != 0:
+        return False
+    import numpy as np
+
+    t = np.asarray(trajectories)
+    return safe_plot(np.arange(t.shape[-1]), [np.atleast_2d(t)], [title], title, figsave)

@@ -109,3 +109,31 @@ def test_legacy_plan_is_cached_per_index_tensor():
 
     for n1, n2, same in run_world(W, job):
         assert n1 == 1 and n2 == 2 and same
+
+
+def test_offline_plan_generation_equals_collective_build():
+    """``experiments/OGB/GenerateCache.py::generate_comm_plan`` (no process group, global COO list) == the plans the ranks build
+    together through the exchange collective."""
+    import importlib.util
+    import os
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("_gen_cache", os.path.join(root, "experiments", "OGB", "GenerateCache.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    W, V = 3, 30
+    e = random_graph(V, 4, seed=11, symmetric=False)
+    off = torch.tensor([0, 7, 19, 30])
+
+    def job(comm):
+        r = comm.get_rank()
+        mine = torch.nonzero((e[:, 0] >= off[r]) & (e[:, 0] < off[r + 1]), as_tuple=True)[0]
+        return COO_to_NCCLEdgeConditionedCommPlan(r, W, e[:, 0], e[:, 1], mine, off, None, exchange=comm.engine.exchange_ids)
+
+    for r, live in enumerate(run_world(W, job)):
+        offline = gen.generate_comm_plan(e.t(), off, r, W)
+        for a, b in ((live.source_graph_plan, offline.source_graph_plan), (live.dest_graph_plan, offline.dest_graph_plan)):
+            for f in ("local_edge_idx", "local_vertex_idx", "boundary_edge_idx", "boundary_edge_buffer_map", "boundary_vertex_idx"):
+                assert torch.equal(getattr(a, f), getattr(b, f)), (r, f)
+            assert list(a.boundary_edge_splits) == list(b.boundary_edge_splits)
+            assert list(a.boundary_vertex_splits) == list(b.boundary_vertex_splits)

@@ -220,7 +220,7 @@ def offline_exchange(global_edge_owner_key: torch.Tensor, global_vertex_ids: tor
     pre-build and store the plans of all ranks (``experiments/OGB/GenerateCache.py``)."""
     dev = global_vertex_ids.device
     koff, voff = key_offset.to(dev).long(), vertex_offset.to(dev).long()
-    holder = torch.bucketize(global_edge_owner_key.to(dev).long(), koff, right=True) - 1
+    holder = torch.bucketize(global_edge_owner_key.to(dev).long().contiguous(), koff, right=True) - 1
     ids = global_vertex_ids.to(dev).long()
     wanted = (ids >= voff[rank]) & (ids < voff[rank + 1]) & (holder != rank)  # edges of other ranks that read my vertices
 

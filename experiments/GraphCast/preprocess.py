@@ -14,6 +14,62 @@ from dgraph_b200.data.graphcast_graph import DistributedGraphCastGraphGenerator 
 from dgraph_b200.utils.cli import run_cli  # noqa: E402
 
 
+# ---- the reference's helper names (``experiments/GraphCast/preprocess.py:17-87``), on networkx graphs -------------------------
+def create_graphcast_meshgraph(mesh_level: int = 6):
+    """``(vertices [V, 3], edges [E, 2])`` of the bidirected multimesh (every refinement level merged)."""
+    from dgraph_b200.data.graphcast_graph import multimesh
+
+    v, _faces, e, _max_len = multimesh(mesh_level)
+    return torch.from_numpy(v).float(), torch.from_numpy(e).long()
+
+
+def graphcast_graph_to_nxgraph(mesh_graph):
+    import networkx as nx
+
+    G = nx.Graph()
+    G.add_nodes_from(range(int(mesh_graph[0].shape[0])))
+    G.add_edges_from(map(tuple, mesh_graph[1].tolist()))
+    return G
+
+
+def save_nx_meshgraph(nx_graph, filename):
+    import pickle
+
+    with open(filename, "wb") as f:
+        pickle.dump(nx_graph, f)
+
+
+def partition_graph(G, num_ranks: int):
+    """Vertex placement ``[num_nodes]`` of a networkx graph (METIS in the reference; the native multilevel partitioner here)."""
+    from dgraph_b200.data.partition import multilevel
+
+    e = torch.tensor(list(G.edges()), dtype=torch.long).reshape(-1, 2)
+    return multilevel(e, G.number_of_nodes(), num_ranks)
+
+
+def node_renumbering(node_rank_placement, num_parts):
+    """New -> old vertex list: old ids grouped by rank."""
+    return torch.argsort(torch.as_tensor(node_rank_placement).long(), stable=True)
+
+
+def edge_renumbering(edge_indices, renumbered_nodes):
+    """``[E, 2]`` edges in old ids -> ``[2, E]`` in new ids (through the inverse of the new -> old list)."""
+    new_to_old = torch.as_tensor(renumbered_nodes).long()
+    old_to_new = torch.empty_like(new_to_old)
+    old_to_new[new_to_old] = torch.arange(new_to_old.numel())
+    e = torch.as_tensor(list(edge_indices) if not torch.is_tensor(edge_indices) else edge_indices).long().reshape(-1, 2)
+    return torch.stack([old_to_new[e[:, 0]], old_to_new[e[:, 1]]])
+
+
+def metis_partition_graph(nx_graph, num_ranks):
+    """``(placement, new -> old vertex list, renumbered edges)`` of the mesh graph (the reference's function stops after the
+    renumbering, ``preprocess.py:76-87``; grid placement and bipartite edges are handled by
+    ``DistributedGraphCastGraphGenerator(placement="multilevel")``)."""
+    placement = partition_graph(nx_graph, num_ranks)
+    nodes = node_renumbering(placement, num_ranks)
+    return placement, nodes, edge_renumbering(list(nx_graph.edges()), nodes)
+
+
 def main(world_size: int = 4, mesh_level: int = 6, lat: int = 721, lon: int = 1440, out_dir: str = "graphcast_cache", placement: str = "multilevel"):
     gen = DistributedGraphCastGraphGenerator((lat, lon), mesh_level, placement=placement)
     g = gen.global_graph()

@@ -21,6 +21,25 @@ def print_on_rank_zero(comm, *a):
         print(*a, flush=True)
 
 
+def print_on_all_ranks(comm, *a):
+    """Every rank prints in rank order (barriers in between), reference ``Trainer.py:39-44``."""
+    for r in range(comm.get_world_size()):
+        if comm.get_rank() == r:
+            print(f"[rank {r}]", *a, flush=True)
+        comm.barrier()
+
+
+def stop():
+    """Tear the process group down and exit (debugging aid of the reference, ``Trainer.py:25-29``)."""
+    import sys
+
+    import torch.distributed as dist
+
+    if dist.is_available() and dist.is_initialized():
+        dist.destroy_process_group()
+    sys.exit(0)
+
+
 class Trainer:
     def __init__(self, dataset, comm, device, model_config: ModelConfig = None, training_config: TrainingConfig = None,
                  fused: bool = True):

@@ -23,6 +23,65 @@ def add_opposite_edges(edge_index: torch.Tensor) -> torch.Tensor:
     return torch.unique(e, dim=1)
 
 
+def node_renumbering(node_rank_placement, num_parts):
+    """Old vertex ids listed rank by rank: position = new id, value = old id (reference ``preprocess.py:50-59``)."""
+    pl = torch.as_tensor(node_rank_placement).long()
+    return torch.argsort(pl, stable=True)
+
+
+def edge_renumbering(edge_indices, renumbered_nodes):
+    """``[E, 2]`` edges in old ids -> ``[2, E]`` edges in new ids.  ``renumbered_nodes`` is the new -> old list from
+    :func:`node_renumbering`; the edges need its inverse (the reference indexes with the list itself, which is only right when the
+    permutation is its own inverse)."""
+    new_to_old = torch.as_tensor(renumbered_nodes).long()
+    old_to_new = torch.empty_like(new_to_old)
+    old_to_new[new_to_old] = torch.arange(new_to_old.numel())
+    e = torch.as_tensor(edge_indices).long()
+    return torch.stack([old_to_new[e[:, 0]], old_to_new[e[:, 1]]])
+
+
+def partition_graph(coo_list, num_ranks: int):
+    """Partition an undirected graph given as ``[E, 2]`` pairs and renumber it rank-contiguously: ``(new -> old vertex list,
+    [2, E] edges in new ids)``.  METIS in the reference (``preprocess.py:15-29``), the native multilevel partitioner here."""
+    e = torch.as_tensor(coo_list).long()
+    V = int(e.max()) + 1 if e.numel() else 0
+    placement = multilevel(e, V, num_ranks)
+    nodes = node_renumbering(placement, num_ranks)
+    return nodes, edge_renumbering(e, nodes)
+
+
+def partition_directed_graph(coo_list, num_nodes: int, num_parts: int):
+    """Same for a directed edge list with isolated vertices allowed (``preprocess.py:32-47``); direction is ignored for the cut."""
+    e = torch.as_tensor(coo_list).long()
+    placement = multilevel(e, num_nodes, num_parts)
+    nodes = node_renumbering(placement, num_parts)
+    return nodes, edge_renumbering(e, nodes)
+
+
+def save_networkx_graph(coo_list, num_nodes, dname, directed=False):
+    """Pickle the graph as a networkx object ``{dname}_directed={directed}.pkl`` (``preprocess.py:83-99``)."""
+    import pickle
+
+    import networkx as nx
+
+    G = nx.DiGraph() if directed else nx.Graph()
+    G.add_nodes_from(range(int(num_nodes)))
+    pairs = [tuple(map(int, p)) for p in torch.as_tensor(coo_list).tolist()]
+    G.add_edges_from(pairs)
+    if directed:
+        G.add_edges_from([(d, s_) for s_, d in pairs])
+    with open(f"{dname}_directed={directed}.pkl", "wb") as f:
+        pickle.dump(G, f)
+    return G
+
+
+def load_networkx_graph(dname):
+    import pickle
+
+    with open(f"{dname}.pkl", "rb") as f:
+        return pickle.load(f)
+
+
 def main(dataset: str = "arxiv", world_size: int = 8, out: str = "", method: str = "multilevel", scale: float = 1.0, root_dir: str = "data"):
     name = {"arxiv": "ogbn-arxiv", "products": "ogbn-products"}.get(dataset, dataset)
     g, _, _, synthetic = _load_raw(name, root_dir, scale)

@@ -156,3 +156,37 @@ def torch_alltoallv_with_comm_map(send_tensor: torch.Tensor, send_splits: List[i
     else:
         dist.all_to_all(recv, send)
     return torch.cat(recv, dim=dim)
+
+
+# ---- the two cache-construction helpers of the reference (``_nccl_cache.py:70-160``), on top of ``indices_utils`` ------------
+def all_to_all_cache_helper(indices, edge_placement, edge_vertex_ranks, num_rows, rank, world_size):
+    """Gather-side bookkeeping: ``(send_comm_vector [W], recv_comm_vector [W], send_local_placement {peer: local rows to ship},
+    recv_local_placement {peer: positions among this rank's edges that peer's rows fill})``.  An edge lives on
+    ``edge_placement[e]`` and reads a vertex owned by ``edge_vertex_ranks[e]``."""
+    from dgraph_b200.parallel import indices_utils as U
+
+    place, owner = edge_placement.reshape(-1), edge_vertex_ranks.reshape(-1)
+    cross = place != owner
+    send_v = U._get_send_comm_vector(owner[cross], place[cross], rank, world_size)
+    recv_v = U._get_recv_comm_vector(owner[cross], place[cross], rank, world_size)
+    recv_place = U._get_local_recv_placement(recv_v, owner[place == rank], rank)
+    send_place = U._get_local_send_placement(send_v, indices, owner, place, rank, num_rows)
+    return send_v, recv_v, send_place, recv_place
+
+
+def all_to_all_cache_with_local_reduce_helper(indices, edge_placement, edge_vertex_ranks, num_output_rows, rank, world_size):
+    """Scatter-side bookkeeping with local pre-reduction: ``(renumbered_indices, num_remote_rows, remapped_ranks,
+    receiving_ranks, recv_placement)`` -- this rank's remote-bound edge rows are summed per distinct target (``renumbered``
+    addresses a compact ``[num_remote_rows]`` buffer whose rows go to ``remapped_ranks``); ``recv_placement[peer]`` are the
+    local rows the peer's pre-reduced rows add to."""
+    from dgraph_b200.parallel import indices_utils as U
+    from dgraph_b200.parallel.rank_local import RankLocalRenumberingWithMapping
+
+    idx, place, owner = indices.reshape(-1), edge_placement.reshape(-1), edge_vertex_ranks.reshape(-1)
+    mine = place == rank
+    remote = mine & (owner != rank)
+    renumbered, unique_idx, remapped = RankLocalRenumberingWithMapping(idx[remote], owner[remote])
+    receiving = torch.unique(owner[remote])
+    incoming = (place != owner) & (owner == rank)
+    recv_placement = U._get_local_unique_recv_placement(idx, place, incoming, num_output_rows, rank, world_size)
+    return renumbered, int(unique_idx.numel()), remapped, receiving, recv_placement

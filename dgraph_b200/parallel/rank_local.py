@@ -104,3 +104,19 @@ def LocalAggregateWithRemapping(global_data: torch.Tensor, global_indices: torch
     out = torch.zeros((u.numel(), num_features), dtype=rows.dtype, device=device or rows.device)
     out.index_add_(0, inv, rows)
     return out.unsqueeze(0), u
+
+
+def RankLocalReNumbering(_indices: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``(renumbered, unique)``: every index replaced by its position among the sorted distinct values
+    (reference ``RankLocalOps.py:248-258``, there an O(U) Python loop)."""
+    u, inv = torch.unique(_indices, return_inverse=True)
+    return inv.reshape(_indices.shape), u
+
+
+def RankLocalGather(_src: torch.Tensor, indices: torch.Tensor, rank_mapping: torch.Tensor, rank: int) -> torch.Tensor:
+    """Rows ``_src[indices[i]]`` for the entries with ``rank_mapping[i] == rank`` (compact, 2-D source)."""
+    sel = indices.reshape(-1)[rank_mapping.reshape(-1) == rank].long()
+    return _rows(_src).index_select(0, sel)
+
+
+OutOfPlaceRankLocalMaskedGather = RankLocalGather  # the reference defines the same body under both names

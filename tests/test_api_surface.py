@@ -177,3 +177,35 @@ def test_benchmark_graph_utils_all_pairs_through_legacy_api():
         assert torch.allclose(got, gd.vertex_data[others])
         to_me = sd.edge_indices[0] == r
         assert torch.allclose(back[0], sd.vertex_data[0, to_me].sum(0))
+
+
+def test_indices_utils_counts_and_placements():
+    from dgraph_b200.parallel import indices_utils as U
+    from dgraph_b200.parallel.legacy_cache import all_to_all_cache_helper, all_to_all_cache_with_local_reduce_helper
+    from dgraph_b200.parallel.rank_local import RankLocalGather, RankLocalReNumbering
+
+    W = 3
+    # edge e lives on place[e] and addresses vertex idx[e] owned by owner[e]; 4 vertices per rank
+    place = torch.tensor([0, 0, 0, 1, 1, 2, 2, 2])
+    idx = torch.tensor([[1, 5, 9, 4, 0, 8, 1, 5]])
+    owner = idx[0] // 4
+    send, recv = U._get_send_recv_comm_vectors(owner, place, 0, W)  # data flows owner -> place
+    assert send.tolist() == [0, 1, 1] and recv.tolist() == [0, 1, 1]
+    sp = U._get_local_send_placement(send, idx, owner, place, 0, 4)
+    assert sp[1].tolist() == [0] and sp[2].tolist() == [1]
+    lrm = owner[place == 0]
+    rp = U._get_local_recv_placement(recv, lrm, 0)
+    assert rp[1].reshape(-1).tolist() == [1] and rp[2].reshape(-1).tolist() == [2]
+    bufs, rp2 = U._get_local_recv_buffer_w_placement(recv, lrm, 6, 0, "cpu")
+    assert bufs[1].shape == (1, 1, 6) and set(rp2) == {1, 2}
+    assert U._generate_local_rank_mapping(torch.zeros(7), 3).tolist() == [0, 0, 0, 1, 1, 1, 2]
+    sv, rv, s_place, r_place = all_to_all_cache_helper(idx, place, owner, 4, 0, W)
+    assert sv.tolist() == send.tolist() and rv.tolist() == recv.tolist() and s_place[1].tolist() == [0]
+    # scatter direction: rank 2 holds edges 5..7 whose targets live on ranks 2, 0, 1
+    ren, n_remote, remapped, receiving, recv_pl = all_to_all_cache_with_local_reduce_helper(idx, place, owner, 4, 2, W)
+    assert n_remote == 2 and sorted(receiving.tolist()) == [0, 1] and ren.tolist() == [0, 1] and remapped.tolist() == [0, 1]
+    assert recv_pl[0].tolist() == [1]  # rank 0's edge 2 (vertex 9) adds to local row 1 of rank 2
+    r, u = RankLocalReNumbering(torch.tensor([7, 3, 7, 9]))
+    assert r.tolist() == [1, 0, 1, 2] and u.tolist() == [3, 7, 9]
+    src = torch.arange(12.0).view(6, 2)
+    assert torch.equal(RankLocalGather(src, torch.tensor([5, 0, 2]), torch.tensor([1, 0, 1]), 1), src[[5, 2]])

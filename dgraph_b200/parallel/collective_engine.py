@@ -61,6 +61,54 @@ class CollectiveEngine(BackendEngine):
     def get_partition_rank(self) -> int:
         return self.get_rank() % self.ranks_per_graph
 
+    # Names the three reference engines use for the same quantities (``NCCLBackendEngine.py:70-81``,
+    # ``NVSHMEMBackendEngine.py:212-222``, ``MPIBackendEngine.py:374-402``).  With one process group per graph replica
+    # (``Communicator.init_process_group(..., ranks_per_graph=k)``) ``get_rank()`` already is the rank inside the replica.
+    def get_local_rank(self) -> int:
+        return self.get_partition_rank() if not hasattr(self, "replica_id") else self.get_rank()
+
+    def get_partition_size(self) -> int:
+        return self.ranks_per_graph
+
+    def get_partition_num(self) -> int:
+        return getattr(self, "replica_id", self.get_partition_id())
+
+    def to_global_rank(self, local_rank: int) -> int:
+        """Rank of ``local_rank`` of *this* replica in the whole job."""
+        return self.get_partition_num() * self.ranks_per_graph + int(local_rank)
+
+    def get_max(self, val: torch.Tensor) -> torch.Tensor:
+        """In-place all-reduce(MAX) across the engine's ranks (used to agree on symmetric buffer sizes)."""
+        return self.all_reduce(val, "max")
+
+    def destroy(self) -> None:
+        """The reference only clears its initialised flag here; releasing resources is ``finalize``."""
+
+    def _get_splits(self, send_offset, recv_offset):
+        """``(send_splits, recv_splits)`` in rows, from the CSR-style offsets of a halo plan."""
+        return _splits(send_offset), _splits(recv_offset)
+
+    @staticmethod
+    def _scale_splits(splits, factor: int):
+        return [int(s) * int(factor) for s in splits]
+
+    # MPI window management of the reference's MPI engine (``MPIBackendEngine.py:343-365``): there are no windows here; the
+    # calls hand back ordinary buffers so that code written against them keeps running.
+    def Malloc(self, size, device):
+        return None, self.allocate_buffer((int(size),), torch.float32, device)
+
+    @staticmethod
+    def Attach(tensor: torch.Tensor):
+        return None, tensor
+
+    @staticmethod
+    def Detach(win) -> None:
+        return None
+
+    def get_comm(self):
+        """The process group the engine communicates over (``None`` = default group / no group)."""
+        return getattr(self, "_group", None)
+
     # -- halo primitive --------------------------------------------------------------------------
     def put(self, send_buffer, recv_buffer, send_offsets, recv_offsets, remote_offsets=None) -> None:
         ins, outs = _splits(send_offsets), _splits(recv_offsets)

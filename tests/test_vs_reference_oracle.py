@@ -230,3 +230,38 @@ def test_every_public_name_of_the_reference_library_resolves():
             if miss:
                 problems[rel] = miss
     assert not problems, problems
+
+
+def test_every_method_of_the_reference_library_classes_exists():
+    """Method-level version of the name check: every method of every class of the reference's ``DGraph/`` package exists on the
+    class of the same name here (``forward`` / ``backward`` of the two legacy autograd functions excepted: they are plain
+    callables with ``apply`` here)."""
+    import ast
+    import importlib
+
+    ref_root = "/root/reference/DGraph"
+    if not os.path.isdir(ref_root):
+        pytest.skip("reference tree not available")
+    problems = {}
+    for d, _, files in os.walk(ref_root):
+        for f in files:
+            if not f.endswith(".py"):
+                continue
+            path = os.path.join(d, f)
+            rel = os.path.relpath(path, "/root/reference")[:-3].replace(os.sep, ".")
+            rel = rel[:-9] if rel.endswith(".__init__") else rel
+            try:
+                mod = importlib.import_module(rel)
+            except Exception:  # noqa: BLE001 - module-level resolution is the previous test's job
+                continue
+            for node in ast.parse(open(path).read()).body:
+                if not isinstance(node, ast.ClassDef) or not hasattr(mod, node.name):
+                    continue
+                cls = getattr(mod, node.name)
+                meths = [m.name for m in node.body if isinstance(m, ast.FunctionDef) and not m.name.startswith("__")]
+                miss = [m for m in meths if not hasattr(cls, m)]
+                if node.name in ("GatherFunction", "ScatterFunction"):
+                    miss = [m for m in miss if m not in ("forward", "backward")]
+                if miss:
+                    problems[f"{rel}.{node.name}"] = miss
+    assert not problems, problems

@@ -27,7 +27,10 @@ from dgraph_b200.parallel.comm_pattern import CommunicationPattern, build_commun
 
 
 # ------------------------------------------------------------------------------------------------ geometry
-def icosahedron() -> Tuple[np.ndarray, np.ndarray]:
+def icosahedron(face_up: bool = True) -> Tuple[np.ndarray, np.ndarray]:
+    """12 unit vertices, 20 outward-oriented faces.  ``face_up`` tilts the solid about the y axis by half the supplement of its
+    dihedral angle, so that a face (not an edge) is perpendicular to the z axis: the orientation of the reference's mesh
+    (``data_utils/icosahedral_mesh.py:159-177``), which fixes where the lat/lon poles fall relative to the mesh."""
     phi = (1.0 + 5.0 ** 0.5) / 2.0
     v = []
     for a in (-1.0, 1.0):
@@ -35,6 +38,10 @@ def icosahedron() -> Tuple[np.ndarray, np.ndarray]:
             v += [(0.0, a, b), (a, b, 0.0), (b, 0.0, a)]
     v = np.asarray(v, dtype=np.float64)
     v /= np.linalg.norm(v, axis=1, keepdims=True)
+    if face_up:
+        t = (np.pi - 2.0 * np.arcsin(phi / 3.0 ** 0.5)) / 2.0
+        c, s = np.cos(t), np.sin(t)
+        v = np.stack([c * v[:, 0] - s * v[:, 2], v[:, 1], s * v[:, 0] + c * v[:, 2]], axis=1)
     # faces = all triples of mutually adjacent vertices (edge length of the unit icosahedron ~ 1.0515)
     d = np.linalg.norm(v[:, None] - v[None], axis=-1)
     adj = (d > 1e-6) & (d < 1.2)

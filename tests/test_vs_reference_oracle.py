@@ -265,3 +265,74 @@ def test_every_method_of_the_reference_library_classes_exists():
                 if miss:
                     problems[f"{rel}.{node.name}"] = miss
     assert not problems, problems
+
+
+def _load_by_path(path, name):
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def test_graphcast_mesh_and_spatial_helpers_agree_with_reference():
+    """``experiments/GraphCast/data_utils/{icosahedral_mesh,spatial_utils}.py`` of this repository against the reference's files
+    of the same name: same vertex sets per refinement level (vertex numbering differs, so sets are compared), same multimesh
+    edge set, same spherical-geometry functions."""
+    import numpy as np
+    base = "/root/reference/experiments/GraphCast/data_utils/"
+    if not os.path.exists(base):
+        base = os.path.join(ROOT, "baseline", "_ref", "experiments", "GraphCast", "data_utils") + "/"
+    if not os.path.exists(base + "icosahedral_mesh.py"):
+        pytest.skip("reference tree not available")
+    pytest.importorskip("scipy")
+    ri, rs = _load_by_path(base + "icosahedral_mesh.py", "_ref_ico"), _load_by_path(base + "spatial_utils.py", "_ref_sp")
+    mine = os.path.join(ROOT, "experiments", "GraphCast", "data_utils") + "/"
+    oi, osp = _load_by_path(mine + "icosahedral_mesh.py", "_our_ico"), _load_by_path(mine + "spatial_utils.py", "_our_sp")
+
+    def vkey(v):  # order-free fingerprint of a vertex set
+        q = np.round(np.asarray(v, dtype=np.float64) * 1e4).astype(np.int64)
+        return sorted(map(tuple, q))
+
+    a, b = ri.get_hierarchy_of_triangular_meshes_for_sphere(3), oi.get_hierarchy_of_triangular_meshes_for_sphere(3)
+    assert len(a) == len(b) == 4
+    for x, y in zip(a, b):
+        assert x.vertices.shape == y.vertices.shape and x.faces.shape == y.faces.shape
+        assert vkey(x.vertices) == vkey(y.vertices)
+        # faces: same set of corner-coordinate triples, all outward-oriented
+        cx, cy = rs.get_face_centroids(x.vertices, x.faces), osp.get_face_centroids(y.vertices, y.faces)
+        assert vkey(cx) == vkey(cy)
+        v, f = np.asarray(y.vertices, dtype=np.float64), np.asarray(y.faces)
+        n = np.cross(v[f[:, 1]] - v[f[:, 0]], v[f[:, 2]] - v[f[:, 0]])
+        assert ((n * v[f].mean(1)).sum(1) > 0).all()
+    ma, mb = ri.merge_meshes(a), oi.merge_meshes(b)
+    (sa, da), (sb, db) = ri.faces_to_edges(ma.faces), oi.faces_to_edges(mb.faces)
+
+    def ekey(m, s, d):
+        q = np.round(np.asarray(m.vertices, dtype=np.float64) * 1e4).astype(np.int64)
+        return sorted(map(tuple, np.concatenate([q[s], q[d]], axis=1)))
+
+    assert ekey(ma, sa, da) == ekey(mb, sb, db)
+    assert abs(rs.max_edge_length(ma.vertices, sa, da) - osp.max_edge_length(mb.vertices, sb, db)) < 1e-6
+
+    g = torch.Generator().manual_seed(0)
+    ll = torch.rand(64, 2, generator=g) * torch.tensor([180.0, 360.0]) - torch.tensor([90.0, 180.0])
+    th = torch.rand(64, generator=g) * 6 - 3
+    for unit in ("deg", "rad"):
+        q = ll if unit == "deg" else ll * (3.141592653589793 / 180)
+        xa, xb = rs.latlon2xyz(q, unit=unit), osp.latlon2xyz(q, unit=unit)
+        torch.testing.assert_close(xa, xb)
+        torch.testing.assert_close(rs.xyz2latlon(xa, unit=unit), osp.xyz2latlon(xb, unit=unit))
+    # rotations are compared in radians only: with unit="deg" the reference rescales the *points* instead of converting the
+    # angle (spatial_utils.py:107-108); here degrees mean degrees
+    xa = rs.latlon2xyz(ll)
+    for ax in "xyz":
+        torch.testing.assert_close(rs.geospatial_rotation(xa, th, ax), osp.geospatial_rotation(xa, th, ax))
+        torch.testing.assert_close(osp.geospatial_rotation(xa, th * (180 / 3.141592653589793), ax, unit="deg"),
+                                   osp.geospatial_rotation(xa, th, ax), rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(rs.polar_angle(th), osp.polar_angle(th))
+    torch.testing.assert_close(rs.azimuthal_angle(th), osp.azimuthal_angle(th))
+    assert abs(rs.deg2rad(33.0) - osp.deg2rad(33.0)) < 1e-12 and abs(rs.rad2deg(0.7) - osp.rad2deg(0.7)) < 1e-12
+    # the incremental child-vertex builder hands out one index per parent edge, whatever the order of the two endpoints
+    cb = oi._ChildVerticesBuilder(b[0].vertices)
+    i = cb.get_new_child_vertex_index((0, 1))
+    assert cb.get_new_child_vertex_index((1, 0)) == i and cb.get_all_vertices().shape == (13, 3)

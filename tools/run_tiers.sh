@@ -1,5 +1,5 @@
 #!/usr/bin/env bash
-# Test tiers in one place (see tests/README.md).  Usage: tools/run_tiers.sh cpu | gpu | multigpu | reference-compat
+# Test tiers in one place (see tests/README.md).  Usage: tools/run_tiers.sh cpu | gpu | multigpu | reference-compat | reference-dist | graphcast
 set -euo pipefail
 cd "$(dirname "$0")/.."
 case "${1:-cpu}" in
@@ -8,6 +8,11 @@ case "${1:-cpu}" in
   multigpu)  python -m pytest tests/test_peer_engine_multigpu.py -x -q -m gpu ;;
   reference-compat)  # the reference's own single-process tests against this package (needs /root/reference)
              python -m pytest tests/test_vs_reference_oracle.py -q -m "not gpu" ;;
+  reference-dist)    # the reference's own torchrun tests (2 GPUs, NCCL) against this package.  The reference tree is not on a GPU box:
+             # copy its tests next to the installed reference first (here): cp -r /root/reference/tests baseline/_ref/tests
+             T=/root/reference/tests; [ -d "$T" ] || T=baseline/_ref/tests
+             PYTHONPATH="$PWD" python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+               -m pytest "$T/test_comm_info.py" "$T/test_NCCLCommPlan.py" -q -p no:cacheprovider ;;
   graphcast) (cd experiments/GraphCast && python -m pytest tests -q) ;;
   *) echo "unknown tier $1" >&2; exit 2 ;;
 esac

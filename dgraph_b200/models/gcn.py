@@ -13,6 +13,7 @@ tensor exists in forward or backward.  ``fused=False`` is the literal reference 
 """
 from __future__ import annotations
 
+import warnings
 from typing import Optional
 
 import torch
@@ -21,11 +22,13 @@ import torch.nn as nn
 from dgraph_b200.ops.gemm import linear
 from dgraph_b200.ops.segment import graphconv_aggregate
 from dgraph_b200.parallel.comm_pattern import CommunicationPattern
-from dgraph_b200.parallel.kernel_plan import GraphKernelPlan
+from dgraph_b200.parallel.kernel_plan import MAX_COUNTED_DEGREE, GraphKernelPlan
 from dgraph_b200.utils.timing import TimingReport
 
 
 class GraphConvLayer(nn.Module):
+    _warned_hub = False
+
     def __init__(self, message_dim: int, out_channels: int, fused: bool = True):
         super().__init__()
         self.conv = nn.Linear(message_dim, out_channels)
@@ -47,6 +50,10 @@ class GraphConvLayer(nn.Module):
         if self.fused and edge_features is None:
             return self._forward_fused(x, edge_index, num_local_nodes, kernel_plan)
         self._wait_halo(x)
+        return self._forward_edges(x, edge_index, num_local_nodes, edge_features)
+
+    def _forward_edges(self, x, edge_index, num_local_nodes, edge_features):
+        """The reference's formulation, edge by edge (``GCN.py:43-65``)."""
         src, dst = edge_index[:, 0], edge_index[:, 1]
         F_in = (self.conv.weight.shape[1] - (0 if edge_features is None else edge_features.shape[1])) // 2
         x = x[:, :F_in]
@@ -62,6 +69,14 @@ class GraphConvLayer(nn.Module):
         if kp is None:
             kp = GraphKernelPlan.from_edges(edge_index, num_local_nodes, x.shape[0], device=x.device)
         F_in = self.conv.weight.shape[1] // 2
+        if x.is_cuda and kp.max_row_degree() > MAX_COUNTED_DEGREE:
+            # hub vertex beyond the kernels' 16-bit per-column counters: literal formulation (materialises [E, *] tensors)
+            if not GraphConvLayer._warned_hub:
+                GraphConvLayer._warned_hub = True
+                warnings.warn(f"GraphConvLayer: vertex degree {kp.max_row_degree()} > {MAX_COUNTED_DEGREE}, "
+                              "using the unfused edge formulation for this graph")
+            self._wait_halo(x)
+            return self._forward_edges(x, edge_index, num_local_nodes, None)
         if x.is_cuda and x.dtype == torch.bfloat16 and self.conv.weight.shape[0] % 8 == 0 and x.shape[1] % 8 == 0:
             from dgraph_b200.ops.graphconv import graphconv_fused
 

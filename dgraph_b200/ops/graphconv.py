@@ -119,6 +119,7 @@ def graphconv_fused(x_aug, weight, bias, kp, n_local: int, f_in: int):
     """``x_aug`` bf16 ``[n_local + n_halo, F_pad]`` (extra columns zero); ``weight`` fp32 ``[H, 2 * f_in]``; ``bias`` fp32."""
     N.lib()
     assert kp.rowptr.dtype == torch.int32
+    S._check_degree(kp)
     if x_aug.stride(1) != 1 or x_aug.stride(0) % 8:
         x_aug = x_aug.contiguous()
     return _GraphConvFused.apply(x_aug, weight, bias, kp, n_local, f_in)

@@ -121,6 +121,16 @@ def segment_mean(xaug, kp, halo=None):
     return segment_sum(xaug, kp, mean=True, halo=halo)
 
 
+def _check_degree(kp: GraphKernelPlan) -> None:
+    from dgraph_b200.parallel.kernel_plan import MAX_COUNTED_DEGREE
+
+    if kp.max_row_degree() > MAX_COUNTED_DEGREE:
+        raise RuntimeError(
+            f"fused GraphConv aggregation: a vertex has {kp.max_row_degree()} neighbours, more than the {MAX_COUNTED_DEGREE} its "
+            "16-bit per-column counters of active edges can hold (GraphConvLayer falls back to the edge-materialising formulation "
+            "for such graphs)")
+
+
 class _GraphConvAgg(Function):
     @staticmethod
     def forward(ctx, P, Qaug, kp: GraphKernelPlan):
@@ -185,6 +195,7 @@ def graphconv_aggregate(P: torch.Tensor, Qaug: torch.Tensor, kp: GraphKernelPlan
     if P.is_cuda and P.dtype == torch.bfloat16:
         N.lib()
         assert kp.rowptr.dtype == torch.int32, "per-rank edge count must stay below 2^31"
+        _check_degree(kp)
         if P.stride(1) != 1:
             P = P.contiguous()
         if Qaug.stride(1) != 1:

@@ -15,6 +15,9 @@ from typing import Optional
 import torch
 
 
+MAX_COUNTED_DEGREE = 65535  # uint16 per-(row, column) active-edge counters of the add-ReLU aggregation kernel
+
+
 @dataclass
 class GraphKernelPlan:
     num_local: int  # rows that are aggregated into (central side)
@@ -39,6 +42,16 @@ class GraphKernelPlan:
     @property
     def num_aug(self) -> int:
         return self.num_nbr_local + self.num_halo
+
+    def max_row_degree(self) -> int:
+        """Largest CSR segment (edges of one central vertex); one device-to-host read, cached.  The fused GraphConv aggregation
+        counts active edges per (row, column) in 16 bits, so its callers check this against ``MAX_COUNTED_DEGREE``."""
+        d = getattr(self, "_max_row_degree", None)
+        if d is None:
+            rp = self.rowptr
+            d = int((rp[1:] - rp[:-1]).max()) if rp.numel() > 1 else 0
+            self._max_row_degree = d
+        return d
 
     def csr_to_csc(self) -> torch.Tensor:
         """CSC slot of each CSR slot (inverse of ``csc_to_csr``), built on first use.  The forward add-ReLU kernel writes its

@@ -87,3 +87,23 @@ def test_distributed_training_matches_single_process(W):
         assert torch.allclose(torch.tensor(losses), torch.tensor(single[0]), atol=1e-9)
         for k in sd:
             assert torch.allclose(sd[k], single[1][k], atol=1e-9)
+
+
+def test_kernel_plan_degree_guard():
+    """The add-ReLU aggregation kernel counts active edges per (row, column) in 16 bits: plans report their largest segment and
+    the launch wrappers refuse a hub vertex beyond 65535 neighbours instead of wrapping around silently."""
+    import pytest
+    import torch
+    from dgraph_b200.ops.segment import _check_degree
+    from dgraph_b200.parallel.kernel_plan import MAX_COUNTED_DEGREE, GraphKernelPlan
+
+    e = torch.tensor([[0, 1], [0, 2], [0, 3], [1, 0], [2, 0]])
+    kp = GraphKernelPlan.from_edges(e, 4, 4)
+    assert kp.max_row_degree() == 3
+    _check_degree(kp)
+    hub = torch.stack([torch.zeros(MAX_COUNTED_DEGREE + 1, dtype=torch.long), torch.arange(1, MAX_COUNTED_DEGREE + 2)], dim=1)
+    kp2 = GraphKernelPlan.from_edges(hub, 1, MAX_COUNTED_DEGREE + 2)
+    assert kp2.max_row_degree() == MAX_COUNTED_DEGREE + 1
+    with pytest.raises(RuntimeError, match="16-bit"):
+        _check_degree(kp2)
+    assert GraphKernelPlan.from_edges(torch.zeros(0, 2, dtype=torch.long), 0, 0).max_row_degree() == 0

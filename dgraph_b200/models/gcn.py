@@ -13,6 +13,7 @@ tensor exists in forward or backward.  ``fused=False`` is the literal reference 
 """
 from __future__ import annotations
 
+import os
 import warnings
 from typing import Optional
 
@@ -24,6 +25,11 @@ from dgraph_b200.ops.segment import graphconv_aggregate
 from dgraph_b200.parallel.comm_pattern import CommunicationPattern
 from dgraph_b200.parallel.kernel_plan import MAX_COUNTED_DEGREE, GraphKernelPlan
 from dgraph_b200.utils.timing import TimingReport
+
+
+# "0" (default): exchange features, project local + halo rows.  "1": the second convolution exchanges projected rows instead
+# (GraphConvLayer.forward_exchange_q).  "all": both convolutions.  Not yet measured on hardware.
+_QPULL = os.environ.get("DGRAPH_B200_GCN_QPULL", "0")
 
 
 class GraphConvLayer(nn.Module):
@@ -94,6 +100,29 @@ class GraphConvLayer(nn.Module):
         return graphconv_aggregate(P, Q, kp)
 
 
+    def forward_exchange_q(self, x_local, comm_pattern, exchanger, kp: Optional[GraphKernelPlan] = None):
+        """Same layer with the exchange moved behind the projection (opt-in, ``DGRAPH_B200_GCN_QPULL``): every rank projects only
+        the rows it owns, ``Q = x W_j^T`` travels instead of ``x``, and the aggregation reads ``cat([Q_local, Q_halo])``.  Halo rows
+        then cost no GEMM in forward, no ``dX`` GEMM and no weight-gradient work in backward (their ``dQ`` is pull-reduced on the
+        owner first); the price is that the exchanged rows are ``H`` wide, so this pays where ``F_in >= H``."""
+        n = x_local.shape[0]
+        if kp is None:
+            kp = comm_pattern.kernel_plan(x_local.device)
+        F_in = self.conv.weight.shape[1] // 2
+        W = self.conv.weight.to(x_local.dtype)
+        w_i, w_j = W[:, :F_in], W[:, F_in:2 * F_in]
+        pad = x_local.shape[1] - F_in
+        assert pad >= 0, "feature matrix narrower than the layer's input width"
+        if pad:
+            w_i = torch.nn.functional.pad(w_i, (0, pad))
+            w_j = torch.nn.functional.pad(w_j, (0, pad))
+        P = linear(x_local, w_i.contiguous(), self.conv.bias.to(x_local.dtype))
+        Q = linear(x_local, w_j.contiguous(), None)
+        Q_aug = exchanger.augmented(Q, comm_pattern)
+        assert P.shape[0] == n
+        return graphconv_aggregate(P, Q_aug, kp)
+
+
 class CommAwareGCN(nn.Module):
     """2 x (halo exchange -> GraphConvLayer) -> Linear  (``GCN.py:70-118``)."""
 
@@ -116,14 +145,22 @@ class CommAwareGCN(nn.Module):
         kp = comm_pattern.kernel_plan(x.device) if self.conv1.fused else None
         edges = comm_pattern.local_edge_list
         defer = self.conv1.fused  # the fused layer overlaps its local work with the in-flight halo rows (ops/_pending.py)
-        with TimingReport("feature-exchange-1"):
-            aug = self.halo_exchanger.augmented(x, comm_pattern, defer=defer)
-        with TimingReport("process-1"):
-            x = self.conv1(aug, edges, n, kernel_plan=kp)
-        with TimingReport("feature-exchange-2"):
-            aug = self.halo_exchanger.augmented(x, comm_pattern, defer=defer)
-        with TimingReport("process-2"):
-            x = self.conv2(aug, edges, n, kernel_plan=kp)
+        if self.conv1.fused and _QPULL == "all":
+            with TimingReport("process-1"):
+                x = self.conv1.forward_exchange_q(x, comm_pattern, self.halo_exchanger, kp)
+        else:
+            with TimingReport("feature-exchange-1"):
+                aug = self.halo_exchanger.augmented(x, comm_pattern, defer=defer)
+            with TimingReport("process-1"):
+                x = self.conv1(aug, edges, n, kernel_plan=kp)
+        if self.conv2.fused and _QPULL in ("1", "all"):  # opt-in: exchange the projected rows instead of the features
+            with TimingReport("process-2"):
+                x = self.conv2.forward_exchange_q(x, comm_pattern, self.halo_exchanger, kp)
+        else:
+            with TimingReport("feature-exchange-2"):
+                aug = self.halo_exchanger.augmented(x, comm_pattern, defer=defer)
+            with TimingReport("process-2"):
+                x = self.conv2(aug, edges, n, kernel_plan=kp)
         with TimingReport("final-fc"):
             x = linear(x, self.fc.weight.to(x.dtype), self.fc.bias.to(x.dtype))
         return x

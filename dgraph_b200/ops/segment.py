@@ -19,6 +19,7 @@ import torch
 from torch.autograd import Function
 
 from dgraph_b200.ops import _native as N
+from dgraph_b200.ops import _sparsity
 from dgraph_b200.parallel.kernel_plan import GraphKernelPlan
 
 
@@ -160,6 +161,8 @@ class _GraphConvAgg(Function):
     @staticmethod
     def backward(ctx, g):
         kp = ctx.kp
+        # incoming gradient zero outside a known set of rows (loss over the labelled vertices): walk only the edges that start there
+        hint = _sparsity.take(g) if (ctx.has_mask and not ctx.mask_csc) else None
         g = g.contiguous()
         H = g.shape[1]
         dP = dQ = None
@@ -174,8 +177,9 @@ class _GraphConvAgg(Function):
             N.count_launch()
         if ctx.needs_input_grad[1] and ctx.has_mask:
             dQ = torch.empty((kp.num_aug, H), dtype=torch.bfloat16, device=g.device)
+            colptr, row, slot_map = (kp.colptr, kp.row, kp.csc_to_csr) if hint is None else kp.restricted_csc(hint[0])
             N.check(N.lib().dgb_seg_masked_sum(
-                N.ptr(kp.colptr), N.ptr(kp.row), N.ptr(None if ctx.mask_csc else kp.csc_to_csr), N.ptr(mask),
+                N.ptr(colptr), N.ptr(row), N.ptr(None if ctx.mask_csc else slot_map), N.ptr(mask),
                 N.i64(kp.num_aug), N.i32(H), N.ptr(g),
                 N.i64(H), N.ptr(dQ), N.i64(H), N.ptr(None), N.i64(0), N.ptr(None), N.i64(0), N.i64(0), N.stream()),
                 "dgb_seg_masked_sum")

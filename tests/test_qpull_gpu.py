@@ -1,0 +1,44 @@
+"""Opt-in ``DGRAPH_B200_GCN_QPULL`` order of operations (project owned rows, exchange ``Q``) against the default fused layer on
+one GPU in bf16.  Added after the round's GPU budget was spent: non-strict xfail until its first hardware run."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.xfail(strict=False, reason="first hardware run decides (XPASS expected)")
+def test_qpull_matches_default_layer_bf16(monkeypatch):
+    from dgraph_b200 import Communicator
+    from dgraph_b200.data import make_graph, node_features_and_labels
+    from dgraph_b200.models import gcn as gcn_mod
+    from dgraph_b200.models.gcn import CommAwareGCN
+    from dgraph_b200.ops.loss import masked_cross_entropy
+    from dgraph_b200.parallel import HaloExchange, build_communication_pattern
+
+    dev = torch.device("cuda", 0)
+    Communicator._is_initialized = False
+    comm = Communicator.init_process_group("single")
+    try:
+        g = make_graph("tiny", seed=0, device=dev)
+        part = torch.zeros(g.num_nodes, dtype=torch.long, device=dev)
+        pat = build_communication_pattern(g.edge_list, part, 0, 1)
+        x, y = node_features_and_labels(g.num_nodes, g.num_features, g.num_classes, device=dev)
+        Fp = (g.num_features + 7) // 8 * 8
+        xb = torch.zeros(g.num_nodes, Fp, dtype=torch.bfloat16, device=dev)
+        xb[:, :g.num_features] = x.to(torch.bfloat16)
+        idx = torch.arange(0, g.num_nodes, 3, device=dev)
+        outs = []
+        for mode in ("0", "1", "all"):
+            monkeypatch.setattr(gcn_mod, "_QPULL", mode)
+            torch.manual_seed(0)
+            model = CommAwareGCN(g.num_features, 64, g.num_classes, HaloExchange(comm), comm, compute_dtype=torch.bfloat16).to(dev)
+            out = model(xb, pat)
+            loss = masked_cross_entropy(out, y, idx)
+            loss.backward()
+            outs.append((out.float().detach(), [p.grad.float().clone() for p in model.parameters()]))
+        for out, grads in outs[1:]:
+            assert (out - outs[0][0]).norm() <= 2e-2 * outs[0][0].norm()
+            for a, b in zip(grads, outs[0][1]):
+                assert (a - b).norm() <= 5e-2 * b.norm() + 1e-4
+    finally:
+        comm.destroy()

@@ -1,12 +1,15 @@
 """Opt-in ``DGRAPH_B200_GCN_QPULL`` order of operations (project owned rows, exchange ``Q``) against the default fused layer on
-one GPU in bf16.  Added after the round's GPU budget was spent: non-strict xfail until its first hardware run."""
+one GPU in bf16.  Added after the round's GPU budget was spent, so it is opt-in (``DGRAPH_B200_TEST_QPULL=1``) until its first
+hardware run: an in-process kernel fault would take the rest of the GPU tier down with it."""
+import os
+
 import pytest
 import torch
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(os.environ.get("DGRAPH_B200_TEST_QPULL", "0") != "1", reason="opt-in until first hardware run")]
 
 
-@pytest.mark.xfail(strict=False, reason="first hardware run decides (XPASS expected)")
 def test_qpull_matches_default_layer_bf16(monkeypatch):
     from dgraph_b200 import Communicator
     from dgraph_b200.data import make_graph, node_features_and_labels

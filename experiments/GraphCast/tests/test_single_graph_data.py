@@ -13,9 +13,10 @@ def test_graph_sizes(graph_generator, graphcast_config):
         assert g.num_grid == 1_038_240 and g.num_mesh == 40_962
         assert g.mesh_edges.shape[0] == 655_320
         assert g.mesh2grid_edges.shape[0] == 3_114_720
-        # grid2mesh: 1,618,824 in the reference (1,618,746 in the paper, data_utils/utils.py:160); the neighbour-radius
-        # test is floating-point sensitive at the boundary, so allow a small band
-        assert abs(g.grid2mesh_edges.shape[0] - 1_618_824) < 20_000
+        # grid2mesh: 1,618,824 in the reference (1,618,746 in the paper, data_utils/utils.py:160).  With the reference's mesh
+        # orientation (a face, not an edge, perpendicular to the polar axis) the count is reproduced; the neighbour-radius test is
+        # floating-point sensitive at the boundary, so a handful of edges of slack is allowed
+        assert abs(g.grid2mesh_edges.shape[0] - 1_618_824) <= 64, g.grid2mesh_edges.shape[0]
 
 
 def test_single_rank_shard_is_the_whole_graph(graph_generator):

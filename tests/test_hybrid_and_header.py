@@ -134,3 +134,29 @@ def test_hybrid_gradients_equal_sum_over_samples_and_partitions():
         (model(x, pat) ** 2).sum().backward()
     for r in range(4):
         assert torch.allclose(ret[r], opt.flat_g, rtol=1e-4, atol=1e-4 * float(opt.flat_g.abs().max())), r
+
+
+def test_docs_pages_follow_the_sources():
+    """``docs/kernels.md`` is generated from the C header and every ``:::`` target of ``docs/reference.md`` is importable."""
+    import importlib
+    import re
+    import subprocess
+    import sys
+
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "gen_kernel_docs.py"), "--check"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    for ln in open(os.path.join(ROOT, "docs", "reference.md")):
+        m = re.match(r"::: (\S+)", ln)
+        if not m:
+            continue
+        parts = m.group(1).split(".")
+        for i in range(len(parts), 0, -1):
+            try:
+                obj = importlib.import_module(".".join(parts[:i]))
+                break
+            except ImportError:
+                continue
+        else:
+            raise AssertionError(f"cannot import any prefix of {m.group(1)}")
+        for a in parts[i:]:
+            obj = getattr(obj, a)

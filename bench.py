@@ -46,7 +46,8 @@ def parse_args():
     ap.add_argument("--engine", default=None, help="override DGRAPH_B200_ENGINE (torch | peer)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cuda-graph", action="store_true",
-                    help="1 GPU only: capture the whole step (fwd+loss+bwd+Adam) in a CUDA graph and replay it")
+                    help="capture the whole step (fwd+loss+bwd+Adam) in a CUDA graph and replay it (measured on 1 GPU; with several GPUs it "
+                         "switches the peer engine to device-resident barrier epochs -- experimental, not yet run on hardware)")
     ap.add_argument("--cpu", action="store_true", help="CPU/gloo plumbing run (tiny graphs only)")
     return ap.parse_args()
 
@@ -132,6 +133,8 @@ def run_ours(args):
     rank, world, local, dev = setup_dist(args)
     if args.engine:
         os.environ["DGRAPH_B200_ENGINE"] = args.engine
+    if args.cuda_graph and world > 1:  # experimental: barrier epochs in device memory make the multi-GPU step capturable
+        os.environ["DGRAPH_B200_DEVICE_EPOCH"] = "1"
     from dgraph_b200 import Communicator
     from dgraph_b200.data import make_graph, contiguous_partition, node_features_and_labels
     from dgraph_b200.models.gcn import CommAwareGCN
@@ -166,7 +169,7 @@ def run_ours(args):
 
     torch.manual_seed(0)
     model = CommAwareGCN(F_in, args.hidden, g.num_classes, HaloExchange(comm), comm, compute_dtype=cdt).to(dev)
-    use_graph = bool(args.cuda_graph) and world == 1 and not args.cpu
+    use_graph = bool(args.cuda_graph) and not args.cpu and (world == 1 or getattr(comm.engine, "device_epoch", False))
     opt = FusedAdam(model.parameters(), lr=args.lr, comm=comm, capturable=use_graph)
     from dgraph_b200.ops import _sparsity
     from dgraph_b200.ops.loss import masked_cross_entropy

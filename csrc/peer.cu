@@ -47,6 +47,35 @@ __global__ void peer_barrier_kernel(uint32_t* const* pads, int rank, int world, 
   __threadfence_system();
 }
 
+// Same barrier with the epoch kept in device memory: the kernel takes the next epoch from `*epoch_dev` and stores it back, so a
+// CUDA graph that contains barriers replays correctly (a kernel argument would be frozen at capture time).  Every rank launches
+// the same sequence of barriers, hence all counters advance in lock-step.  One engine uses either this form or the host-epoch
+// form for its whole life, never both (the two counters would drift apart).
+__global__ void peer_barrier_dev_kernel(uint32_t* const* pads, int rank, int world, uint32_t* epoch_dev, int* timeout_flag,
+                                        long long max_spin) {
+  __shared__ uint32_t epoch_s;
+  const int d = threadIdx.x;
+  if (d == 0) epoch_s = *epoch_dev + 1u;
+  __syncthreads();
+  const uint32_t epoch = epoch_s;
+  __threadfence_system();  // publish everything earlier kernels of this stream wrote
+  if (d < world) {
+    st_release_sys(pads[d] + rank, epoch);
+    const uint32_t* mine = pads[rank] + d;
+    long long spins = 0;
+    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+      if (++spins > max_spin) {
+        if (timeout_flag) *timeout_flag = 1;
+        break;
+      }
+      __nanosleep(64);
+    }
+  }
+  __syncthreads();
+  if (d == 0) *epoch_dev = epoch;
+  __threadfence_system();
+}
+
 // ------------------------------------------------------------------------------------------------
 // Halo pull: dst[h, :] = peer[halo_owner[h]][halo_row[h], :]   (bf16 or any 2-byte / 4-byte type: copies 16-B chunks)
 // One sub-warp group per row; `row_bytes` multiple of 16.
@@ -130,6 +159,50 @@ __global__ void __launch_bounds__(256) adam_allreduce_kernel(float* __restrict__
                                                              float* __restrict__ g_out, int64_t n, AdamArgs a) {
   const int64_t i4 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i4 >= n) return;  // n is padded to a multiple of 4 by the host
+  float4 gs = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int r = 0; r < world; ++r) {
+    const uint4 raw = ldg_v4(peer_g[r] + i4);
+    gs.x += __uint_as_float(raw.x); gs.y += __uint_as_float(raw.y);
+    gs.z += __uint_as_float(raw.z); gs.w += __uint_as_float(raw.w);
+  }
+  if (g_out) *reinterpret_cast<float4*>(g_out + i4) = gs;
+  float4 pv = *reinterpret_cast<float4*>(p + i4);
+  float4 mv = *reinterpret_cast<float4*>(m + i4);
+  float4 vv = *reinterpret_cast<float4*>(v + i4);
+  float pp[4] = {pv.x, pv.y, pv.z, pv.w}, gg[4] = {gs.x, gs.y, gs.z, gs.w};
+  float mm[4] = {mv.x, mv.y, mv.z, mv.w}, vw[4] = {vv.x, vv.y, vv.z, vv.w};
+  const float inv_c1 = 1.f / a.bias_c1;
+  const float inv_sqrt_c2 = rsqrtf(a.bias_c2);
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const float gr = gg[t] * a.grad_scale + a.weight_decay * pp[t];
+    mm[t] = a.beta1 * mm[t] + (1.f - a.beta1) * gr;
+    vw[t] = a.beta2 * vw[t] + (1.f - a.beta2) * gr * gr;
+    pp[t] -= a.lr * (mm[t] * inv_c1) / (sqrtf(vw[t]) * inv_sqrt_c2 + a.eps);
+  }
+  *reinterpret_cast<float4*>(p + i4) = make_float4(pp[0], pp[1], pp[2], pp[3]);
+  *reinterpret_cast<float4*>(m + i4) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+  *reinterpret_cast<float4*>(v + i4) = make_float4(vw[0], vw[1], vw[2], vw[3]);
+}
+
+// Capturable form of the fused all-reduce + Adam step: step counter and {lr, 1 - beta1^t, 1 - beta2^t} live in device memory
+// (same convention as dgb_adam_flat_capturable in adam.cu), so the launch can sit inside a CUDA graph.
+__global__ void adam_tick_peer_kernel(int* __restrict__ step, float* __restrict__ dev_state, float beta1, float beta2) {
+  const int t = *step + 1;
+  *step = t;
+  dev_state[1] = 1.f - powf(beta1, (float)t);
+  dev_state[2] = 1.f - powf(beta2, (float)t);
+}
+
+__global__ void __launch_bounds__(256) adam_allreduce_dev_kernel(float* __restrict__ p, const float* const* __restrict__ peer_g,
+                                                                 int world, float* __restrict__ m, float* __restrict__ v,
+                                                                 float* __restrict__ g_out, int64_t n, AdamArgs a,
+                                                                 const float* __restrict__ dev_state) {
+  const int64_t i4 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i4 >= n) return;
+  a.lr = dev_state[0];
+  a.bias_c1 = dev_state[1];
+  a.bias_c2 = dev_state[2];
   float4 gs = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int r = 0; r < world; ++r) {
     const uint4 raw = ldg_v4(peer_g[r] + i4);
@@ -354,6 +427,33 @@ DGB_API int dgb_adam_allreduce(float* p, const void* const* peer_g, int world, f
   const int64_t threads = n / 4;
   adam_allreduce_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       p, (const float* const*)peer_g, world, m, v, g_out, n, a);
+  DGB_CHECK_LAUNCH();
+  return 0;
+}
+
+// Barrier whose epoch lives in device memory (`epoch_dev`, one uint32 per engine, zero-initialised): capturable in a CUDA graph.
+DGB_API int dgb_peer_barrier_dev(void* const* pads, int rank, int world, unsigned* epoch_dev, int* timeout_flag,
+                                 long long max_spin, void* stream) {
+  if (world < 1 || world > 64 || !epoch_dev) return (int)cudaErrorInvalidValue;
+  peer_barrier_dev_kernel<<<1, 64, 0, (cudaStream_t)stream>>>((uint32_t* const*)pads, rank, world, epoch_dev, timeout_flag,
+                                                              max_spin);
+  DGB_CHECK_LAUNCH();
+  return 0;
+}
+
+// dgb_adam_allreduce with `step_dev` (int32) and `dev_state` = {lr, 1-beta1^t, 1-beta2^t, unused} in device memory: two launches
+// (tick + update), nothing that changes from step to step is a kernel argument.
+DGB_API int dgb_adam_allreduce_capturable(float* p, const void* const* peer_g, int world, float* m, float* v, float* g_out,
+                                          int64_t n, float beta1, float beta2, float eps, float weight_decay, float grad_scale,
+                                          int* step_dev, float* dev_state, void* stream) {
+  if (n == 0) return 0;
+  if ((n & 3) || !step_dev || !dev_state) return (int)cudaErrorInvalidValue;
+  adam_tick_peer_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_dev, dev_state, beta1, beta2);
+  DGB_CHECK_LAUNCH();
+  AdamArgs a{0.f, beta1, beta2, eps, weight_decay, grad_scale, 1.f, 1.f};
+  const int64_t threads = n / 4;
+  adam_allreduce_dev_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      p, (const float* const*)peer_g, world, m, v, g_out, n, a, dev_state);
   DGB_CHECK_LAUNCH();
   return 0;
 }

@@ -101,10 +101,13 @@ class FusedAdam(torch.optim.Optimizer):
         W = self._global_world() if (self.comm is not None and self.grad_average) else 1
         lr, (b1, b2), eps, wd = g["lr"], g["betas"], g["eps"], g["weight_decay"]
         if self.capturable:
-            assert self._peer is None, "capturable mode is single-engine (no peer-memory fused all-reduce yet)"
-            self.sync_grads()
             if not torch.cuda.is_current_stream_capturing():
                 self.sync_hyper()
+            if self._peer is not None:  # gradient sum over NVLink + Adam, step / lr read from device memory
+                self._peer.adam_allreduce_capturable(self.flat_p, self._g_off, self.flat_m, self.flat_v, self.flat_p.numel(),
+                                                     b1, b2, eps, wd, 1.0 / W, self._dev_step, self._dev_state)
+                return loss
+            self.sync_grads()
             N.check(N.lib().dgb_adam_flat_capturable(N.ptr(self.flat_p), N.ptr(self.flat_g), N.ptr(self.flat_m),
                                                      N.ptr(self.flat_v), N.ptr(None), N.i64(self.flat_p.numel()),
                                                      N.f32(b1), N.f32(b2), N.f32(eps), N.f32(wd), N.f32(1.0 / W),

@@ -408,6 +408,10 @@ class PeerMemoryEngine(TorchDistEngine):
         self._rings: Dict[Tuple, List] = {}
         self._by_off: Dict[int, dict] = {}
         self._timeout_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        # opt-in (DGRAPH_B200_DEVICE_EPOCH=1, not yet run on hardware): barrier epochs counted in device memory, so a training step
+        # with exchanges can be captured in a CUDA graph.  Fixed at construction: the two barrier forms must never be mixed.
+        self.device_epoch = os.environ.get("DGRAPH_B200_DEVICE_EPOCH", "0") == "1"
+        self._epoch_dev = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.arena: Optional[SymmetricArena] = None
         if self._world > 1:
             mb = arena_mb or int(os.environ.get("DGRAPH_B200_ARENA_MB", "8192"))
@@ -519,6 +523,12 @@ class PeerMemoryEngine(TorchDistEngine):
             return
         _pending.wait_all()  # no rank may run ahead of a pull that still reads its peers' slots
         self._epoch += 1
+        spins = ctypes.c_longlong(int(os.environ.get("DGRAPH_B200_BARRIER_SPINS", str(1 << 26))))
+        if self.device_epoch:  # the kernel takes the epoch from (and advances) the device counter: capturable
+            N.check(N.lib().dgb_peer_barrier_dev(N.ptr(self.arena.pad_table), N.i32(self._rank), N.i32(self._world),
+                                                 N.ptr(self._epoch_dev), N.ptr(self._timeout_flag), spins, N.stream()),
+                    "dgb_peer_barrier_dev")
+            return
         N.check(N.lib().dgb_peer_barrier(N.ptr(self.arena.pad_table), N.i32(self._rank), N.i32(self._world),
                                          ctypes.c_uint(self._epoch & 0xFFFFFFFF), N.ptr(self._timeout_flag),
                                          ctypes.c_longlong(int(os.environ.get("DGRAPH_B200_BARRIER_SPINS", str(1 << 26)))),
@@ -581,6 +591,18 @@ class PeerMemoryEngine(TorchDistEngine):
                 "dgb_adam_allreduce")
         N.count_launch(2)
         self.barrier_on_stream()  # nobody zeroes its gradient buffer while a peer is still reading it
+
+    def adam_allreduce_capturable(self, flat_p, flat_g_off, flat_m, flat_v, n, b1, b2, eps, wd, grad_scale, step_dev, dev_state):
+        """``adam_allreduce`` with the step counter and the learning rate in device memory (CUDA-graph capture; needs the
+        device-epoch barriers)."""
+        assert self.device_epoch, "capturable multi-GPU steps need DGRAPH_B200_DEVICE_EPOCH=1 (set before the engine is created)"
+        self.barrier_on_stream()
+        N.check(N.lib().dgb_adam_allreduce_capturable(N.ptr(flat_p), N.ptr(self.arena.ptr_table(flat_g_off)), N.i32(self._world),
+                                                      N.ptr(flat_m), N.ptr(flat_v), N.ptr(None), N.i64(n), N.f32(b1), N.f32(b2),
+                                                      N.f32(eps), N.f32(wd), N.f32(grad_scale), N.ptr(step_dev),
+                                                      N.ptr(dev_state), N.stream()), "dgb_adam_allreduce_capturable")
+        N.count_launch(3)
+        self.barrier_on_stream()
 
     def finalize(self) -> None:
         if self.arena is not None:

@@ -25,7 +25,8 @@ def loss_fn(pred, target, ranks_per_sample, world):
 
 def main(batch_size: int = 1, is_distributed: bool = False, test_run: bool = False, use_synthetic_data: bool = True,
          benchmark: bool = False, backend: str = "single", procs_per_graph: int = 2, iters: int = 10, mesh_level: int = 6,
-         lat: int = 721, lon: int = 1440, hidden_dim: int = 128, save_dir: str = "", resume: str = "", placement: str = "bands"):
+         lat: int = 721, lon: int = 1440, hidden_dim: int = 128, save_dir: str = "", resume: str = "", placement: str = "bands",
+         cuda_graph: bool = False):
     from dgraph_b200.data.graphcast_graph import DistributedGraphCastGraphGenerator, SyntheticWeatherDataset
     from dgraph_b200.models.graphcast import Config, DGraphCast
     from dgraph_b200.optim import FusedAdam
@@ -34,6 +35,8 @@ def main(batch_size: int = 1, is_distributed: bool = False, test_run: bool = Fal
     assert backend in ("single", "nccl", "nvshmem", "mpi")
     assert batch_size == 1, "full-graph training: one sample per step (as the reference)"
     world_env = int(os.environ.get("WORLD_SIZE", "1"))
+    if cuda_graph and world_env > 1:  # experimental: device-resident barrier epochs make steps with halo exchanges capturable
+        os.environ["DGRAPH_B200_DEVICE_EPOCH"] = "1"
     hybrid = is_distributed and 0 < procs_per_graph < world_env and world_env % procs_per_graph == 0
     # hybrid data-parallel x graph-partition: `procs_per_graph` ranks share one sample's graph, replicas take different samples
     comm, rank, world, dev = init_distributed("nccl" if backend == "single" else backend,
@@ -50,7 +53,8 @@ def main(batch_size: int = 1, is_distributed: bool = False, test_run: bool = Fal
                                    grid_rows=sg.grid_rows_global.cpu())
     torch.manual_seed(0)
     model = DGraphCast(cfg, comm).to(dev)
-    opt = FusedAdam(model.parameters(), lr=cfg.training.lr, comm=comm)
+    use_graph = bool(cuda_graph) and dev.type == "cuda" and (comm.get_world_size() == 1 or getattr(comm.engine, "device_epoch", False))
+    opt = FusedAdam(model.parameters(), lr=cfg.training.lr, comm=comm, capturable=use_graph)
     tc = cfg.training
     sched = torch.optim.lr_scheduler.SequentialLR(opt, [
         torch.optim.lr_scheduler.LinearLR(opt, start_factor=1e-3, end_factor=1.0, total_iters=tc.num_iters_step1),
@@ -63,15 +67,27 @@ def main(batch_size: int = 1, is_distributed: bool = False, test_run: bool = Fal
     sampler = CommAwareDistributedSampler(data, comm, shuffle=False)  # every rank of a replica sees the same sample
     order = list(sampler)
     times = []
+    graphed = None
+    if use_graph:
+        # ~600 small launches per step (far more CPU time than GPU time once the graph is split over 8 GPUs) become one
+        # cudaGraphLaunch.  Capturing runs two eager warm-up steps on the first sample.
+        from dgraph_b200.utils.cuda_graph import GraphedTrainStep
+
+        first = data[order[start % len(order)]]
+        graphed = GraphedTrainStep(lambda a, b: loss_fn(model(a, sg), b, world, world), opt,
+                                   (first["invar"].to(dev, cdt), first["outvar"].to(dev, cdt)), warmup=2)
     for it in range(start, start + iters):
         item = data[order[it % len(order)]]
         x, y = item["invar"].to(dev, cdt), item["outvar"].to(dev, cdt)
         comm.barrier()
         t0 = time.perf_counter()
-        opt.zero_grad()
-        loss = loss_fn(model(x, sg), y, world, world)  # factor 1: FusedAdam already averages over the whole world
-        loss.backward()
-        opt.step()
+        if graphed is not None:
+            loss = graphed(x, y)
+        else:
+            opt.zero_grad()
+            loss = loss_fn(model(x, sg), y, world, world)  # factor 1: FusedAdam already averages over the whole world
+            loss.backward()
+            opt.step()
         sched.step()
         lv = float(loss.detach())
         times.append((time.perf_counter() - t0) * 1e3)

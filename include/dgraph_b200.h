@@ -149,6 +149,14 @@ int dgb_halo_grad_reduce(void* gx, int64_t ld_gx, const void* g_local, int64_t l
 int dgb_adam_allreduce(float* p, const void* const* peer_g, int world, float* m, float* v, float* g_out, int64_t n, float lr,
                        float beta1, float beta2, float eps, float weight_decay, float grad_scale, int step, void* stream);
 int dgb_allreduce_sum_f32(float* out, const void* const* peer, int world, int64_t n, void* stream);
+/* CUDA-graph-capturable forms: the barrier epoch, the optimizer step and the learning rate are read from device memory instead of
+ * being kernel arguments (which a graph freezes at capture time).  An engine uses either dgb_peer_barrier or dgb_peer_barrier_dev
+ * for its whole life.  No counterpart in the reference (no CUDA graphs there). */
+int dgb_peer_barrier_dev(void* const* pads, int rank, int world, unsigned* epoch_dev, int* timeout_flag, long long max_spin,
+                         void* stream);
+int dgb_adam_allreduce_capturable(float* p, const void* const* peer_g, int world, float* m, float* v, float* g_out, int64_t n,
+                                  float beta1, float beta2, float eps, float weight_decay, float grad_scale, int* step_dev,
+                                  float* dev_state, void* stream);
 
 /* ---- fused masked cross-entropy (csrc/loss_ops.cu); reference: ATen chain in experiments/OGB/main.py:115,140-148 ---- */
 int dgb_masked_ce_fwd(const void* logits, int64_t ld, int is_f32, const int64_t* labels, const int64_t* idx,

@@ -1,0 +1,99 @@
+"""Multi-GPU training step inside a CUDA graph (peer-memory engine with device-resident barrier epochs) against the same steps
+run eagerly.  Experimental: written after the round's GPU budget was spent, so it only runs with
+``DGRAPH_B200_TEST_DEVICE_EPOCH=1`` on a box with >= 2 GPUs (a barrier that never completes would hang the worker processes)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+from tests._graphs import random_graph, partition
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu, pytest.mark.timeout(300),
+              pytest.mark.skipif(os.environ.get("DGRAPH_B200_TEST_DEVICE_EPOCH", "0") != "1", reason="opt-in until first hardware run")]
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, W, port, e, part, xg, yg, state, ret):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(W),
+                      DGRAPH_B200_ARENA_MB="256", DGRAPH_B200_DEVICE_EPOCH="1")
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=W, device_id=dev)
+    from dgraph_b200 import Communicator
+    from dgraph_b200.models.gcn import CommAwareGCN
+    from dgraph_b200.ops.loss import masked_cross_entropy
+    from dgraph_b200.optim import FusedAdam
+    from dgraph_b200.parallel import HaloExchange, build_communication_pattern
+    from dgraph_b200.utils.cuda_graph import GraphedTrainStep
+
+    comm = Communicator.init_process_group("nccl")
+    assert comm.engine.device_epoch
+    pat = build_communication_pattern(e.to(dev), part.to(dev), rank, W)
+    gids = pat.local_vertices_global
+    xl, yl = xg.to(dev)[gids].bfloat16(), yg.to(dev)[gids]
+    idx = torch.arange(0, gids.numel(), 2, device=dev)
+    ex = HaloExchange(comm)
+
+    def run(graphed: bool):
+        torch.manual_seed(0)
+        model = CommAwareGCN(xg.shape[1], 64, 5, ex, comm, compute_dtype=torch.bfloat16).to(dev)
+        model.load_state_dict(state)
+        opt = FusedAdam(model.parameters(), lr=1e-2, comm=comm, capturable=True)
+
+        def forward_loss(a, b):
+            return masked_cross_entropy(model(a, pat), b, idx)
+
+        losses = []
+        if graphed:
+            step = GraphedTrainStep(forward_loss, opt, (xl, yl), warmup=2)  # two eager steps, then capture
+            for _ in range(2):
+                losses.append(float(step(xl, yl)))
+        else:
+            for _ in range(4):
+                opt.zero_grad()
+                loss = forward_loss(xl, yl)
+                loss.backward()
+                opt.step()
+                losses.append(float(loss))
+            losses = losses[2:]
+        return losses, {k: v.detach().float().cpu() for k, v in model.state_dict().items()}
+
+    eager = run(False)
+    graph = run(True)
+    comm.engine.check_timeouts()
+    ret[rank] = (eager, graph)
+    comm.destroy()
+    comm.engine.finalize()
+    dist.destroy_process_group()
+
+
+def test_graphed_multi_gpu_step_matches_eager():
+    W = 2
+    if torch.cuda.device_count() < W:
+        pytest.skip(f"needs {W} GPUs")
+    from dgraph_b200.models.gcn import CommAwareGCN
+
+    torch.manual_seed(0)
+    V, F = 2000, 32
+    e = random_graph(V, 8, seed=11)
+    part = partition(V, W, "contiguous")
+    xg, yg = torch.randn(V, F), torch.randint(0, 5, (V,))
+    state = {k: v.clone() for k, v in CommAwareGCN(F, 64, 5, None, None).state_dict().items()}
+    ret = mp.Manager().dict()
+    mp.spawn(_worker, args=(W, _free_port(), e, part, xg, yg, state, ret), nprocs=W, join=True)
+    for r in range(W):
+        (l_e, sd_e), (l_g, sd_g) = ret[r]
+        assert torch.allclose(torch.tensor(l_e), torch.tensor(l_g), rtol=1e-3, atol=1e-4), (l_e, l_g)
+        for k in sd_e:
+            assert torch.allclose(sd_e[k], sd_g[k], rtol=1e-3, atol=1e-4), k

@@ -577,6 +577,32 @@ class PeerMemoryEngine(TorchDistEngine):
         self.mark_read(off)
         return pub[: info.n_nbr_local], (self.arena.ptr_table(off), info.halo_owner, info.halo_row, info.n_nbr_local)
 
+    # ---- small all-reduces over peer memory --------------------------------------------------------
+    def all_reduce(self, tensor, op="sum"):
+        """Opt-in (``DGRAPH_B200_PEER_ALLREDUCE=1``, not yet run end to end on hardware): fp32 sums of up to 1 M elements -- BatchNorm
+        statistics, loss scalars -- are published in a symmetric slot and summed by ONE kernel that reads every peer's copy
+        (``dgb_allreduce_sum_f32``; same summation order on every rank, so the results are bit-identical across ranks).  No NCCL
+        call, hence capturable with the device-epoch barriers.  Everything else takes the NCCL path."""
+        if (self._world > 1 and op == "sum" and os.environ.get("DGRAPH_B200_PEER_ALLREDUCE", "0") == "1" and tensor.is_cuda
+                and tensor.dtype == torch.float32 and tensor.is_contiguous() and 0 < tensor.numel() <= (1 << 20)):
+            n = tensor.numel()
+            n4 = (n + 3) // 4 * 4
+            buf, off = self.slot_tensor(("allreduce", n4), (n4,), torch.float32, ring=False)
+            if n4 != n:
+                buf[n:].zero_()
+            buf[:n].copy_(tensor.reshape(-1))
+            self.barrier_on_stream()
+            flat = tensor.reshape(-1)
+            out = flat if n4 == n else torch.empty(n4, dtype=torch.float32, device=tensor.device)
+            N.check(N.lib().dgb_allreduce_sum_f32(N.ptr(out), N.ptr(self.arena.ptr_table(off)), N.i32(self._world), N.i64(n4),
+                                                  N.stream()), "dgb_allreduce_sum_f32")
+            N.count_launch(2)
+            self.mark_read(off)
+            if n4 != n:
+                flat.copy_(out[:n])
+            return tensor
+        return super().all_reduce(tensor, op)
+
     # ---- fused gradient all-reduce + Adam ----------------------------------------------------------
     def symmetric_flat(self, key: str, numel: int, dtype=torch.float32) -> Tuple[torch.Tensor, int]:
         n = (numel + 3) // 4 * 4

@@ -69,6 +69,16 @@ def _worker(rank, W, port, e, part, xg, yg, state, ret):
             losses = losses[2:]
         return losses, {k: v.detach().float().cpu() for k, v in model.state_dict().items()}
 
+    # small all-reduce through peer memory (opt-in switch) == the arithmetic sum
+    os.environ["DGRAPH_B200_PEER_ALLREDUCE"] = "1"
+    t = torch.arange(10, device=dev, dtype=torch.float32) + rank
+    comm.all_reduce(t)
+    assert torch.equal(t, torch.arange(10, device=dev, dtype=torch.float32) * W + sum(range(W)))
+    t = torch.full((8,), float(rank + 1), device=dev)
+    comm.all_reduce(t)  # same slot again: the engine orders the overwrite after the peers' reads
+    assert torch.equal(t, torch.full((8,), float(sum(range(1, W + 1))), device=dev))
+    os.environ["DGRAPH_B200_PEER_ALLREDUCE"] = "0"
+
     eager = run(False)
     graph = run(True)
     comm.engine.check_timeouts()

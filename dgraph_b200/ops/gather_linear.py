@@ -40,14 +40,14 @@ class _GatherLinear(Function):
         for s, i in zip(srcs, idxs):
             M = int(i.shape[0]) if i is not None else int(s.shape[0])
         wp = pack_segment_weight(weight, ks)
-        pre = gather_gemm_bf16(srcs, idxs, wp, bias, M, ks, act=None)
+        # ReLU runs in the GEMM epilogue and its gradient needs only the output; SiLU's gradient needs the pre-activation, so
+        # that one is stored and the activation is a second kernel
+        pre = gather_gemm_bf16(srcs, idxs, wp, bias, M, ks, act="relu" if act == "relu" else None)
         ctx.act, ctx.n_src, ctx.ks, ctx.scatter_plans = act, n_src, ks, scatter_plans
         ctx.save_for_backward(weight, pre if act else None, *srcs, *[i for i in idxs if i is not None])
         ctx.idx_none = [i is None for i in idxs]
         if act == "silu":
             return F.silu(pre)
-        if act == "relu":
-            return torch.relu(pre)
         return pre
 
     @staticmethod
@@ -65,7 +65,7 @@ class _GatherLinear(Function):
 
             g = silu_backward(g, pre)
         elif ctx.act == "relu":
-            g = g * (pre > 0).to(g.dtype)
+            g = torch.ops.aten.threshold_backward(g, pre, 0)  # `pre` holds the ReLU output here: g where out > 0 else 0
         wb = weight.to(torch.bfloat16)
         dcat = gemm_bf16_tn(g, wb.t().contiguous())  # [M, sum(ks)]
         dw = None

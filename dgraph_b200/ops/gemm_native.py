@@ -137,5 +137,5 @@ def gemm_bf16_nn_grad_w(g: torch.Tensor, x: torch.Tensor, x_idx: Optional[torch.
 
 def act_backward(g: torch.Tensor, y: torch.Tensor, act: str) -> torch.Tensor:
     if act == "relu":
-        return g * (y > 0).to(g.dtype)
+        return torch.ops.aten.threshold_backward(g, y, 0)  # g where y > 0 else 0, one kernel (was compare + cast + multiply)
     raise NotImplementedError(f"fused backward for activation {act}")

@@ -119,3 +119,27 @@ def test_wgrad_with_gathered_rows_matches_reference(M, N1, N2, V):
     dw = gemm_bf16_nn_grad_w(g, x, idx)
     ref = g.float().t() @ x.float()[idx.long()]
     assert torch.allclose(dw, ref, rtol=1e-2, atol=2e-2 * (M ** 0.5)), (dw - ref).abs().max().item()
+
+
+def test_gather_linear_relu_forward_backward_matches_fp32():
+    """The GraphSAGE layer's op: ``relu(Linear(cat([x_local, agg])))`` with the ReLU in the GEMM epilogue and a gradient that needs
+    only the output -- against autograd through the fp32 statement."""
+    from dgraph_b200.ops.gather_linear import gather_linear, gather_linear_ref
+
+    torch.manual_seed(5)
+    M, K, N = 3000, 64, 256
+    a = torch.randn(M, K, device="cuda").bfloat16().requires_grad_()
+    b = torch.randn(M, K, device="cuda").bfloat16().requires_grad_()
+    w = (torch.randn(N, 2 * K, device="cuda") * 0.1).requires_grad_()
+    bias = (torch.randn(N, device="cuda") * 0.1).requires_grad_()
+    y = gather_linear([a, b], [None, None], w, bias, act="relu")
+    go = torch.randn_like(y)
+    y.backward(go)
+    a32, b32 = a.detach().float().requires_grad_(), b.detach().float().requires_grad_()
+    w32, bias32 = w.detach().bfloat16().float().requires_grad_(), bias.detach().clone().requires_grad_()
+    yr = gather_linear_ref([a32, b32], [None, None], w32, bias32, act="relu")
+    yr.backward(go.float())
+    assert (y.float() - yr).norm() <= 1e-2 * yr.norm()
+    assert ((y > 0) == (yr > 0)).float().mean() > 0.99
+    for got, want in [(a.grad, a32.grad), (b.grad, b32.grad), (w.grad, w32.grad), (bias.grad, bias32.grad)]:
+        assert (got.float() - want).norm() <= 3e-2 * want.norm() + 1e-3

@@ -5,8 +5,11 @@ Every public name of the reference package is re-exported from here so existing 
 build_communication_pattern}``, ``DGraph.distributed.nccl.{NCCLBackendEngine, TIMINGS, NCCLGraphCommPlan, ...}``,
 ``DGraph.data.*``, ``DGraph.utils.TimingReport``.
 """
-from dgraph_b200.communicator import Communicator
-from dgraph_b200.communicator_base import CommunicatorBase
+# The package attributes ``Communicator`` / ``CommunicatorBase`` are classes although submodules of the same names exist (as in
+# the reference).  Importing a submodule for the first time rebinds the package attribute to the module, so both submodules are
+# loaded here, before the classes are bound: a later ``import DGraph.CommunicatorBase`` then changes nothing.
+from DGraph.Communicator import Communicator
+from DGraph.CommunicatorBase import CommunicatorBase
 from dgraph_b200.__version__ import __version__
 
 __all__ = ["Communicator", "CommunicatorBase", "__version__"]

@@ -119,7 +119,8 @@ def xyz2sph(xyz: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
 
 
 def edge_features(sender_xyz: np.ndarray, receiver_xyz: np.ndarray) -> np.ndarray:
-    """[E, 4]: sender relative to receiver in the receiver's local frame, [len, dx, dy, dz] / max len."""
+    """[E, 4]: sender relative to receiver in the receiver's local frame, [dx, dy, dz, len] / max len -- the column order of the
+    reference (``data_utils/utils.py:60-82``), so that the first Linear of an edge embedder means the same in both code bases."""
     lat, lon = xyz2sph(receiver_xyz)
     cl, sl, cp, sp = np.cos(lon), np.sin(lon), np.cos(lat), np.sin(lat)
     # R = R_y(lat) @ R_z(-lon): brings the receiver to (1, 0, 0)
@@ -132,7 +133,7 @@ def edge_features(sender_xyz: np.ndarray, receiver_xyz: np.ndarray) -> np.ndarra
     disp = rot(sender_xyz) - rot(receiver_xyz)
     n = np.linalg.norm(disp, axis=1, keepdims=True)
     mx = max(float(n.max()) if n.size else 1.0, 1e-12)
-    return np.concatenate([n, disp], axis=1) / mx
+    return np.concatenate([disp, n], axis=1) / mx
 
 
 def grid2mesh_edges(grid_xyz: np.ndarray, mesh_xyz: np.ndarray, max_edge_len: float, k: int = 4, frac: float = 0.6):
@@ -148,8 +149,7 @@ def grid2mesh_edges(grid_xyz: np.ndarray, mesh_xyz: np.ndarray, max_edge_len: fl
 def mesh2grid_edges(grid_xyz: np.ndarray, mesh_xyz: np.ndarray, faces: np.ndarray):
     from scipy.spatial import cKDTree
 
-    cent = mesh_xyz[faces].mean(axis=1)
-    cent /= np.linalg.norm(cent, axis=1, keepdims=True)
+    cent = mesh_xyz[faces].mean(axis=1)  # flat-face centroids (not pushed onto the sphere), as in data_utils/utils.py:117-120
     _, fi = cKDTree(cent).query(grid_xyz, k=1)
     src = faces[fi].reshape(-1)
     dst = np.repeat(np.arange(grid_xyz.shape[0]), 3)

@@ -31,15 +31,33 @@ def node_offsets(num_nodes: int, world_size: int) -> torch.Tensor:
     return torch.tensor([num_nodes * r // world_size for r in range(world_size + 1)], dtype=torch.long)
 
 
+def offsets_from_rank_mapping(rank_mapping: Optional[torch.Tensor], num_nodes: int, world_size: int) -> torch.Tensor:
+    """Vertex ranges ``[W + 1]`` described by a per-vertex rank tensor (the ``*_rank_mapping_file`` arguments of the reference's
+    OGB-LSC entry point).  The plans address vertices by contiguous ranges (as ``_NCCLCommPlan.py:210`` does with ``bucketize``),
+    so the mapping has to be non-decreasing; ``None`` gives the even split."""
+    if rank_mapping is None:
+        return node_offsets(num_nodes, world_size)
+    rm = torch.as_tensor(rank_mapping).reshape(-1).long()
+    if rm.numel() != num_nodes:
+        raise ValueError(f"rank mapping has {rm.numel()} entries for {num_nodes} vertices")
+    if rm.numel() and (bool((rm[1:] < rm[:-1]).any()) or int(rm.min()) < 0 or int(rm.max()) >= world_size):
+        raise ValueError("rank mapping must be non-decreasing with values in [0, world_size): renumber the vertices so that "
+                         "every rank owns one contiguous range")
+    off = torch.zeros(world_size + 1, dtype=torch.long)
+    off[1:] = torch.bincount(rm, minlength=world_size).cumsum(0)
+    return off
+
+
 class DistributedHeteroGraphDataset:
     def __init__(self, rank: int, world_size: int, num_nodes: List[int], features: List[torch.Tensor],
                  edges: List[torch.Tensor], labels: torch.Tensor, num_classes: int, comm=None,
-                 split: Optional[Dict[str, torch.Tensor]] = None, cache_dir: Optional[str] = None):
+                 split: Optional[Dict[str, torch.Tensor]] = None, cache_dir: Optional[str] = None,
+                 offsets: Optional[List[torch.Tensor]] = None):
         """``edges[k]`` is ``[E_k, 2]`` with column 0 = source id, column 1 = destination id of relation ``RELATIONS[k]``;
         ``features[t]`` holds this rank's rows of node type ``t``; ``labels`` this rank's paper labels."""
         self.rank, self.world_size, self.comm = rank, world_size, comm
         self.num_nodes, self.num_classes = list(num_nodes), num_classes
-        self.offsets = [node_offsets(n, world_size) for n in num_nodes]
+        self.offsets = list(offsets) if offsets is not None else [node_offsets(n, world_size) for n in num_nodes]
         self.paper_vertex_offset, self.author_vertex_offset, self.institution_vertex_offset = self.offsets
         self.features, self.edges, self.labels = features, edges, labels
         self.split = split or {}
@@ -195,7 +213,8 @@ class DGraph_MAG240M_Dataset(DistributedHeteroGraphDataset):
     the same width (what the reference currently trains with: ``randn(..., 1)``, ``MAG240M_dataset.py:150-170``)."""
 
     def __init__(self, rank, world_size, data_dir="data/MAG240M", comm=None, features: str = "random", feature_dim: int = 0,
-                 cache_dir: Optional[str] = None, dtype=torch.float32, seed: int = 0, **kw):
+                 cache_dir: Optional[str] = None, dtype=torch.float32, seed: int = 0, paper_rank_mappings=None,
+                 author_rank_mappings=None, institution_rank_mappings=None, **kw):
         from dgraph_b200.data.ogb_raw import MAG240MFiles, find_mag240m
 
         if find_mag240m(data_dir) is None:
@@ -203,7 +222,8 @@ class DGraph_MAG240M_Dataset(DistributedHeteroGraphDataset):
                                "no network access here -- use SyntheticHeterogeneousDataset for MAG240M-shaped runs")
         f = MAG240MFiles(data_dir)
         n = [f.num_papers, f.num_authors, f.num_institutions]
-        offs = [node_offsets(k, world_size) for k in n]
+        offs = [offsets_from_rank_mapping(m, k, world_size)
+                for m, k in zip((paper_rank_mappings, author_rank_mappings, institution_rank_mappings), n)]
         rng = [(int(o[rank]), int(o[rank + 1])) for o in offs]
         cites = _edges_touching(f.edge_index("cites"), rng[0], rng[0])
         writes = _edges_touching(f.edge_index("writes"), rng[1], rng[0])  # author -> paper
@@ -257,4 +277,5 @@ class DGraph_MAG240M_Dataset(DistributedHeteroGraphDataset):
         labels = f.labels()[rng[0][0]:rng[0][1]].contiguous()
         sp = f.split()
         split = {"train": sp["train"], "valid": sp.get("valid", sp.get("val")), "test": sp.get("test-dev", sp.get("test"))}
-        super().__init__(rank, world_size, n, feats, edges, labels, f.num_classes, comm=comm, split=split, cache_dir=cache_dir)
+        super().__init__(rank, world_size, n, feats, edges, labels, f.num_classes, comm=comm, split=split, cache_dir=cache_dir,
+                         offsets=offs)

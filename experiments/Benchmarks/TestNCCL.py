@@ -98,6 +98,66 @@ def run_legacy(comm, F, iters, dev, use_cache):
     return _time(gather, iters, dev), _time(scatter, iters, dev)
 
 
+class NCCLBenchmark:
+    """The reference's benchmark object (``TestNCCL.py:23-111``): per-iteration device times of the vector-addressed
+    ``comm.gather`` / ``comm.scatter`` (``indices`` + stacked ``rank_mappings``).  ``cache=False`` drops the engine's plan cache
+    before every call (the reference's "without cache" arm); any other value keeps it."""
+
+    def __init__(self, comm, world_size: int, rank: int):
+        self.comm, self.world_size, self.rank = comm, world_size, rank
+
+    def comm_stats_gather(self, edge_rank_placement, edge_src_rank):
+        """Messages this rank receives (its edges whose source lives elsewhere) and sends (others' edges whose source is here)."""
+        mine = edge_rank_placement == self.rank
+        return {"local_comm_rev": (edge_src_rank[mine] != self.rank).sum(), "local_comm_send": (edge_src_rank[~mine] == self.rank).sum()}
+
+    comm_stats_scatter = comm_stats_gather
+
+    def _device(self, t):
+        return t.device
+
+    def _drop_cache(self, cache):
+        if cache is False and hasattr(self.comm.engine, "_legacy_plans"):
+            self.comm.engine._legacy_plans.clear()
+
+    def benchmark_gather(self, data, edge_rank_placement, edge_src_rank, edge_indices, cache=None, num_iters: int = 1000):
+        maps = torch.cat([edge_rank_placement, edge_src_rank], dim=0)
+
+        def one():
+            self._drop_cache(cache)
+            self.comm.gather(data, edge_indices, maps)
+
+        self.comm.barrier()
+        return _time(one, num_iters, self._device(data))
+
+    def benchmark_scatter(self, data, edge_rank_placement, edge_dest_rank, edge_indices, num_local_vertices, cache=None,
+                          num_iters: int = 1000):
+        maps = torch.cat([edge_rank_placement, edge_dest_rank], dim=0)
+
+        def one():
+            self._drop_cache(cache)
+            self.comm.scatter(data, edge_indices, maps, num_local_vertices)
+
+        self.comm.barrier()
+        return _time(one, num_iters, self._device(data))
+
+
+def run_gather_benchmark(benchmark: NCCLBenchmark, num_iters: int, graph_data, cache=None):
+    """Times ``comm.gather`` on a ``GatherGraphData`` (``graph_utils.py``): this rank's vertex rows as ``[1, n_local, F]``."""
+    F = graph_data.vertex_data.shape[-1]
+    local = graph_data.vertex_data[graph_data.vertex_rank_mapping == benchmark.rank, :].view(1, -1, F).contiguous()
+    return benchmark.benchmark_gather(local, graph_data.edge_rank_placement, graph_data.edge_src_rank, graph_data.edge_indices,
+                                      num_iters=num_iters, cache=cache)
+
+
+def run_scatter_benchmark(benchmark: NCCLBenchmark, num_iters: int, graph_data, cache=None):
+    """Times ``comm.scatter`` on a ``ScatterGraphData``: this rank's edge rows as ``[1, e_local, F]``."""
+    F = graph_data.vertex_data.shape[-1]
+    local = graph_data.vertex_data[graph_data.data_rank_mapping == benchmark.rank].view(1, -1, F).contiguous()
+    return benchmark.benchmark_scatter(local, graph_data.edge_rank_placement, graph_data.edge_dest_rank, graph_data.edge_indices,
+                                       graph_data.num_local_vertices, num_iters=num_iters, cache=cache)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--message_size", type=int, default=128)

@@ -23,6 +23,21 @@ def loss_fn(pred, target, ranks_per_sample, world):
     return torch.nn.functional.mse_loss(pred.float(), target.float()) * (ranks_per_sample / world)
 
 
+def compute_loss(ground_truth, prediction, comm):
+    """The reference's signature (``train_graphcast.py:29-34``): mean squared error per sample, summed over the batch, scaled by
+    ``ranks_per_sample / world_size`` so that a sum over all ranks averages over the samples in flight.  Accepts ``[N, C]`` (one
+    sample) or ``[B, N, C]``."""
+    d = (ground_truth.float() - prediction.float()).pow(2)
+    d = d.unsqueeze(0) if d.dim() == 2 else d
+    per_sample = d.mean(dim=(1, 2)).sum()
+    rps = getattr(comm, "_ranks_per_sample", None)
+    if rps is None:
+        eng = getattr(comm, "engine", None)
+        rps = getattr(eng, "ranks_per_graph", comm.get_world_size())
+    world = comm.get_global_world_size() if hasattr(comm, "get_global_world_size") else comm.get_world_size()
+    return per_sample * rps / world
+
+
 def main(batch_size: int = 1, is_distributed: bool = False, test_run: bool = False, use_synthetic_data: bool = True,
          benchmark: bool = False, backend: str = "single", procs_per_graph: int = 2, iters: int = 10, mesh_level: int = 6,
          lat: int = 721, lon: int = 1440, hidden_dim: int = 128, save_dir: str = "", resume: str = "", placement: str = "bands",

@@ -11,6 +11,15 @@ from _common import cleanup, init_distributed  # noqa: E402
 from dgraph_b200.utils.cli import run_cli  # noqa: E402
 
 
+def _load_optional_file(file_path: str):
+    """``torch.load`` of a placement tensor if the file exists, else ``None`` (``main.py:24-27``)."""
+    import torch
+
+    if file_path and os.path.exists(file_path):
+        return torch.load(file_path, weights_only=False)
+    return None
+
+
 def main(comm_type: str = "nccl", dataset: str = "synthetic", num_papers: int = 2048, num_authors: int = 512,
          num_institutions: int = 16, optimized_graph_structure: bool = True, paper_rank_mapping_file: str = "",
          author_rank_mapping_file: str = "", institution_rank_mapping_file: str = "", data_dir: str = "data/MAG240M",
@@ -25,7 +34,10 @@ def main(comm_type: str = "nccl", dataset: str = "synthetic", num_papers: int = 
     if dataset == "synthetic":
         ds = SyntheticHeterogeneousDataset(rank, world, num_papers, num_authors, num_institutions, comm=comm)
     else:
-        ds = DGraph_MAG240M_Dataset(rank, world, data_dir=data_dir, comm=comm)
+        ds = DGraph_MAG240M_Dataset(rank, world, data_dir=data_dir, comm=comm,
+                                    paper_rank_mappings=_load_optional_file(paper_rank_mapping_file),
+                                    author_rank_mappings=_load_optional_file(author_rank_mapping_file),
+                                    institution_rank_mappings=_load_optional_file(institution_rank_mapping_file))
     trainer = Trainer(ds, comm, dev, ModelConfig(hidden_channels=hidden_channels), TrainingConfig(epochs=epochs),
                       fused=optimized_graph_structure).prepare_data()
     times = trainer.train()

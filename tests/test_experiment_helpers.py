@@ -1,0 +1,169 @@
+"""Helper functions that the reference's experiment modules define next to their entry points, under the same module paths and
+names here (``experiments/``): they are built on this package's vectorised / native code, so each is checked against a direct
+statement of what it computes."""
+import importlib.util
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from dgraph_b200.parallel.emulator import run_world
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXP = os.path.join(ROOT, "experiments")
+
+
+def _load(rel, extra_path=()):
+    path = os.path.join(EXP, rel)
+    added = [os.path.dirname(path), *extra_path]
+    for p in added:
+        sys.path.insert(0, p)
+    try:
+        spec = importlib.util.spec_from_file_location("_exp_" + rel.replace("/", "_").replace("-", "_")[:-3], path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        return mod
+    finally:
+        for p in added:
+            sys.path.remove(p)
+
+
+def test_nccl_benchmark_object_runs_the_legacy_api():
+    tn = _load("Benchmarks/TestNCCL.py")
+    gu = _load("Benchmarks/graph_utils.py")
+    W, F = 3, 4
+    gd = gu.get_nccl_gather_benchmark_data(F, W, "cpu")
+    sd = gu.get_nccl_scatter_benchmark_data(F, W, "cpu")
+
+    def job(comm):
+        b = tn.NCCLBenchmark(comm, W, comm.get_rank())
+        st = b.comm_stats_gather(gd.edge_rank_placement[0], gd.edge_src_rank[0])
+        tg = tn.run_gather_benchmark(b, 3, gd)
+        ts = tn.run_scatter_benchmark(b, 3, sd, cache=False)
+        return int(st["local_comm_rev"]), int(st["local_comm_send"]), tg.shape, ts.shape
+
+    for rev, send, sg, ss in run_world(W, job):
+        assert rev == W - 1 and send == W - 1  # all-pairs: one message from and to every other rank
+        assert sg == (3,) and ss == (3,)
+
+
+def test_graphcast_utils_and_preprocess_helpers():
+    ut = _load("GraphCast/data_utils/utils.py")
+    pp = _load("GraphCast/data_utils/preprocess.py")
+    gg = _load("GraphCast/data_utils/graphcast_graph.py")
+    assert ut.padded_size(10, 4) == 12 and ut.padded_size(12, 4) == 12
+    assert ut.pad_indices(torch.arange(5), 4).tolist() == [0, 1, 2, 3, 4, -1, -1, -1]
+    # node features: (cos lat, sin lon, cos lon) in radians; the reference's degree-valued variant on request
+    pos = torch.tensor([[1.0, 0.0, 0.0], [0.0, 1.0, 0.0], [0.0, 0.0, 1.0]])
+    nf = ut.generate_node_features(pos)
+    assert torch.allclose(nf, torch.tensor([[1.0, 0.0, 1.0], [1.0, 1.0, 0.0], [0.0, 0.0, 1.0]]), atol=1e-6)
+    nf_deg = ut.generate_node_features(pos, degrees_as_radians=True)
+    assert abs(float(nf_deg[1, 1]) - np.sin(90.0)) < 1e-5
+    # edge features: [dx, dy, dz, len] / max len, receiver rotated to (1, 0, 0)
+    ef = ut.generate_edge_features(pos[[1, 2]], pos[[0, 0]])
+    assert ef.shape == (2, 4) and torch.allclose(ef[:, 3], torch.ones(2), atol=1e-6)
+    assert torch.allclose(ef[:, :3].norm(dim=1), ef[:, 3], atol=1e-6)
+    n, e, s, d = ut.create_graph(torch.tensor([0, 1]), torch.tensor([1, 2]), pos)
+    assert s.tolist() == [0, 1, 1, 2] and d.tolist() == [1, 2, 0, 1] and e.shape == (4, 4) and n.shape == (3, 3)
+    gen = gg.DistributedGraphCastGraphGenerator((19, 36), mesh_level=2)
+    g = gen.global_graph()
+    lat = torch.linspace(90, -90, 19)
+    lon = torch.arange(36) * 10.0
+    ll = torch.stack(torch.meshgrid(lat, lon, indexing="ij"), -1).reshape(-1, 2)
+    f, sm, dg = ut.create_mesh2grid_graph(ll, g.mesh_xyz, np.asarray(gen_faces(gen)))
+    assert sm.numel() == 3 * ll.shape[0] and torch.equal(dg, torch.arange(ll.shape[0]).repeat_interleave(3))
+    assert torch.equal(torch.stack([sm, dg], 1), g.mesh2grid_edges) and torch.allclose(f, g.mesh2grid_edge_features, atol=1e-6)
+    topo = gg.GraphCastTopology.from_generator(gen, 0, 2)
+    assert topo.mesh_rank_placement.numel() == g.num_mesh and topo.grid_rank_placement.numel() == g.num_grid
+    assert topo.ranks_per_graph == 2 and torch.equal(topo.grid2mesh_graph_dst_indices, g.grid2mesh_edges[:, 1])
+    pytest.importorskip("networkx")
+    G = pp.graphcast_graph_to_nxgraph((None, None, g.mesh_edges[:, 0], g.mesh_edges[:, 1]))
+    pl = pp.partition_graph(G, 2)
+    assert pl.shape == (g.num_mesh,) and abs(int((pl == 0).sum()) - g.num_mesh // 2) <= 0.05 * g.num_mesh
+    assert (pp.partition_graph(G, 1) == 0).all()
+    with pytest.raises(ValueError):
+        pp.partition_graph(G, 0)
+
+
+def gen_faces(gen):
+    from dgraph_b200.data.graphcast_graph import multimesh
+
+    return multimesh(gen.mesh_level, gen.multi)[1]
+
+
+def test_lsc_dataset_helpers():
+    sys.path.insert(0, os.path.join(EXP, "OGB-LSC"))
+    try:
+        from lsc_datasets import MAG240M_dataset as m, distributed_graph_dataset as d, synthetic_dataset as s
+    finally:
+        sys.path.remove(os.path.join(EXP, "OGB-LSC"))
+    assert d.get_vertex_offsets(10, 4).tolist() == [0, 3, 6, 9, 10]
+    owner, mine = d.get_rank_mappings(10, 4, 3)
+    assert owner.tolist() == [0, 0, 0, 1, 1, 1, 2, 2, 2, 3] and mine == 1
+    ei = torch.tensor([[0, 9], [4, 2]])
+    a, b = d.edge_mapping_from_vertex_mapping(ei, owner, owner)
+    assert a.tolist() == [0, 3] and b.tolist() == [1, 0]
+    assert m.get_edge_mappings(ei[0], ei[1], owner).tolist() == [1, 0]
+    mask, k = m.load_or_generate_vertex_rank_mask(None, 10, 4, 1)
+    assert mask.tolist() == (owner == 1).tolist() and k == 3
+    assert s.generate_config_hash([1, 2, 3]) == s.generate_config_hash((1, 2, 3)) != s.generate_config_hash([1, 2, 4])
+    e = s._generate_author_2_paper_edges(50, 100)
+    assert e.shape[0] == 2 and int(e[0].max()) < 50 and int(e[1].max()) < 100 and torch.unique(e, dim=1).shape == e.shape
+    rng = np.random.default_rng(0)
+    pf = rng.standard_normal((20, 70)).astype(np.float32)
+    idx = np.stack([rng.integers(0, 8, 50), rng.integers(0, 20, 50)])
+    out = np.zeros((8, 70), dtype=np.float32)
+    m._generate_features_from_paper_features(out, 8, 20, pf, idx, 70, dim_chunk_size=32)
+    ref, cnt = np.zeros((8, 70)), np.zeros(8)
+    for r, c in idx.T:
+        ref[r] += pf[c]
+        cnt[r] += 1
+    assert np.allclose(out, ref / np.maximum(cnt, 1)[:, None], atol=1e-5)
+    blk = m.get_col_slice(pf, 2, 9, 3, 11, chunk=3)
+    assert np.array_equal(blk, pf[2:9, 3:11])
+    dst = np.zeros_like(pf)
+    m.save_col_slice(blk, dst, 2, 9, 3, 11, chunk=4)
+    assert np.array_equal(dst[2:9, 3:11], blk) and np.count_nonzero(dst) == np.count_nonzero(blk)
+
+
+def test_rank_mapping_files_become_contiguous_offsets():
+    from dgraph_b200.data.hetero import node_offsets, offsets_from_rank_mapping
+
+    assert torch.equal(offsets_from_rank_mapping(None, 10, 4), node_offsets(10, 4))
+    assert offsets_from_rank_mapping(torch.tensor([0, 0, 0, 0, 1, 2, 2]), 7, 4).tolist() == [0, 4, 5, 7, 7]
+    with pytest.raises(ValueError):
+        offsets_from_rank_mapping(torch.tensor([0, 1, 0]), 3, 2)
+    with pytest.raises(ValueError):
+        offsets_from_rank_mapping(torch.tensor([0, 1]), 3, 2)
+
+
+def test_distributed_bn_functional_forms_and_misc():
+    dl = _load("OGB-LSC/distributed_layers.py", extra_path=(EXP,))
+    x = torch.randn(40, 5, dtype=torch.float64, requires_grad=True)
+    gam = torch.randn(1, 5, dtype=torch.float64, requires_grad=True)
+    bet = torch.randn(1, 5, dtype=torch.float64, requires_grad=True)
+    out, xh, mean, var, n = dl._compute_bn_forward(x.detach(), gam.detach(), bet.detach())
+    ref = torch.nn.functional.batch_norm(x, None, None, gam.view(-1), bet.view(-1), training=True, eps=1e-5)
+    assert torch.allclose(out, ref, atol=1e-12) and float(n) == 40
+    go = torch.randn_like(ref)
+    ref.backward(go)
+    dx, dg, db = dl._compute_bn_backward(go, x.detach(), xh, mean, var, n, gam.detach(), bet.detach())
+    assert torch.allclose(dx, x.grad, atol=1e-12) and torch.allclose(dg, gam.grad, atol=1e-12) and torch.allclose(db, bet.grad, atol=1e-12)
+    oc = _load("OGB/ogb_comm_dataset.py", extra_path=(EXP,))
+    pl = torch.tensor([0, 1, 0, 1, 1])
+    masks = oc._build_local_split_masks(pl, {"train": torch.tensor([0, 3]), "valid": torch.tensor([4])}, 1)
+    assert masks["train"].tolist() == [False, True, False] and masks["valid"].tolist() == [False, False, True]
+    pat = oc.generate_communication_pattern(torch.tensor([[0, 1], [1, 0], [2, 3], [3, 2]]), pl, 0, 2)
+    assert pat.num_local_vertices == 2 and pat.num_halo_vertices == 2
+    tg = _load("GraphCast/train_graphcast.py", extra_path=(EXP,))
+
+    class _C:
+        _ranks_per_sample = 2
+
+        def get_world_size(self):
+            return 4
+
+    a, b = torch.zeros(6, 3), torch.ones(6, 3)
+    assert abs(float(tg.compute_loss(a, b, _C())) - 0.5) < 1e-7

@@ -48,6 +48,19 @@ def test_nccl_benchmark_object_runs_the_legacy_api():
         assert rev == W - 1 and send == W - 1  # all-pairs: one message from and to every other rank
         assert sg == (3,) and ss == (3,)
 
+    # one-sided calling convention (TestNVSHMEM.py): the gathered rows are the other ranks' vertices
+    nv = _load("Benchmarks/TestNVSHMEM.py")
+
+    def job2(comm):
+        b = nv.NVSHMEMBenchmark(comm)
+        r = comm.get_rank()
+        pl = gd.edge_rank_placement
+        got = comm.gather(gd.vertex_data[r:r + 1].unsqueeze(0), nv._mine(gd.edge_indices, pl, r), nv._mine(gd.edge_src_rank, pl, r))
+        return got[0], nv.run_gather_benchmark(b, 2, gd).shape, nv.run_scatter_benchmark(b, 2, sd).shape
+
+    for r, (got, sg, ss) in enumerate(run_world(W, job2)):
+        assert torch.allclose(got, gd.vertex_data[[j for j in range(W) if j != r]]) and sg == (2,) and ss == (2,)
+
 
 def test_graphcast_utils_and_preprocess_helpers():
     ut = _load("GraphCast/data_utils/utils.py")

@@ -311,6 +311,92 @@ class DistributedGraphCastGraphGenerator:
             grid_rows_global=grid_rows, mesh_rows_global=mesh_rows)
 
 
+# ---- dictionary-style stages of the reference's generator (``data_utils/graphcast_graph.py:198-437``) ------------------------------
+# Same method names and dictionary keys; the values are the consistent versions of what the (work-in-progress) reference code
+# computes: vertices renumbered so that every rank owns one contiguous range, edges ordered by the rank that holds them.
+def _rank_sort(placement: torch.Tensor):
+    """``(sorted placement, new -> old permutation, old -> new map)`` of a stable sort by rank."""
+    sorted_pl, new_to_old = torch.sort(placement.reshape(-1).long(), stable=True)
+    old_to_new = torch.empty_like(new_to_old)
+    old_to_new[new_to_old] = torch.arange(new_to_old.numel())
+    return sorted_pl, new_to_old, old_to_new
+
+
+def _get_mesh_graph_partition(mesh_level: int, world_size: int) -> torch.Tensor:
+    """Placement of the multimesh vertices on ``world_size`` ranks by the native multilevel partitioner (METIS upstream)."""
+    from dgraph_b200.data.partition import multilevel
+
+    v, _, edges, _ = multimesh(mesh_level, True)
+    return multilevel(torch.from_numpy(np.ascontiguousarray(edges)).long(), v.shape[0], world_size)
+
+
+def _get_mesh_graph(self, mesh_vertex_rank_placement: torch.Tensor) -> dict:
+    g = self.global_graph()
+    assert mesh_vertex_rank_placement.numel() == g.num_mesh
+    node_pl, new_to_old, old_to_new = _rank_sort(mesh_vertex_rank_placement)
+    src, dst = old_to_new[g.mesh_edges[:, 0]], old_to_new[g.mesh_edges[:, 1]]
+    edge_pl, order = torch.sort(node_pl[src], stable=True)  # an edge lives with its source vertex
+    src, dst = src[order], dst[order]
+    return {"node_features": g.mesh_node_features[new_to_old], "edge_features": g.mesh_edge_features[order],
+            "src_indices": src, "dst_indices": dst, "node_rank_placement": node_pl, "edge_rank_placement": edge_pl,
+            "src_rank_placement": edge_pl, "dst_rank_placement": node_pl[dst], "mesh_vertex_renumbering": new_to_old,
+            "renumbered_vertices": old_to_new}
+
+
+def _get_grid_placement(self, mesh_vertex_rank_placement: torch.Tensor, grid2mesh_mesh_dst_indices: torch.Tensor) -> torch.Tensor:
+    """Rank of every grid-to-mesh edge: the rank of the mesh vertex it ends at."""
+    return mesh_vertex_rank_placement.reshape(-1)[grid2mesh_mesh_dst_indices.long()]
+
+
+def _get_grid2mesh_graph(self, mesh_graph_dict: dict) -> dict:
+    g = self.global_graph()
+    node_pl, old_to_new = mesh_graph_dict["node_rank_placement"], mesh_graph_dict["renumbered_vertices"]
+    world = int(node_pl.max()) + 1 if node_pl.numel() else 1
+    src_grid, dst_mesh = g.grid2mesh_edges[:, 0], old_to_new[g.grid2mesh_edges[:, 1]]
+    edge_rank = node_pl[dst_mesh]
+    # a grid vertex goes where most of its mesh neighbours live (grid vertices without an edge: rank 0)
+    votes = torch.zeros(g.num_grid, world, dtype=torch.long)
+    votes.index_put_((src_grid, edge_rank), torch.ones_like(src_grid), accumulate=True)
+    grid_pl_sorted, grid_new_to_old, grid_old_to_new = _rank_sort(votes.argmax(1))
+    edge_pl, order = torch.sort(edge_rank, stable=True)
+    return {"node_features": torch.tensor([]), "edge_features": g.grid2mesh_edge_features[order],
+            "src_indices": grid_old_to_new[src_grid][order], "dst_indices": dst_mesh[order],
+            "grid2mesh_edge_rank_placement": edge_pl, "grid_vertex_rank_placement": grid_pl_sorted,
+            "renumbered_grid": grid_old_to_new, "grid_vertex_renumbering": grid_new_to_old}
+
+
+def _get_mesh2grid_graph(self, grid_vertex_rank_placement: torch.Tensor, renumbered_vertices: torch.Tensor,
+                         renumbered_grid: torch.Tensor) -> dict:
+    g = self.global_graph()
+    src = renumbered_vertices[g.mesh2grid_edges[:, 0]]
+    dst = renumbered_grid[g.mesh2grid_edges[:, 1]]
+    edge_pl, order = torch.sort(grid_vertex_rank_placement[dst], stable=True)  # an edge lives with the grid vertex it ends at
+    return {"node_features": torch.tensor([]), "edge_features": g.mesh2grid_edge_features[order], "src_indices": src[order],
+            "dst_indices": dst[order], "mesh2grid_edge_rank_placement": edge_pl}
+
+
+def _get_graphcast_graph(self, mesh_vertex_rank_placement: torch.Tensor, rank: int = 0, world_size: Optional[int] = None):
+    """This rank's shard (features, local edge lists, the three halo plans) for a given mesh placement; the grid follows its
+    mesh neighbours.  (Upstream returns one record of global tensors here and builds the plans in a second step.)"""
+    pl = mesh_vertex_rank_placement.reshape(-1).long()
+    world = int(pl.max()) + 1 if world_size is None else int(world_size)
+    assert 0 <= rank < world and int(pl.max()) < world, "mesh vertex placement does not match rank / world size"
+    m = self.get_mesh_graph(pl)
+    g2m = self.get_grid2mesh_graph(m)
+    grid_pl = torch.empty(self.global_graph().num_grid, dtype=torch.long)
+    grid_pl[g2m["grid_vertex_renumbering"]] = g2m["grid_vertex_rank_placement"]
+    self._placements[world] = (grid_pl, pl)
+    return self.shard(rank, world)
+
+
+DistributedGraphCastGraphGenerator.get_mesh_graph_partition = staticmethod(_get_mesh_graph_partition)
+DistributedGraphCastGraphGenerator.get_mesh_graph = _get_mesh_graph
+DistributedGraphCastGraphGenerator.get_grid_placement = _get_grid_placement
+DistributedGraphCastGraphGenerator.get_grid2mesh_graph = _get_grid2mesh_graph
+DistributedGraphCastGraphGenerator.get_mesh2grid_graph = _get_mesh2grid_graph
+DistributedGraphCastGraphGenerator.get_graphcast_graph = _get_graphcast_graph
+
+
 def build_graphcast_comm_patterns(generator: DistributedGraphCastGraphGenerator, rank: int, world_size: int):
     """Reference name (``graphcast_graph.py:85-159``): the three plans of one rank."""
     return generator.shard(rank, world_size).patterns
@@ -342,3 +428,19 @@ class SyntheticWeatherDataset(torch.utils.data.Dataset):
 
     def __getitem__(self, i):
         return {"invar": self._field(i), "outvar": self._field(i + 1)}
+
+    @staticmethod
+    def generate_data(num_days: int, num_channels: int, grid_size: Tuple[int, int], base_temp: float = 15.0,
+                      amplitude: float = 10.0, noise_level: float = 2.0, seed: Optional[int] = None) -> np.ndarray:
+        """Dense ``[num_days, num_channels, n_lat, n_lon]`` temperature-like field of the reference's generator
+        (``dataset.py:100-171``): base + 0.5 colder per channel ("altitude") + a linear south-north ramp of ``+-amplitude`` +
+        an annual sine + Gaussian noise.  Written with broadcasting, so only the result is materialised.  The streaming
+        ``__getitem__`` above never builds this array (it is 4 x 73 x 721 x 1440 x 8 bytes = 2.4 GB at the default size)."""
+        n_lat, n_lon = grid_size
+        rng = np.random.default_rng(seed)
+        altitude = (-0.5 * np.arange(num_channels))[None, :, None, None]
+        ramp = np.linspace(-amplitude, amplitude, n_lat)[None, None, :, None]
+        season = np.sin(2 * np.pi * np.arange(num_days) / 365.0)[:, None, None, None]
+        out = rng.normal(scale=noise_level, size=(num_days, num_channels, n_lat, n_lon))
+        out += base_temp + altitude + ramp + season
+        return out

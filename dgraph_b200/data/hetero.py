@@ -92,6 +92,38 @@ class DistributedHeteroGraphDataset:
     def get_target(self, name: str) -> torch.Tensor:
         return self.labels[self.get_mask(name).to(self.labels.device)]
 
+    def __len__(self) -> int:
+        return 1  # one full graph
+
+    def __getitem__(self, idx):
+        """``(features, edge_index, edge_type, rank_mappings)`` as in the reference (``distributed_graph_dataset.py:240-282``):
+        per node type this rank's features; per relation the ``[2, E_k]`` (source, destination) edges this rank holds, the
+        ``(source type, destination type)`` pair, and the owner ranks ``[source owners, destination owners]`` of the endpoints."""
+        edge_index = [e.t().contiguous() for e in self.edges]
+        rank_mappings = []
+        for (st, dt), e in zip(RELATIONS, self.edges):
+            rank_mappings.append([torch.bucketize(e[:, 0].contiguous(), self.offsets[st], right=True) - 1,
+                                  torch.bucketize(e[:, 1].contiguous(), self.offsets[dt], right=True) - 1])
+        return self.features, edge_index, list(RELATIONS), rank_mappings
+
+    def _get_vertex_rank_mask(self, mask_type: str) -> Tuple[torch.Tensor, torch.Tensor]:
+        """``(global paper ids of the split, positions inside that list of the papers this rank owns)``
+        (``distributed_graph_dataset.py:332-355``); ``"val"`` and ``"valid"`` name the same split."""
+        name = {"val": "valid"}.get(mask_type, mask_type)
+        if name not in self.split and mask_type in self.split:
+            name = mask_type
+        if name not in self.split:
+            raise ValueError(f"Invalid mask type: {mask_type}")
+        ids = self.split[name].reshape(-1)
+        lo, hi = self.local_range(0)
+        return ids, torch.nonzero((ids >= lo) & (ids < hi), as_tuple=True)[0]
+
+    def get_NCCL_comm_plans(self) -> List[NCCLEdgeConditionedGraphCommPlan]:
+        """The five edge-conditioned plans in the order of ``RELATIONS`` (built on first use)."""
+        if self.comm_plans is None:
+            self.prepare_plans(fused=False, reference_layout=True)
+        return self.comm_plans
+
     def add_batch_dimension(self):
         """``[N, F] -> [1, N, F]`` (the layout the reference's gather/scatter API expects)."""
         if not self.batched:
@@ -279,3 +311,17 @@ class DGraph_MAG240M_Dataset(DistributedHeteroGraphDataset):
         split = {"train": sp["train"], "valid": sp.get("valid", sp.get("val")), "test": sp.get("test-dev", sp.get("test"))}
         super().__init__(rank, world_size, n, feats, edges, labels, f.num_classes, comm=comm, split=split, cache_dir=cache_dir,
                          offsets=offs)
+        self.files = f
+
+    def generate_feature_data(self):
+        """Rank 0 writes the author / institution feature files (means of neighbouring papers' / authors' features) next to the
+        processed dataset unless they exist, everybody waits (``MAG240M_dataset.py:262-320``).  Returns their paths."""
+        from dgraph_b200.data.ogb_raw import generate_mag240m_feature_files
+
+        paths = None
+        if self.rank == 0:
+            paths = generate_mag240m_feature_files(self.files)
+        if self.comm is not None:
+            self.comm.barrier()
+        return paths or {"author": os.path.join(self.files.dir, "author_feat.npy"),
+                         "institution": os.path.join(self.files.dir, "institution_feat.npy")}

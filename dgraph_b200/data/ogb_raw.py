@@ -126,3 +126,50 @@ class MAG240MFiles:
 
     def labels(self) -> torch.Tensor:
         return torch.from_numpy(np.nan_to_num(np.asarray(self.paper_label), nan=-1.0).astype(np.int64))
+
+
+def mean_neighbor_features(out, num_nodes: int, num_src: int, src_feat, edge_index, num_features: int, dim_chunk_size: int = 64,
+                           row_chunk: int = 100_000) -> None:
+    """``out[v] = mean over edges (v, p) of src_feat[p]`` written into ``out`` (a ``np.memmap`` or array ``[num_nodes, F]``), 64
+    columns at a time: the author / institution feature generation of MAG240M (the reference does it with a ``torch_sparse``
+    SpMM, ``MAG240M_dataset.py:65-102``).  A CSR segment mean over the rows sorted by ``v``; only one column block of the source
+    features is resident at a time."""
+    row = torch.as_tensor(np.asarray(edge_index[0]), dtype=torch.long)
+    col = torch.as_tensor(np.asarray(edge_index[1]), dtype=torch.long)
+    order = torch.argsort(row, stable=True)
+    col = col[order]
+    lengths = torch.bincount(row, minlength=num_nodes)
+    for i in range(0, num_features, dim_chunk_size):
+        j = min(i + dim_chunk_size, num_features)
+        block = np.empty((num_src, j - i), dtype=np.float32)
+        for r0 in range(0, num_src, row_chunk):
+            r1 = min(r0 + row_chunk, num_src)
+            block[r0:r1] = src_feat[r0:r1, i:j]
+        red = torch.segment_reduce(torch.from_numpy(block)[col], "mean", lengths=lengths, unsafe=True)
+        red = torch.nan_to_num(red, nan=0.0).numpy()  # vertices without neighbours
+        for r0 in range(0, num_nodes, row_chunk):
+            r1 = min(r0 + row_chunk, num_nodes)
+            out[r0:r1, i:j] = red[r0:r1]
+    if hasattr(out, "flush"):
+        out.flush()
+
+
+def generate_mag240m_feature_files(files: "MAG240MFiles", num_features: int = 0) -> Dict[str, str]:
+    """Writes ``author_feat.npy`` (mean of the written papers' features) and ``institution_feat.npy`` (mean of the affiliated
+    authors' features) next to the processed files, fp16 ``np.memmap``s as in the OGB example the reference follows
+    (``MAG240M_dataset.py:262-320``).  Existing files are kept.  Returns the two paths."""
+    if files.paper_feat is None:
+        raise FileNotFoundError("paper/node_feat.npy is missing")
+    F = int(num_features) or int(files.paper_feat.shape[1])
+    a_path, i_path = os.path.join(files.dir, "author_feat.npy"), os.path.join(files.dir, "institution_feat.npy")
+    if not os.path.exists(a_path):
+        out = np.memmap(a_path, mode="w+", dtype=np.float16, shape=(files.num_authors, F))
+        mean_neighbor_features(out, files.num_authors, files.num_papers, files.paper_feat, files.edge_index("writes"), F)
+        del out
+    if not os.path.exists(i_path):
+        authors = np.memmap(a_path, mode="r", dtype=np.float16, shape=(files.num_authors, F))
+        aff = np.asarray(files.edge_index("affiliated_with"))
+        out = np.memmap(i_path, mode="w+", dtype=np.float16, shape=(files.num_institutions, F))
+        mean_neighbor_features(out, files.num_institutions, files.num_authors, authors, aff[::-1], F)  # (institution, author)
+        del out
+    return {"author": a_path, "institution": i_path}

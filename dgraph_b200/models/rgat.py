@@ -102,6 +102,11 @@ class CommAwareGAT(nn.Module):
         self.comm.all_reduce(mx, op="max")  # one constant for all segments: softmax-invariant, overflow-safe
         return torch.exp(sc - mx.to(sc.dtype))
 
+    @staticmethod
+    def _calc_attention_messages(neighbor_features, numerator, denominator):
+        """``h_j * alpha_ij`` with ``alpha_ij = numerator / (denominator + 1e-16)`` (``RGAT.py:157-165``)."""
+        return neighbor_features * (numerator / (denominator + 1e-16))
+
     def _forward_comm_plan(self, x, comm_plan, x_j=None):
         h = F.linear(x, self.conv1.weight.to(x.dtype))
         source_plan = comm_plan.source_graph_plan
@@ -115,7 +120,7 @@ class CommAwareGAT(nn.Module):
         h_j = self.comm.gather(h_j, comm_plan=source_plan)
         num = self._process_messages(h_i, h_j)
         den = self.comm.gather(self.comm.scatter(num, comm_plan=dest_plan), comm_plan=dest_plan)
-        out = self.comm.scatter(h_j * (num / (den + 1e-16)), comm_plan=dest_plan)
+        out = self.comm.scatter(self._calc_attention_messages(h_j, num, den), comm_plan=dest_plan)
         return self._apply_res_and_bias(out, x)
 
     def _forward_coo(self, x, edge_index, rank_mapping, x_j=None):

@@ -14,11 +14,27 @@ import torch
 from torch.utils.data import Sampler
 
 
-def SingleProcessDummyCommunicator():
+def _communicator_class():
     from dgraph_b200.communicator import Communicator
-    from dgraph_b200.parallel.local_engine import LocalEngine
 
-    return Communicator._from_engine(LocalEngine(), backend="single")
+    return Communicator
+
+
+class SingleProcessDummyCommunicator(_communicator_class()):
+    """World-size-1 communicator for debugging and single-GPU runs: a full :class:`Communicator` on the local engine (every
+    gather / scatter / halo call works and costs no communication) that does not claim the process-wide singleton."""
+
+    def __init__(self):
+        from dgraph_b200.parallel.local_engine import LocalEngine
+
+        super().__init__("single", _engine=LocalEngine())
+        self._ranks_per_sample = 1
+
+    def __str__(self) -> str:
+        return self.backend
+
+    def rank_cuda_device(self):
+        return torch.cuda.current_device()
 
 
 class CommAwareDistributedSampler(Sampler):

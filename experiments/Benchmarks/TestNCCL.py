@@ -116,6 +116,14 @@ class NCCLBenchmark:
     def _device(self, t):
         return t.device
 
+    def print(self, message):
+        if self.rank == 0:
+            print(message, flush=True)
+
+    def save_np(self, np_array, filename, rank_to_save: int = 0):
+        if self.rank == rank_to_save:
+            np.save(filename, np_array)
+
     def _drop_cache(self, cache):
         if cache is False and hasattr(self.comm.engine, "_legacy_plans"):
             self.comm.engine._legacy_plans.clear()

@@ -21,6 +21,9 @@ class NVSHMEMBenchmark:
         self.comm_object = comm_object
         self.rank, self.world_size = comm_object.get_rank(), comm_object.get_world_size()
 
+    print = _nccl.NCCLBenchmark.print
+    save_np = _nccl.NCCLBenchmark.save_np
+
     def benchmark_gather(self, data, edge_src_rank, edge_indices, num_iters: int = 1000):
         self.comm_object.barrier()
         return _time(lambda: self.comm_object.gather(data, edge_indices, edge_src_rank), num_iters, data.device)

@@ -35,21 +35,11 @@ def get_edge_mappings(src_indices: torch.Tensor, dst_indices: torch.Tensor, rank
 def _generate_features_from_paper_features(out, num_nodes: int, num_papers: int, paper_feat, edge_index, num_features: int,
                                            dim_chunk_size: int = 64) -> None:
     """Features of authors / institutions as the mean of their neighbours' features (``MAG240M_dataset.py:65-102``, there a
-    ``torch_sparse`` SpMM): ``out[v] = mean_{(v, p) in edge_index} paper_feat[p]``, computed 64 columns at a time with a CSR
-    segment mean (``torch.segment_reduce``), so neither ``torch_sparse`` nor the full-width matrix in memory is needed."""
-    row = torch.as_tensor(np.asarray(edge_index[0]), dtype=torch.long)
-    col = torch.as_tensor(np.asarray(edge_index[1]), dtype=torch.long)
-    order = torch.argsort(row, stable=True)
-    col = col[order]
-    lengths = torch.bincount(row, minlength=num_nodes)
-    for i in range(0, num_features, dim_chunk_size):
-        j = min(i + dim_chunk_size, num_features)
-        inputs = torch.from_numpy(np.ascontiguousarray(get_col_slice(paper_feat, 0, num_papers, i, j))).float()
-        red = torch.segment_reduce(inputs[col], "mean", lengths=lengths, unsafe=True)
-        red = torch.nan_to_num(red, nan=0.0)  # vertices without neighbours
-        save_col_slice(red.numpy().astype(out.dtype, copy=False), out, 0, num_nodes, i, j)
-    if hasattr(out, "flush"):
-        out.flush()
+    ``torch_sparse`` SpMM): ``out[v] = mean_{(v, p) in edge_index} paper_feat[p]``, 64 columns at a time
+    (``dgraph_b200.data.ogb_raw.mean_neighbor_features``: a CSR segment mean, no ``torch_sparse``)."""
+    from dgraph_b200.data.ogb_raw import mean_neighbor_features
+
+    mean_neighbor_features(out, num_nodes, num_papers, paper_feat, edge_index, num_features, dim_chunk_size)
 
 
 def load_or_generate_vertex_rank_mask(rank_mapping: Optional[torch.Tensor], num_vertices: int, world_size: int, rank: int):

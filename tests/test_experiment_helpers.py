@@ -180,3 +180,31 @@ def test_distributed_bn_functional_forms_and_misc():
 
     a, b = torch.zeros(6, 3), torch.ones(6, 3)
     assert abs(float(tg.compute_loss(a, b, _C())) - 0.5) < 1e-7
+
+
+def test_graphcast_generator_dictionary_stages_are_consistent():
+    """``get_mesh_graph`` / ``get_grid2mesh_graph`` / ``get_mesh2grid_graph`` / ``get_graphcast_graph`` (the reference generator's
+    stage names): renumbering keeps the edge sets, every rank owns one contiguous range, edges are ordered by holder rank."""
+    from dgraph_b200.data.graphcast_graph import DistributedGraphCastGraphGenerator as G, SyntheticWeatherDataset
+
+    gen = G((19, 36), mesh_level=2)
+    g = gen.global_graph()
+    pl = G.get_mesh_graph_partition(2, 2)
+    assert pl.numel() == g.num_mesh and abs(int((pl == 0).sum()) - g.num_mesh // 2) <= 0.05 * g.num_mesh
+    m = gen.get_mesh_graph(pl)
+    nondecreasing = lambda t: bool((t[1:] >= t[:-1]).all())  # noqa: E731
+    assert nondecreasing(m["node_rank_placement"]) and nondecreasing(m["edge_rank_placement"])
+    old = torch.stack([m["mesh_vertex_renumbering"][m["src_indices"]], m["mesh_vertex_renumbering"][m["dst_indices"]]], 1)
+    assert set(map(tuple, old.tolist())) == set(map(tuple, g.mesh_edges.tolist()))
+    assert torch.equal(m["renumbered_vertices"][m["mesh_vertex_renumbering"]], torch.arange(g.num_mesh))
+    assert torch.equal(m["src_rank_placement"], m["node_rank_placement"][m["src_indices"]])
+    assert torch.equal(gen.get_grid_placement(pl, g.grid2mesh_edges[:, 1]), pl[g.grid2mesh_edges[:, 1]])
+    g2m = gen.get_grid2mesh_graph(m)
+    assert nondecreasing(g2m["grid2mesh_edge_rank_placement"]) and nondecreasing(g2m["grid_vertex_rank_placement"])
+    assert g2m["src_indices"].numel() == g.grid2mesh_edges.shape[0]
+    m2g = gen.get_mesh2grid_graph(g2m["grid_vertex_rank_placement"], m["renumbered_vertices"], g2m["renumbered_grid"])
+    assert nondecreasing(m2g["mesh2grid_edge_rank_placement"]) and m2g["dst_indices"].numel() == 3 * g.num_grid
+    shards = [gen.get_graphcast_graph(pl, rank=r) for r in range(2)]
+    assert sum(s.num_local_mesh for s in shards) == g.num_mesh and sum(s.num_local_grid for s in shards) == g.num_grid
+    d = SyntheticWeatherDataset.generate_data(3, 4, (5, 6), base_temp=15.0, amplitude=10.0, noise_level=0.0)
+    assert d.shape == (3, 4, 5, 6) and np.allclose(d[0, 0, :, 0], [5, 10, 15, 20, 25]) and np.allclose(d[0, 2] - d[0, 0], -1.0)

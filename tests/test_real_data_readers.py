@@ -125,3 +125,44 @@ def test_mag240m_files_give_the_same_plans_as_the_full_edge_lists(tmp_path):
             assert torch.equal(p.halo_vertices_global, q.halo_vertices_global)
             assert torch.equal(torch.unique(p.local_edge_list, dim=0), torch.unique(q.local_edge_list, dim=0))
         assert ds.get_mask("train").numel() + ds.get_mask("valid").numel() + ds.get_mask("test").numel() == hi - lo
+
+
+def test_mag240m_feature_files_and_reference_accessors(tmp_path):
+    """``generate_feature_data`` writes the author / institution feature files (means over neighbours) once; the dataset's
+    reference-style accessors (``ds[0]``, ``_get_vertex_rank_mask``, ``get_NCCL_comm_plans``) describe the same graph."""
+    from dgraph_b200.data.hetero import RELATIONS, DGraph_MAG240M_Dataset
+
+    edges, feat, _ = _fake_mag(str(tmp_path), P=40, A=20, I=5, F=8)
+    ds = DGraph_MAG240M_Dataset(0, 1, data_dir=str(tmp_path))
+    paths = ds.generate_feature_data()
+    A, I, F = 20, 5, 8
+    af = np.memmap(paths["author"], mode="r", dtype=np.float16, shape=(A, F))
+    w = edges["author___writes___paper"]
+    ref = np.zeros((A, F))
+    cnt = np.zeros(A)
+    for a, p in w.T:
+        ref[a] += feat[p].astype(np.float64)
+        cnt[a] += 1
+    ref /= np.maximum(cnt, 1)[:, None]
+    assert np.allclose(np.asarray(af, dtype=np.float64), ref, atol=2e-2)
+    inf = np.memmap(paths["institution"], mode="r", dtype=np.float16, shape=(I, F))
+    aff = edges["author___affiliated_with___institution"]
+    ref_i = np.zeros((I, F))
+    cnt_i = np.zeros(I)
+    for a, i in aff.T:
+        ref_i[i] += np.asarray(af[a], dtype=np.float64)
+        cnt_i[i] += 1
+    ref_i /= np.maximum(cnt_i, 1)[:, None]
+    assert np.allclose(np.asarray(inf, dtype=np.float64), ref_i, atol=2e-2)
+    mtime = os.path.getmtime(paths["author"])
+    assert ds.generate_feature_data() == paths and os.path.getmtime(paths["author"]) == mtime  # kept, not rewritten
+    feats, edge_index, edge_type, rank_mappings = ds[0]
+    assert len(ds) == 1 and edge_type == list(RELATIONS) and len(feats) == 3 and len(edge_index) == 5
+    assert edge_index[0].shape[0] == 2 and all((rm[0] == 0).all() and (rm[1] == 0).all() for rm in rank_mappings)
+    ids, pos = ds._get_vertex_rank_mask("val")
+    assert torch.equal(ids[pos], ids) and ids.numel() == 10
+    import pytest
+
+    with pytest.raises(ValueError):
+        ds._get_vertex_rank_mask("nope")
+    assert len(ds.get_NCCL_comm_plans()) == 5

@@ -29,14 +29,24 @@ class SyntheticWeatherDataset(torch.utils.data.Dataset):
         self.grid_size, self.mesh_level = tuple(grid_size), mesh_level
         self.rank, self.world_size, self.ranks_per_graph = rank, world_size, max(int(ranks_per_graph), 1)
         self.extra_args = kwargs
-        # ranks of one replica share a graph; `mesh_vertex_placement` (a METIS-style placement file in the reference) selects
-        # the partitioner-based placement, otherwise latitude bands are used
-        placement = "multilevel" if mesh_vertex_placement is not None else "bands"
-        self._gen = DistributedGraphCastGraphGenerator(self.grid_size, mesh_level, placement=placement)
+        self.base_temp, self.amplitude, self.noise_level = base_temp, amplitude, noise_level
+        # ranks of one replica share a graph.  `mesh_vertex_placement` (the per-vertex rank tensor of a partitioner run, a file in
+        # the reference) is used as given -- the grid follows its mesh neighbours; without it the graph is cut in latitude bands
+        self._gen = DistributedGraphCastGraphGenerator(self.grid_size, mesh_level)
         g_rank, g_world = rank % self.ranks_per_graph, self.ranks_per_graph if world_size > 1 else 1
-        self._graph = self._gen.shard(g_rank, g_world).to(self.device, torch.float32)
+        if mesh_vertex_placement is not None and g_world > 1:
+            graph = self._gen.get_graphcast_graph(torch.as_tensor(mesh_vertex_placement), rank=g_rank, world_size=g_world)
+        else:
+            graph = self._gen.shard(g_rank, g_world)
+        self._graph = graph.to(self.device, torch.float32)
         self._fields = _Fields(self.num_channels, self.grid_size, num_samples=self.num_days,
                                grid_rows=self._graph.grid_rows_global.cpu())
+
+    def generate_data(self, num_days: int, num_channels: int, grid_size: Tuple[int, int], base_temp: float, amplitude: float,
+                      noise_level: float):
+        """Dense ``[days, channels, lat, lon]`` field of the reference's generator (``dataset.py:100-171``).  ``__getitem__`` does
+        not go through it: samples are produced row by row for this rank's grid points only."""
+        return _Fields.generate_data(num_days, num_channels, grid_size, base_temp, amplitude, noise_level)
 
     def get_static_graph(self) -> DistributedGraphCastGraph:
         return self._graph

@@ -11,7 +11,11 @@ class _AnyCollectiveEngine(type(TorchDistEngine)):
 
 
 class NCCLBackendEngine(TorchDistEngine, metaclass=_AnyCollectiveEngine):
-    """Constructing it gives the ``torch.distributed`` engine (NCCL on GPUs, gloo on CPU)."""
+    """Constructing it gives the ``torch.distributed`` engine (NCCL on GPUs, gloo on CPU).  First positional argument:
+    ``ranks_per_graph``, as in the reference (``NCCLBackendEngine.py:43``)."""
+
+    def __init__(self, ranks_per_graph: int = -1, *args, **kwargs):
+        super().__init__(ranks_per_graph=ranks_per_graph, **kwargs)
 
 from dgraph_b200.parallel.comm_plan import (
     NCCLGraphCommPlan, NCCLEdgeConditionedGraphCommPlan, COO_to_NCCLCommPlan, COO_to_NCCLEdgeConditionedCommPlan,

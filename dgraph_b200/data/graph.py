@@ -86,6 +86,6 @@ class DistributedGraph:
         return self.edge_loc, self.edge_dest_rank_mapping
 
 
-def get_round_robin_node_rank_map(num_nodes: int, num_ranks: int) -> torch.Tensor:
-    """``node i -> rank i % num_ranks`` (``graph.py:270-288``, vectorised)."""
-    return torch.arange(num_nodes) % num_ranks
+def get_round_robin_node_rank_map(num_nodes: int, world_size: int) -> torch.Tensor:
+    """``node i -> rank i % world_size`` (``graph.py:270-288``, vectorised)."""
+    return torch.arange(num_nodes) % world_size

@@ -53,7 +53,7 @@ class DistributedOGBWrapper:
         cache = os.path.join(dir_name, f"{dname}_graph_data_{self._world}.pt")
         if self._rank == 0 and (force_reprocess or not os.path.exists(cache)):
             g, y, split, self.synthetic = _load_raw(dname, dir_name, scale)
-            graph = process_homogenous_data(g, y, self._world, split, node_rank_placement)
+            graph = process_homogenous_data(g, y, self._rank, self._world, split, node_rank_placement)
             torch.save(graph, cache)
         comm_object.barrier()
         self.graph_obj: DistributedGraph = torch.load(cache, weights_only=False)

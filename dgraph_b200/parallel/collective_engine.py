@@ -94,8 +94,9 @@ class CollectiveEngine(BackendEngine):
 
     # MPI window management of the reference's MPI engine (``MPIBackendEngine.py:343-365``): there are no windows here; the
     # calls hand back ordinary buffers so that code written against them keeps running.
-    def Malloc(self, size, device):
-        return None, self.allocate_buffer((int(size),), torch.float32, device)
+    @staticmethod
+    def Malloc(size, device):
+        return None, torch.zeros(int(size), dtype=torch.float32, device=device)
 
     @staticmethod
     def Attach(tensor: torch.Tensor):
@@ -122,7 +123,22 @@ class CollectiveEngine(BackendEngine):
             r2.copy_(got)
 
     # -- gather / scatter -------------------------------------------------------------------------
-    def gather(self, src_tensor, indices=None, rank_mappings=None, *, comm_plan=None, **kwargs):
+    @staticmethod
+    def _reference_keywords(src_tensor, rank_mappings, output_size, kwargs):
+        """Keyword names the three reference engines use for the same arguments (``NCCLBackendEngine.py:113,183``:
+        ``local_send_tensor``; ``MPIBackendEngine.py:417,478``: ``send_tensor``, ``rank_mapping``, ``num_output_rows``;
+        ``NVSHMEMBackendEngine.py``: ``input_tensor``, ``num_output_rows``)."""
+        for k in ("local_send_tensor", "send_tensor", "input_tensor"):
+            if src_tensor is None and k in kwargs:
+                src_tensor = kwargs.pop(k)
+        if rank_mappings is None and "rank_mapping" in kwargs:
+            rank_mappings = kwargs.pop("rank_mapping")
+        if output_size is None and "num_output_rows" in kwargs:
+            output_size = kwargs.pop("num_output_rows")
+        return src_tensor, rank_mappings, output_size
+
+    def gather(self, src_tensor=None, indices=None, rank_mappings=None, *, comm_plan=None, **kwargs):
+        src_tensor, rank_mappings, _ = self._reference_keywords(src_tensor, rank_mappings, None, kwargs)
         plan = comm_plan
         if plan is None and isinstance(indices, NCCLGraphCommPlan):
             plan = indices
@@ -130,13 +146,16 @@ class CollectiveEngine(BackendEngine):
             plan = self._legacy_plan("g", src_tensor, indices, rank_mappings)
         return CommPlan_GatherFunction.apply(src_tensor, plan, self)
 
-    def scatter(self, src_tensor, indices=None, rank_mappings=None, output_size=None, *, comm_plan=None, **kwargs):
+    def scatter(self, src_tensor=None, indices=None, rank_mappings=None, output_size=None, *, comm_plan=None, **kwargs):
+        src_tensor, rank_mappings, output_size = self._reference_keywords(src_tensor, rank_mappings, output_size, kwargs)
         plan = comm_plan
         if plan is None and isinstance(indices, NCCLGraphCommPlan):
             plan = indices
         if plan is None:
-            if isinstance(rank_mappings, int) and output_size is not None and isinstance(output_size, torch.Tensor):
-                rank_mappings, output_size = output_size, rank_mappings  # NVSHMEM / MPI argument order
+            # the MPI engine of the reference takes (tensor, indices, num_output_rows, rank_mapping=None): a row count in the
+            # third position is recognised by its type
+            if isinstance(rank_mappings, int) and (output_size is None or isinstance(output_size, torch.Tensor)):
+                rank_mappings, output_size = output_size, rank_mappings
             plan = self._legacy_plan("s", src_tensor, indices, rank_mappings, output_size)
         return CommPlan_ScatterFunction.apply(src_tensor, plan, self)
 

@@ -27,7 +27,10 @@ class BackendEngine(object):
         sz = tensor.shape[dim] // W
         return tensor.narrow(dim, r * sz, sz)
 
-    def scatter(self, src_tensor, indices=None, rank_mappings=None, output_size=None, *args, **kwargs) -> torch.Tensor:
+    def scatter(self, src_tensor, indices=None, output_size=None, rank_mappings=None, *args, **kwargs) -> torch.Tensor:
+        """Abstract, in the reference's parameter order (``Engine.py:46-54``).  The concrete engines take
+        ``(src_tensor, indices, rank_mappings, output_size)`` like the reference's NCCL / NVSHMEM engines and recognise the row
+        count by its type, so both orders work."""
         raise NotImplementedError
 
     def gather(self, src_tensor, indices=None, rank_mappings=None, *args, **kwargs) -> torch.Tensor:

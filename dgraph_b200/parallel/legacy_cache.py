@@ -87,78 +87,82 @@ def NCCLScatterCacheGenerator(indices, edge_placement, edge_dest_ranks, num_outp
         scatter_local_indices=p.local_vertex_idx, num_output_rows=num_output_rows, rank=rank, world_size=world_size, plan=p)
 
 
-def _nccl_alltoall_v(local_send_tensor: torch.Tensor, local_recv_tensor: torch.Tensor, indices: torch.Tensor,
-                     local_rank_mapping: torch.Tensor, edge_rank_loc: torch.Tensor, src_rank_loc: torch.Tensor, rank: int,
-                     world_size: int, send_comm_vector: List[int], recv_comm_vector: List[int]):
-    """Variable all-to-all of rows with one ``P2POp`` pair per peer (``alltoallv_impl.py:7-131``)."""
-    F = local_send_tensor.shape[-1]
-    send = local_send_tensor.reshape(-1, F)
-    recv_parts, ops = {}, []
-    so = 0
-    for r in range(world_size):
-        k = send_comm_vector[r]
-        if r != rank and k:
-            ops.append(dist.P2POp(dist.isend, send[so:so + k].contiguous(), r))
-        so += k
-        kr = recv_comm_vector[r]
-        if r != rank and kr:
-            recv_parts[r] = torch.empty((kr, F), dtype=send.dtype, device=send.device)
-            ops.append(dist.P2POp(dist.irecv, recv_parts[r], r))
+def _peer_exchange(send: Dict[int, torch.Tensor], recv: Dict[int, torch.Tensor], rank: int) -> None:
+    """One ``isend`` / ``irecv`` pair per peer with something to move, batched (``dist.batch_isend_irecv``)."""
+    ops = []
+    for r in sorted(set(send) | set(recv)):
+        if r == rank:
+            continue
+        if r in send and send[r].numel():
+            ops.append(dist.P2POp(dist.isend, send[r].contiguous(), r))
+        if r in recv and recv[r].numel():
+            ops.append(dist.P2POp(dist.irecv, recv[r], r))
     if ops:
         for req in dist.batch_isend_irecv(ops):
             req.wait()
-    ro = 0
+
+
+def _nccl_alltoall_v(local_send_tensor: torch.Tensor, local_recv_tensor: torch.Tensor, indices: torch.Tensor,
+                     local_rank_mapping: torch.Tensor, edge_rank_loc: torch.Tensor, src_rank_loc: torch.Tensor, rank: int,
+                     world_size: int, cache=None):
+    """Remote half of the legacy gather (``alltoallv_impl.py:7-131``): for every edge held by rank ``i != rank`` whose vertex
+    lives here, send row ``indices % rows`` of ``local_send_tensor [1, rows, F]`` to ``i``; rows arriving from peer ``i`` land
+    in the slots of ``local_recv_tensor [1, E_local, F]`` where ``local_rank_mapping == i`` (in order).  ``edge_rank_loc`` /
+    ``src_rank_loc`` describe ALL edges (holder, vertex owner); with a :class:`NCCLGatherCache` the per-peer row lists come from
+    the cache and the index tensors are not read."""
+    F = local_send_tensor.shape[-1]
+    rows = local_send_tensor.shape[-2]
+    send2d = local_send_tensor.reshape(-1, F)
+    if cache is None:
+        holder, owner, idx = edge_rank_loc.reshape(-1), src_rank_loc.reshape(-1), indices.reshape(-1)
+        if not bool((holder != owner).any()):
+            return local_recv_tensor
+        send_rows = {i: idx[(owner == rank) & (holder == i)].long() % rows for i in range(world_size) if i != rank}
+        lrm = local_rank_mapping.reshape(-1)
+        recv_slots = {i: torch.nonzero(lrm == i, as_tuple=True)[0] for i in range(world_size) if i != rank}
+    else:
+        send_rows = {i: t.reshape(-1).long() for i, t in cache.gather_send_local_placement.items() if i != rank}
+        recv_slots = {i: t.reshape(-1).long() for i, t in cache.gather_recv_local_placement.items() if i != rank}
+    send = {i: send2d.index_select(0, r) for i, r in send_rows.items() if r.numel()}
+    recv = {i: torch.zeros((s.numel(), F), dtype=send2d.dtype, device=send2d.device) for i, s in recv_slots.items() if s.numel()}
+    _peer_exchange(send, recv, rank)
     out = local_recv_tensor.reshape(-1, F)
-    for r in range(world_size):
-        kr = recv_comm_vector[r]
-        if r in recv_parts:
-            out[ro:ro + kr] = recv_parts[r]
-        ro += kr
+    for i, buf in recv.items():
+        out[recv_slots[i]] = buf
     return local_recv_tensor
 
 
-def _nccl_alltoallv_with_dict(send_tensor_dict: Dict[int, torch.Tensor], recv_tensor_dict: Dict[int, torch.Tensor], rank: int,
+def _nccl_alltoallv_with_dict(send_buffer_dict: Dict[int, torch.Tensor], recv_buffer_dict: Dict[int, torch.Tensor], rank: int,
                               world_size: int):
-    """Same, with per-peer tensors (``alltoallv_impl.py:134-161``)."""
-    ops = []
-    for r, t in send_tensor_dict.items():
-        if r != rank and t.numel():
-            ops.append(dist.P2POp(dist.isend, t.contiguous(), r))
-    for r, t in recv_tensor_dict.items():
-        if r != rank and t.numel():
-            ops.append(dist.P2POp(dist.irecv, t, r))
-    if ops:
-        for req in dist.batch_isend_irecv(ops):
-            req.wait()
-    return recv_tensor_dict
+    """Per-peer tensors in, the filled receive dictionary out (``alltoallv_impl.py:134-161``)."""
+    _peer_exchange(send_buffer_dict, recv_buffer_dict, rank)
+    return recv_buffer_dict
 
 
-def torch_alltoallv_with_comm_map(send_tensor: torch.Tensor, send_splits: List[int], recv_splits: List[int], dim: int = 1):
-    """``dist.all_to_all`` on split lists along ``dim`` (``alltoallv_impl.py:164-180``)."""
-    send = [t.contiguous() for t in torch.split(send_tensor, send_splits, dim=dim)]
-    shape = list(send_tensor.shape)
-    recv = []
-    for k in recv_splits:
-        shape[dim] = k
-        recv.append(torch.empty(shape, dtype=send_tensor.dtype, device=send_tensor.device))
-    if dist.get_backend() == "gloo":  # gloo has no list all-to-all: one send / receive pair per peer instead
-        me = dist.get_rank()
-        recv[me].copy_(send[me])
-        ops = []
-        for r in range(dist.get_world_size()):
-            if r != me and send[r].numel():
-                ops.append(dist.P2POp(dist.isend, send[r], r))
-            if r != me and recv[r].numel():
-                ops.append(dist.P2POp(dist.irecv, recv[r], r))
-        if ops:
-            for req in dist.batch_isend_irecv(ops):
-                req.wait()
+def torch_alltoallv_with_comm_map(contiguous_send_tensor: torch.Tensor, contiguous_recv_tensor: torch.Tensor,
+                                  send_comm_map, recv_comm_map, rank: int, world_size: int):
+    """``dist.all_to_all`` over the slices of two ``[1, rows, F]`` buffers cut along dim 1 by ``send_comm_map`` / ``recv_comm_map``
+    (rows per rank); returns the list of receive slices, which are views of ``contiguous_recv_tensor``
+    (``alltoallv_impl.py:164-180``).  gloo has no list all-to-all: one send / receive pair per peer there."""
+    send_sizes = [int(x) for x in (send_comm_map.tolist() if torch.is_tensor(send_comm_map) else send_comm_map)]
+    recv_sizes = [int(x) for x in (recv_comm_map.tolist() if torch.is_tensor(recv_comm_map) else recv_comm_map)]
+    assert len(send_sizes) == world_size and len(recv_sizes) == world_size, "comm maps must have world_size entries"
+    send_list = [t.contiguous() for t in torch.split(contiguous_send_tensor, send_sizes, dim=1)]
+    recv_views = list(torch.split(contiguous_recv_tensor, recv_sizes, dim=1))
+    if dist.get_backend() == "gloo":
+        recv_views[rank].copy_(send_list[rank])
+        bufs = {r: torch.empty_like(recv_views[r]) for r in range(world_size) if r != rank}
+        _peer_exchange({r: send_list[r] for r in range(world_size) if r != rank}, bufs, rank)
+        for r, b in bufs.items():
+            recv_views[r].copy_(b)
     else:
-        dist.all_to_all(recv, send)
-    return torch.cat(recv, dim=dim)
+        bufs = [torch.empty_like(v) for v in recv_views]
+        dist.all_to_all(bufs, send_list)
+        for v, b in zip(recv_views, bufs):
+            v.copy_(b)
+    return recv_views
 
 
-# ---- the two cache-construction helpers of the reference (``_nccl_cache.py:70-160``), on top of ``indices_utils`` ------------
 def all_to_all_cache_helper(indices, edge_placement, edge_vertex_ranks, num_rows, rank, world_size):
     """Gather-side bookkeeping: ``(send_comm_vector [W], recv_comm_vector [W], send_local_placement {peer: local rows to ship},
     recv_local_placement {peer: positions among this rank's edges that peer's rows fill})``.  An edge lives on

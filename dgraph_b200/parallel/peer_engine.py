@@ -454,13 +454,15 @@ class PeerMemoryEngine(TorchDistEngine):
         return (self._world > 1 and plan is not None and getattr(plan, "edge_owner", None) is not None and t.is_cuda
                 and t.dtype == torch.bfloat16 and (F * 2) % 16 == 0 and t.dim() in (2, 3) and (t.dim() == 2 or t.shape[0] == 1))
 
-    def gather(self, src_tensor, indices=None, rank_mappings=None, *, comm_plan=None, **kwargs):
+    def gather(self, src_tensor=None, indices=None, rank_mappings=None, *, comm_plan=None, **kwargs):
+        src_tensor, rank_mappings, _ = self._reference_keywords(src_tensor, rank_mappings, None, kwargs)
         plan = comm_plan if comm_plan is not None else (indices if hasattr(indices, "boundary_edge_idx") else None)
         if self._peer_plan_ok(src_tensor, plan):
             return _PlanGatherPeer.apply(src_tensor, plan, self)
         return super().gather(src_tensor, indices, rank_mappings, comm_plan=comm_plan, **kwargs)
 
-    def scatter(self, src_tensor, indices=None, rank_mappings=None, output_size=None, *, comm_plan=None, **kwargs):
+    def scatter(self, src_tensor=None, indices=None, rank_mappings=None, output_size=None, *, comm_plan=None, **kwargs):
+        src_tensor, rank_mappings, output_size = self._reference_keywords(src_tensor, rank_mappings, output_size, kwargs)
         plan = comm_plan if comm_plan is not None else (indices if hasattr(indices, "boundary_edge_idx") else None)
         if self._peer_plan_ok(src_tensor, plan):
             return _PlanScatterPeer.apply(src_tensor, plan, self)

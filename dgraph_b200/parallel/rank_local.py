@@ -72,9 +72,14 @@ def RankLocalMaskedGather(_src: torch.Tensor, indices: torch.Tensor, rank_mappin
     return _rows(_src).index_select(0, indices.reshape(-1)[m].long()).unsqueeze(0)
 
 
-def RankLocalMaskedScatter(_src: torch.Tensor, _output: torch.Tensor, indices: torch.Tensor, rank_mapping: torch.Tensor, rank: int):
-    """``_output[:, indices[i]] += _src[:, i]`` for entries with ``rank_mapping[i] == rank`` (plain sum, no ReLU)."""
-    idx, rm = indices.reshape(-1), rank_mapping.reshape(-1)
+def RankLocalMaskedScatter(_src: torch.Tensor, _output: torch.Tensor, local_indices_slice: torch.Tensor,
+                           local_dest_ranks: torch.Tensor, rank: int):
+    """``_output[:, local_indices_slice[i] % rows] += _src[:, i]`` for entries with ``local_dest_ranks[i] == rank`` (plain sum, no
+    ReLU; indices may be global ids of a contiguous even split, hence the modulo as in ``RankLocalOps.py:220-245``)."""
+    rows = _rows(_output).shape[0]
+    idx, rm = local_indices_slice.reshape(-1), local_dest_ranks.reshape(-1)
+    if rows:
+        idx = idx % rows  # identity for local ids; no host synchronisation to find out
     if _native_ok(_src, _output):
         return _launch(_output, _src, idx, None, rm, rank, 1)
     m = rm == rank
@@ -96,14 +101,24 @@ def RankLocalRenumberingWithMapping(_indices: torch.Tensor, rank_mapping: torch.
     return inv, u, rm
 
 
-def LocalAggregateWithRemapping(global_data: torch.Tensor, global_indices: torch.Tensor, num_features: int, device=None):
-    """Pre-reduce rows that target the same global index: returns ``(summed_rows [1, U, F], unique_indices)``."""
+def LocalAggregateWithRemapping(global_data: torch.Tensor, global_indices: torch.Tensor, global_mapping=None, num_features=None,
+                                device=None):
+    """Pre-reduce rows that target the same global index (``RankLocalOps.py:287-327``):
+    ``(summed_rows [1, U, F], rank of every distinct index [U])`` in ascending index order.  Without ``global_mapping`` -- the
+    short form ``(data, indices, num_features)`` -- the second result is the list of distinct indices itself."""
+    if global_mapping is not None and not torch.is_tensor(global_mapping):  # short form: third argument is the feature count
+        global_mapping, num_features, device = None, global_mapping, (num_features if device is None else device)
     idx = global_indices.reshape(-1)
     u, inv = torch.unique(idx, return_inverse=True)
     rows = _rows(global_data)
-    out = torch.zeros((u.numel(), num_features), dtype=rows.dtype, device=device or rows.device)
-    out.index_add_(0, inv, rows)
-    return out.unsqueeze(0), u
+    F = int(num_features) if num_features is not None else rows.shape[1]
+    out = torch.zeros((u.numel(), F), dtype=rows.dtype, device=device or rows.device)
+    out.index_add_(0, inv.to(out.device), rows.to(out.device))
+    if global_mapping is None:
+        return out.unsqueeze(0), u
+    owner = torch.zeros_like(u)
+    owner.scatter_(0, inv, global_mapping.reshape(-1).to(u.dtype))
+    return out.unsqueeze(0), owner
 
 
 def RankLocalReNumbering(_indices: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:

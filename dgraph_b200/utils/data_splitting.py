@@ -3,16 +3,23 @@
 import torch
 
 
-def largest_split(global_size: int, world_size: int) -> int:
-    """Ceil-div: rows of the largest shard when ``global_size`` rows are split over ``world_size`` ranks."""
-    return (global_size + world_size - 1) // world_size
+def largest_split(size: int, num_splits: int) -> int:
+    """Ceil-div: rows of the largest shard when ``size`` rows are split into ``num_splits`` shards."""
+    return (size + num_splits - 1) // num_splits
 
 
-def split_per_rank(global_size: int, rank: int, world_size: int):
+def split_range(global_size: int, current_rank: int, world_size: int):
     """``(start, end)`` of this rank's contiguous shard; the last shards may be short or empty."""
     sz = largest_split(global_size, world_size)
-    start = min(rank * sz, global_size)
+    start = min(current_rank * sz, global_size)
     return start, min(start + sz, global_size)
+
+
+def split_per_rank(global_size: int, current_rank: int, world_size: int) -> int:
+    """Number of rows of ``current_rank``'s shard (the reference's return value, ``DGraph/utils.py:21-26``; never negative
+    here -- ranks beyond the data get 0)."""
+    start, end = split_range(global_size, current_rank, world_size)
+    return end - start
 
 
 def try_barrier(comm=None) -> bool:

@@ -80,8 +80,9 @@ class TimingReport:
         TimingReport._barrier()
 
     @staticmethod
-    def add_time(name: str, ms: float):
-        TimingReport._timers.setdefault(name, []).append(ms)
+    def add_time(name: str, elapsed_time: float):
+        """Manually add one entry (milliseconds) under ``name``."""
+        TimingReport._timers.setdefault(name, []).append(elapsed_time)
 
     @staticmethod
     def get_timers() -> Dict[str, List[float]]:

@@ -44,6 +44,8 @@ def test_rank_local_aggregate_and_hetero_accessors():
     idx = torch.tensor([7, 3, 7, 9, 3])
     summed, uniq = LocalAggregateWithRemapping(data, idx, 2)
     assert uniq.tolist() == [3, 7, 9] and summed.shape == (1, 3, 2)
+    summed_r, owners = LocalAggregateWithRemapping(data, idx, torch.tensor([1, 0, 1, 2, 0]), 2, torch.device("cpu"))  # reference form
+    assert torch.equal(summed_r, summed) and owners.tolist() == [0, 1, 2]
     assert torch.equal(summed[0], torch.stack([data[0, 1] + data[0, 4], data[0, 0] + data[0, 2], data[0, 3]]))
     renum, uniq2, ranks = RankLocalRenumberingWithMapping(idx, torch.tensor([1, 0, 1, 2, 0]))
     assert renum.tolist() == [1, 0, 1, 2, 0] and uniq2.tolist() == [3, 7, 9] and ranks.tolist() == [0, 1, 2]
@@ -111,16 +113,25 @@ def _a2av_worker(rank, W, port, ret):
     from dgraph_b200.parallel.legacy_cache import (NCCLGatherCacheGenerator, NCCLScatterCacheGenerator, _nccl_alltoall_v,
                                                    _nccl_alltoallv_with_dict, torch_alltoallv_with_comm_map)
 
+    other = 1 - rank
+    # every rank owns 3 rows; all edges: holder, owner of the addressed vertex, global vertex id (row = id % 3)
+    holder = torch.tensor([[0, 0, 0, 1, 1]])
+    owner = torch.tensor([[1, 0, 1, 0, 1]])
+    ids = torch.tensor([[4, 1, 5, 2, 3]])
+    x = torch.arange(6, dtype=torch.float32).view(1, 3, 2) + 100 * rank
+    mine = holder[0] == rank
+    recv = torch.zeros(1, int(mine.sum()), 2)
+    _nccl_alltoall_v(x, recv, ids, owner[:, mine], holder, owner, rank, W)
+    got_v = recv.clone()
+    d = _nccl_alltoallv_with_dict({other: torch.full((3,), float(rank))}, {other: torch.zeros(3)}, rank, W)
     # rank r sends (r + 1) rows to the other rank and keeps 1
     send_counts = [1, rank + 1] if rank == 0 else [rank + 1, 1]
     recv_counts = [1, 2] if rank == 0 else [1, 1]
     send = torch.arange(sum(send_counts) * 2, dtype=torch.float32).view(1, -1, 2) + 100 * rank
-    recv = torch.zeros(1, sum(recv_counts), 2)
-    _nccl_alltoall_v(send, recv, None, None, None, None, rank, W, send_counts, recv_counts)
-    got_v = recv.clone()
-    other = 1 - rank
-    d = _nccl_alltoallv_with_dict({other: torch.full((3,), float(rank))}, {other: torch.zeros(3)}, rank, W)
-    cat = torch_alltoallv_with_comm_map(send, send_counts, recv_counts, dim=1)
+    rbuf = torch.zeros(1, sum(recv_counts), 2)
+    views = torch_alltoallv_with_comm_map(send, rbuf, torch.tensor(send_counts), torch.tensor(recv_counts), rank, W)
+    assert len(views) == W and views[0].data_ptr() == rbuf.data_ptr()
+    cat = rbuf
     # legacy caches: 8 vertices, 4 per rank; every rank owns the edges whose source it owns
     e = torch.tensor([[0, 5], [1, 2], [2, 7], [3, 4], [4, 1], [5, 6], [6, 0], [7, 3]])
     place, dest = e[:, 0] // 4, e[:, 1] // 4
@@ -137,11 +148,14 @@ def test_legacy_alltoallv_helpers_and_caches_gloo():
     ret = mgr.dict()
     mp.spawn(_a2av_worker, args=(2, _free_port(), ret), nprocs=2, join=True)
     r0, r1 = ret[0], ret[1]
-    # rank 0 receives rank 1's first two rows into its second segment; rank 1 receives rank 0's rows 1..2 into its first segment
-    assert torch.equal(r0[0][0, 1:], torch.tensor([[100., 101.], [102., 103.]]))
-    assert torch.equal(r1[0][0, :1], torch.tensor([[2., 3.]]))
+    # gather halves: rank 0 holds edges to vertices 4, 1, 5 -> its remote slots 0 and 2 get rank 1's rows 1 and 2; slot 1 is local
+    # (left for the local gather); rank 1 holds edges to 2, 3 -> slot 0 gets rank 0's row 2
+    assert torch.equal(r0[0][0], torch.tensor([[102., 103.], [0., 0.], [104., 105.]]))
+    assert torch.equal(r1[0][0], torch.tensor([[4., 5.], [0., 0.]]))
     assert r0[1].tolist() == [1.0] * 3 and r1[1].tolist() == [0.0] * 3
-    assert r0[2].shape == (1, 3, 2) and r1[2].shape == (1, 2, 2)
+    # list all-to-all: rank 0 keeps its row 0 and receives rank 1's first two rows; rank 1 receives rank 0's row 1 and keeps its last
+    assert torch.equal(r0[2][0], torch.tensor([[0., 1.], [100., 101.], [102., 103.]]))
+    assert torch.equal(r1[2][0], torch.tensor([[2., 3.], [104., 105.]]))
     # what one rank sends for a gather is what the other receives, and scatter is the mirror image
     assert r0[3][1] == r1[4][0] and r1[3][0] == r0[4][1]
     assert r0[5] == r0[4] and r0[6] == r0[3]
@@ -209,3 +223,32 @@ def test_indices_utils_counts_and_placements():
     assert r.tolist() == [1, 0, 1, 2] and u.tolist() == [3, 7, 9]
     src = torch.arange(12.0).view(6, 2)
     assert torch.equal(RankLocalGather(src, torch.tensor([5, 0, 2]), torch.tensor([1, 0, 1]), 1), src[[5, 2]])
+
+
+def test_engine_calls_accept_the_reference_engines_argument_names_and_orders():
+    """The three reference engines name and order the gather / scatter arguments differently (NCCL ``local_send_tensor``; MPI
+    ``send_tensor, indices, num_output_rows, rank_mapping``; NVSHMEM ``input_tensor, indices, rank_mappings, num_output_rows``):
+    every form reaches the same plan."""
+    W, F = 3, 2
+    idx_all = torch.tensor([[0, 1, 2, 3, 4, 5]])  # rank r addresses rows 2r, 2r+1 of a 2-rows-per-rank matrix ... of everyone
+
+    def job(comm):
+        r = comm.get_rank()
+        x = (torch.arange(2 * F, dtype=torch.float64).view(1, 2, F) + 100 * r)
+        own = torch.div(idx_all, 2, rounding_mode="floor")
+        a = comm.gather(x, idx_all, own)
+        b = comm.gather(local_send_tensor=x, indices=idx_all, rank_mappings=own)
+        c = comm.gather(send_tensor=x, indices=idx_all, rank_mapping=own)
+        e = torch.ones(1, idx_all.shape[1], F, dtype=torch.float64) * (r + 1)
+        s0 = comm.scatter(e, idx_all, own, 2)
+        s1 = comm.scatter(e, idx_all, 2, own)  # MPI order
+        s2 = comm.scatter(input_tensor=e, indices=idx_all, rank_mappings=own, num_output_rows=2)
+        s3 = comm.scatter(e, idx_all, 2)  # MPI order, owners from the even split
+        return a, b, c, s0, s1, s2, s3
+
+    for r, (a, b, c, s0, s1, s2, s3) in enumerate(run_world(W, job)):
+        assert torch.equal(a, b) and torch.equal(a, c) and a.shape == (1, 6, F)
+        assert torch.equal(a[0, 2 * 1], torch.arange(F, dtype=torch.float64) + 100)  # row 0 of rank 1
+        for s in (s1, s2, s3):
+            assert torch.equal(s0, s)
+        assert torch.equal(s0, torch.full((1, 2, F), float(sum(range(1, W + 1))), dtype=torch.float64))

@@ -18,8 +18,8 @@ def test_process_homogenous_data_uses_inverse_permutation():
     e = random_graph(V, 4, seed=1)
     x = torch.arange(V, dtype=torch.float32).unsqueeze(1)  # feature = original id
     place = torch.tensor([2, 0, 1, 1, 0, 2, 2, 0, 1, 0, 2])  # not an involution
-    g = process_homogenous_data({"node_feat": x, "edge_index": e.t().contiguous(), "num_nodes": V}, torch.arange(V), W,
-                                {"train": torch.tensor([0, 5, 9])}, place)
+    g = process_homogenous_data({"node_feat": x, "edge_index": e.t().contiguous(), "num_nodes": V}, torch.arange(V), 0, W,
+                                {"train": torch.tensor([0, 5, 9])}, place)  # the reference's argument order
     assert isinstance(g, DistributedGraph)
     assert torch.equal(g.node_loc, torch.sort(place).values)
     orig = g.node_features[:, 0].long()  # new id -> original id
@@ -49,7 +49,10 @@ def test_partitioners_balanced_and_bfs_cuts_less_than_hash():
 
 def test_split_helpers():
     assert largest_split(10, 4) == 3
-    assert [split_per_rank(10, r, 4) for r in range(4)] == [(0, 3), (3, 6), (6, 9), (9, 10)]
+    assert [split_per_rank(10, r, 4) for r in range(4)] == [3, 3, 3, 1]  # shard sizes, as in the reference
+    from dgraph_b200.utils.data_splitting import split_range
+
+    assert [split_range(10, r, 4) for r in range(4)] == [(0, 3), (3, 6), (6, 9), (9, 10)]
 
 
 def test_native_multilevel_partitioner_quality_balance_determinism():

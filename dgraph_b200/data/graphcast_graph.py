@@ -223,13 +223,23 @@ class DistributedGraphCastGraph:
 class DistributedGraphCastGraphGenerator:
     """Builds the global graph once and shards it (``graphcast_graph.py:162-437``)."""
 
-    def __init__(self, lat_lon: Tuple[int, int] = (721, 1440), mesh_level: int = 6, multi: bool = True,
-                 placement: str = "bands"):
-        """``placement``: ``"bands"`` = contiguous latitude bands (no graph partitioner needed); ``"multilevel"`` = the mesh is cut
+    def __init__(self, lat_lon_grid=(721, 1440), mesh_level: int = 6, ranks_per_graph: int = 1, rank: int = 0, world_size: int = 1,
+                 multi: bool = True, placement: str = "bands", lat_lon=None):
+        """Positional order of the reference (``graphcast_graph.py:169-176``): ``lat_lon_grid`` -- there a ``[n_lat, n_lon, 2]``
+        tensor of the regular grid's coordinates, here also just ``(n_lat, n_lon)`` --, ``mesh_level``, ``ranks_per_graph``,
+        ``rank``, ``world_size`` (defaults for ``get_graphcast_graph`` / ``build_graphcast_comm_patterns``).  ``placement``: ``"bands"`` = contiguous latitude bands (no graph partitioner needed); ``"multilevel"`` = the mesh is cut
         by the native multilevel partitioner (the reference's METIS step, ``data_utils/preprocess.py:14-30``) with every mesh
         vertex weighted by the grid vertices it feeds, and each grid vertex follows the majority of its mesh2grid sources
         (the reference derives the grid placement from the bipartite edges as well, ``graphcast_graph.py:85-159``)."""
         assert placement in ("bands", "multilevel")
+        if lat_lon is not None:
+            lat_lon_grid = lat_lon
+        if torch.is_tensor(lat_lon_grid):  # the reference passes the coordinate grid itself: only its extent is needed here
+            assert lat_lon_grid.dim() == 3 and lat_lon_grid.shape[-1] == 2, "expected a [n_lat, n_lon, 2] grid tensor"
+            self.lat_lon_grid, lat_lon_grid = lat_lon_grid, (int(lat_lon_grid.shape[0]), int(lat_lon_grid.shape[1]))
+        lat_lon = tuple(int(v) for v in lat_lon_grid)
+        self.ranks_per_graph, self.rank, self.world_size = int(ranks_per_graph), int(rank), int(world_size)
+        self.local_rank = self.rank % max(self.ranks_per_graph, 1)
         self.lat_lon, self.mesh_level, self.multi, self.placement = lat_lon, mesh_level, multi, placement
         self._global: Optional[GraphCastGraph] = None
         self._placements = {}
@@ -375,10 +385,14 @@ def _get_mesh2grid_graph(self, grid_vertex_rank_placement: torch.Tensor, renumbe
             "dst_indices": dst[order], "mesh2grid_edge_rank_placement": edge_pl}
 
 
-def _get_graphcast_graph(self, mesh_vertex_rank_placement: torch.Tensor, rank: int = 0, world_size: Optional[int] = None):
+def _get_graphcast_graph(self, mesh_vertex_rank_placement: torch.Tensor, rank: Optional[int] = None,
+                         world_size: Optional[int] = None):
     """This rank's shard (features, local edge lists, the three halo plans) for a given mesh placement; the grid follows its
     mesh neighbours.  (Upstream returns one record of global tensors here and builds the plans in a second step.)"""
     pl = mesh_vertex_rank_placement.reshape(-1).long()
+    rank = self.rank if rank is None else int(rank)
+    if world_size is None:
+        world_size = self.world_size if self.world_size > 1 else None
     world = int(pl.max()) + 1 if world_size is None else int(world_size)
     assert 0 <= rank < world and int(pl.max()) < world, "mesh vertex placement does not match rank / world size"
     m = self.get_mesh_graph(pl)
@@ -397,9 +411,25 @@ DistributedGraphCastGraphGenerator.get_mesh2grid_graph = _get_mesh2grid_graph
 DistributedGraphCastGraphGenerator.get_graphcast_graph = _get_graphcast_graph
 
 
-def build_graphcast_comm_patterns(generator: DistributedGraphCastGraphGenerator, rank: int, world_size: int):
-    """Reference name (``graphcast_graph.py:85-159``): the three plans of one rank."""
-    return generator.shard(rank, world_size).patterns
+def build_graphcast_comm_patterns(graph, rank: Optional[int] = None, world_size: Optional[int] = None):
+    """Reference name (``graphcast_graph.py:85-159``): the three plans (grid2mesh, mesh, mesh2grid) of one rank.  ``graph`` is a
+    generator (then ``rank`` / ``world_size`` say which shard) or -- the reference's form -- a topology record with the fields
+    ``rank``, ``world_size``, ``mesh_rank_placement``, ``grid_rank_placement`` and the six global ``*_src_indices`` /
+    ``*_dst_indices`` tensors (``GraphCastTopology`` in ``experiments/GraphCast/data_utils/graphcast_graph.py``)."""
+    if isinstance(graph, DistributedGraphCastGraphGenerator):
+        return graph.shard(graph.rank if rank is None else rank, graph.world_size if world_size is None else world_size).patterns
+    r, W = int(graph.rank if rank is None else rank), int(graph.world_size if world_size is None else world_size)
+    mesh_pl, grid_pl = graph.mesh_rank_placement.reshape(-1).long(), graph.grid_rank_placement.reshape(-1).long()
+
+    def build(src, dst, central_is_dst, central_pl, nbr_pl):
+        c, n = (dst, src) if central_is_dst else (src, dst)
+        ed = torch.stack([c.reshape(-1).long(), n.reshape(-1).long()], 1)
+        return build_communication_pattern(ed, central_pl, r, W, neighbor_partitioning=None if central_pl is nbr_pl else nbr_pl)
+
+    return GraphCastCommPatterns(
+        grid2mesh=build(graph.grid2mesh_graph_src_indices, graph.grid2mesh_graph_dst_indices, True, mesh_pl, grid_pl),
+        mesh=build(graph.mesh_graph_src_indices, graph.mesh_graph_dst_indices, False, mesh_pl, mesh_pl),
+        mesh2grid=build(graph.mesh2grid_graph_src_indices, graph.mesh2grid_graph_dst_indices, True, grid_pl, mesh_pl))
 
 
 # ------------------------------------------------------------------------------------------------ synthetic data

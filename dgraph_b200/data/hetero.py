@@ -82,15 +82,16 @@ class DistributedHeteroGraphDataset:
     def local_range(self, t: int) -> Tuple[int, int]:
         return int(self.offsets[t][self.rank]), int(self.offsets[t][self.rank + 1])
 
-    def get_mask(self, name: str) -> torch.Tensor:
-        """Global paper indices of a split -> local row indices on this rank."""
+    def get_mask(self, mask_type: str) -> torch.Tensor:
+        """Global paper indices of a split (``"train"``, ``"valid"`` / ``"val"``, ``"test"``) -> local row indices on this rank."""
+        name = mask_type if mask_type in self.split else {"val": "valid", "valid": "val"}.get(mask_type, mask_type)
         idx = self.split[name]
         lo, hi = self.local_range(0)
         m = (idx >= lo) & (idx < hi)
         return idx[m] - lo
 
-    def get_target(self, name: str) -> torch.Tensor:
-        return self.labels[self.get_mask(name).to(self.labels.device)]
+    def get_target(self, mask_type: str) -> torch.Tensor:
+        return self.labels[self.get_mask(mask_type).to(self.labels.device)]
 
     def __len__(self) -> int:
         return 1  # one full graph

@@ -69,14 +69,14 @@ class DistributedOGBWrapper:
 class DGraphOGBDataset:
     """Halo-plan flavour used by the GCN trainer: ``ds[0] -> (local_feats, local_labels, comm_pattern)``."""
 
-    def __init__(self, dname: str, comm, root_dir: str = "data", node_rank_placement: Optional[torch.Tensor] = None,
-                 scale: float = 1.0, seed: int = 0, device="cpu", partition: str = "contiguous"):
+    def __init__(self, dname: str, comm, node_rank_placement: Optional[torch.Tensor] = None, root_dir: Optional[str] = "data",
+                 *args, scale: float = 1.0, seed: int = 0, device="cpu", partition: str = "contiguous", **kwargs):
         """``partition`` (used when no placement tensor is given): ``"contiguous"`` blocks of vertex ids, ``"multilevel"`` = the
         native multilevel partitioner (deterministic, so every rank computes the same placement), ``"round_robin"`` = the
         reference's default (``ogb_comm_dataset.py:54-90``)."""
         self.comm, self.rank, self.world = comm, comm.get_rank(), comm.get_world_size()
         name = {"arxiv": "ogbn-arxiv", "products": "ogbn-products"}.get(dname, dname)
-        g, y, split, self.synthetic = _load_raw(name, root_dir, scale, seed)
+        g, y, split, self.synthetic = _load_raw(name, root_dir or "dataset", scale, seed)
         self.num_classes = num_classes.get(name, int(y.max()) + 1)
         V = int(g["num_nodes"])
         edges = torch.as_tensor(g["edge_index"]).t().contiguous().long().to(device)
@@ -107,5 +107,5 @@ class DGraphOGBDataset:
     def __len__(self):
         return 1
 
-    def __getitem__(self, idx):
+    def __getitem__(self, index):
         return self.local_features, self.local_labels, self.comm_pattern

@@ -38,8 +38,8 @@ class SingleProcessDummyCommunicator(_communicator_class()):
 
 
 class CommAwareDistributedSampler(Sampler):
-    def __init__(self, dataset, comm=None, num_replicas: int = None, replica_id: int = None, shuffle: bool = True, seed: int = 0,
-                 drop_last: bool = False):
+    def __init__(self, dataset, comm=None, shuffle: bool = True, seed: int = 0, drop_last: bool = False,
+                 num_replicas: int = None, replica_id: int = None):
         self.dataset = dataset
         self.num_replicas = num_replicas if num_replicas is not None else (comm.get_num_replicas() if comm is not None else 1)
         self.replica_id = replica_id if replica_id is not None else (comm.get_replica_id() if comm is not None else 0)

@@ -70,7 +70,12 @@ def metis_partition_graph(nx_graph, num_ranks):
     return placement, nodes, edge_renumbering(list(nx_graph.edges()), nodes)
 
 
-def main(world_size: int = 4, mesh_level: int = 6, lat: int = 721, lon: int = 1440, out_dir: str = "graphcast_cache", placement: str = "multilevel"):
+def main(load_graph: str = "", mesh_level: int = 6, num_ranks: int = 0, world_size: int = 4, lat: int = 721, lon: int = 1440,
+         out_dir: str = "graphcast_cache", placement: str = "multilevel"):
+    """``load_graph`` / ``mesh_level`` / ``num_ranks`` are the reference's arguments (``preprocess.py:89``); the mesh is always
+    rebuilt here (a fraction of a second), so a pickled graph is not needed and ``load_graph`` is ignored.  ``num_ranks`` is an alias of
+    ``world_size``."""
+    world_size = int(num_ranks) or world_size
     gen = DistributedGraphCastGraphGenerator((lat, lon), mesh_level, placement=placement)
     g = gen.global_graph()
     grid_pl, mesh_pl = gen.placements(world_size)

@@ -62,7 +62,7 @@ def main(batch_size: int = 1, is_distributed: bool = False, test_run: bool = Fal
         mesh_level, lat, lon, iters = min(mesh_level, 3), min(lat, 46), min(lon, 90), min(iters, 3)
     cfg.model.mesh_level, cfg.model.hidden_dim, cfg.data.latlon_res = mesh_level, hidden_dim, (lat, lon)
     cdt = torch.bfloat16 if dev.type == "cuda" else torch.float32
-    gen = DistributedGraphCastGraphGenerator(cfg.data.latlon_res, cfg.model.mesh_level, cfg.model.multimesh, placement=placement)
+    gen = DistributedGraphCastGraphGenerator(cfg.data.latlon_res, cfg.model.mesh_level, multi=cfg.model.multimesh, placement=placement)
     sg = gen.shard(g_rank, g_world).to(dev, cdt)
     data = SyntheticWeatherDataset(cfg.model.input_grid_dim, cfg.data.latlon_res, num_samples=max(iters, 2),
                                    grid_rows=sg.grid_rows_global.cpu())

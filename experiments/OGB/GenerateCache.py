@@ -32,8 +32,11 @@ def generate_comm_plan(coo_list, offsets, rank, world_size, dest_offsets=None):
     return NCCLEdgeConditionedGraphCommPlan(rank=rank, world_size=world_size, source_graph_plan=sp, dest_graph_plan=dp)
 
 
-def main(dataset: str = "arxiv", world_size: int = 8, rank: int = 0, out_dir: str = "cache", scale: float = 1.0,
-         node_rank_placement_file: str = ""):
+def main(dset: str = "", world_size: int = 8, node_rank_placement_file: str = "", rank: int = 0, out_dir: str = "cache",
+         scale: float = 1.0, dataset: str = "arxiv"):
+    """Argument order of the reference (``GenerateCache.py:66``): ``dset`` (e.g. ``ogbn-arxiv``), ``world_size``,
+    ``node_rank_placement_file``; ``--dataset arxiv`` is the short form used by the other entry points here."""
+    dataset = dset or dataset
     name = {"arxiv": "ogbn-arxiv", "products": "ogbn-products"}.get(dataset, dataset)
     g, _, _, _ = _load_raw(name, "data", scale)
     V = int(g["num_nodes"])

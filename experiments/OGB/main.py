@@ -136,7 +136,7 @@ def main(backend: str = "nccl", dataset: str = "arxiv", epochs: int = 10, lr: fl
     comm, rank, world, dev = init_distributed(backend)
     TimingReport.init(comm, enabled=timing_report)
     placement = torch.load(node_rank_placement_file, weights_only=False) if node_rank_placement_file else None
-    ds = DGraphOGBDataset(dataset, comm, root_dir, placement, scale=scale, device=dev, partition=partition)
+    ds = DGraphOGBDataset(dataset, comm, placement, root_dir, scale=scale, device=dev, partition=partition)
     if rank == 0:
         print(f"{dataset}{' (synthetic stand-in)' if ds.synthetic else ''}: V={ds.num_nodes} E={ds.num_edges} world={world}")
     os.makedirs(log_dir, exist_ok=True)

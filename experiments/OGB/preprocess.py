@@ -17,9 +17,9 @@ from dgraph_b200.data.partition import bfs_blocks, contiguous_blocks, edge_cut_f
 from dgraph_b200.utils.cli import run_cli  # noqa: E402
 
 
-def add_opposite_edges(edge_index: torch.Tensor) -> torch.Tensor:
+def add_opposite_edges(edge_indices: torch.Tensor) -> torch.Tensor:
     """Symmetrise a ``[2, E]`` edge index and drop duplicates."""
-    e = torch.cat([edge_index, edge_index.flip(0)], dim=1)
+    e = torch.cat([edge_indices, edge_indices.flip(0)], dim=1)
     return torch.unique(e, dim=1)
 
 
@@ -82,7 +82,11 @@ def load_networkx_graph(dname):
         return pickle.load(f)
 
 
-def main(dataset: str = "arxiv", world_size: int = 8, out: str = "", method: str = "multilevel", scale: float = 1.0, root_dir: str = "data"):
+def main(dset_name: str = "", world_size: int = 8, out: str = "", method: str = "multilevel", scale: float = 1.0,
+         root_dir: str = "data", dataset: str = "arxiv"):
+    """``dset_name`` is the reference's (positional) argument, e.g. ``ogbn-arxiv`` (``preprocess.py:108``); ``--dataset arxiv`` is the
+    short form used by the other entry points here."""
+    dataset = dset_name or dataset
     name = {"arxiv": "ogbn-arxiv", "products": "ogbn-products"}.get(dataset, dataset)
     g, _, _, synthetic = _load_raw(name, root_dir, scale)
     V = int(g["num_nodes"])

@@ -19,10 +19,10 @@ def dist_print_ephemeral(msg: str, rank: int):
         print(msg, end="\r", flush=True)
 
 
-def calculate_accuracy(log_probs, labels) -> float:
+def calculate_accuracy(pred, labels) -> float:
     if labels.numel() == 0:
         return 0.0
-    return float((log_probs.argmax(1) == labels.reshape(-1)).float().mean() * 100.0)
+    return float((pred.argmax(1) == labels.reshape(-1)).float().mean() * 100.0)
 
 
 def safe_plot(x, ys, labels, title, path):

@@ -208,3 +208,25 @@ def test_graphcast_generator_dictionary_stages_are_consistent():
     assert sum(s.num_local_mesh for s in shards) == g.num_mesh and sum(s.num_local_grid for s in shards) == g.num_grid
     d = SyntheticWeatherDataset.generate_data(3, 4, (5, 6), base_temp=15.0, amplitude=10.0, noise_level=0.0)
     assert d.shape == (3, 4, 5, 6) and np.allclose(d[0, 0, :, 0], [5, 10, 15, 20, 25]) and np.allclose(d[0, 2] - d[0, 0], -1.0)
+
+
+def test_reference_constructor_orders_and_topology_patterns():
+    """Positional constructor orders of the reference's experiment classes, and ``build_graphcast_comm_patterns`` on a topology
+    record (the reference's calling form) giving the plans the generator builds itself."""
+    from dgraph_b200.data.graphcast_graph import DistributedGraphCastGraphGenerator as G, build_graphcast_comm_patterns
+    from dgraph_b200.utils.dist_utils import CommAwareDistributedSampler
+
+    gg = _load("GraphCast/data_utils/graphcast_graph.py")
+    grid = torch.zeros(19, 36, 2)
+    gen = G(grid, 2, 2, 1, 2)  # lat_lon_grid tensor, mesh_level, ranks_per_graph, rank, world_size
+    assert gen.lat_lon == (19, 36) and gen.rank == 1 and gen.world_size == 2 and gen.local_rank == 1
+    topo = gg.GraphCastTopology.from_generator(gen, 1, 2)
+    a = build_graphcast_comm_patterns(topo)
+    b = build_graphcast_comm_patterns(gen)  # rank / world size from the constructor
+    for name in ("grid2mesh", "mesh", "mesh2grid"):
+        pa, pb = getattr(a, name), getattr(b, name)
+        assert pa.num_local_vertices == pb.num_local_vertices and pa.num_halo_vertices == pb.num_halo_vertices
+        assert torch.equal(pa.send_offset, pb.send_offset) and torch.equal(pa.recv_offset, pb.recv_offset)
+        assert torch.equal(torch.sort(pa.halo_vertices_global).values, torch.sort(pb.halo_vertices_global).values)
+    ds = list(range(10))
+    assert list(CommAwareDistributedSampler(ds, None, False, 0, False, num_replicas=2, replica_id=1)) == [1, 3, 5, 7, 9]

@@ -190,9 +190,19 @@ class DistributedHeteroGraphDataset:
 class SyntheticHeterogeneousDataset(DistributedHeteroGraphDataset):
     """MAG240M-shaped random heterogeneous graph (``synthetic_dataset.py:29-199``)."""
 
-    def __init__(self, rank: int, world_size: int, num_papers: int = 32768, num_authors: int = 16384,
+    def __init__(self, rank, world_size=None, num_papers: int = 32768, num_authors: int = 16384,
                  num_institutions: int = 256, num_features: int = 16, num_classes: int = 153, seed: int = 0, comm=None,
                  cache_dir: Optional[str] = None, dtype=torch.float32):
+        """Two calling forms: ``(rank, world_size, num_papers, ...)`` and the reference's
+        ``(synthetic_config, comm, cached_comm_plans=None)`` (``synthetic_dataset.py:80-85``), where ``synthetic_config`` has the
+        attributes ``num_papers``, ``num_authors``, ``num_institutions``, ``num_features``, ``num_classes``."""
+        if hasattr(rank, "num_papers"):
+            cfg, comm = rank, (world_size if world_size is not None else comm)
+            cached = num_papers if isinstance(num_papers, str) else None  # third positional argument: plan-cache location
+            cache_dir = cache_dir or (os.path.dirname(cached) or "." if cached else None)
+            num_papers, num_authors, num_institutions = cfg.num_papers, cfg.num_authors, cfg.num_institutions
+            num_features, num_classes = cfg.num_features, cfg.num_classes
+            rank, world_size = comm.get_rank(), comm.get_world_size()
         g = torch.Generator().manual_seed(seed)
         n = [num_papers, num_authors, num_institutions]
 
@@ -245,10 +255,18 @@ class DGraph_MAG240M_Dataset(DistributedHeteroGraphDataset):
     papers' / affiliated authors' features (what the reference computes with ``torch_sparse``), ``"random"`` = unit normal of
     the same width (what the reference currently trains with: ``randn(..., 1)``, ``MAG240M_dataset.py:150-170``)."""
 
-    def __init__(self, rank, world_size, data_dir="data/MAG240M", comm=None, features: str = "random", feature_dim: int = 0,
+    def __init__(self, rank, world_size=None, data_dir="data/MAG240M", comm=None, features: str = "random", feature_dim: int = 0,
                  cache_dir: Optional[str] = None, dtype=torch.float32, seed: int = 0, paper_rank_mappings=None,
                  author_rank_mappings=None, institution_rank_mappings=None, **kw):
+        """Two calling forms: ``(rank, world_size, data_dir, comm=...)`` and the reference's
+        ``(comm, data_dir, comm_plan_only=True, paper_rank_mappings=None, ...)`` (``MAG240M_dataset.py:119-130``)."""
         from dgraph_b200.data.ogb_raw import MAG240MFiles, find_mag240m
+
+        if hasattr(rank, "get_rank"):  # reference form: the communicator comes first, the data directory second
+            comm = rank
+            if isinstance(world_size, str):
+                data_dir = world_size
+            rank, world_size = comm.get_rank(), comm.get_world_size()
 
         if find_mag240m(data_dir) is None:
             raise RuntimeError(f"no processed MAG240M files under {data_dir} (expected mag240m_kddcup2021/processed/...); there is "

@@ -230,3 +230,18 @@ def test_reference_constructor_orders_and_topology_patterns():
         assert torch.equal(torch.sort(pa.halo_vertices_global).values, torch.sort(pb.halo_vertices_global).values)
     ds = list(range(10))
     assert list(CommAwareDistributedSampler(ds, None, False, 0, False, num_replicas=2, replica_id=1)) == [1, 3, 5, 7, 9]
+
+
+def test_hetero_datasets_take_the_reference_constructor_form():
+    from dgraph_b200.data.hetero import SyntheticHeterogeneousDataset
+    from dgraph_b200.utils.dist_utils import SingleProcessDummyCommunicator
+
+    class Cfg:
+        num_papers, num_authors, num_institutions, num_features, num_classes = 64, 32, 4, 6, 9
+
+    comm = SingleProcessDummyCommunicator()
+    a = SyntheticHeterogeneousDataset(Cfg(), comm)
+    b = SyntheticHeterogeneousDataset(0, 1, 64, 32, 4, 6, 9)
+    assert a.num_nodes == b.num_nodes == [64, 32, 4] and a.num_classes == 9 and a.comm is comm
+    assert all(torch.equal(x, y) for x, y in zip(a.features, b.features)) and torch.equal(a.labels, b.labels)
+    assert torch.equal(a.get_mask("val"), a.get_mask("valid"))

@@ -35,26 +35,34 @@ class NVSHMEMBenchmark:
 
 
 def _mine(t, placement, rank):
+    """This rank's columns of an all-ranks ``[1, E]`` (or ``[1, E, F]``) tensor; a tensor that is already local passes through."""
+    if t.shape[1] != placement.shape[1]:
+        return t.contiguous()
     return t[:, placement[0] == rank].contiguous()
 
 
-def run_gather_benchmark(benchmark: NVSHMEMBenchmark, num_iters: int, graph_data):
-    """``graph_data``: a ``GatherGraphData`` holding the edges of ALL ranks (``graph_utils.py``); this rank's share is cut out."""
-    r = benchmark.rank
-    F = graph_data.vertex_data.shape[-1]
-    local = graph_data.vertex_data[graph_data.vertex_rank_mapping == r, :].view(1, -1, F).contiguous()
-    pl = graph_data.edge_rank_placement
-    return benchmark.benchmark_gather(local, _mine(graph_data.edge_src_rank, pl, r), _mine(graph_data.edge_indices, pl, r),
-                                      num_iters=num_iters)
+def _local_rows(graph_data, mapping, rank):
+    v = graph_data.vertex_data
+    F = v.shape[-1]
+    if v.dim() == 3 and (mapping.dim() == 1 or v.shape[1] != mapping.shape[-1]):
+        return v.contiguous()  # already this rank's [1, n, F]
+    return v[mapping == rank].view(1, -1, F).contiguous()
 
 
-def run_scatter_benchmark(benchmark: NVSHMEMBenchmark, num_iters: int, graph_data):
-    r = benchmark.rank
-    F = graph_data.vertex_data.shape[-1]
-    pl = graph_data.edge_rank_placement
-    local = graph_data.vertex_data[graph_data.data_rank_mapping == r].view(1, -1, F).contiguous()
-    return benchmark.benchmark_scatter(local, _mine(graph_data.edge_dest_rank, pl, r), _mine(graph_data.edge_indices, pl, r),
-                                       graph_data.num_local_vertices, num_iters=num_iters)
+def run_gather_benchmark(benchmark: NVSHMEMBenchmark, num_iters: int, gather_graph_data):
+    """``gather_graph_data``: a ``GatherGraphData`` -- this rank's share (``get_nvshmem_gather_benchmark_data``) or the record of
+    all ranks' edges (``get_nccl_gather_benchmark_data``), from which this rank's share is cut."""
+    r, g = benchmark.rank, gather_graph_data
+    pl = g.edge_rank_placement
+    return benchmark.benchmark_gather(_local_rows(g, g.vertex_rank_mapping, r), _mine(g.edge_src_rank, pl, r),
+                                      _mine(g.edge_indices, pl, r), num_iters=num_iters)
+
+
+def run_scatter_benchmark(benchmark: NVSHMEMBenchmark, num_iters: int, scatter_graph_data):
+    r, g = benchmark.rank, scatter_graph_data
+    pl = g.edge_rank_placement
+    return benchmark.benchmark_scatter(_mine(g.vertex_data, pl, r), _mine(g.edge_dest_rank, pl, r), _mine(g.edge_indices, pl, r),
+                                       g.num_local_vertices, num_iters=num_iters)
 
 
 def main():

@@ -92,13 +92,31 @@ def get_nccl_scatter_benchmark_data(sample_size, world_size, device, ranks_per_n
                             edge_dest_rank=target.to(device), edge_indices=target.clone().to(device), num_local_vertices=1)
 
 
-def get_nvshmem_gather_benchmark_data(sample_size, world_size, device, ranks_per_node=None, intra_node_only=False, **_):
-    """Same pattern; the one-sided engine takes the same tensors here (no separate symmetric-heap staging is needed)."""
-    return get_nccl_gather_benchmark_data(sample_size, world_size, device, ranks_per_node, intra_node_only)
+def _local_share(full, rank: int):
+    """Cut a rank's share out of an all-ranks record: its vertex rows as ``[1, n_local, F]`` and its edges as ``[1, E_local]``."""
+    mine = full.edge_rank_placement[0] == rank
+    return mine
 
 
-def get_nvshmem_scatter_benchmark_data(sample_size, world_size, device, ranks_per_node=None, intra_node_only=False, **_):
-    return get_nccl_scatter_benchmark_data(sample_size, world_size, device, ranks_per_node, intra_node_only)
+def get_nvshmem_gather_benchmark_data(sample_size, rank, world_size, device, ranks_per_node=None, intra_node_only=False):
+    """One-sided convention of the reference (``graph_utils.py:121-166``): the record holds THIS rank's vertex rows
+    ``[1, n_local, F]`` and the owner ranks / global ids of THIS rank's edges ``[1, E_local]``; ``edge_rank_placement`` stays the
+    all-ranks tensor."""
+    full = get_nccl_gather_benchmark_data(sample_size, world_size, device, ranks_per_node, intra_node_only)
+    mine = _local_share(full, rank)
+    F = full.vertex_data.shape[-1]
+    return GatherGraphData(vertex_data=full.vertex_data[full.vertex_rank_mapping == rank].view(1, -1, F),
+                           vertex_rank_mapping=full.vertex_rank_mapping, edge_rank_placement=full.edge_rank_placement,
+                           edge_src_rank=full.edge_src_rank[:, mine].contiguous(), edge_indices=full.edge_indices[:, mine].contiguous())
+
+
+def get_nvshmem_scatter_benchmark_data(sample_size, rank, world_size, device, ranks_per_node=None, intra_node_only=False):
+    """Scatter counterpart (``graph_utils.py:169-230``): this rank's edge rows ``[1, E_local, F]`` with their destinations."""
+    full = get_nccl_scatter_benchmark_data(sample_size, world_size, device, ranks_per_node, intra_node_only)
+    mine = _local_share(full, rank)
+    return ScatterGraphData(vertex_data=full.vertex_data[:, mine].contiguous(), data_rank_mapping=full.data_rank_mapping,
+                            edge_rank_placement=full.edge_rank_placement, edge_dest_rank=full.edge_dest_rank[:, mine].contiguous(),
+                            edge_indices=full.edge_indices[:, mine].contiguous(), num_local_vertices=full.num_local_vertices)
 
 
 def safe_create_dir(directory, rank):

@@ -61,6 +61,19 @@ def test_nccl_benchmark_object_runs_the_legacy_api():
     for r, (got, sg, ss) in enumerate(run_world(W, job2)):
         assert torch.allclose(got, gd.vertex_data[[j for j in range(W) if j != r]]) and sg == (2,) and ss == (2,)
 
+    # the one-sided generators hand every rank only its own share (reference graph_utils.py:121-230): same results
+    def job3(comm):
+        r = comm.get_rank()
+        lg = gu.get_nvshmem_gather_benchmark_data(F, r, W, "cpu")
+        ls = gu.get_nvshmem_scatter_benchmark_data(F, r, W, "cpu")
+        assert lg.vertex_data.shape == (1, 1, F) and lg.edge_indices.shape == (1, W - 1) and ls.vertex_data.shape == (1, W - 1, F)
+        b = nv.NVSHMEMBenchmark(comm)
+        got = comm.gather(lg.vertex_data, lg.edge_indices, lg.edge_src_rank)
+        return got[0], nv.run_gather_benchmark(b, 2, lg).shape, nv.run_scatter_benchmark(b, 2, ls).shape
+
+    for r, (got, sg, ss) in enumerate(run_world(W, job3)):
+        assert torch.allclose(got, gd.vertex_data[[j for j in range(W) if j != r]]) and sg == (2,) and ss == (2,)
+
 
 def test_graphcast_utils_and_preprocess_helpers():
     ut = _load("GraphCast/data_utils/utils.py")

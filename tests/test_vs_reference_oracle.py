@@ -484,3 +484,108 @@ def test_positional_signatures_of_the_reference_library_are_accepted():
                                 obj = shim
                         check(f"{modname}.{node.name}.{m.name}", m2, obj)
     assert not problems, "\n".join(problems)
+
+
+def test_positional_signatures_of_the_reference_experiment_modules_are_accepted():
+    """Argument-level parity for ``experiments/``: a positional call written against a reference function / method binds to the
+    parameter of the same name here.  Exemptions (with reasons) are listed; constructors with two calling forms are checked by
+    ``tests/test_experiment_helpers.py`` instead."""
+    import ast
+    import copy
+    import importlib
+    import inspect
+    import sys
+
+    ref = "/root/reference/experiments"
+    if not os.path.isdir(ref):
+        ref = os.path.join(ROOT, "baseline", "_ref", "experiments")
+    if not os.path.isdir(os.path.join(ref, "GraphCast")):
+        pytest.skip("reference experiments tree not available")
+    ours = os.path.join(ROOT, "experiments")
+    exempt = {
+        # private timing helpers of one script, rewritten around this package's static graph object
+        "GraphCast/microbenchmark_graphcast.py:load_data", "GraphCast/microbenchmark_graphcast.py:time_mesh_edge_block",
+        "OGB/main.py:_run_experiment",
+        # legacy cache plumbing (three cache objects + three file names upstream; one relation at a time here)
+        "OGB-LSC/CacheGenerator.py:get_cache",
+        "OGB-LSC/lsc_datasets/distributed_graph_dataset.py:DistributedHeteroGraphDataset._save_comm_plans",
+        "OGB-LSC/lsc_datasets/distributed_graph_dataset.py:DistributedHeteroGraphDataset._load_comm_plans",
+        "OGB-LSC/lsc_datasets/distributed_graph_dataset.py:DistributedHeteroGraphDataset._generate_comm_plans",
+        # autograd internals / static helper / legacy COO path with this package's keyword-only arguments
+        "OGB-LSC/RGAT.py:CommAwareGAT._calc_attention_messages", "OGB-LSC/RGAT.py:CommAwareGAT._forward_coo",
+        "OGB-LSC/distributed_layers.py:DistributedBN_Impl.forward", "OGB-LSC/distributed_layers.py:DistributedBN_Impl.backward",
+        "OGB-LSC/distributed_layers.py:DistributedBN_with_Recompute.forward",
+        "OGB-LSC/distributed_layers.py:DistributedBN_with_Recompute.backward",
+        # two calling forms, dispatched on the type of the first argument (tests/test_experiment_helpers.py)
+        "OGB-LSC/lsc_datasets/MAG240M_dataset.py:DGraph_MAG240M_Dataset.__init__",
+        "OGB-LSC/lsc_datasets/synthetic_dataset.py:SyntheticHeterogeneousDataset.__init__",
+        "OGB-LSC/lsc_datasets/distributed_graph_dataset.py:DistributedHeteroGraphDataset.__init__",
+    }
+
+    def load(path):
+        d = os.path.dirname(path)
+        extra = [d, os.path.dirname(d)]
+        for p in extra:
+            sys.path.insert(0, p)
+        try:
+            if os.path.basename(d) == "lsc_datasets":
+                return importlib.import_module("lsc_datasets." + os.path.basename(path)[:-3])
+            return _load_by_path(path, "_expsig_" + os.path.relpath(path, ours).replace(os.sep, "_").replace("-", "_")[:-3])
+        finally:
+            for p in extra:
+                sys.path.remove(p)
+
+    problems = []
+
+    def check(name, node, obj):
+        if name in exempt:
+            return
+        try:
+            sig = inspect.signature(obj)
+        except (TypeError, ValueError):
+            return
+        ps = list(sig.parameters.values())
+        pos = [p.name for p in ps if p.kind in (p.POSITIONAL_ONLY, p.POSITIONAL_OR_KEYWORD)]
+        names = {p.name for p in ps}
+        var_pos = any(p.kind == p.VAR_POSITIONAL for p in ps)
+        var_kw = any(p.kind == p.VAR_KEYWORD for p in ps)
+        for i, arg in enumerate(node.args.posonlyargs + node.args.args):
+            if i < len(pos):
+                if pos[i] != arg.arg:
+                    problems.append(f"{name}: parameter {i} is '{pos[i]}' here, '{arg.arg}' in the reference")
+            elif not var_pos and not (arg.arg in names or var_kw):
+                problems.append(f"{name}: no place for parameter {i} '{arg.arg}'")
+
+    for root, _, files in os.walk(ref):
+        for f in sorted(files):
+            rel = os.path.relpath(os.path.join(root, f), ref)
+            if not f.endswith(".py") or f == "__init__.py" or "/tests/" in "/" + rel or rel.startswith("NVSHMEM-Enabled"):
+                continue
+            mine = os.path.join(ours, rel)
+            if not os.path.exists(mine):
+                continue
+            tree = ast.parse(open(os.path.join(root, f)).read())
+            mod = load(mine)
+            for node in tree.body:
+                if isinstance(node, ast.FunctionDef) and hasattr(mod, node.name):
+                    check(f"{rel}:{node.name}", node, getattr(mod, node.name))
+                elif isinstance(node, ast.ClassDef) and hasattr(mod, node.name):
+                    cls = getattr(mod, node.name)
+                    for m in (b for b in node.body if isinstance(b, ast.FunctionDef)):
+                        if not hasattr(cls, m.name):
+                            continue
+                        obj, m2 = getattr(cls, m.name), copy.deepcopy(m)
+                        static = isinstance(inspect.getattr_static(cls, m.name), staticmethod)
+                        if not static and m2.args.args and m2.args.args[0].arg in ("self", "cls", "ctx"):
+                            m2.args.args = m2.args.args[1:]
+                            try:
+                                sig = inspect.signature(obj)
+                            except (TypeError, ValueError):
+                                continue
+                            ps = list(sig.parameters.values())
+                            if ps and ps[0].name in ("self", "cls", "ctx"):
+                                shim = lambda *a, **k: None  # noqa: E731
+                                shim.__signature__ = sig.replace(parameters=ps[1:])
+                                obj = shim
+                        check(f"{rel}:{node.name}.{m.name}", m2, obj)
+    assert not problems, "\n".join(problems)

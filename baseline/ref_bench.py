@@ -129,11 +129,11 @@ def run(args):
 
         e2e = None
         if not args.no_e2e:
-            def loop_e2e(k):
-                for _ in range(k):
-                    xd = xh.to(dev, non_blocking=True)
-                    yd = yh.to(dev, non_blocking=True)
-                    float(step(xd, yd).detach())
+            # the same host <-> device loop as our arm (harness code only: double-buffered H2D, loss read one step later)
+            from dgraph_b200.utils.e2e import make_e2e_loop
+
+            bufs = [(torch.empty_like(xh, device=dev), torch.empty_like(yh, device=dev)) for _ in range(2)]
+            loop_e2e = make_e2e_loop(step, (xh, yh), bufs, [])
 
             loop_e2e(2)
             ms_e2e = timed(loop_e2e, args.steps) / args.steps

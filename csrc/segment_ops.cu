@@ -8,8 +8,10 @@
 // Design: one sub-warp group (G lanes) owns one output row and walks its CSR segment; every lane keeps
 // 8 bf16 columns (one 16-byte load) in fp32 registers, so the reduction is atomic-free and deterministic.
 // Neighbour indices are loaded coalesced and broadcast with shuffles; UNROLL independent 16-byte row loads
-// are in flight per lane.  When HALO is set, neighbour rows >= n_local are read *directly from the owner
-// GPU's matrix* through NVLink peer pointers (pull), so no halo buffer is materialised.
+// are in flight per lane.  When HALO is set, a negative neighbour index names a row of ANOTHER rank's matrix
+// (~idx = owner << peer_shift | row): the lane group reads it *directly from the owner GPU* through the NVLink peer
+// pointer table (pull), in the same batch of loads as its local neighbours, so no halo buffer is materialised and
+// the NVLink latency overlaps the local gathers.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -55,25 +57,41 @@ struct SegParams {
   __nv_bfloat16* dp_out;
   int64_t ld_dp;
   int64_t dp_rows;
-  // halo pull: rows >= n_local of `src` live on peers
-  int64_t n_local;
-  const __nv_bfloat16* const* peer_base;  // [W] base pointer of the same matrix on every rank
-  const int* halo_owner;                  // [n_halo]
-  const int* halo_row;                    // [n_halo] row inside the owner's matrix
+  // SEG_MASKED_SUM / SEG_SUM: output rows r >= out_split go to out2[(r - out_split), :] (the CSC walk of a distributed layer writes
+  // the gradients of halo rows straight into the symmetric slot the owners reduce from; no copy)
+  __nv_bfloat16* out2;
+  int64_t ld_out2;
+  int64_t out_split;
+  // halo pull (HALO kernels): idx[k] < 0 encodes a remote row, ~idx[k] = (owner << peer_shift) | row in the owner's matrix
+  const __nv_bfloat16* const* peer_base;  // [world] base pointer of the same matrix on every rank
+  int world;
+  int peer_shift;
   uint32_t ld_peer_b;
   int rows_per_group;  // consecutive rows per lane group (set by launch_seg)
 };
 
+constexpr int kMaxPeers = 64;
+
 template <bool HALO>
-__device__ __forceinline__ const char* src_row(const SegParams& p, const char* src_lane, uint32_t lane_off, int j) {
+__device__ __forceinline__ const char* src_row(const SegParams& p, const char* const* s_peer, const char* src_lane,
+                                               uint32_t lane_off, int j) {
   if (HALO) {
-    if (j >= p.n_local) {
-      const int h = j - (int)p.n_local;
-      return reinterpret_cast<const char*>(p.peer_base[p.halo_owner[h]]) + (uint64_t)(uint32_t)p.halo_row[h] * p.ld_peer_b +
-             lane_off;
+    if (j < 0) {  // remote row: owner's base from the shared-memory copy of the peer table, no dependent global load
+      const uint32_t c = ~(uint32_t)j;
+      return s_peer[c >> p.peer_shift] + (uint64_t)(c & ((1u << p.peer_shift) - 1u)) * p.ld_peer_b + lane_off;
     }
   }
   return src_lane + (uint64_t)(uint32_t)j * p.ld_src_b;  // one IMAD.WIDE.U32
+}
+
+// HALO kernels issue ONE load form for local and remote rows (coherent, no L1 allocation, evict_last hint for the local L2; a peer
+// address bypasses the local L2 anyway), so the batch of UNROLL loads stays branch-free.
+__device__ __forceinline__ uint4 ldg_any_hint_v4(const void* p, uint64_t pol) {
+  uint4 r;
+  asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p), "l"(pol));
+  return r;
 }
 
 // SEG_ADD_RELU on packed bf16 pairs (two columns per 32-bit lane word): HADD2 + HMNMX2 + HSET2 replace per-column
@@ -144,8 +162,8 @@ __device__ __forceinline__ void seg_accumulate(const uint4& v, const uint4& v2, 
 // hardware block scheduler otherwise keeps all SMs inside one compact window of rows, which is what makes the evict_last L2
 // policy on the gathered rows pay.
 template <int MODE, int G, int NC, bool HALO, bool FULL, int AUX>
-__device__ __forceinline__ void seg_rows(const SegParams& p, int r, const int stride, const int n_rows, const int g,
-                                         const unsigned gmask) {
+__device__ __forceinline__ void seg_rows(const SegParams& p, const char* const* s_peer, int r, const int stride, const int n_rows,
+                                         const int g, const unsigned gmask) {
   constexpr int UNROLL = 4;
   constexpr bool USES_MASK = (MODE == SEG_ADD_RELU && AUX != 0) || MODE == SEG_MASKED_SUM;
   constexpr bool MAPPED = USES_MASK && AUX == 2;
@@ -236,11 +254,11 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, int r, const int st
         const int j = __shfl_sync(gmask, my_j, t0 + u, G);
         if (MODE == SEG_SUM) w[u] = __shfl_sync(gmask, my_w, t0 + u, G); else w[u] = 1.f;
         sl[u] = MAPPED ? __shfl_sync(gmask, my_s, t0 + u, G) : 0;
-        const char* row = src_row<HALO>(p, src_lane, g * 16, j);
+        const char* row = src_row<HALO>(p, s_peer, src_lane, g * 16, j);
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
           if (colok[c]) {
-            v[u][c] = HALO ? ldg_v4(row + c * G * 16) : ldg_hint_v4(row + c * G * 16, pol_keep);
+            v[u][c] = HALO ? ldg_any_hint_v4(row + c * G * 16, pol_keep) : ldg_hint_v4(row + c * G * 16, pol_keep);
             if (MODE == SEG_ADD_RELU_BWD) v2[u][c] = ldg_nc_v4(src2_lane + (uint64_t)(uint32_t)j * p.ld_src2_b + c * G * 16);
             if (MODE == SEG_MASKED_SUM)
               mb[u][c] = MAPPED ? __ldg(mask_lane + (int64_t)sl[u] * nchunk + c * G) : ldg_stream_u8(mp + u * nchunk + c * G);
@@ -265,11 +283,11 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, int r, const int st
       const int j = __shfl_sync(gmask, my_j, t0, G);
       const float w = (MODE == SEG_SUM) ? __shfl_sync(gmask, my_w, t0, G) : 1.f;
       const int sl = MAPPED ? __shfl_sync(gmask, my_s, t0, G) : 0;
-      const char* row = src_row<HALO>(p, src_lane, g * 16, j);
+      const char* row = src_row<HALO>(p, s_peer, src_lane, g * 16, j);
 #pragma unroll
       for (int c = 0; c < NC; ++c) {
         if (colok[c]) {
-          const uint4 v = HALO ? ldg_v4(row + c * G * 16) : ldg_hint_v4(row + c * G * 16, pol_keep);
+          const uint4 v = HALO ? ldg_any_hint_v4(row + c * G * 16, pol_keep) : ldg_hint_v4(row + c * G * 16, pol_keep);
           uint4 v2 = make_uint4(0, 0, 0, 0);
           uint32_t mb = 0, mout = 0;
           if (MODE == SEG_ADD_RELU_BWD) v2 = ldg_nc_v4(src2_lane + (uint64_t)(uint32_t)j * p.ld_src2_b + c * G * 16);
@@ -292,7 +310,9 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, int r, const int st
 #pragma unroll
         for (int t = 0; t < 8; ++t) acc[c][t] *= scale;
       }
-      stg_cs_v4(p.out + (int64_t)r * p.ld_out + colo, pack8(acc[c]));
+      __nv_bfloat16* orow = p.out + (int64_t)r * p.ld_out;
+      if ((MODE == SEG_MASKED_SUM || MODE == SEG_SUM) && r >= p.out_split) orow = p.out2 + (int64_t)(r - p.out_split) * p.ld_out2;
+      stg_cs_v4(orow + colo, pack8(acc[c]));
       if (MODE == SEG_MASKED_SUM && p.dp_out && r < p.dp_rows) {
         float gr[8];
         unpack8(ldg_nc_v4(reinterpret_cast<const char*>(p.src) + (uint64_t)r * p.ld_src_b + colo * 2), gr);
@@ -323,7 +343,12 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, int r, const int st
 }
 
 template <int MODE, int G, int NC, bool HALO>
-__global__ void __launch_bounds__(256, (NC == 1 && !HALO) ? (MODE == SEG_SUM ? 5 : 4) : 1) seg_reduce_kernel(const SegParams p) {
+__global__ void __launch_bounds__(256, (NC == 1) ? (MODE == SEG_SUM ? 5 : 4) : 1) seg_reduce_kernel(const SegParams p) {
+  __shared__ const char* s_peer[HALO ? kMaxPeers : 1];
+  if (HALO) {
+    if ((int)threadIdx.x < p.world) s_peer[threadIdx.x] = reinterpret_cast<const char*>(p.peer_base[threadIdx.x]);
+    __syncthreads();
+  }
   const int lane = threadIdx.x & 31;
   const int g = lane & (G - 1);
   const int sub = lane / G;
@@ -337,17 +362,17 @@ __global__ void __launch_bounds__(256, (NC == 1 && !HALO) ? (MODE == SEG_SUM ? 5
   if (MODE == SEG_ADD_RELU || MODE == SEG_MASKED_SUM) {
     const int aux = p.mask == nullptr ? 0 : (p.slot_map ? 2 : 1);
     if (full) {
-      if (aux == 2) seg_rows<MODE, G, NC, HALO, true, 2>(p, r, stride, r_end, g, gmask);
-      else if (aux == 1) seg_rows<MODE, G, NC, HALO, true, 1>(p, r, stride, r_end, g, gmask);
-      else if (MODE == SEG_ADD_RELU) seg_rows<MODE, G, NC, HALO, true, 0>(p, r, stride, r_end, g, gmask);
+      if (aux == 2) seg_rows<MODE, G, NC, HALO, true, 2>(p, s_peer, r, stride, r_end, g, gmask);
+      else if (aux == 1) seg_rows<MODE, G, NC, HALO, true, 1>(p, s_peer, r, stride, r_end, g, gmask);
+      else if (MODE == SEG_ADD_RELU) seg_rows<MODE, G, NC, HALO, true, 0>(p, s_peer, r, stride, r_end, g, gmask);
     } else {
-      if (aux == 2) seg_rows<MODE, G, NC, HALO, false, 2>(p, r, stride, r_end, g, gmask);
-      else if (aux == 1) seg_rows<MODE, G, NC, HALO, false, 1>(p, r, stride, r_end, g, gmask);
-      else if (MODE == SEG_ADD_RELU) seg_rows<MODE, G, NC, HALO, false, 0>(p, r, stride, r_end, g, gmask);
+      if (aux == 2) seg_rows<MODE, G, NC, HALO, false, 2>(p, s_peer, r, stride, r_end, g, gmask);
+      else if (aux == 1) seg_rows<MODE, G, NC, HALO, false, 1>(p, s_peer, r, stride, r_end, g, gmask);
+      else if (MODE == SEG_ADD_RELU) seg_rows<MODE, G, NC, HALO, false, 0>(p, s_peer, r, stride, r_end, g, gmask);
     }
   } else {
-    if (full) seg_rows<MODE, G, NC, HALO, true, 0>(p, r, stride, r_end, g, gmask);
-    else seg_rows<MODE, G, NC, HALO, false, 0>(p, r, stride, r_end, g, gmask);
+    if (full) seg_rows<MODE, G, NC, HALO, true, 0>(p, s_peer, r, stride, r_end, g, gmask);
+    else seg_rows<MODE, G, NC, HALO, false, 0>(p, s_peer, r, stride, r_end, g, gmask);
   }
 }
 
@@ -366,6 +391,7 @@ static int launch_seg(const SegParams& p, cudaStream_t s) {
   SegParams q = p;
   q.rows_per_group = rows_per_group;
   if (q.ptr_end == nullptr) q.ptr_end = q.ptr + 1;
+  if (q.out2 == nullptr) q.out_split = q.n_rows;
 #define DGB_LAUNCH(G, NC)                                                                 \
   do {                                                                                    \
     const int64_t rows_per_block = (int64_t)warps_per_block * (32 / (G)) * rows_per_group; \
@@ -412,20 +438,28 @@ static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t
 static inline bool fits32(int64_t v) { return v >= 0 && v < (int64_t(1) << 32); }
 
 // out[r,:] = (mean ? 1/deg : 1) * sum_{k in seg r} w[k] * src[idx[k],:]          (bf16 in/out, fp32 accumulate)
-// Halo-pull variant: rows >= n_local are fetched from peer_base[halo_owner[h]] + halo_row[h]*ld_peer.
+// Pull variant (peer_base != null): idx[k] < 0 names a remote row, ~idx[k] = (owner << peer_shift) | row, fetched from
+// peer_base[owner] + row * ld_peer inside the kernel.  out2 (optional): rows >= out_split are written to out2[r - out_split].
+static inline bool peer_args_ok(const void* const* peer_base, int world, int peer_shift, int64_t ld_peer) {
+  if (!peer_base) return true;
+  return world >= 1 && world <= kMaxPeers && peer_shift >= 1 && peer_shift <= 30 && ((int64_t)world << peer_shift) <= ((int64_t)1 << 31) &&
+         ld_peer % 8 == 0 && fits32(ld_peer * 2);
+}
+
 DGB_API int dgb_seg_sum(const int* ptr, const int* idx, int64_t n_rows, int H, const void* src, int64_t ld_src,
-                        const float* slot_w, int mean, void* out, int64_t ld_out, int64_t n_local,
-                        const void* const* peer_base, const int* halo_owner, const int* halo_row, int64_t ld_peer,
-                        void* stream) {
-  if (H % 8 || ld_src % 8 || ld_out % 8 || !aligned16(src) || !aligned16(out)) return (int)cudaErrorInvalidValue;
+                        const float* slot_w, int mean, void* out, int64_t ld_out, const void* const* peer_base, int world,
+                        int peer_shift, int64_t ld_peer, void* out2, int64_t ld_out2, int64_t out_split, void* stream) {
+  if (H % 8 || ld_src % 8 || ld_out % 8 || !aligned16(src) || !aligned16(out) || (out2 && (ld_out2 % 8 || !aligned16(out2))))
+    return (int)cudaErrorInvalidValue;
   SegParams p{};
   p.ptr = ptr; p.idx = idx; p.n_rows = n_rows; p.H = H;
-  if (!fits32(ld_src * 2) || !fits32(ld_peer * 2)) return (int)cudaErrorInvalidValue;
+  if (!fits32(ld_src * 2) || !peer_args_ok(peer_base, world, peer_shift, ld_peer)) return (int)cudaErrorInvalidValue;
   p.src = (const __nv_bfloat16*)src; p.ld_src_b = (uint32_t)(ld_src * 2);
   p.slot_w = slot_w; p.mean = mean;
   p.out = (__nv_bfloat16*)out; p.ld_out = ld_out;
-  p.n_local = n_local; p.peer_base = (const __nv_bfloat16* const*)peer_base;
-  p.halo_owner = halo_owner; p.halo_row = halo_row; p.ld_peer_b = (uint32_t)(ld_peer * 2);
+  p.out2 = (__nv_bfloat16*)out2; p.ld_out2 = ld_out2; p.out_split = out_split;
+  p.peer_base = (const __nv_bfloat16* const*)peer_base; p.world = world; p.peer_shift = peer_shift;
+  p.ld_peer_b = (uint32_t)(ld_peer * 2);
   return peer_base ? launch_seg<SEG_SUM, true>(p, (cudaStream_t)stream) : launch_seg<SEG_SUM, false>(p, (cudaStream_t)stream);
 }
 
@@ -433,36 +467,34 @@ DGB_API int dgb_seg_sum(const int* ptr, const int* idx, int64_t n_rows, int H, c
 // mask_slot_map (optional): mask row of edge slot k is mask_slot_map[k] instead of k -- pass the CSR->CSC slot permutation so
 // that the backward CSC walk (dgb_seg_masked_sum with slot_map = null) streams the mask rows sequentially.
 // ptr_end (optional, null = ptr + 1) and accumulate: walk only slots [ptr[r], ptr_end[r]) of every row and, with accumulate = 1,
-// add to the out / cnt rows an earlier launch produced.  Two launches -- local-neighbour part while the halo rows are still
-// in flight over NVLink, halo-neighbour part afterwards -- give the same result as one launch over the whole rows (up to one
-// extra bf16 rounding of out).
+// add to the out / cnt rows an earlier launch produced.
+// Pull variant (peer_base != null): Q rows with idx[k] < 0 are read from the owner GPU inside the kernel (see dgb_seg_sum); this is
+// the fused halo exchange + aggregation of a distributed GraphConv layer (no halo buffer, no exchange kernel).
 DGB_API int dgb_seg_add_relu_fwd_ex(const int* ptr, const int* ptr_end, const int* idx, int64_t n_rows, int H, const void* P,
                                     int64_t ld_p, const void* Q, int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt,
                                     int64_t ld_cnt, unsigned char* mask, const int* mask_slot_map, int accumulate,
-                                    int64_t n_local, const void* const* peer_base, const int* halo_owner,
-                                    const int* halo_row, int64_t ld_peer, void* stream) {
+                                    const void* const* peer_base, int world, int peer_shift, int64_t ld_peer, void* stream) {
   if (H % 8 || ld_p % 8 || ld_q % 8 || ld_out % 8 || (cnt && ld_cnt % 8) || !aligned16(P) || !aligned16(Q) ||
       !aligned16(out))
     return (int)cudaErrorInvalidValue;
   SegParams p{};
   p.ptr = ptr; p.ptr_end = ptr_end; p.accumulate = accumulate; p.idx = idx; p.n_rows = n_rows; p.H = H;
-  if (!fits32(ld_q * 2) || !fits32(ld_peer * 2)) return (int)cudaErrorInvalidValue;
+  if (!fits32(ld_q * 2) || !peer_args_ok(peer_base, world, peer_shift, ld_peer)) return (int)cudaErrorInvalidValue;
   p.src = (const __nv_bfloat16*)Q; p.ld_src_b = (uint32_t)(ld_q * 2);
   p.rowop = (const __nv_bfloat16*)P; p.ld_rowop = ld_p;
   p.out = (__nv_bfloat16*)out; p.ld_out = ld_out; p.cnt = cnt; p.ld_cnt = ld_cnt; p.mask = mask;
   p.slot_map = mask ? mask_slot_map : nullptr;
-  p.n_local = n_local; p.peer_base = (const __nv_bfloat16* const*)peer_base;
-  p.halo_owner = halo_owner; p.halo_row = halo_row; p.ld_peer_b = (uint32_t)(ld_peer * 2);
+  p.peer_base = (const __nv_bfloat16* const*)peer_base; p.world = world; p.peer_shift = peer_shift;
+  p.ld_peer_b = (uint32_t)(ld_peer * 2);
   return peer_base ? launch_seg<SEG_ADD_RELU, true>(p, (cudaStream_t)stream)
                    : launch_seg<SEG_ADD_RELU, false>(p, (cudaStream_t)stream);
 }
 
 DGB_API int dgb_seg_add_relu_fwd(const int* ptr, const int* idx, int64_t n_rows, int H, const void* P, int64_t ld_p,
                                  const void* Q, int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt,
-                                 int64_t ld_cnt, unsigned char* mask, int64_t n_local, const void* const* peer_base,
-                                 const int* halo_owner, const int* halo_row, int64_t ld_peer, void* stream) {
+                                 int64_t ld_cnt, unsigned char* mask, void* stream) {
   return dgb_seg_add_relu_fwd_ex(ptr, nullptr, idx, n_rows, H, P, ld_p, Q, ld_q, out, ld_out, cnt, ld_cnt, mask, nullptr, 0,
-                                 n_local, peer_base, halo_owner, halo_row, ld_peer, stream);
+                                 nullptr, 0, 0, 0, stream);
 }
 
 // dQ[j,:] = sum_{k in CSC seg j} (P[row[k],:] + Q[j,:] > 0) ? dOut[row[k],:] : 0       (transposed walk)
@@ -483,12 +515,14 @@ DGB_API int dgb_seg_add_relu_bwd(const int* colptr, const int* row, int64_t n_au
 // dQ[j,:] = sum_{k in CSC seg j} mask[slot_map[k]] ? dOut[row[k],:] : 0, with the ReLU bit masks the forward kernel saved
 // (one byte per edge slot and 8-column chunk): one row gather per edge instead of two, no recomputation.  slot_map = null
 // means the mask rows are already in this walk's slot order (forward used dgb_seg_add_relu_fwd_mapped).  When dP is given,
-// rows j < dp_rows also write dP[j,:] = dOut[j,:] * cnt[j,:] in the same pass.
+// rows j < dp_rows also write dP[j,:] = dOut[j,:] * cnt[j,:] in the same pass.  dQ2 (optional): rows j >= dq_split (the halo rows of
+// a distributed layer) are written to dQ2[j - dq_split, :] -- the symmetric slot their owners pull-reduce from.
 DGB_API int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slot_map, const unsigned char* mask,
                                int64_t n_aug, int H, const void* dOut, int64_t ld_g, void* dQ, int64_t ld_dq,
                                const unsigned short* cnt, int64_t ld_cnt, void* dP, int64_t ld_dp, int64_t dp_rows,
-                               void* stream) {
-  if (H % 8 || ld_g % 8 || ld_dq % 8 || !fits32(ld_g * 2) || !mask || (dP && (ld_dp % 8 || ld_cnt % 8 || !cnt)))
+                               void* dQ2, int64_t ld_dq2, int64_t dq_split, void* stream) {
+  if (H % 8 || ld_g % 8 || ld_dq % 8 || !fits32(ld_g * 2) || !mask || (dP && (ld_dp % 8 || ld_cnt % 8 || !cnt)) ||
+      (dQ2 && (ld_dq2 % 8 || !aligned16(dQ2))))
     return (int)cudaErrorInvalidValue;
   SegParams p{};
   p.ptr = colptr; p.idx = row; p.n_rows = n_aug; p.H = H;
@@ -497,6 +531,7 @@ DGB_API int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slo
   p.out = (__nv_bfloat16*)dQ; p.ld_out = ld_dq;
   p.cnt = const_cast<unsigned short*>(cnt); p.ld_cnt = ld_cnt;
   p.dp_out = (__nv_bfloat16*)dP; p.ld_dp = ld_dp; p.dp_rows = dP ? dp_rows : 0;
+  p.out2 = (__nv_bfloat16*)dQ2; p.ld_out2 = ld_dq2; p.out_split = dq_split;
   return launch_seg<SEG_MASKED_SUM, false>(p, (cudaStream_t)stream);
 }
 

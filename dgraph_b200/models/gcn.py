@@ -10,6 +10,11 @@ B200 formulation (``fused=True``): ``W = [W_i | W_j]`` so ``W [x_i; x_j] + b = P
 ``P = x_local W_i^T + b`` and ``Q = x_aug W_j^T`` -- two node-level tcgen05 GEMMs (25x fewer FLOPs than the per-edge
 GEMM at ogbn-products' average degree) followed by ONE fused gather-add-ReLU-segment-sum kernel; no ``[E, *]``
 tensor exists in forward or backward.  ``fused=False`` is the literal reference formulation (oracle).
+
+With several ranks on the peer-memory engine the exchange is part of the layer (``ops/graphconv.py::_GraphConvPullQ``): a layer whose
+input needs a gradient (or is at least as wide as the layer) projects its owned rows straight into the symmetric slot and the
+aggregation kernel pulls the remote ``Q`` rows over NVLink while it reduces; the first layer (static, narrow input features)
+exchanges the features themselves -- without a copy when they live in ``HaloExchange.symmetric_rows``.
 """
 from __future__ import annotations
 
@@ -27,9 +32,9 @@ from dgraph_b200.parallel.kernel_plan import MAX_COUNTED_DEGREE, GraphKernelPlan
 from dgraph_b200.utils.timing import TimingReport
 
 
-# "0" (default): exchange features, project local + halo rows.  "1": the second convolution exchanges projected rows instead
-# (GraphConvLayer.forward_exchange_q).  "all": both convolutions.  Not yet measured on hardware.
-_QPULL = os.environ.get("DGRAPH_B200_GCN_QPULL", "0")
+# Debug / oracle switch: "auto" (default, rule in GraphConvLayer.exchanges_projected_rows), "x" = always exchange the input
+# features (the reference's order of operations), "q" = always exchange the projected rows.
+_EXCHANGE = os.environ.get("DGRAPH_B200_GCN_EXCHANGE", "auto")
 
 
 class GraphConvLayer(nn.Module):
@@ -100,15 +105,30 @@ class GraphConvLayer(nn.Module):
         return graphconv_aggregate(P, Q, kp)
 
 
-    def forward_exchange_q(self, x_local, comm_pattern, exchanger, kp: Optional[GraphKernelPlan] = None):
-        """Same layer with the exchange moved behind the projection (opt-in, ``DGRAPH_B200_GCN_QPULL``): every rank projects only
-        the rows it owns, ``Q = x W_j^T`` travels instead of ``x``, and the aggregation reads ``cat([Q_local, Q_halo])``.  Halo rows
-        then cost no GEMM in forward, no ``dX`` GEMM and no weight-gradient work in backward (their ``dQ`` is pull-reduced on the
-        owner first); the price is that the exchanged rows are ``H`` wide, so this pays where ``F_in >= H``."""
+    def exchanges_projected_rows(self, x_local) -> bool:
+        """Which rows travel.  Exchanging ``Q = x W_j^T`` (``H`` wide) instead of ``x`` removes every halo-row GEMM (forward ``Q``,
+        backward ``dX`` and half of ``dW``) but needs the transposed exchange of ``dQ`` in backward; exchanging ``x`` of a layer
+        whose input needs no gradient (the first layer) has no backward exchange at all.  So: projected rows when the input needs
+        a gradient or is at least as wide as the layer, features otherwise."""
+        if _EXCHANGE in ("x", "q"):
+            return _EXCHANGE == "q"
+        return bool(x_local.requires_grad) or x_local.shape[1] >= self.conv.weight.shape[0]
+
+    def forward_exchange_q(self, x_local, comm_pattern, exchanger, kp: Optional[GraphKernelPlan] = None, tag=0):
+        """Same layer with the exchange moved behind the projection: every rank projects only the rows it owns, ``Q = x W_j^T``
+        travels instead of ``x``.  On the peer-memory engine this is ONE autograd node whose kernels do the exchange themselves
+        (``ops/graphconv.py::graphconv_pull_q``); on the other engines (CPU / gloo / NCCL all-to-all) it is the same algebra through
+        ``exchanger.augmented``, which also serves as the oracle of the fused node."""
         n = x_local.shape[0]
         if kp is None:
             kp = comm_pattern.kernel_plan(x_local.device)
         F_in = self.conv.weight.shape[1] // 2
+        engine = exchanger._fused_engine(x_local) if hasattr(exchanger, "_fused_engine") else None
+        if (engine is not None and engine.get_world_size() > 1 and self.conv.weight.shape[0] % 8 == 0
+                and kp.max_row_degree() <= MAX_COUNTED_DEGREE):
+            from dgraph_b200.ops.graphconv import graphconv_pull_q
+
+            return graphconv_pull_q(x_local, self.conv.weight, self.conv.bias, kp, F_in, engine, comm_pattern, tag)
         W = self.conv.weight.to(x_local.dtype)
         w_i, w_j = W[:, :F_in], W[:, F_in:2 * F_in]
         pad = x_local.shape[1] - F_in
@@ -145,22 +165,16 @@ class CommAwareGCN(nn.Module):
         kp = comm_pattern.kernel_plan(x.device) if self.conv1.fused else None
         edges = comm_pattern.local_edge_list
         defer = self.conv1.fused  # the fused layer overlaps its local work with the in-flight halo rows (ops/_pending.py)
-        if self.conv1.fused and _QPULL == "all":
-            with TimingReport("process-1"):
-                x = self.conv1.forward_exchange_q(x, comm_pattern, self.halo_exchanger, kp)
-        else:
-            with TimingReport("feature-exchange-1"):
-                aug = self.halo_exchanger.augmented(x, comm_pattern, defer=defer)
-            with TimingReport("process-1"):
-                x = self.conv1(aug, edges, n, kernel_plan=kp)
-        if self.conv2.fused and _QPULL in ("1", "all"):  # opt-in: exchange the projected rows instead of the features
-            with TimingReport("process-2"):
-                x = self.conv2.forward_exchange_q(x, comm_pattern, self.halo_exchanger, kp)
-        else:
-            with TimingReport("feature-exchange-2"):
-                aug = self.halo_exchanger.augmented(x, comm_pattern, defer=defer)
-            with TimingReport("process-2"):
-                x = self.conv2(aug, edges, n, kernel_plan=kp)
+        multi = comm_pattern.world_size > 1
+        for li, conv in enumerate((self.conv1, self.conv2), start=1):
+            if conv.fused and multi and conv.exchanges_projected_rows(x):
+                with TimingReport(f"process-{li}"):  # the exchange happens inside the layer's kernels
+                    x = conv.forward_exchange_q(x, comm_pattern, self.halo_exchanger, kp, tag=li)
+            else:
+                with TimingReport(f"feature-exchange-{li}"):
+                    aug = self.halo_exchanger.augmented(x, comm_pattern, defer=defer)
+                with TimingReport(f"process-{li}"):
+                    x = conv(aug, edges, n, kernel_plan=kp)
         with TimingReport("final-fc"):
             x = linear(x, self.fc.weight.to(x.dtype), self.fc.bias.to(x.dtype))
         return x

@@ -5,8 +5,6 @@ pull of the neighbour rows, ONE bf16 CSR mean-aggregation kernel (``ops.segment_
 gather-GEMM over the two un-concatenated sources ``[x_local | agg]``."""
 from __future__ import annotations
 
-import os
-
 import torch
 import torch.nn as nn
 
@@ -50,10 +48,13 @@ class CommAwareSAGE(nn.Module):
         n = x.shape[0]
         kp = comm_pattern.kernel_plan(x.device)
         engine = getattr(self.comm, "engine", None)
-        fused_pull = (os.environ.get("DGRAPH_B200_FUSED_PULL", "0") == "1" and hasattr(engine, "aggregate_pull")
-                      and x.is_cuda and x.dtype == torch.bfloat16)
+        # peer-memory engine, several ranks: remote neighbour rows are read inside the aggregation kernel (no halo buffer, no exchange
+        # kernel) unless the graph re-reads every halo row so often that one pull into local memory is cheaper (engine.pull_mode)
+        fused_pull = (hasattr(engine, "aggregate_pull") and x.is_cuda and x.dtype == torch.bfloat16 and comm_pattern.world_size > 1
+                      and (x.shape[1] * 2) % 16 == 0
+                      and engine.pull_mode(engine.pattern_info(comm_pattern), kp) == "kernel")
         for conv in self.convs:
-            if fused_pull:  # remote neighbour rows are read inside the aggregation kernel; no halo buffer at all
+            if fused_pull:
                 x = conv(x, kp, n, act="relu", agg=engine.aggregate_pull(x, comm_pattern, mean=True))
             else:
                 x = conv(self.halo_exchanger.augmented(x, comm_pattern), kp, n, act="relu")

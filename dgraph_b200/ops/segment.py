@@ -72,16 +72,17 @@ def _ld(t: torch.Tensor) -> int:
     return t.stride(0)
 
 
-def _native_seg_sum(ptr, idx, n_rows, src, slot_w, mean, halo=None):
+def _native_seg_sum(ptr, idx, n_rows, src, slot_w, mean, peer=None, out=None, out2=None, out_split=0):
+    """``peer = (pointer table [W], W, shift, ld_peer)``: ``idx`` is a ``GraphKernelPlan.col_peer(shift)`` array and negative entries are
+    read from the owner rank inside the kernel.  ``out2``: rows ``>= out_split`` go to ``out2[r - out_split]`` (a symmetric slot)."""
     H = src.shape[1]
-    out = torch.empty((n_rows, H), dtype=torch.bfloat16, device=src.device)
-    peer = halo_owner = halo_row = None
-    n_local, ld_peer = src.shape[0], 0
-    if halo is not None:
-        peer, halo_owner, halo_row, n_local, ld_peer = halo
+    if out is None:
+        out = torch.empty((n_rows if out2 is None else out_split, H), dtype=torch.bfloat16, device=src.device)
+    table, world, shift, ld_peer = (None, 0, 0, 0) if peer is None else peer
     N.check(N.lib().dgb_seg_sum(N.ptr(ptr), N.ptr(idx), N.i64(n_rows), N.i32(H), N.ptr(src), N.i64(_ld(src)),
-                                N.ptr(slot_w), N.i32(1 if mean else 0), N.ptr(out), N.i64(_ld(out)), N.i64(n_local),
-                                N.ptr(peer), N.ptr(halo_owner), N.ptr(halo_row), N.i64(ld_peer), N.stream()),
+                                N.ptr(slot_w), N.i32(1 if mean else 0), N.ptr(out), N.i64(_ld(out)), N.ptr(table), N.i32(world),
+                                N.i32(shift), N.i64(ld_peer), N.ptr(out2), N.i64(0 if out2 is None else _ld(out2)),
+                                N.i64(out_split), N.stream()),
             "dgb_seg_sum")
     N.count_launch()
     return out
@@ -98,28 +99,28 @@ def _mean_bwd_weights(kp: GraphKernelPlan):
 
 class _SegSum(Function):
     @staticmethod
-    def forward(ctx, xaug, kp, mean, halo):
+    def forward(ctx, xaug, kp, mean):
         ctx.kp, ctx.mean = kp, mean
-        return _native_seg_sum(kp.rowptr, kp.col, kp.num_local, xaug, None, mean, halo)
+        return _native_seg_sum(kp.rowptr, kp.col, kp.num_local, xaug, None, mean)
 
     @staticmethod
     def backward(ctx, g):
         kp = ctx.kp
         w = _mean_bwd_weights(kp) if ctx.mean else None
         gx = _native_seg_sum(kp.colptr, kp.row, kp.num_aug, g.contiguous(), w, False)
-        return gx, None, None, None
+        return gx, None, None
 
 
-def segment_sum(xaug: torch.Tensor, kp: GraphKernelPlan, mean: bool = False, halo=None) -> torch.Tensor:
+def segment_sum(xaug: torch.Tensor, kp: GraphKernelPlan, mean: bool = False) -> torch.Tensor:
     """``out[i] = sum_{j in N(i)} xaug[j]`` (``mean=True`` divides by the degree).  ``xaug = cat([local, halo])``."""
     if xaug.is_cuda and xaug.dtype == torch.bfloat16:
         N.lib()
-        return _SegSum.apply(xaug if xaug.stride(1) == 1 else xaug.contiguous(), kp, mean, halo)
+        return _SegSum.apply(xaug if xaug.stride(1) == 1 else xaug.contiguous(), kp, mean)
     return segment_sum_ref(xaug, kp, mean)
 
 
-def segment_mean(xaug, kp, halo=None):
-    return segment_sum(xaug, kp, mean=True, halo=halo)
+def segment_mean(xaug, kp):
+    return segment_sum(xaug, kp, mean=True)
 
 
 def _check_degree(kp: GraphKernelPlan) -> None:
@@ -147,7 +148,7 @@ class _GraphConvAgg(Function):
         N.check(N.lib().dgb_seg_add_relu_fwd_ex(
             N.ptr(kp.rowptr), N.ptr(None), N.ptr(kp.col), N.i64(n), N.i32(H), N.ptr(P), N.i64(_ld(P)), N.ptr(Qaug),
             N.i64(_ld(Qaug)), N.ptr(out), N.i64(H), N.ptr(cnt), N.i64(H), N.ptr(mask), N.ptr(smap), N.i32(0),
-            N.i64(Qaug.shape[0]), N.ptr(None), N.ptr(None), N.ptr(None), N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
+            N.ptr(None), N.i32(0), N.i32(0), N.i64(0), N.stream()), "dgb_seg_add_relu_fwd")
         ctx.mask_csc = smap is not None
         N.count_launch()
         if mask is not None:
@@ -181,7 +182,8 @@ class _GraphConvAgg(Function):
             N.check(N.lib().dgb_seg_masked_sum(
                 N.ptr(colptr), N.ptr(row), N.ptr(None if ctx.mask_csc else slot_map), N.ptr(mask),
                 N.i64(kp.num_aug), N.i32(H), N.ptr(g),
-                N.i64(H), N.ptr(dQ), N.i64(H), N.ptr(None), N.i64(0), N.ptr(None), N.i64(0), N.i64(0), N.stream()),
+                N.i64(H), N.ptr(dQ), N.i64(H), N.ptr(None), N.i64(0), N.ptr(None), N.i64(0), N.i64(0), N.ptr(None), N.i64(0),
+                N.i64(0), N.stream()),
                 "dgb_seg_masked_sum")
             N.count_launch()
         elif ctx.needs_input_grad[1]:

@@ -18,6 +18,7 @@ from typing import Iterable, Optional
 import torch
 
 from dgraph_b200.ops import _native as N
+from dgraph_b200.ops import _wcache
 
 
 class FusedAdam(torch.optim.Optimizer):
@@ -92,6 +93,7 @@ class FusedAdam(torch.optim.Optimizer):
     @torch.no_grad()
     def step(self, closure=None):
         loss = closure() if closure is not None else None
+        _wcache.bump()  # the kernels below rewrite the parameters behind PyTorch's back: packed bf16 copies are stale
         for p, o, n in self._views:  # a grad that autograd re-allocated (first backward after set_to_none) is folded in
             if p.grad is not None and p.grad.data_ptr() != self.flat_g.data_ptr() + 4 * o:
                 self.flat_g[o:o + n].add_(p.grad.reshape(-1))
@@ -158,6 +160,7 @@ class FusedAdam(torch.optim.Optimizer):
         for k, v in sd["param_groups"][0].items():
             if k != "params":
                 self.param_groups[0][k] = v
+        _wcache.bump()
         if self.capturable:
             self._dev_step.fill_(self._step)
             self.sync_hyper()

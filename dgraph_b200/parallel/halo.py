@@ -56,6 +56,19 @@ class HaloExchange:
               and x_local.dtype == torch.bfloat16 and x_local.dim() == 2 and (x_local.shape[1] * 2) % 16 == 0)
         return engine if ok else None
 
+    def symmetric_rows(self, comm_pattern: CommunicationPattern, num_features: int, dtype=torch.bfloat16, device=None,
+                       tag=0) -> torch.Tensor:
+        """``[num_local, num_features]`` buffer for features that will be exchanged.  On the peer-memory engine it sits at the head of
+        a symmetric ``[local | halo]`` buffer, so ``augmented`` / the pull kernels use it in place (no copy into a slot); elsewhere
+        it is ordinary memory.  Plays the role of the reference's ``comm.alloc_buffer`` for one-sided back-ends
+        (``DGraph/Communicator.py:99-104``).  Fill it between training steps (see ``PeerMemoryEngine.symmetric_rows``)."""
+        engine = getattr(self.comm, "engine", None)
+        if engine is not None and hasattr(engine, "symmetric_rows") and dtype == torch.bfloat16 and (num_features * 2) % 16 == 0:
+            return engine.symmetric_rows(comm_pattern, num_features, dtype, tag=tag)
+        if device is None:
+            device = comm_pattern.local_edge_list.device
+        return torch.empty((comm_pattern.num_local_vertices, num_features), dtype=dtype, device=device)
+
     def augmented(self, x_local: torch.Tensor, comm_pattern: CommunicationPattern, defer: bool = False) -> torch.Tensor:
         """``cat([x_local, halo])`` -- on the peer-memory engine this is one symmetric buffer filled by ONE pull
         kernel (no ``cat`` copy); elsewhere it is the reference's exchange followed by ``torch.cat``."""

@@ -63,6 +63,30 @@ class GraphKernelPlan:
             self._csr_to_csc = t
         return t
 
+    def col_peer(self, shift: int) -> torch.Tensor:
+        """``col`` for the pull kernels: a halo neighbour ``h`` becomes ``~((owner[h] << shift) | row_on_owner[h])`` (negative), so
+        the kernel forms the NVLink address from the index alone -- no table look-ups behind the index load.  Local neighbours
+        keep their row number.  Cached per ``shift``."""
+        cache = self.__dict__.setdefault("_col_peer", {})
+        t = cache.get(shift)
+        if t is None or t.device != self.col.device:
+            assert self.halo_owner is not None and self.halo_remote_row is not None, "plan was built without halo addressing"
+            nl = self.num_nbr_local
+            dev = self.col.device
+            code = ~((self.halo_owner.to(dev).long() << shift) | self.halo_remote_row.to(dev).long())
+            table = torch.cat([torch.arange(nl, device=dev, dtype=torch.long), code])
+            t = table[self.col.long()].to(torch.int32).contiguous()
+            cache[shift] = t
+        return t
+
+    def remote_edge_count(self) -> int:
+        """Edges whose neighbour row lives on another rank (each costs one NVLink row read in the pull kernels)."""
+        c = getattr(self, "_remote_edges", None)
+        if c is None:
+            c = int((self.col >= self.num_nbr_local).sum())
+            self._remote_edges = c
+        return c
+
     def rowmid(self) -> torch.Tensor:
         """First halo-neighbour slot of every CSR row (rows are neighbour-sorted, local neighbours first): the local part of
         row r is ``[rowptr[r], rowmid[r])``, the halo part ``[rowmid[r], rowptr[r+1])``."""

@@ -109,8 +109,10 @@ class SymmetricArena:
         self._top = off + nbytes
         return off
 
-    def tensor(self, offset: int, shape, dtype) -> torch.Tensor:
-        return tensor_from_ptr(self.base + offset, shape, dtype, self.device, owner=self)
+    def tensor(self, offset: int, shape, dtype, guard=None) -> torch.Tensor:
+        """Tensor over arena memory.  ``guard`` (any object) lives exactly as long as the tensor's storage, i.e. as long as any view
+        of it -- autograd's saved copies included."""
+        return tensor_from_ptr(self.base + offset, shape, dtype, self.device, owner=(self, guard))
 
     def close(self):
         if self._owned and self.base:
@@ -139,8 +141,12 @@ class _PatternPeerInfo:
             self.rot = 0
         counts = engine.all_gather_ints([self.n_nbr_local, self.n_halo, int(pat.send_offset[-1])])
         self.nbr_local_all = [c[0] for c in counts]
+        self.max_nbr_local = max(self.nbr_local_all)
         self.max_aug = max(c[0] + c[1] for c in counts)
-        self.max_halo = max(c[1] for c in counts)
+        self.max_halo = max(max(c[1] for c in counts), 1)
+        # remote rows are addressed as (owner << peer_shift) | row inside the pull kernels (GraphKernelPlan.col_peer)
+        self.peer_shift = max(1, (max(self.max_nbr_local, 2) - 1).bit_length())
+        assert (W << self.peer_shift) <= (1 << 31), "per-rank partition too large for the 32-bit (owner, row) neighbour code"
         # backward: boundary rows of mine and where their halo copies live on the consumers
         so = pat.send_offset.tolist()
         send_idx = pat.send_local_idx.to("cpu", torch.long)
@@ -285,8 +291,9 @@ class _PlanScatterPeer(Function):
 
 
 class _SlotGuard:
-    """Frees a ring entry when the autograd graph that needs it dies without ever running backward (forward-only loops with
-    ``requires_grad`` inputs would otherwise grow the ring on every call)."""
+    """Frees a ring entry when the last tensor that aliases it dies.  The guard rides in the storage owner of the tensor that
+    ``slot_tensor(..., track=True)`` hands out, so it lives exactly as long as any view of the buffer -- including the copies that
+    autograd saved for a backward pass -- no matter which layer saved it or whether its producer's backward ever runs."""
 
     def __init__(self, engine, key, off):
         self.engine, self.key, self.off = engine, key, off
@@ -304,7 +311,8 @@ class _SlotGuard:
 
 
 def _halo_grad_reduce(engine, pat, g_aug):
-    """Backward of any halo read: gradients of halo rows are published in a symmetric slot and pull-reduced by the owners."""
+    """Backward of any halo read: gradients of halo rows are published in a symmetric slot and pull-reduced by the owners (in
+    place, on the rows of ``g_aug`` that this rank owns)."""
     info = engine.pattern_info(pat)
     F = g_aug.shape[1]
     g_aug = g_aug.contiguous()
@@ -312,12 +320,8 @@ def _halo_grad_reduce(engine, pat, g_aug):
     gh, off = engine.slot_tensor(("halo_bwd", info.uid), (info.max_halo, F), g_aug.dtype, ring=False)
     gh[: info.n_halo].copy_(g_aug[info.n_nbr_local:])
     engine.barrier_on_stream()
-    gx = g_aug[: info.n_nbr_local].clone()
-    N.check(N.lib().dgb_halo_grad_reduce(N.ptr(gx), N.i64(F), N.ptr(g_aug), N.i64(F), N.i32(F), N.i64(info.n_bnd),
-                                         N.ptr(info.bnd_row), N.ptr(info.bnd_ptr), N.ptr(info.src_rank),
-                                         N.ptr(info.src_row), N.ptr(engine.arena.ptr_table(off)), N.i64(F),
-                                         N.stream()), "dgb_halo_grad_reduce")
-    N.count_launch(2)
+    gx = g_aug[: info.n_nbr_local]
+    engine.halo_grad_reduce_inplace(info, gx, F, F, off, F)
     engine.mark_read(off)  # the next writer of this slot inserts a barrier only if none happened in between
     return gx
 
@@ -328,17 +332,14 @@ class _FusedPullAggregate(Function):
 
     @staticmethod
     def forward(ctx, x, engine, pat, kp, mean):
+        from dgraph_b200.ops.segment import _native_seg_sum
+
         info = engine.pattern_info(pat)
         F = x.shape[1]
-        pub, off = engine.slot_tensor(("pub", info.uid), (max(info.nbr_local_all), F), x.dtype, ring=False)
-        pub[: info.n_nbr_local].copy_(x)
+        pub, off = engine.published(x, info)  # no copy when x already lives in a symmetric slot (engine.symmetric_rows)
         engine.barrier_on_stream()
-        out = torch.empty((kp.num_local, F), dtype=torch.bfloat16, device=x.device)
-        N.check(N.lib().dgb_seg_sum(N.ptr(kp.rowptr), N.ptr(kp.col), N.i64(kp.num_local), N.i32(F), N.ptr(pub), N.i64(F),
-                                    N.ptr(None), N.i32(1 if mean else 0), N.ptr(out), N.i64(F), N.i64(info.n_nbr_local),
-                                    N.ptr(engine.arena.ptr_table(off)), N.ptr(info.halo_owner), N.ptr(info.halo_row), N.i64(F),
-                                    N.stream()), "dgb_seg_sum(halo pull)")
-        N.count_launch(2)
+        out = _native_seg_sum(kp.rowptr, kp.col_peer(info.peer_shift), kp.num_local, pub, None, mean,
+                              peer=(engine.arena.ptr_table(off), engine.get_world_size(), info.peer_shift, pub.stride(0)))
         engine.mark_read(off)
         ctx.engine, ctx.pat, ctx.kp, ctx.mean = engine, pat, kp, mean
         return out
@@ -347,24 +348,37 @@ class _FusedPullAggregate(Function):
     def backward(ctx, g):
         from dgraph_b200.ops.segment import _mean_bwd_weights, _native_seg_sum
 
-        kp = ctx.kp
+        kp, engine = ctx.kp, ctx.engine
+        info = engine.pattern_info(ctx.pat)
+        F = g.shape[1]
         w = _mean_bwd_weights(kp) if ctx.mean else None
-        g_aug = _native_seg_sum(kp.colptr, kp.row, kp.num_aug, g.contiguous(), w, False)
-        return _halo_grad_reduce(ctx.engine, ctx.pat, g_aug), None, None, None, None
+        # the CSC walk writes the halo rows' gradients straight into the symmetric slot; the owners reduce them in place
+        gh, off = engine.slot_tensor(("halo_bwd", info.uid), (info.max_halo, F), torch.bfloat16, ring=False)
+        gx = _native_seg_sum(kp.colptr, kp.row, kp.num_aug, g.contiguous(), w, False, out2=gh, out_split=info.n_nbr_local)
+        engine.barrier_on_stream()
+        engine.halo_grad_reduce_inplace(info, gx, F, F, off, F)
+        engine.mark_read(off)
+        return gx, None, None, None, None
 
 
 class _HaloAug(Function):
     """``aug = cat([x, halo(x)])`` through the symmetric arena; backward pull-reduces halo gradients on the owners."""
 
     @staticmethod
-    def forward(ctx, x, engine, pat, defer=False):
+    def forward(ctx, x, engine, pat, defer=False, track=False):
         info = engine.pattern_info(pat)
         F = x.shape[1]
         assert x.dim() == 2 and (F * x.element_size()) % 16 == 0, "feature rows must be multiples of 16 bytes"
-        aug, off = engine.slot_tensor(("halo_fwd", info.uid), (info.max_aug, F), x.dtype, ring=True,
-                                      track=torch.is_grad_enabled() and x.requires_grad)
-        aug = aug[: info.n_nbr_local + info.n_halo]
-        aug[: info.n_nbr_local].copy_(x)
+        own = engine.symmetric_slot_of(x, info.max_aug)
+        if own is not None:  # the rows already sit at the head of an augmented symmetric buffer (engine.symmetric_rows): no copy
+            off = own
+            aug = engine.arena.tensor(off, (info.max_aug, F), x.dtype)[: info.n_nbr_local + info.n_halo]
+        else:
+            # `track` (decided by the caller: grad mode is always off in here) keeps this ring entry out of circulation while any
+            # view of the buffer is alive, e.g. saved for a backward pass (see _SlotGuard)
+            aug, off = engine.slot_tensor(("halo_fwd", info.uid), (info.max_aug, F), x.dtype, ring=True, track=track)
+            aug = aug[: info.n_nbr_local + info.n_halo]
+            aug[: info.n_nbr_local].copy_(x)
         engine.barrier_on_stream()
         rb = F * x.element_size()
 
@@ -388,14 +402,11 @@ class _HaloAug(Function):
         N.count_launch(2)
         engine.mark_read(off)
         ctx.engine, ctx.pat = engine, pat
-        ctx.slot_guard = _SlotGuard(engine, ("halo_fwd", info.uid), off)
         return aug
 
     @staticmethod
     def backward(ctx, g_aug):
-        engine, pat = ctx.engine, ctx.pat
-        ctx.slot_guard.release()
-        return _halo_grad_reduce(engine, pat, g_aug), None, None, None
+        return _halo_grad_reduce(ctx.engine, ctx.pat, g_aug), None, None, None, None
 
 
 class PeerMemoryEngine(TorchDistEngine):
@@ -407,6 +418,7 @@ class PeerMemoryEngine(TorchDistEngine):
         self._uid = 0
         self._rings: Dict[Tuple, List] = {}
         self._by_off: Dict[int, dict] = {}
+        self._sym_rows: Dict[int, Tuple] = {}
         self._timeout_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
         # opt-in (DGRAPH_B200_DEVICE_EPOCH=1, not yet run on hardware): barrier epochs counted in device memory, so a training step
         # with exchanges can be captured in a CUDA graph.  Fixed at construction: the two barrier forms must never be mixed.
@@ -490,17 +502,83 @@ class PeerMemoryEngine(TorchDistEngine):
             off = self.arena.slot(f"{rk}#{len(entries)}", max(nbytes, 16))
             pick = {"off": off, "busy": False, "read_epoch": -1}
             entries.append(pick)
+        guard = None
         if ring and track:
             pick["busy"] = True
-        # peers read this slot during epoch `read_epoch`; they are provably done once any later barrier has completed
-        if pick["read_epoch"] == self._epoch:
-            self.barrier_on_stream()
+            guard = _SlotGuard(self, key, pick["off"])
         self._by_off[pick["off"]] = pick
-        return self.arena.tensor(pick["off"], shape, dtype), pick["off"]
+        self.note_write(pick["off"])
+        return self.arena.tensor(pick["off"], shape, dtype, guard), pick["off"]
+
+    def note_write(self, off):
+        """This rank is about to overwrite slot ``off``.  Peers read it during epoch ``read_epoch``; they are provably done once any
+        later barrier has completed, so a barrier is inserted only when none happened since."""
+        e = self._by_off.get(off)
+        if e is not None and e["read_epoch"] == self._epoch:
+            self.barrier_on_stream()
 
     def mark_read(self, off):
-        """Record that peers read slot ``off`` after the latest barrier (see ``slot_tensor``)."""
+        """Record that peers read slot ``off`` after the latest barrier (see ``note_write``)."""
         self._by_off[off]["read_epoch"] = self._epoch
+
+    # ---- zero-copy publication --------------------------------------------------------------------
+    def symmetric_rows(self, pat, F: int, dtype=torch.bfloat16, tag=0) -> torch.Tensor:
+        """``[num_local, F]`` tensor at the head of an augmented symmetric buffer of its own.  Features written here (host -> device
+        copy, a producing kernel's ``out=``) are exchanged without the copy into a slot: ``halo_exchange_aug`` pulls the halo rows
+        in right behind them and returns the same memory as ``cat([x, halo])``; ``aggregate_pull`` lets peers read it in place.
+        Peers read these rows between the exchange's barrier and the next barrier on the stream, so refill the buffer only in stream
+        order behind a later barrier -- e.g. between training steps (the optimizer step ends with one)."""
+        if self._world == 1:
+            return torch.empty((pat.num_local_vertices, F), dtype=dtype, device=self.device)
+        info = self.pattern_info(pat)
+        buf, off = self.slot_tensor(("rows", info.uid, F, tag), (info.max_aug, F), dtype, ring=False)
+        self._sym_rows[buf.data_ptr()] = (off, info.max_aug, F, dtype)
+        return buf[: info.n_nbr_local]
+
+    def symmetric_slot_of(self, x: torch.Tensor, min_rows: int):
+        """Arena offset of ``x`` when it is a ``symmetric_rows`` buffer with at least ``min_rows`` rows of the same width."""
+        if self.arena is None:
+            return None
+        hit = self._sym_rows.get(x.data_ptr())
+        if hit is None or not x.is_contiguous():
+            return None
+        off, rows, F, dtype = hit
+        return off if (rows >= min_rows and x.dim() == 2 and x.shape[1] == F and x.dtype == dtype) else None
+
+    def published(self, x: torch.Tensor, info):
+        """``(tensor peers may read, arena offset)`` holding the rows of ``x``: ``x`` itself when it already lives in a symmetric
+        buffer, else a copy into the pattern's publication slot."""
+        own = self.symmetric_slot_of(x, info.n_nbr_local)
+        if own is not None:
+            return x, own
+        pub, off = self.slot_tensor(("pub", info.uid, x.shape[1]), (info.max_nbr_local, x.shape[1]), x.dtype, ring=False)
+        pub[: info.n_nbr_local].copy_(x)
+        return pub, off
+
+    # ---- what travels and how ------------------------------------------------------------------------
+    def pull_mode(self, info, kp) -> str:
+        """How a consumer fetches the remote rows it needs.  ``"kernel"``: the consuming kernel reads them from the owners while
+        it runs (each remote edge costs one NVLink row read, nothing is staged).  ``"buffer"``: one pull kernel copies every halo
+        row once into local memory first.  Peer loads bypass the local L2, so re-reads cross NVLink again: ``auto`` takes the
+        in-kernel route only while the remote edges re-read a halo row fewer than ``DGRAPH_B200_PULL_REUSE`` (1.6) times on
+        average.  A rank decides for itself: both routes read the same slots behind the same barrier."""
+        mode = os.environ.get("DGRAPH_B200_PULL", "auto")
+        if mode in ("kernel", "buffer"):
+            return mode
+        c = getattr(info, "_pull_mode", None)
+        if c is None:
+            reuse = kp.remote_edge_count() / max(info.n_halo, 1)
+            c = info._pull_mode = "kernel" if reuse < float(os.environ.get("DGRAPH_B200_PULL_REUSE", "1.6")) else "buffer"
+        return c
+
+    def halo_grad_reduce_inplace(self, info, gx, ld_gx, H, slot_off, ld_slot):
+        """``gx[b] += sum over the ranks holding b as a halo row of their slot rows`` for my boundary rows ``b`` (ONE deterministic
+        pull-reduce kernel; ``gx`` may be a strided view such as the ``dQ`` half of a ``[n, 2H]`` buffer)."""
+        N.check(N.lib().dgb_halo_grad_reduce(N.ptr(gx), N.i64(ld_gx), N.ptr(gx), N.i64(ld_gx), N.i32(H), N.i64(info.n_bnd),
+                                             N.ptr(info.bnd_row), N.ptr(info.bnd_ptr), N.ptr(info.src_rank), N.ptr(info.src_row),
+                                             N.ptr(self.arena.ptr_table(slot_off)), N.i64(ld_slot), N.stream()),
+                "dgb_halo_grad_reduce")
+        N.count_launch()
 
     def release_slot(self, key, off):
         for rk, entries in self._rings.items():
@@ -552,7 +630,9 @@ class PeerMemoryEngine(TorchDistEngine):
         on a side stream; hand the buffer only to a consumer that waits for ``ops._pending.take(buffer)``."""
         if self._world == 1:
             return x
-        return _HaloAug.apply(x, self, pat, bool(defer) and os.environ.get("DGRAPH_B200_OVERLAP", "0") != "0")
+        # grad mode is off inside autograd.Function.forward, so whether the buffer may be saved for a backward pass is decided here
+        return _HaloAug.apply(x, self, pat, bool(defer) and os.environ.get("DGRAPH_B200_OVERLAP", "0") != "0",
+                              torch.is_grad_enabled())
 
     def halo_exchange(self, x: torch.Tensor, pat) -> torch.Tensor:
         if self._world == 1:
@@ -569,12 +649,12 @@ class PeerMemoryEngine(TorchDistEngine):
             return segment_sum(x, kp, mean=mean)
         return _FusedPullAggregate.apply(x, self, pat, kp, mean)
 
-    def publish(self, x: torch.Tensor, pat, tag: str = "pubx"):
-        """Copy ``x`` into a symmetric slot and order it for the peers; returns ``(peer pointer table, halo_owner, halo_row,
-        n_local)`` -- the ``peers`` entry that ``ops.gemm_native.gather_gemm_bf16`` needs to pull remote rows itself."""
+    def publish(self, x: torch.Tensor, pat):
+        """Make ``x`` readable by the peers (in place when it is a ``symmetric_rows`` buffer, else one copy into a slot) and order it;
+        returns ``(local tensor, (peer pointer table, halo_owner, halo_row, n_local))`` -- the ``peers`` entry that
+        ``ops.gemm_native.gather_gemm_bf16`` needs to pull remote rows itself."""
         info = self.pattern_info(pat)
-        pub, off = self.slot_tensor((tag, info.uid), (max(info.nbr_local_all), x.shape[1]), x.dtype, ring=False)
-        pub[: info.n_nbr_local].copy_(x)
+        pub, off = self.published(x, info)
         self.barrier_on_stream()
         self.mark_read(off)
         return pub[: info.n_nbr_local], (self.arena.ptr_table(off), info.halo_owner, info.halo_row, info.n_nbr_local)

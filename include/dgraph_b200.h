@@ -26,31 +26,39 @@ int dgb_sm_count(void);
 /* ---- segment aggregation (csrc/segment_ops.cu) ----------------------------------------------------------------------
  * Reference: scatter_add of GraphConvLayer (experiments/OGB/GCN.py:57-65); K6/K7 masked scatter/gather kernels
  * (DGraph/distributed/csrc/local_data_kernels.cuh:301-406).  CSR/CSC walk, one sub-warp per output row, no atomics. */
+/* Pull variant (peer_base != null): idx[k] < 0 names a row of another rank, ~idx[k] = (owner << peer_shift) | row; the kernel reads it
+ * from peer_base[owner] + row * ld_peer over NVLink in the same batch of loads as the local rows (reference: the in-kernel remote get
+ * of DGraph/distributed/csrc/nvshmem_comm_kernels.cuh:255-299).  out2 (optional): rows >= out_split are written to out2[r - out_split]. */
 int dgb_seg_sum(const int* ptr, const int* idx, int64_t n_rows, int H, const void* src, int64_t ld_src, const float* slot_w,
-                int mean, void* out, int64_t ld_out, int64_t n_local, const void* const* peer_base, const int* halo_owner,
-                const int* halo_row, int64_t ld_peer, void* stream);
+                int mean, void* out, int64_t ld_out, const void* const* peer_base, int world, int peer_shift, int64_t ld_peer,
+                void* out2, int64_t ld_out2, int64_t out_split, void* stream);
 /* out[r] = sum_k relu(P[r] + Q[idx[k]]); optional per-(row,col) active-edge counts and per-edge ReLU bit masks */
 int dgb_seg_add_relu_fwd(const int* ptr, const int* idx, int64_t n_rows, int H, const void* P, int64_t ld_p, const void* Q,
                          int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt, int64_t ld_cnt, unsigned char* mask,
-                         int64_t n_local, const void* const* peer_base, const int* halo_owner, const int* halo_row,
-                         int64_t ld_peer, void* stream);
+                         void* stream);
 
 /* Extended form: mask row of edge slot k at mask_slot_map[k] (null = k); ptr_end (null = ptr + 1) restricts every row to
- * slots [ptr[r], ptr_end[r]); accumulate = 1 adds to the out / cnt rows of an earlier launch (local-neighbour pass overlapped
- * with the NVLink halo pull, halo-neighbour pass afterwards).  No counterpart in the reference (GCN.py:43-65 materialises
- * [E, 2F] edge tensors). */
+ * slots [ptr[r], ptr_end[r]); accumulate = 1 adds to the out / cnt rows of an earlier launch.  With peer_base the Q rows of remote
+ * neighbours (idx < 0, encoded as in dgb_seg_sum) are pulled from their owners inside the kernel: halo exchange + gather + add + ReLU +
+ * segment sum of a distributed GraphConv layer in ONE launch (reference op chain P1 + P2: haloExchange.py:137 -> GCN.py:43-65). */
 int dgb_seg_add_relu_fwd_ex(const int* ptr, const int* ptr_end, const int* idx, int64_t n_rows, int H, const void* P,
                             int64_t ld_p, const void* Q, int64_t ld_q, void* out, int64_t ld_out, unsigned short* cnt,
-                            int64_t ld_cnt, unsigned char* mask, const int* mask_slot_map, int accumulate, int64_t n_local,
-                            const void* const* peer_base, const int* halo_owner, const int* halo_row, int64_t ld_peer,
-                            void* stream);
+                            int64_t ld_cnt, unsigned char* mask, const int* mask_slot_map, int accumulate,
+                            const void* const* peer_base, int world, int peer_shift, int64_t ld_peer, void* stream);
 int dgb_seg_add_relu_bwd(const int* colptr, const int* row, int64_t n_aug, int H, const void* dOut, int64_t ld_g,
                          const void* P, int64_t ld_p, const void* Q, int64_t ld_q, void* dQ, int64_t ld_dq, void* stream);
 int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slot_map, const unsigned char* mask, int64_t n_aug,
                        int H, const void* dOut, int64_t ld_g, void* dQ, int64_t ld_dq, const unsigned short* cnt,
-                       int64_t ld_cnt, void* dP, int64_t ld_dp, int64_t dp_rows, void* stream);
+                       int64_t ld_cnt, void* dP, int64_t ld_dp, int64_t dp_rows, void* dQ2, int64_t ld_dq2, int64_t dq_split,
+                       void* stream);
 int dgb_mul_cnt(const void* g, int64_t ld_g, const unsigned short* cnt, int64_t ld_c, void* out, int64_t ld_o, int64_t rows,
                 int H, void* stream);
+
+/* ---- weight packing (csrc/pack_ops.cu) -------------------------------------------------------------------------------
+ * fp32 W = [W_i | W_j] of GraphConvLayer.conv (experiments/OGB/GCN.py:31) -> bf16 wcat [2H, Fp], wcat_t [Fp, 2H] (optional),
+ * fp32 bcat [2H] (optional) in one launch per layer and optimizer step. */
+int dgb_pack_graphconv_weights(const float* W, const float* bias, int H, int f_in, int Fp, void* wcat, void* wcat_t, float* bcat,
+                               void* stream);
 
 /* ---- tcgen05 GEMM / gather-GEMM (csrc/gemm_tcgen05.cu) ---------------------------------------------------------------
  * Reference: nn.Linear -> cuBLAS sgemm on gathered + concatenated operands (experiments/OGB/GCN.py:43-52,

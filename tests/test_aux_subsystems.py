@@ -156,8 +156,9 @@ def test_packed_counter_arithmetic_of_the_aggregation_kernel():
 
 
 def test_symmetric_slot_rings_bookkeeping():
-    """Host-side slot logic of the peer-memory engine with a fake arena (no GPU): rings grow on demand, tracked entries stay
-    reserved until released, and re-using a slot that peers read in the current epoch inserts a barrier first."""
+    """Host-side slot logic of the peer-memory engine with a fake arena (no GPU): rings grow on demand, a tracked entry stays
+    reserved exactly as long as the tensor handed out for it is alive (whoever holds it, e.g. autograd's saved tensors), and re-using
+    a slot that peers read in the current epoch inserts a barrier first."""
     from dgraph_b200.parallel.peer_engine import PeerMemoryEngine
 
     class FakeArena:
@@ -170,8 +171,10 @@ def test_symmetric_slot_rings_bookkeeping():
                 self.top += (nbytes + 255) // 256 * 256
             return self.slots[name]
 
-        def tensor(self, off, shape, dtype):
-            return torch.empty(shape, dtype=dtype)
+        def tensor(self, off, shape, dtype, guard=None):
+            t = torch.empty(shape, dtype=dtype)
+            t._guard = guard  # the real arena puts the guard into the storage's owner
+            return t
 
     eng = object.__new__(PeerMemoryEngine)
     eng._world, eng._rank, eng._epoch, eng._rings, eng._by_off, eng.arena = 2, 0, 0, {}, {}, FakeArena()
@@ -184,10 +187,15 @@ def test_symmetric_slot_rings_bookkeeping():
     eng.barrier_on_stream = fake_barrier
     t1, o1 = eng.slot_tensor("halo", (4, 8), torch.float32, ring=True, track=True)
     t2, o2 = eng.slot_tensor("halo", (4, 8), torch.float32, ring=True, track=True)
-    assert o1 != o2 and t1.shape == (4, 8)  # first entry is saved for backward -> a second one is added
-    eng.release_slot("halo", o1)
-    _, o3 = eng.slot_tensor("halo", (4, 8), torch.float32, ring=True, track=True)
+    assert o1 != o2 and t1.shape == (4, 8)  # first buffer is still alive (saved for backward) -> a second entry is added
+    saved = [t1]  # any holder counts, not only the producer's autograd node
+    del t1
+    _, o2b = eng.slot_tensor("halo", (4, 8), torch.float32, ring=True, track=True)
+    assert o2b not in (o1, o2)
+    saved.clear()  # last reference gone -> entry free again
+    t3, o3 = eng.slot_tensor("halo", (4, 8), torch.float32, ring=True, track=True)
     assert o3 == o1  # released entry is re-used, the ring does not grow
+    del t3, t2
     eng.new_step()
     _, o4 = eng.slot_tensor("halo", (4, 8), torch.float32, ring=True, track=False)
     assert o4 == o1 and not barriers

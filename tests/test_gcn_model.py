@@ -109,10 +109,11 @@ def test_kernel_plan_degree_guard():
     assert GraphKernelPlan.from_edges(torch.zeros(0, 2, dtype=torch.long), 0, 0).max_row_degree() == 0
 
 
-@pytest.mark.parametrize("mode", ["1", "all"])
+@pytest.mark.parametrize("mode", ["auto", "q"])
 def test_exchanging_projected_rows_gives_the_same_training(mode, monkeypatch):
-    """``DGRAPH_B200_GCN_QPULL``: the convolution projects only owned rows and exchanges ``Q = x W_j^T`` instead of ``x``.  Same
-    losses and weights as the default order of operations (fp64, 3 emulated ranks, random partition)."""
+    """A convolution may project only its owned rows and exchange ``Q = x W_j^T`` instead of ``x`` (``GraphConvLayer.
+    exchanges_projected_rows``: the default for every layer whose input needs a gradient).  Same losses and weights as the
+    reference's order of operations, exchange first (fp64, 3 emulated ranks, random partition)."""
     from dgraph_b200.models import gcn as gcn_mod
 
     torch.manual_seed(0)
@@ -122,8 +123,9 @@ def test_exchanging_projected_rows_gives_the_same_training(mode, monkeypatch):
     yg = torch.randint(0, 5, (V,))
     state = {k: v.clone() for k, v in CommAwareGCN(7, 16, 5, None, None).double().state_dict().items()}
     part = partition(V, W, "random")
+    monkeypatch.setattr(gcn_mod, "_EXCHANGE", "x")
     base = run_world(W, _train_job, e, part, xg, yg, W, state, 3)
-    monkeypatch.setattr(gcn_mod, "_QPULL", mode)
+    monkeypatch.setattr(gcn_mod, "_EXCHANGE", mode)
     alt = run_world(W, _train_job, e, part, xg, yg, W, state, 3)
     for (l0, sd0), (l1, sd1) in zip(base, alt):
         assert torch.allclose(torch.tensor(l0), torch.tensor(l1), atol=1e-9)

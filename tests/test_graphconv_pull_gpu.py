@@ -1,0 +1,156 @@
+"""The distributed GraphConv layer with the exchange inside its kernels (``ops/graphconv.py::_GraphConvPullQ``) on ONE GPU.
+
+W ranks are W engines of one process whose symmetric arenas are plain device buffers; barriers are no-ops and every phase is run
+rank after rank on one stream, so no kernel ever waits for another one (B200_PROFILING.md rule).  A rank's forward reads what its
+peers' GEMMs wrote, therefore every phase is run twice: the first pass fills the slots, the second one is the result.  Oracle: the
+layer on the whole graph in one piece (fp32 PyTorch formulation of the same op)."""
+import pytest
+import torch
+
+from tests._graphs import random_graph, partition
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(180)]
+
+
+def _make_engines(W, pats, arena_bytes=64 << 20):
+    from dgraph_b200.parallel.peer_engine import PeerMemoryEngine, SymmetricArena
+
+    counts = [[p.num_local_vertices, p.num_halo_vertices, int(p.send_offset[-1])] for p in pats]
+    bufs = [torch.zeros(arena_bytes, dtype=torch.uint8, device="cuda") for _ in range(W)]
+    ptrs = [b.data_ptr() for b in bufs]
+
+    class _Emu(PeerMemoryEngine):
+        def __init__(self, rank):  # noqa: D401 - no process group: everything the kernels need is set by hand
+            self._rank, self._world, self._group = rank, W, None
+            self._ranks_per_graph = -1
+            self.device = torch.device("cuda", torch.cuda.current_device())
+            self._epoch, self._uid = 0, 0
+            self._rings, self._by_off, self._sym_rows = {}, {}, {}
+            self._timeout_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self.device_epoch = False
+            self.arena = SymmetricArena(arena_bytes, rank, W, self.device, local_ptrs=ptrs)
+            self._keep = bufs
+
+        def get_rank(self):
+            return self._rank
+
+        def get_world_size(self):
+            return self._world
+
+        def all_gather_ints(self, vals):
+            assert len(vals) == 3
+            return counts
+
+        def barrier_on_stream(self):
+            self._epoch += 1
+
+    return [_Emu(r) for r in range(W)]
+
+
+@pytest.mark.parametrize("W,mode", [(2, "kernel"), (3, "kernel"), (3, "buffer"), (4, "buffer")])
+@pytest.mark.parametrize("F,f_in,H", [(24, 20, 32), (104, 100, 256)])  # F = padded feature width, f_in = the layer's input width
+def test_pull_q_layer_matches_whole_graph(W, mode, F, f_in, H, monkeypatch):
+    from dgraph_b200.ops.graphconv import graphconv_pull_q
+    from dgraph_b200.parallel import build_all_patterns
+    from dgraph_b200.parallel.kernel_plan import GraphKernelPlan
+    from dgraph_b200.ops.segment import graphconv_aggregate_ref
+
+    monkeypatch.setenv("DGRAPH_B200_PULL", mode)
+    torch.manual_seed(0)
+    V = 500
+    e = random_graph(V, 8, seed=3 * W + 1, symmetric=True)
+    part = partition(V, W, "random")
+    pats = build_all_patterns(e, part, W)
+    engines = _make_engines(W, pats)
+    xg = torch.zeros(V, F, device="cuda")
+    xg[:, :f_in] = torch.randn(V, f_in, device="cuda")
+    weight = (torch.randn(H, 2 * f_in, device="cuda") * 0.2).requires_grad_(True)
+    bias = (torch.randn(H, device="cuda") * 0.1).requires_grad_(True)
+    gout = torch.randn(V, H, device="cuda")
+
+    # ---- oracle: the whole graph as one rank, fp32 -------------------------------------------------------------------------------
+    xr = xg.clone().bfloat16().float().requires_grad_(True)
+    wr = weight.detach().bfloat16().float().requires_grad_(True)
+    br = bias.detach().clone().requires_grad_(True)
+    kpg = GraphKernelPlan.from_edges(e.cuda(), V, V, device="cuda")
+    P = xr[:, :f_in] @ wr[:, :f_in].t() + br
+    Q = xr[:, :f_in] @ wr[:, f_in:].t()
+    want = graphconv_aggregate_ref(P, Q, kpg)
+    want.backward(gout.bfloat16().float())
+
+    xs = [xg[p.local_vertices_global.cuda()].bfloat16().requires_grad_(True) for p in pats]
+    kps = [p.kernel_plan("cuda") for p in pats]
+    outs = [None] * W
+    for _ in range(2):  # pass 1 fills every rank's slot, pass 2 reads complete peers
+        for r in range(W):
+            outs[r] = graphconv_pull_q(xs[r], weight, bias, kps[r], f_in, engines[r], pats[r], tag=1)
+    for r in range(W):
+        gids = pats[r].local_vertices_global.cuda()
+        assert torch.allclose(outs[r].float(), want[gids].detach(), rtol=3e-2, atol=0.25), f"forward rank {r}"
+
+    dws, dbs = [], []
+    for it in range(2):
+        for r in range(W):
+            gids = pats[r].local_vertices_global.cuda()
+            xs[r].grad = None
+            dx_, dw_, db_ = torch.autograd.grad(outs[r], [xs[r], weight, bias], gout[gids].bfloat16(), retain_graph=True)
+            if it == 1:
+                dws.append(dw_)
+                dbs.append(db_)
+                ref = xr.grad[gids][:, :f_in]
+                assert torch.allclose(dx_.float()[:, :f_in], ref, rtol=5e-2, atol=0.05 * float(ref.abs().max()) + 1e-3), f"dx rank {r}"
+    dw, db = sum(dws), sum(dbs)
+    assert torch.allclose(dw, wr.grad, rtol=5e-2, atol=0.03 * float(wr.grad.abs().max()))
+    assert torch.allclose(db, br.grad, rtol=5e-2, atol=0.03 * float(br.grad.abs().max()))
+
+
+def test_pull_modes_agree_bitwise():
+    """In-kernel pull and pull-into-buffer read the same rows in the same order: identical outputs."""
+    import os
+
+    from dgraph_b200.ops.graphconv import graphconv_pull_q
+    from dgraph_b200.parallel import build_all_patterns
+
+    torch.manual_seed(1)
+    W, V, F, H = 3, 400, 64, 64
+    e = random_graph(V, 9, seed=11, symmetric=True)
+    pats = build_all_patterns(e, partition(V, W, "random"), W)
+    xg = torch.randn(V, F, device="cuda")
+    weight = torch.randn(H, 2 * F, device="cuda") * 0.2
+    bias = torch.randn(H, device="cuda") * 0.1
+    res = {}
+    for mode in ("kernel", "buffer"):
+        os.environ["DGRAPH_B200_PULL"] = mode
+        try:
+            engines = _make_engines(W, pats)
+            xs = [xg[p.local_vertices_global.cuda()].bfloat16() for p in pats]
+            for _ in range(2):
+                outs = [graphconv_pull_q(xs[r], weight, bias, pats[r].kernel_plan("cuda"), F, engines[r], pats[r], tag=0)
+                        for r in range(W)]
+            res[mode] = outs
+        finally:
+            os.environ.pop("DGRAPH_B200_PULL", None)
+    for a, b in zip(res["kernel"], res["buffer"]):
+        assert torch.equal(a, b)
+
+
+def test_packed_weights_kernel_and_cache():
+    from dgraph_b200.ops import _wcache
+    from dgraph_b200.ops.graphconv import packed_weights
+
+    torch.manual_seed(2)
+    H, f_in, Fp = 48, 100, 104
+    w = torch.randn(H, 2 * f_in, device="cuda")
+    b = torch.randn(H, device="cuda")
+    wcat, wcat_t, bcat = packed_weights(w, b, f_in, Fp)
+    ref = torch.zeros(2 * H, Fp, device="cuda")
+    ref[:H, :f_in] = w[:, :f_in]
+    ref[H:, :f_in] = w[:, f_in:]
+    assert torch.equal(wcat, ref.bfloat16()) and torch.equal(wcat_t, ref.bfloat16().t().contiguous())
+    assert torch.equal(bcat[:H], b) and float(bcat[H:].abs().sum()) == 0.0
+    assert packed_weights(w, b, f_in, Fp)[0] is wcat  # cached
+    w.mul_(2.0)  # in-place update (stock optimizers): version counter moves
+    assert packed_weights(w, b, f_in, Fp)[0] is not wcat
+    w2 = packed_weights(w, b, f_in, Fp)[0]
+    _wcache.bump()  # native optimizer kernels: explicit invalidation
+    assert packed_weights(w, b, f_in, Fp)[0] is not w2

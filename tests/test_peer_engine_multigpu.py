@@ -105,34 +105,66 @@ def _worker(rank, W, port, e, part, xg, yg, state, ret):
     dist.all_gather(alld, deg)
     ok = ok and torch.allclose(sc[0, :, 0].float(), sum(alld)[offp[rank]:offp[rank + 1]], rtol=2e-2, atol=0.5)
 
-    # 3 training steps must match the single-process run on the whole graph
-    torch.manual_seed(0)
-    model = CommAwareGCN(xg.shape[1], 64, 5, ex, comm, compute_dtype=torch.bfloat16).to(dev)
-    model.load_state_dict(state)
-    opt = FusedAdam(model.parameters(), lr=1e-2, comm=comm)
-    xl, yl = xg.to(dev)[gids].bfloat16(), yg.to(dev)[gids]
-    losses = []
-    for _ in range(3):
-        opt.zero_grad()
-        out = model(xl, pat)
-        loss = torch.nn.functional.cross_entropy(out.float(), yl, reduction="sum") / xg.shape[0] * W
-        loss.backward()
-        opt.step()
-        l = loss.detach().clone() / W
-        dist.all_reduce(l)
-        losses.append(float(l))
-    comm.engine.check_timeouts()
-    ret[rank] = (bool(ok), losses, {k: v.detach().cpu() for k, v in model.state_dict().items()})
+    # 3 training steps must match the single-process run on the whole graph: the default path (exchange fused into the layer
+    # kernels, features in symmetric rows, whichever pull route the engine picks), both pull routes forced, and the reference's
+    # order of operations (exchange x, then project) as the oracle of the fused node
+    from dgraph_b200.models import gcn as gcn_mod
+    from dgraph_b200.models.sage import CommAwareSAGE
+
+    def train(make_model, st, exchange, pull, sym, steps=3):
+        gcn_mod._EXCHANGE = exchange
+        if pull is None:
+            os.environ.pop("DGRAPH_B200_PULL", None)
+        else:
+            os.environ["DGRAPH_B200_PULL"] = pull
+        torch.manual_seed(0)
+        model = make_model().to(dev)
+        model.load_state_dict(st)
+        opt = FusedAdam(model.parameters(), lr=1e-2, comm=comm)
+        xl, yl = xg.to(dev)[gids].bfloat16(), yg.to(dev)[gids]
+        if sym:
+            buf = ex.symmetric_rows(pat, xl.shape[1], torch.bfloat16, tag=7)
+            buf.copy_(xl)
+            xl = buf
+        losses = []
+        for _ in range(steps):
+            opt.zero_grad()
+            out = model(xl, pat)
+            loss = torch.nn.functional.cross_entropy(out.float(), yl, reduction="sum") / xg.shape[0] * W
+            loss.backward()
+            opt.step()
+            l = loss.detach().clone() / W
+            dist.all_reduce(l)
+            losses.append(float(l))
+        comm.engine.check_timeouts()
+        return losses, {k: v.detach().cpu() for k, v in model.state_dict().items()}
+
+    def gcn():
+        return CommAwareGCN(xg.shape[1], 64, 5, ex, comm, compute_dtype=torch.bfloat16)
+
+    def sage():  # three exchanged layers of EQUAL width: every exchange asks for the same slot shape (ring-slot protection)
+        return CommAwareSAGE(xg.shape[1], xg.shape[1], 5, ex, comm, num_layers=3, compute_dtype=torch.bfloat16)
+
+    runs = {
+        "gcn_default": train(gcn, state["gcn"], "auto", None, True),
+        "gcn_pull_kernel": train(gcn, state["gcn"], "q", "kernel", False),
+        "gcn_pull_buffer": train(gcn, state["gcn"], "q", "buffer", True),
+        "gcn_exchange_x": train(gcn, state["gcn"], "x", None, False),
+        "sage3_kernel": train(sage, state["sage"], "auto", "kernel", False, steps=2),
+        "sage3_buffer": train(sage, state["sage"], "auto", "buffer", False, steps=2),
+    }
+    ret[rank] = (bool(ok), runs)
     comm.destroy()
     comm.engine.finalize()
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("W", [2])
+@pytest.mark.parametrize("W", [2, 4, 8])
 def test_peer_engine_halo_and_training(W):
     if torch.cuda.device_count() < W:
         pytest.skip(f"needs {W} GPUs")
     from dgraph_b200.models.gcn import CommAwareGCN
+    from dgraph_b200.models.sage import CommAwareSAGE
     from dgraph_b200.optim import FusedAdam
     from dgraph_b200.communicator import Communicator
     from dgraph_b200.parallel import HaloExchange, build_communication_pattern
@@ -144,30 +176,39 @@ def test_peer_engine_halo_and_training(W):
     part = partition(V, W, "contiguous")
     xg = torch.randn(V, F)
     yg = torch.randint(0, 5, (V,))
-    ref = CommAwareGCN(F, 64, 5, None, None)
-    state = {k: v.clone() for k, v in ref.state_dict().items()}
+    state = {"gcn": {k: v.clone() for k, v in CommAwareGCN(F, 64, 5, None, None).state_dict().items()},
+             "sage": {k: v.clone() for k, v in CommAwareSAGE(F, F, 5, None, None, num_layers=3).state_dict().items()}}
     # single-process oracle on GPU 0
     dev = torch.device("cuda", 0)
     comm = Communicator._from_engine(LocalEngine(), backend="single")
     pat = build_communication_pattern(e.to(dev), torch.zeros(V, dtype=torch.long, device=dev), 0, 1)
-    m = CommAwareGCN(F, 64, 5, HaloExchange(comm), comm, compute_dtype=torch.bfloat16).to(dev)
-    m.load_state_dict(state)
-    opt = FusedAdam(m.parameters(), lr=1e-2)
-    single = []
-    for _ in range(3):
-        opt.zero_grad()
-        loss = torch.nn.functional.cross_entropy(m(xg.to(dev).bfloat16(), pat).float(), yg.to(dev), reduction="sum") / V
-        loss.backward()
-        opt.step()
-        single.append(float(loss.detach()))
+    ex = HaloExchange(comm)
+    single = {}
+    for name, mk, steps in (("gcn", lambda: CommAwareGCN(F, 64, 5, ex, comm, compute_dtype=torch.bfloat16), 3),
+                            ("sage", lambda: CommAwareSAGE(F, F, 5, ex, comm, num_layers=3, compute_dtype=torch.bfloat16), 2)):
+        m = mk().to(dev)
+        m.load_state_dict(state[name])
+        opt = FusedAdam(m.parameters(), lr=1e-2)
+        ls = []
+        for _ in range(steps):
+            opt.zero_grad()
+            loss = torch.nn.functional.cross_entropy(m(xg.to(dev).bfloat16(), pat).float(), yg.to(dev), reduction="sum") / V
+            loss.backward()
+            opt.step()
+            ls.append(float(loss.detach()))
+        single[name] = (ls, {k: v.detach().cpu() for k, v in m.state_dict().items()})
     mgr = mp.Manager()
     ret = mgr.dict()
     mp.spawn(_worker, args=(W, _free_port(), e, part, xg, yg, state, ret), nprocs=W, join=True)
     for r in range(W):
-        ok, losses, sd = ret[r]
+        ok, runs = ret[r]
         assert ok
-        assert torch.allclose(torch.tensor(losses), torch.tensor(single), rtol=3e-2, atol=3e-2), (losses, single)
-        for k, v in sd.items():
-            # Adam normalises every gradient to +-lr: near-zero bf16 gradients may flip sign, so compare in the mean
-            d = (v - m.state_dict()[k].cpu()).abs()
-            assert d.mean() < 2e-3 and d.max() <= 6.5e-2, (k, float(d.mean()), float(d.max()))
+        for name, (losses, sd) in runs.items():
+            want_l, want_sd = single["gcn" if name.startswith("gcn") else "sage"]
+            assert torch.allclose(torch.tensor(losses), torch.tensor(want_l), rtol=3e-2, atol=3e-2), (name, losses, want_l)
+            for k, v in sd.items():
+                # Adam normalises every gradient to +-lr: near-zero bf16 gradients may flip sign, so compare in the mean
+                d = (v - want_sd[k]).abs()
+                assert d.mean() < 2e-3 and d.max() <= 6.5e-2, (name, k, float(d.mean()), float(d.max()))
+        # the two pull routes read the same rows in the same order: identical training, bit for bit
+        assert runs["gcn_pull_kernel"][0] == runs["gcn_pull_buffer"][0], (runs["gcn_pull_kernel"][0], runs["gcn_pull_buffer"][0])

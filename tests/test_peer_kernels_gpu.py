@@ -133,8 +133,8 @@ def test_fused_pull_kernels_emulated(W):
         kp = pat.kernel_plan("cuda")
         aug = xg[torch.cat([pat.local_vertices_global, pat.halo_vertices_global]).cuda()].contiguous()
         want = _native_seg_sum(kp.rowptr, kp.col, kp.num_local, aug, None, True)
-        got = _native_seg_sum(kp.rowptr, kp.col, kp.num_local, pubs[r], None, True,
-                              halo=(table, i.halo_owner, i.halo_row, i.n_nbr_local, F))
+        got = _native_seg_sum(kp.rowptr, kp.col_peer(i.peer_shift), kp.num_local, pubs[r], None, True,
+                              peer=(table, W, i.peer_shift, F))
         assert torch.equal(got, want)
         # gather-GEMM over cat([x[src], x_aug[dst]]): dst rows beyond n_local are pulled from the owner
         src = pat.local_edge_list[:, 0].cuda().int()

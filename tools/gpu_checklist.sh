@@ -25,7 +25,6 @@ python -m dgraph_b200.build > "$OUT/build.log" 2>&1 || { echo "build failed" | t
 step tests_gpu            900 python -m pytest tests -q -m gpu -p no:cacheprovider
 step test_fused_mlp       180 env DGRAPH_B200_FUSED_MLP=1 python -m pytest tests/test_mlp_fused_gpu.py -q -m gpu -p no:cacheprovider
 step test_gemm_bres       180 env DGRAPH_B200_GEMM_BRES=1 python -m pytest tests/test_gemm_bres_gpu.py -q -m gpu -p no:cacheprovider
-step test_qpull           180 env DGRAPH_B200_TEST_QPULL=1 python -m pytest tests/test_qpull_gpu.py -q -m gpu -p no:cacheprovider
 step smoke                180 python -c "import __graft_entry__ as g; g.smoke()"
 
 # ---- timing, one GPU ----------------------------------------------------------------------------------------------------------
@@ -46,7 +45,7 @@ if [ "${1:-}" = "multi" ]; then
     for n in 2 4 8; do
       [ "$n" -le "$N" ] || continue
       step bench_${n}gpu            600 $TR --nproc-per-node $n --master-port 29601 bench.py --gpus $n --steps 20 --warmup 3
-      step bench_${n}gpu_qpull      600 env DGRAPH_B200_GCN_QPULL=1 $TR --nproc-per-node $n --master-port 29602 bench.py --gpus $n --steps 20 --warmup 3 --no-e2e
+      step bench_${n}gpu_xchg       600 env DGRAPH_B200_GCN_EXCHANGE=x $TR --nproc-per-node $n --master-port 29602 bench.py --gpus $n --steps 20 --warmup 3 --no-e2e
       step bench_${n}gpu_cudagraph  600 $TR --nproc-per-node $n --master-port 29603 bench.py --gpus $n --steps 20 --warmup 3 --no-e2e --cuda-graph
     done
     step graphcast_${N}gpu            900 $TR --nproc-per-node $N --master-port 29604 experiments/GraphCast/train_graphcast.py --is_distributed True --backend nccl --procs_per_graph $N --iters 8

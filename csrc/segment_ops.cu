@@ -62,6 +62,7 @@ struct SegParams {
   __nv_bfloat16* out2;
   int64_t ld_out2;
   int64_t out_split;
+  int out2_skip_empty;  // rows >= out_split with an empty segment are not written (their reader knows they are structurally zero)
   // halo pull (HALO kernels): idx[k] < 0 encodes a remote row, ~idx[k] = (owner << peer_shift) | row in the owner's matrix
   const __nv_bfloat16* const* peer_base;  // [world] base pointer of the same matrix on every rank
   int world;
@@ -198,7 +199,8 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, const char* const* 
   if (rnn < n_rows) { nnbeg = p.ptr[rnn]; nnend = p.ptr_end[rnn]; }
 
   const bool accum = (MODE == SEG_ADD_RELU) && p.accumulate != 0;
-  if (!(accum && beg == end)) {  // an accumulate pass leaves rows without edges in its range untouched
+  const bool skip_out2 = (MODE == SEG_MASKED_SUM || MODE == SEG_SUM) && p.out2_skip_empty && beg == end && r >= p.out_split;
+  if (!(accum && beg == end) && !skip_out2) {  // an accumulate pass leaves rows without edges in its range untouched
   float acc[NC][8];
   float rop[NC][8];
   uint4 rop2[NC];  // SEG_ADD_RELU: the row operand stays packed (bf16x2)
@@ -516,11 +518,12 @@ DGB_API int dgb_seg_add_relu_bwd(const int* colptr, const int* row, int64_t n_au
 // (one byte per edge slot and 8-column chunk): one row gather per edge instead of two, no recomputation.  slot_map = null
 // means the mask rows are already in this walk's slot order (forward used dgb_seg_add_relu_fwd_mapped).  When dP is given,
 // rows j < dp_rows also write dP[j,:] = dOut[j,:] * cnt[j,:] in the same pass.  dQ2 (optional): rows j >= dq_split (the halo rows of
-// a distributed layer) are written to dQ2[j - dq_split, :] -- the symmetric slot their owners pull-reduce from.
+// a distributed layer) are written to dQ2[j - dq_split, :] -- the symmetric slot their owners pull-reduce from; with dq2_skip_empty
+// those of them that have no edge in this (restricted) walk are not written at all (the owners' restricted plan never reads them).
 DGB_API int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slot_map, const unsigned char* mask,
                                int64_t n_aug, int H, const void* dOut, int64_t ld_g, void* dQ, int64_t ld_dq,
                                const unsigned short* cnt, int64_t ld_cnt, void* dP, int64_t ld_dp, int64_t dp_rows,
-                               void* dQ2, int64_t ld_dq2, int64_t dq_split, void* stream) {
+                               void* dQ2, int64_t ld_dq2, int64_t dq_split, int dq2_skip_empty, void* stream) {
   if (H % 8 || ld_g % 8 || ld_dq % 8 || !fits32(ld_g * 2) || !mask || (dP && (ld_dp % 8 || ld_cnt % 8 || !cnt)) ||
       (dQ2 && (ld_dq2 % 8 || !aligned16(dQ2))))
     return (int)cudaErrorInvalidValue;
@@ -531,7 +534,7 @@ DGB_API int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slo
   p.out = (__nv_bfloat16*)dQ; p.ld_out = ld_dq;
   p.cnt = const_cast<unsigned short*>(cnt); p.ld_cnt = ld_cnt;
   p.dp_out = (__nv_bfloat16*)dP; p.ld_dp = ld_dp; p.dp_rows = dP ? dp_rows : 0;
-  p.out2 = (__nv_bfloat16*)dQ2; p.ld_out2 = ld_dq2; p.out_split = dq_split;
+  p.out2 = (__nv_bfloat16*)dQ2; p.ld_out2 = ld_dq2; p.out_split = dq_split; p.out2_skip_empty = dQ2 ? dq2_skip_empty : 0;
   return launch_seg<SEG_MASKED_SUM, false>(p, (cudaStream_t)stream);
 }
 

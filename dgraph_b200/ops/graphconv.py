@@ -64,10 +64,12 @@ def _aggregate(kp, ptr, ptr_end, idx, n_local, H, P, ld_p, Q, ld_q, out, cnt, ma
     N.count_launch()
 
 
-def _masked_sum(colptr, row, slot_map, mask, n_aug, H, g, dQ, ld_dq, cnt, dP, ld_dp, dp_rows, dQ2=None, ld_dq2=0, split=0):
+def _masked_sum(colptr, row, slot_map, mask, n_aug, H, g, dQ, ld_dq, cnt, dP, ld_dp, dp_rows, dQ2=None, ld_dq2=0, split=0,
+                skip_empty=False):
     N.check(N.lib().dgb_seg_masked_sum(N.ptr(colptr), N.ptr(row), N.ptr(slot_map), N.ptr(mask), N.i64(n_aug), N.i32(H), N.ptr(g),
                                        N.i64(H), N.ptr(dQ), N.i64(ld_dq), N.ptr(cnt), N.i64(H), N.ptr(dP), N.i64(ld_dp),
-                                       N.i64(dp_rows), N.ptr(dQ2), N.i64(ld_dq2), N.i64(split), N.stream()),
+                                       N.i64(dp_rows), N.ptr(dQ2), N.i64(ld_dq2), N.i64(split), N.i32(1 if skip_empty else 0),
+                                       N.stream()),
             "dgb_seg_masked_sum")
     N.count_launch()
 
@@ -199,10 +201,15 @@ class _GraphConvPullQ(Function):
         dPQ = torch.empty((n, 2 * H), dtype=torch.bfloat16, device=dev)  # [dP | dQ] of the owned rows
         dQ = dPQ[:, H:]
         dQh, goff = engine.slot_tensor(("dqh", info.uid, ctx.tag), (info.max_halo, H), torch.bfloat16)
+        # Structural sparsity travels with the exchange: when the incoming gradient is zero outside the labelled rows, a halo row
+        # receives a gradient only if one of its edges starts at a labelled row.  The owners learn once per label set which of
+        # their halo copies those are (engine.restricted_reduce_plan) and read only them; the walk does not even write the others.
+        rplan = None if hint is None else engine.restricted_reduce_plan(info, kp, hint[0], colptr)
         # one CSC walk: dQ of owned rows -> dPQ, dQ of halo rows -> the symmetric slot, dP = g * cnt
-        _masked_sum(colptr, row, slot_map, mask, kp.num_aug, H, g, dQ, 2 * H, cnt, dPQ, 2 * H, n, dQh, H, n)
+        _masked_sum(colptr, row, slot_map, mask, kp.num_aug, H, g, dQ, 2 * H, cnt, dPQ, 2 * H, n, dQh, H, n,
+                    skip_empty=rplan is not None)
         engine.barrier_on_stream()
-        engine.halo_grad_reduce_inplace(info, dQ, 2 * H, H, goff, H)  # dQ[b] += sum over the ranks that hold b as a halo row
+        engine.halo_grad_reduce_inplace(info, dQ, 2 * H, H, goff, H, plan=rplan)  # dQ[b] += sum over the holders of b's halo copies
         engine.mark_read(goff)
         dx = dw = db = None
         if ctx.needs_input_grad[0]:

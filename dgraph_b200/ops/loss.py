@@ -24,6 +24,20 @@ def masked_cross_entropy_ref(logits: torch.Tensor, labels: torch.Tensor, idx: Op
     return F.cross_entropy(up(logits.index_select(0, idx)), labels.reshape(-1).index_select(0, idx))
 
 
+def _rows_unique(idx: torch.Tensor, V: int) -> bool:
+    """``idx`` lists every row at most once (one device-to-host read per index tensor and version, then cached on the tensor)."""
+    tag = (idx.data_ptr(), idx.numel(), idx._version)
+    hit = getattr(idx, "_dgb_unique", None)
+    if hit is not None and hit[0] == tag:
+        return hit[1]
+    u = bool(torch.bincount(idx, minlength=1).max() <= 1) if idx.numel() else True
+    try:
+        idx._dgb_unique = (tag, u)
+    except Exception:  # noqa: BLE001
+        pass
+    return u
+
+
 class _MaskedCE(Function):
     @staticmethod
     def forward(ctx, logits, labels, idx):
@@ -54,9 +68,12 @@ class _MaskedCE(Function):
         if idx is None:
             return dsel[:, :C].to(logits.dtype), None, None
         dlogits = torch.zeros((V, C), dtype=logits.dtype, device=logits.device)
-        dlogits.index_copy_(0, idx, dsel[:, :C].to(logits.dtype))
-        if logits.dtype == torch.bfloat16:
-            _sparsity.put(dlogits, idx, dsel)  # padded compact rows [n_sel, ld_o]
+        if _rows_unique(idx, V):
+            dlogits.index_copy_(0, idx, dsel[:, :C].to(logits.dtype))
+            if logits.dtype == torch.bfloat16:
+                _sparsity.put(dlogits, idx, dsel)  # padded compact rows [n_sel, ld_o]
+        else:  # a row listed twice counts twice in the loss: its gradient rows add up, and the compact rows are no longer "the rows"
+            dlogits.index_add_(0, idx, dsel[:, :C].to(logits.dtype))
         return dlogits, None, None
 
 

@@ -183,7 +183,7 @@ class _GraphConvAgg(Function):
                 N.ptr(colptr), N.ptr(row), N.ptr(None if ctx.mask_csc else slot_map), N.ptr(mask),
                 N.i64(kp.num_aug), N.i32(H), N.ptr(g),
                 N.i64(H), N.ptr(dQ), N.i64(H), N.ptr(None), N.i64(0), N.ptr(None), N.i64(0), N.i64(0), N.ptr(None), N.i64(0),
-                N.i64(0), N.stream()),
+                N.i64(0), N.i32(0), N.stream()),
                 "dgb_seg_masked_sum")
             N.count_launch()
         elif ctx.needs_input_grad[1]:

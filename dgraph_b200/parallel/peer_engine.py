@@ -571,14 +571,56 @@ class PeerMemoryEngine(TorchDistEngine):
             c = info._pull_mode = "kernel" if reuse < float(os.environ.get("DGRAPH_B200_PULL_REUSE", "1.6")) else "buffer"
         return c
 
-    def halo_grad_reduce_inplace(self, info, gx, ld_gx, H, slot_off, ld_slot):
+    def halo_grad_reduce_inplace(self, info, gx, ld_gx, H, slot_off, ld_slot, plan=None):
         """``gx[b] += sum over the ranks holding b as a halo row of their slot rows`` for my boundary rows ``b`` (ONE deterministic
-        pull-reduce kernel; ``gx`` may be a strided view such as the ``dQ`` half of a ``[n, 2H]`` buffer)."""
-        N.check(N.lib().dgb_halo_grad_reduce(N.ptr(gx), N.i64(ld_gx), N.ptr(gx), N.i64(ld_gx), N.i32(H), N.i64(info.n_bnd),
-                                             N.ptr(info.bnd_row), N.ptr(info.bnd_ptr), N.ptr(info.src_rank), N.ptr(info.src_row),
+        pull-reduce kernel; ``gx`` may be a strided view such as the ``dQ`` half of a ``[n, 2H]`` buffer).  ``plan``: a restricted
+        ``(bnd_row, bnd_ptr, src_rank, src_row)`` from :meth:`restricted_reduce_plan`."""
+        bnd_row, bnd_ptr, src_rank, src_row = plan if plan is not None else (info.bnd_row, info.bnd_ptr, info.src_rank, info.src_row)
+        N.check(N.lib().dgb_halo_grad_reduce(N.ptr(gx), N.i64(ld_gx), N.ptr(gx), N.i64(ld_gx), N.i32(H), N.i64(bnd_row.numel()),
+                                             N.ptr(bnd_row), N.ptr(bnd_ptr), N.ptr(src_rank), N.ptr(src_row),
                                              N.ptr(self.arena.ptr_table(slot_off)), N.i64(ld_slot), N.stream()),
                 "dgb_halo_grad_reduce")
         N.count_launch()
+
+    def restricted_reduce_plan(self, info, kp, rows, colptr_r):
+        """Pull-reduce plan limited to the halo copies that can carry a non-zero gradient when the incoming gradient is zero outside
+        the central rows ``rows``: a halo row of rank q matters only if the restricted CSC (``colptr_r`` =
+        ``kp.restricted_csc(rows)[0]``) gives it an edge.  Every rank publishes one flag per halo row, the owners gather the flags of
+        their copies over NVLink (one barrier + one ``gather_rows_peer_kernel``, once per label set; cached like the restricted
+        CSC itself) and compact their boundary tables.  COLLECTIVE: all ranks must call it in the same order."""
+        cache = info.__dict__.setdefault("_restricted_reduce", {})
+        key = (rows.data_ptr(), rows.numel(), rows._version)
+        hit = cache.get(key)
+        if hit is not None and hit[0] is rows:
+            return hit[1]
+        dev = self.device
+        n, n_halo = info.n_nbr_local, info.n_halo
+        flags, off = self.slot_tensor(("nzflags", info.uid), (info.max_halo, 4), torch.int32)
+        if n_halo:
+            cp = colptr_r.long()
+            flags[:n_halo].zero_()
+            flags[:n_halo, 0] = (cp[n + 1:n + n_halo + 1] > cp[n:n + n_halo]).to(torch.int32)
+        self.barrier_on_stream()
+        n_src = int(info.src_row.numel())
+        got = torch.zeros((max(n_src, 1), 4), dtype=torch.int32, device=dev)
+        if n_src:
+            N.check(N.lib().dgb_gather_rows_peer(N.ptr(got), N.i64(16), N.i64(n_src), N.i32(16), N.ptr(self.arena.ptr_table(off)),
+                                                 N.i64(16), N.ptr(info.src_rank), N.ptr(info.src_row), N.stream()),
+                    "dgb_gather_rows_peer")
+            N.count_launch()
+        self.mark_read(off)
+        keep = got[:n_src, 0] != 0
+        pref = torch.zeros(n_src + 1, dtype=torch.long, device=dev)
+        torch.cumsum(keep, 0, out=pref[1:])
+        cnt = pref[info.bnd_ptr.long()[1:]] - pref[info.bnd_ptr.long()[:-1]]
+        live = cnt > 0
+        ptr = torch.zeros(int(live.sum()) + 1, dtype=torch.int32, device=dev)
+        ptr[1:] = cnt[live].cumsum(0).to(torch.int32)
+        plan = (info.bnd_row[live].contiguous(), ptr, info.src_rank[keep].contiguous(), info.src_row[keep].contiguous())
+        if len(cache) >= 4:
+            cache.clear()
+        cache[key] = (rows, plan)
+        return plan
 
     def release_slot(self, key, off):
         for rk, entries in self._rings.items():

@@ -50,7 +50,7 @@ int dgb_seg_add_relu_bwd(const int* colptr, const int* row, int64_t n_aug, int H
 int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slot_map, const unsigned char* mask, int64_t n_aug,
                        int H, const void* dOut, int64_t ld_g, void* dQ, int64_t ld_dq, const unsigned short* cnt,
                        int64_t ld_cnt, void* dP, int64_t ld_dp, int64_t dp_rows, void* dQ2, int64_t ld_dq2, int64_t dq_split,
-                       void* stream);
+                       int dq2_skip_empty, void* stream);
 int dgb_mul_cnt(const void* g, int64_t ld_g, const unsigned short* cnt, int64_t ld_c, void* out, int64_t ld_o, int64_t rows,
                 int H, void* stream);
 

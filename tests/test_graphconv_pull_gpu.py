@@ -47,9 +47,10 @@ def _make_engines(W, pats, arena_bytes=64 << 20):
     return [_Emu(r) for r in range(W)]
 
 
-@pytest.mark.parametrize("W,mode", [(2, "kernel"), (3, "kernel"), (3, "buffer"), (4, "buffer")])
+@pytest.mark.parametrize("W,mode,how", [(2, "kernel", "random"), (3, "kernel", "random"), (3, "buffer", "random"),
+                                        (4, "buffer", "random"), (8, "kernel", "contiguous")])
 @pytest.mark.parametrize("F,f_in,H", [(24, 20, 32), (104, 100, 256)])  # F = padded feature width, f_in = the layer's input width
-def test_pull_q_layer_matches_whole_graph(W, mode, F, f_in, H, monkeypatch):
+def test_pull_q_layer_matches_whole_graph(W, mode, how, F, f_in, H, monkeypatch):
     from dgraph_b200.ops.graphconv import graphconv_pull_q
     from dgraph_b200.parallel import build_all_patterns
     from dgraph_b200.parallel.kernel_plan import GraphKernelPlan
@@ -59,7 +60,7 @@ def test_pull_q_layer_matches_whole_graph(W, mode, F, f_in, H, monkeypatch):
     torch.manual_seed(0)
     V = 500
     e = random_graph(V, 8, seed=3 * W + 1, symmetric=True)
-    part = partition(V, W, "random")
+    part = partition(V, W, how)
     pats = build_all_patterns(e, part, W)
     engines = _make_engines(W, pats)
     xg = torch.zeros(V, F, device="cuda")
@@ -132,6 +133,59 @@ def test_pull_modes_agree_bitwise():
             os.environ.pop("DGRAPH_B200_PULL", None)
     for a, b in zip(res["kernel"], res["buffer"]):
         assert torch.equal(a, b)
+
+
+def test_restricted_reduce_equals_dense_reduce():
+    """A gradient that is zero outside the labelled rows: the backward that carries this fact through the exchange (restricted CSC walk,
+    halo rows without an edge not written, owners read only the halo copies that can be non-zero) gives bit-identical ``dx`` and the same
+    ``dW`` as the dense backward on the same gradient."""
+    from dgraph_b200.ops import _sparsity
+    from dgraph_b200.ops.graphconv import graphconv_pull_q
+    from dgraph_b200.parallel import build_all_patterns
+
+    torch.manual_seed(3)
+    W, V, F, H = 4, 600, 64, 64
+    e = random_graph(V, 7, seed=5, symmetric=True)
+    pats = build_all_patterns(e, partition(V, W, "random"), W)
+    engines = _make_engines(W, pats)
+    xg = torch.randn(V, F, device="cuda")
+    weight = (torch.randn(H, 2 * F, device="cuda") * 0.2).requires_grad_(True)
+    bias = (torch.randn(H, device="cuda") * 0.1).requires_grad_(True)
+    xs = [xg[p.local_vertices_global.cuda()].bfloat16().requires_grad_(True) for p in pats]
+    kps = [p.kernel_plan("cuda") for p in pats]
+    idxs = [torch.arange(0, p.num_local_vertices, 7, device="cuda") for p in pats]
+    gs = []
+    for r in range(W):
+        g = torch.zeros(pats[r].num_local_vertices, H, device="cuda", dtype=torch.bfloat16)
+        g[idxs[r]] = torch.randn(idxs[r].numel(), H, device="cuda").bfloat16()
+        gs.append(g)
+    for _ in range(2):
+        outs = [graphconv_pull_q(xs[r], weight, bias, kps[r], F, engines[r], pats[r], tag=0) for r in range(W)]
+    # the restricted plans are built collectively: emulate the two phases (publish flags everywhere, then gather)
+    for it in range(2):
+        for r in range(W):
+            info = engines[r].pattern_info(pats[r])
+            info.__dict__.pop("_restricted_reduce", None)
+            engines[r].restricted_reduce_plan(info, kps[r], idxs[r], kps[r].restricted_csc(idxs[r])[0])
+    res = {}
+    for sparse in (False, True):
+        for it in range(2):
+            got = []
+            for r in range(W):
+                if sparse:
+                    _sparsity.put(gs[r], idxs[r], gs[r][idxs[r]])
+                else:
+                    _sparsity.clear()
+                got.append(torch.autograd.grad(outs[r], [xs[r], weight, bias], gs[r], retain_graph=True))
+        res[sparse] = got
+    assert _sparsity.STATS["hit"] >= W
+    for r in range(W):
+        fewer = engines[r].pattern_info(pats[r])._restricted_reduce
+        plan = next(iter(fewer.values()))[1]
+        assert plan[2].numel() < engines[r].pattern_info(pats[r]).src_row.numel()  # really restricted
+        assert torch.equal(res[True][r][0], res[False][r][0])
+        for a, b in zip(res[True][r][1:], res[False][r][1:]):
+            assert torch.allclose(a, b, rtol=1e-3, atol=1e-3 * float(b.abs().max()))
 
 
 def test_packed_weights_kernel_and_cache():

@@ -81,6 +81,18 @@ __device__ __forceinline__ uint32_t pack_bf2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
+// acc_lo += lo half, acc_hi += hi half of a packed bf16 pair, fp32 accumulate: the sm_100 mixed-precision add (`add.f32.bf16`, SASS
+// FHADD.BF16 with an .H0 / .H1 operand selector) takes the bf16 operand as it sits in the register -- no shift / mask to widen it first.
+__device__ __forceinline__ void fadd_bf16x2(uint32_t w, float& acc_lo, float& acc_hi) {
+  unsigned short l, h;
+  asm("mov.b32 {%0, %1}, %2;" : "=h"(l), "=h"(h) : "r"(w));
+  asm("add.rn.f32.bf16 %0, %1, %0;" : "+f"(acc_lo) : "h"(l));
+  asm("add.rn.f32.bf16 %0, %1, %0;" : "+f"(acc_hi) : "h"(h));
+}
+__device__ __forceinline__ void fadd_bf16x8(const uint4& v, float* acc) {
+  fadd_bf16x2(v.x, acc[0], acc[1]); fadd_bf16x2(v.y, acc[2], acc[3]);
+  fadd_bf16x2(v.z, acc[4], acc[5]); fadd_bf16x2(v.w, acc[6], acc[7]);
+}
 __device__ __forceinline__ void unpack8(const uint4& v, float* f) {
   f[0] = bf_lo(v.x); f[1] = bf_hi(v.x); f[2] = bf_lo(v.y); f[3] = bf_hi(v.y);
   f[4] = bf_lo(v.z); f[5] = bf_hi(v.z); f[6] = bf_lo(v.w); f[7] = bf_hi(v.w);

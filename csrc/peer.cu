@@ -122,19 +122,14 @@ halo_grad_reduce_kernel(__nv_bfloat16* __restrict__ gx, int64_t ld_gx, const __n
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
     const int colo = (g + c * G) * 8;
-    if (colo < H) unpack8(ldg_nc_v4(g_local + (int64_t)r * ld_gl + colo), acc[c]);
+    if (colo < H) unpack8(ldg_v4(g_local + (int64_t)r * ld_gl + colo), acc[c]);  // coherent load: gx may alias g_local
   }
   for (int k = bnd_ptr[b]; k < bnd_ptr[b + 1]; ++k) {
     const __nv_bfloat16* src = peer_base[src_rank[k]] + (int64_t)src_row[k] * ld_peer;
 #pragma unroll
     for (int c = 0; c < NC; ++c) {
       const int colo = (g + c * G) * 8;
-      if (colo < H) {
-        float f[8];
-        unpack8(ldg_v4(src + colo), f);
-#pragma unroll
-        for (int t = 0; t < 8; ++t) acc[c][t] += f[t];
-      }
+      if (colo < H) fadd_bf16x8(ldg_v4(src + colo), acc[c]);
     }
   }
 #pragma unroll

@@ -95,30 +95,41 @@ __device__ __forceinline__ uint4 ldg_any_hint_v4(const void* p, uint64_t pol) {
   return r;
 }
 
-// SEG_ADD_RELU on packed bf16 pairs (two columns per 32-bit lane word): HADD2 + HMNMX2 + HSET2 replace per-column
-// FADD / FSETP / predicated count + mask updates (9 -> ~5 instructions per column-edge; ncu: the scalar version was
-// issue-bound at 69 % SM throughput).  The message m = P[i] + Q[j] is rounded to bf16 before the ReLU -- exactly what a bf16
-// Linear -> ReLU produces -- and still accumulated in fp32; the sign of the rounded sum equals the sign of the exact sum, so
-// the saved mask is unchanged.
+// SEG_ADD_RELU on packed bf16 pairs (two columns per 32-bit lane word).  Per pair and edge: one HFMA2.BF16_V2.RELU forms the message
+// m = relu(P[i] * 1 + Q[j]) (rounded to bf16 once -- exactly what a bf16 Linear -> ReLU produces; fma pipe), one HSET2 turns it into the
+// activity mask (alu pipe), two FHADD.BF16 accumulate the halves in fp32 straight from the packed register (fma pipe; no shift / mask
+// to widen them), one IADD counts and one LOP3 collects the mask bit.  History (ncu, 61.9 M edges x 256): scalar fp32 version 72 SASS
+// instructions per edge-lane and issue-bound at 69 % SM throughput; HADD2 + HMNMX2 + HSET2 + shift / mask widening 47 (alu pipe 65 %);
+// this form 35, three per pair on each of the two pipes.
 //   cnt trick: mk is 0xFFFF per active half.  word -= mk adds 1 to the low count and (hi_active - lo_active) to the high one;
 //   the caller repairs the high half once per row with word += word << 16.
 __device__ __forceinline__ void add_relu_pair(uint32_t q2, uint32_t p2, float& a_lo, float& a_hi, uint32_t& cn, uint32_t& mout,
                                               uint32_t bitc) {
+  uint32_t rb;
+  asm("fma.rn.relu.bf16x2 %0, %1, %2, %3;" : "=r"(rb) : "r"(p2), "r"(0x3f803f80u), "r"(q2));
   const __nv_bfloat162 zero = __floats2bfloat162_rn(0.f, 0.f);
-  const __nv_bfloat162 s = __hadd2(*reinterpret_cast<const __nv_bfloat162*>(&p2), *reinterpret_cast<const __nv_bfloat162*>(&q2));
-  const uint32_t mk = __hgt2_mask(s, zero);
-  const __nv_bfloat162 r = __hmax2(s, zero);
-  const uint32_t rb = *reinterpret_cast<const uint32_t*>(&r);
-  a_lo += __uint_as_float(rb << 16);
-  a_hi += __uint_as_float(rb & 0xffff0000u);
+  const uint32_t mk = __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&rb), zero);  // relu(s) > 0  <=>  s > 0
+  fadd_bf16x2(rb, a_lo, a_hi);
   cn -= mk;
   mout |= mk & bitc;
+}
+
+// acc[2c], acc[2c + 1] += the halves of word c that the mask byte selects: predicated FHADD.BF16, predicates from one R2P
+__device__ __forceinline__ void masked_add8(const uint4& v, uint32_t mbyte, float* acc) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    unsigned short l, h;
+    asm("mov.b32 {%0, %1}, %2;" : "=h"(l), "=h"(h) : "r"(w[c]));
+    if (mbyte & (1u << (2 * c))) asm("add.rn.f32.bf16 %0, %1, %0;" : "+f"(acc[2 * c]) : "h"(l));
+    if (mbyte & (2u << (2 * c))) asm("add.rn.f32.bf16 %0, %1, %0;" : "+f"(acc[2 * c + 1]) : "h"(h));
+  }
 }
 
 // One edge worth of work for one lane chunk (8 columns).
 template <int MODE>
 __device__ __forceinline__ void seg_accumulate(const uint4& v, const uint4& v2, const float* rop, const uint4& rop2, float w,
-                                               uint32_t mbyte, float* acc, uint32_t* cn2, uint32_t& mout) {
+                                               bool weighted, uint32_t mbyte, float* acc, uint32_t* cn2, uint32_t& mout) {
   if (MODE == SEG_ADD_RELU) {
     uint32_t m = 0;
     add_relu_pair(v.x, rop2.x, acc[0], acc[1], cn2[0], m, 0x00020001u);
@@ -128,21 +139,25 @@ __device__ __forceinline__ void seg_accumulate(const uint4& v, const uint4& v2, 
     mout = m | (m >> 16);  // only the low byte is stored
     return;
   }
+  if (MODE == SEG_MASKED_SUM) {
+    masked_add8(v, mbyte, acc);
+    return;
+  }
+  if (MODE == SEG_SUM && !weighted) {  // plain / mean aggregation: widening adds straight from the packed words
+    fadd_bf16x8(v, acc);
+    return;
+  }
   float f[8];
   unpack8(v, f);
   if (MODE == SEG_SUM) {
 #pragma unroll
     for (int t = 0; t < 8; ++t) acc[t] = fmaf(w, f[t], acc[t]);
-  } else if (MODE == SEG_ADD_RELU_BWD) {  // f = dOut[i], f2 = P[i], rop = Q[j]
+  } else {  // SEG_ADD_RELU_BWD: f = dOut[i], f2 = P[i], rop = Q[j]
     float f2[8];
     unpack8(v2, f2);
 #pragma unroll
     for (int t = 0; t < 8; ++t)
       if (f2[t] + rop[t] > 0.f) acc[t] += f[t];
-  } else {  // SEG_MASKED_SUM
-#pragma unroll
-    for (int t = 0; t < 8; ++t)
-      if (mbyte & (1u << t)) acc[t] += f[t];
   }
 }
 
@@ -171,6 +186,7 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, const char* const* 
   const int nchunk = FULL ? (G * NC) : (p.H >> 3);  // 8-column chunks per row
   const uint64_t pol_keep = l2_policy_evict_last();
   const uint64_t pol_stream = l2_policy_evict_first();
+  const bool weighted = (MODE == SEG_SUM) && p.slot_w != nullptr;
 
   // pipeline registers: current row (beg, end, first-group indices) and the bounds of the next one
   int beg = p.ptr[r], end = p.ptr_end[r];
@@ -273,7 +289,7 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, const char* const* 
         for (int c = 0; c < NC; ++c) {
           if (colok[c]) {
             uint32_t mout = 0;
-            seg_accumulate<MODE>(v[u][c], v2[u][c], rop[c], rop2[c], w[u], mb[u][c], acc[c], cn2[c], mout);
+            seg_accumulate<MODE>(v[u][c], v2[u][c], rop[c], rop2[c], w[u], weighted, mb[u][c], acc[c], cn2[c], mout);
             if (MODE == SEG_ADD_RELU && AUX == 1) stg_cs_u8(mp + u * nchunk + c * G, mout);
             if (MODE == SEG_ADD_RELU && AUX == 2) stg_cs_u8(mask_lane + (int64_t)sl[u] * nchunk + c * G, mout);
           }
@@ -294,7 +310,7 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, const char* const* 
           uint32_t mb = 0, mout = 0;
           if (MODE == SEG_ADD_RELU_BWD) v2 = ldg_nc_v4(src2_lane + (uint64_t)(uint32_t)j * p.ld_src2_b + c * G * 16);
           if (MODE == SEG_MASKED_SUM) mb = MAPPED ? __ldg(mask_lane + (int64_t)sl * nchunk + c * G) : ldg_stream_u8(mp + c * G);
-          seg_accumulate<MODE>(v, v2, rop[c], rop2[c], w, mb, acc[c], cn2[c], mout);
+          seg_accumulate<MODE>(v, v2, rop[c], rop2[c], w, weighted, mb, acc[c], cn2[c], mout);
           if (MODE == SEG_ADD_RELU && AUX == 1) stg_cs_u8(mp + c * G, mout);
           if (MODE == SEG_ADD_RELU && AUX == 2) stg_cs_u8(mask_lane + (int64_t)sl * nchunk + c * G, mout);
         }

@@ -26,7 +26,11 @@ def _as_bf16_rowmajor(t: torch.Tensor) -> torch.Tensor:
     return t
 
 
-_BRES = os.environ.get("DGRAPH_B200_GEMM_BRES", "0") == "1"  # opt-in, not yet validated on hardware
+# B-resident tall-skinny variant (csrc/gemm_bres_tcgen05.cu): its N tile of B stays in shared memory and 5-8 A stages stream past
+# it.  Measured on B200 (profiles/bench_gemm.jsonl): 2.45 M x 256 x 104 0.473 -> 0.322 ms, x 512 x 104 0.887 -> 0.599 ms; no gain for
+# K >= 256, so it is taken for K <= 128 only.  DGRAPH_B200_GEMM_BRES=0 switches it off, =1 forces it for every shape it supports.
+_BRES = os.environ.get("DGRAPH_B200_GEMM_BRES", "auto")
+_BRES_MAX_K = 128
 
 
 def _alloc_out(M: int, Nn: int, dtype, device) -> torch.Tensor:
@@ -47,8 +51,8 @@ def gemm_bf16_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] 
         out = _alloc_out(M, Nn, out_dtype, a.device)
     assert out.stride(1) == 1 and out.dtype in (torch.bfloat16, torch.float32)
     bias_f = None if bias is None else bias.float().contiguous()
-    if _BRES and out.dtype == torch.bfloat16:
-        # experimental B-resident variant for small K (csrc/gemm_bres_tcgen05.cu); 801 = shape not supported -> default kernel
+    if out.dtype == torch.bfloat16 and (_BRES == "1" or (_BRES == "auto" and K <= _BRES_MAX_K)):
+        # 801 = shape not supported by this variant -> default kernel
         rc = N.lib().dgb_gemm_bf16_tn_bres(N.ptr(a), N.i64(a.stride(0)), N.ptr(b), N.i64(b.stride(0)), N.ptr(out),
                                            N.i64(out.stride(0)), N.i32(M), N.i32(Nn), N.i32(K), N.ptr(bias_f),
                                            N.i32(_ACT[act]), N.stream())

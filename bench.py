@@ -38,6 +38,13 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="products", choices=["products", "papers100m", "graphcast", "rgat", "halo"],
+                    help="products = the headline (BASELINE.json config 2); the others: benchmarks/workloads.py")
+    ap.add_argument("--rgat-mult", type=float, default=1.0, help="rgat: multiple of the reference's SyntheticDatasetConfig graph")
+    ap.add_argument("--rgat-hidden", type=int, default=64)
+    ap.add_argument("--rgat-relations", default="all", choices=["all", "first"],
+                    help="rgat: 'first' mirrors the reference as shipped, which processes relation 0 only (RGAT.py:356-358)")
+    ap.add_argument("--halo-max-rows", type=int, default=10_000_000)
     ap.add_argument("--graph", default="ogbn-products")
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the graph (debug only; <1 is NOT the named config)")
     ap.add_argument("--hidden", type=int, default=256)
@@ -318,6 +325,23 @@ def main():
     import builtins
 
     builtins._DGB_JSON_OUT = _JSON_OUT  # baseline/ref_bench.py prints its line through the same descriptor
+    if args.config != "products":
+        torch_local = int(os.environ.get("LOCAL_RANK", "0"))
+        if args.impl == "reference":
+            sys.path.insert(0, os.path.join(ROOT, "baseline"))
+            try:
+                import ref_workloads
+            except Exception as e:  # noqa: BLE001
+                if int(os.environ.get("RANK", "0")) == 0:
+                    print(json.dumps({"impl": "reference", "unavailable": f"reference harness import failed: {e!r}"[:300]}),
+                          file=_JSON_OUT, flush=True)
+                return
+            ref_workloads.run(args, _JSON_OUT, ClockSampler(torch_local))
+            return
+        from benchmarks import workloads
+
+        workloads.run(args, _JSON_OUT, ClockSampler(torch_local))
+        return
     if args.impl == "reference":
         sys.path.insert(0, os.path.join(ROOT, "baseline"))
         try:

@@ -77,7 +77,7 @@ __device__ __forceinline__ void staging_reusable(int lane) {
   __syncwarp();
 }
 
-__global__ void __maxnreg__(144)
+__global__ void __launch_bounds__(THREADS, 1)
 mlp2_ln_fused_kernel(const __grid_constant__ CUtensorMap tmap_w1, const __grid_constant__ CUtensorMap tmap_w2,
                      const __grid_constant__ CUtensorMap tmap_pre, const __grid_constant__ CUtensorMap tmap_z,
                      const __grid_constant__ CUtensorMap tmap_y, const Params p) {

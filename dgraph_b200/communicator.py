@@ -65,7 +65,13 @@ def _make_hybrid_engine(rpg: int, use_cuda: bool, **kwargs):
         if rank // rpg == g:
             mine = grp
     kw = {k: v for k, v in kwargs.items() if k != "ranks_per_graph"}
-    eng = TorchDistEngine(dist_backend="nccl" if use_cuda else "gloo", group=mine, ranks_per_graph=rpg, **kw)
+    if use_cuda and os.environ.get("DGRAPH_B200_ENGINE", "peer") != "torch":
+        # halo / plan traffic over NVLink inside the replica, ONE fused gradient-sum + Adam kernel over the whole job
+        from dgraph_b200.parallel.peer_engine import PeerMemoryEngine
+
+        eng = PeerMemoryEngine(ranks_per_graph=rpg, group=mine, **kw)
+    else:
+        eng = TorchDistEngine(dist_backend="nccl" if use_cuda else "gloo", group=mine, ranks_per_graph=rpg, **kw)
     eng.replica_id, eng.num_replicas, eng.global_rank, eng.global_world = rank // rpg, world // rpg, rank, world
     return eng
 

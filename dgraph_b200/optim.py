@@ -40,7 +40,7 @@ class FusedAdam(torch.optim.Optimizer):
         # peer-memory engine: gradients live in the symmetric arena so the Adam kernel can sum all ranks' buffers itself
         self._peer = None
         eng = getattr(comm, "engine", None)
-        if eng is not None and hasattr(eng, "adam_allreduce") and comm.get_world_size() > 1 and dev.type == "cuda":
+        if eng is not None and hasattr(eng, "adam_allreduce") and self._global_world() > 1 and dev.type == "cuda":
             self._peer = eng
             self.flat_g, self._g_off = eng.symmetric_flat("adam_grad", total)
             self.flat_g = self.flat_g[:total]

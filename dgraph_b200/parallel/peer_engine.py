@@ -53,12 +53,18 @@ def tensor_from_ptr(ptr: int, shape, dtype, device, owner=None) -> torch.Tensor:
 
 
 class SymmetricArena:
-    """One device allocation per rank, mapped into every peer; bump-allocated named slots at symmetric offsets."""
+    """One device allocation per rank, mapped into every peer; bump-allocated named slots at symmetric offsets.
 
-    def __init__(self, nbytes: int, rank: int, world: int, device: torch.device, group=None, local_ptrs: Optional[List[int]] = None):
+    ``members`` (optional): the ranks of ``group`` (the ranks that map one another) that form this engine's *graph replica*, in
+    replica-rank order.  ``ptr_table`` then lists only those -- halo traffic stays inside the replica -- while ``ptr_table_all`` lists
+    every mapped rank (the data-parallel gradient sum of the hybrid DP x graph-partition layout reads all of them)."""
+
+    def __init__(self, nbytes: int, rank: int, world: int, device: torch.device, group=None, local_ptrs: Optional[List[int]] = None,
+                 members: Optional[List[int]] = None):
         self.rank, self.world, self.device, self.nbytes = rank, world, device, int(nbytes)
+        self.members = list(members) if members is not None else list(range(world))
         self._slots: Dict[str, Tuple[int, int]] = {}
-        self._top = _ALIGN  # first 256 bytes: signal pad
+        self._top = 2 * _ALIGN  # first 256 bytes: signal pad of the replica's barriers; next 256: pad of the whole-world barriers
         lib = N.lib()
         if local_ptrs is not None:  # in-process emulation: all "ranks" are arenas of this process
             self.base = local_ptrs[rank]
@@ -83,15 +89,26 @@ class SymmetricArena:
                 q = ctypes.c_void_p()
                 N.check(lib.dgb_symm_import(hb, ctypes.byref(q)), f"dgb_symm_import(rank {r})")
                 self.peer_bases.append(q.value)
-        self._ptr_tables: Dict[int, torch.Tensor] = {}
+        self._ptr_tables: Dict[Tuple, torch.Tensor] = {}
         self.pad_table = self.ptr_table(0)
+        self.pad_table_all = self.ptr_table_all(_ALIGN)
 
     def ptr_table(self, offset: int) -> torch.Tensor:
-        """Device array ``[W]`` of ``peer_base[r] + offset`` (int64 == pointer)."""
-        t = self._ptr_tables.get(offset)
+        """Device array of ``peer_base[r] + offset`` (int64 == pointer) over the replica's ranks, in replica-rank order."""
+        t = self._ptr_tables.get((offset, 0))
         if t is None:
-            t = torch.tensor([b + offset for b in self.peer_bases], dtype=torch.int64, device=self.device)
-            self._ptr_tables[offset] = t
+            t = torch.tensor([self.peer_bases[r] + offset for r in self.members], dtype=torch.int64, device=self.device)
+            self._ptr_tables[(offset, 0)] = t
+        return t
+
+    def ptr_table_all(self, offset) -> torch.Tensor:
+        """Same over every mapped rank; ``offset`` may be a per-rank list (slots need not be symmetric across replicas)."""
+        key = (tuple(offset) if isinstance(offset, (list, tuple)) else offset, 1)
+        t = self._ptr_tables.get(key)
+        if t is None:
+            offs = list(offset) if isinstance(offset, (list, tuple)) else [offset] * len(self.peer_bases)
+            t = torch.tensor([b + o for b, o in zip(self.peer_bases, offs)], dtype=torch.int64, device=self.device)
+            self._ptr_tables[key] = t
         return t
 
     def slot(self, name: str, nbytes: int) -> int:
@@ -410,25 +427,40 @@ class _HaloAug(Function):
 
 
 class PeerMemoryEngine(TorchDistEngine):
+    """``group`` (optional): the process group of one graph replica in the hybrid data-parallel x graph-partition layout
+    (``Communicator.init_process_group(..., ranks_per_graph=k)``, reference arithmetic ``nccl/NCCLBackendEngine.py:56-64``).  Halo /
+    plan traffic and its barriers then stay inside the replica, while every rank of the job still maps every other rank's arena so
+    that the fused gradient all-reduce + Adam kernel sums over the whole world."""
+
     def __init__(self, ranks_per_graph: int = -1, arena_mb: Optional[int] = None, group=None, **kwargs):
         super().__init__(dist_backend="nccl", ranks_per_graph=ranks_per_graph, group=group, **kwargs)
         self.device = torch.device("cuda", torch.cuda.current_device())
         N.lib()
         self._epoch = 0
+        self._epoch_all = 0
+        self._job_rank = dist.get_rank() if dist.is_initialized() else 0
+        self._job_world = dist.get_world_size() if dist.is_initialized() else 1
         self._uid = 0
         self._rings: Dict[Tuple, List] = {}
         self._by_off: Dict[int, dict] = {}
         self._sym_rows: Dict[int, Tuple] = {}
+        self._flat_offsets: Dict[int, List[int]] = {}
         self._timeout_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._timeout_host = self._timeout_ev = None
+        self._spins = ctypes.c_longlong(int(os.environ.get("DGRAPH_B200_BARRIER_SPINS", str(1 << 26))))  # read once
         # opt-in (DGRAPH_B200_DEVICE_EPOCH=1, not yet run on hardware): barrier epochs counted in device memory, so a training step
         # with exchanges can be captured in a CUDA graph.  Fixed at construction: the two barrier forms must never be mixed.
         self.device_epoch = os.environ.get("DGRAPH_B200_DEVICE_EPOCH", "0") == "1"
         self._epoch_dev = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.arena: Optional[SymmetricArena] = None
-        if self._world > 1:
+        self._epoch_all_dev = torch.zeros(1, dtype=torch.int32, device=self.device)
+        if self._job_world > 1:
             mb = arena_mb or int(os.environ.get("DGRAPH_B200_ARENA_MB", "8192"))
-            self.arena = SymmetricArena(mb << 20, self._rank, self._world, self.device, group=self._group)
-            dist.barrier(group=self._group)
+            members = None
+            if group is not None and self._world != self._job_world:  # replica = a contiguous block of job ranks
+                members = dist.get_process_group_ranks(group)
+            self.arena = SymmetricArena(mb << 20, self._job_rank, self._job_world, self.device, group=None, members=members)
+            dist.barrier()
 
     # ---- small host-side helpers ---------------------------------------------------------------
     def all_gather_ints(self, vals: List[int]) -> List[List[int]]:
@@ -639,26 +671,47 @@ class PeerMemoryEngine(TorchDistEngine):
         return torch.empty(size, dtype=dtype, device=device)
 
     # ---- ordering --------------------------------------------------------------------------------
-    def barrier_on_stream(self):
-        """All ranks' streams have reached this point (epoch-flag barrier kernel; no host synchronisation)."""
-        if self._world == 1:
+    def barrier_on_stream(self, scope: str = "graph"):
+        """All ranks' streams have reached this point (epoch-flag barrier kernel; no host synchronisation).  ``scope="graph"``: the
+        ranks of this graph replica; ``scope="world"``: every rank of the job (hybrid layout; identical when there is one replica)."""
+        whole = scope == "world" and self._job_world != self._world
+        if (self._job_world if whole else self._world) == 1:
             return
         _pending.wait_all()  # no rank may run ahead of a pull that still reads its peers' slots
-        self._epoch += 1
-        spins = ctypes.c_longlong(int(os.environ.get("DGRAPH_B200_BARRIER_SPINS", str(1 << 26))))
+        self._epoch += 1  # a world barrier orders the replica too: slots read before it may be rewritten after it
+        if whole:
+            self._epoch_all += 1
+            pads, rank, world, epoch, epoch_dev = (self.arena.pad_table_all, self._job_rank, self._job_world, self._epoch_all,
+                                                   self._epoch_all_dev)
+        else:
+            pads, rank, world, epoch, epoch_dev = self.arena.pad_table, self._rank, self._world, self._epoch, self._epoch_dev
         if self.device_epoch:  # the kernel takes the epoch from (and advances) the device counter: capturable
-            N.check(N.lib().dgb_peer_barrier_dev(N.ptr(self.arena.pad_table), N.i32(self._rank), N.i32(self._world),
-                                                 N.ptr(self._epoch_dev), N.ptr(self._timeout_flag), spins, N.stream()),
-                    "dgb_peer_barrier_dev")
+            N.check(N.lib().dgb_peer_barrier_dev(N.ptr(pads), N.i32(rank), N.i32(world), N.ptr(epoch_dev),
+                                                 N.ptr(self._timeout_flag), self._spins, N.stream()), "dgb_peer_barrier_dev")
             return
-        N.check(N.lib().dgb_peer_barrier(N.ptr(self.arena.pad_table), N.i32(self._rank), N.i32(self._world),
-                                         ctypes.c_uint(self._epoch & 0xFFFFFFFF), N.ptr(self._timeout_flag),
-                                         ctypes.c_longlong(int(os.environ.get("DGRAPH_B200_BARRIER_SPINS", str(1 << 26)))),
-                                         N.stream()), "dgb_peer_barrier")
+        N.check(N.lib().dgb_peer_barrier(N.ptr(pads), N.i32(rank), N.i32(world), ctypes.c_uint(epoch & 0xFFFFFFFF),
+                                         N.ptr(self._timeout_flag), self._spins, N.stream()), "dgb_peer_barrier")
 
     def check_timeouts(self):
+        """Raise if any barrier since the last call gave up waiting (a rank did not arrive within ``DGRAPH_B200_BARRIER_SPINS`` polls of
+        ~64 ns each -- default 2^26, about 5 s; the kernels behind a timed-out barrier read incomplete peer data, so the step that
+        contains it is garbage).  Synchronises with the device."""
         if int(self._timeout_flag.item()) != 0:
-            raise RuntimeError("peer barrier timed out (a rank did not arrive)")
+            raise RuntimeError("peer barrier timed out (a rank did not arrive): results since the last check are invalid")
+
+    def poll_timeouts(self):
+        """Cheap per-step form of :meth:`check_timeouts` (called by the fused optimizer step): copies the flag into pinned host memory
+        on the stream and inspects the copy made one step earlier, so it never waits for the device -- a timeout surfaces one step
+        late instead of never."""
+        if self.arena is None or torch.cuda.is_current_stream_capturing():
+            return
+        if self._timeout_host is None:
+            self._timeout_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+            self._timeout_ev = torch.cuda.Event()
+        elif self._timeout_ev.query() and int(self._timeout_host[0]) != 0:
+            raise RuntimeError("peer barrier timed out (a rank did not arrive): the last optimizer steps used incomplete peer data")
+        self._timeout_host.copy_(self._timeout_flag, non_blocking=True)
+        self._timeout_ev.record()
 
     # ---- fused halo exchange ---------------------------------------------------------------------
     def side_stream(self) -> "torch.cuda.Stream":
@@ -731,33 +784,48 @@ class PeerMemoryEngine(TorchDistEngine):
     def symmetric_flat(self, key: str, numel: int, dtype=torch.float32) -> Tuple[torch.Tensor, int]:
         n = (numel + 3) // 4 * 4
         mx = max(c[0] for c in self.all_gather_ints([n]))
-        return self.slot_tensor(("flat", key), (mx,), dtype)
+        t, off = self.slot_tensor(("flat", key), (mx,), dtype)
+        if self._job_world != self._world:  # hybrid layout: replicas need not have allocated their slots in the same order
+            offs = torch.tensor([off], dtype=torch.long, device=self.device)
+            allo = [torch.zeros_like(offs) for _ in range(self._job_world)]
+            dist.all_gather(allo, offs)
+            self._flat_offsets[off] = [int(o) for o in allo]
+        return t, off
+
+    def _grad_table(self, flat_g_off):
+        """Pointers to the flat gradient buffer of every rank that holds a copy of the weights (the whole job)."""
+        if self._job_world != self._world:
+            return self.arena.ptr_table_all(self._flat_offsets[flat_g_off]), self._job_world
+        return self.arena.ptr_table(flat_g_off), self._world
 
     def adam_allreduce(self, flat_p, flat_g_off, flat_m, flat_v, n, lr, b1, b2, eps, wd, grad_scale, step):
-        self.barrier_on_stream()  # every rank finished writing its gradients
-        N.check(N.lib().dgb_adam_allreduce(N.ptr(flat_p), N.ptr(self.arena.ptr_table(flat_g_off)), N.i32(self._world),
-                                           N.ptr(flat_m), N.ptr(flat_v), N.ptr(None), N.i64(n), N.f32(lr), N.f32(b1),
-                                           N.f32(b2), N.f32(eps), N.f32(wd), N.f32(grad_scale), N.i32(step), N.stream()),
-                "dgb_adam_allreduce")
+        table, w = self._grad_table(flat_g_off)
+        self.barrier_on_stream("world")  # every rank finished writing its gradients
+        N.check(N.lib().dgb_adam_allreduce(N.ptr(flat_p), N.ptr(table), N.i32(w), N.ptr(flat_m), N.ptr(flat_v), N.ptr(None),
+                                           N.i64(n), N.f32(lr), N.f32(b1), N.f32(b2), N.f32(eps), N.f32(wd), N.f32(grad_scale),
+                                           N.i32(step), N.stream()), "dgb_adam_allreduce")
         N.count_launch(2)
-        self.barrier_on_stream()  # nobody zeroes its gradient buffer while a peer is still reading it
+        self.barrier_on_stream("world")  # nobody zeroes its gradient buffer while a peer is still reading it
+        self.poll_timeouts()
 
     def adam_allreduce_capturable(self, flat_p, flat_g_off, flat_m, flat_v, n, b1, b2, eps, wd, grad_scale, step_dev, dev_state):
         """``adam_allreduce`` with the step counter and the learning rate in device memory (CUDA-graph capture; needs the
         device-epoch barriers)."""
         assert self.device_epoch, "capturable multi-GPU steps need DGRAPH_B200_DEVICE_EPOCH=1 (set before the engine is created)"
-        self.barrier_on_stream()
-        N.check(N.lib().dgb_adam_allreduce_capturable(N.ptr(flat_p), N.ptr(self.arena.ptr_table(flat_g_off)), N.i32(self._world),
-                                                      N.ptr(flat_m), N.ptr(flat_v), N.ptr(None), N.i64(n), N.f32(b1), N.f32(b2),
-                                                      N.f32(eps), N.f32(wd), N.f32(grad_scale), N.ptr(step_dev),
-                                                      N.ptr(dev_state), N.stream()), "dgb_adam_allreduce_capturable")
+        table, w = self._grad_table(flat_g_off)
+        self.barrier_on_stream("world")
+        N.check(N.lib().dgb_adam_allreduce_capturable(N.ptr(flat_p), N.ptr(table), N.i32(w), N.ptr(flat_m), N.ptr(flat_v),
+                                                      N.ptr(None), N.i64(n), N.f32(b1), N.f32(b2), N.f32(eps), N.f32(wd),
+                                                      N.f32(grad_scale), N.ptr(step_dev), N.ptr(dev_state), N.stream()),
+                "dgb_adam_allreduce_capturable")
         N.count_launch(3)
-        self.barrier_on_stream()
+        self.barrier_on_stream("world")
+        self.poll_timeouts()
 
     def finalize(self) -> None:
         if self.arena is not None:
             torch.cuda.synchronize()
             if dist.is_initialized():
-                dist.barrier(group=self._group)
+                dist.barrier()
             self.arena.close()
             self.arena = None

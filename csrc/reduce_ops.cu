@@ -10,6 +10,9 @@
 namespace dgb {
 
 constexpr int CS_THREADS = 256;
+// Most blocks (= rows of partial sums) any column reduction here launches: 148 SMs x 4.  The allocation-free entry point below sizes
+// its built-in scratch array with the same constant, so raising it can never make a launch write past that array.
+constexpr int COLSUM_MAX_BLOCKS = 592;
 
 // partial[b, 0:N]   = sum over the block's rows of x[r, :]
 // partial[b, N:2N]  = sum of squares (only when SQ)
@@ -66,7 +69,7 @@ __global__ void colsum_final_kernel(const float* __restrict__ partial, int nbloc
 static int colsum_blocks(int64_t M) {
   int64_t b = (M + 1023) / 1024;
   if (b < 1) b = 1;
-  if (b > 592) b = 592;  // 148 SMs x 4
+  if (b > COLSUM_MAX_BLOCKS) b = COLSUM_MAX_BLOCKS;
   return (int)b;
 }
 
@@ -137,7 +140,7 @@ DGB_API int dgb_colsum_bf16(const void* x, int64_t ld, int64_t M, int N, int wit
 
 namespace dgb {
 constexpr int COLSUM_NOALLOC_MAX_WIDTH = 1024;
-constexpr int COLSUM_NOALLOC_MAX_BLOCKS = 592;  // == upper bound of colsum_blocks()
+constexpr int COLSUM_NOALLOC_MAX_BLOCKS = COLSUM_MAX_BLOCKS;  // the one cap colsum_blocks() uses
 constexpr int COLSUM_NOALLOC_MAX_DEVICES = 64;
 }  // namespace dgb
 
@@ -185,5 +188,6 @@ DGB_API int dgb_colsum_bf16_noalloc(const void* x, int64_t ld, int64_t M, int N,
     DGB_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * width, (cudaStream_t)stream));
     return 0;
   }
+  static_assert(dgb::COLSUM_NOALLOC_MAX_BLOCKS >= dgb::COLSUM_MAX_BLOCKS, "built-in scratch must cover every launch");
   return dgb::colsum_launch(x, ld, M, N, with_sq, scratch, out, (cudaStream_t)stream);
 }

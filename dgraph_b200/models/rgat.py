@@ -152,14 +152,16 @@ class CommAwareRGAT(nn.Module):
             self.layers.append(nn.ModuleList([
                 CommAwareGAT(cin, hidden_channels, heads=heads, bias=True, residual=True, comm=comm, hetero=True)
                 for _ in range(num_relations)]))
-            self.bn_layers.append(DistributedBatchNorm1D(hidden_channels, recompute=True, comm=comm))
+            # the ReLU that follows every BatchNorm (in_place_relus below, kept for the reference's module list) runs inside the
+            # normalisation kernel
+            self.bn_layers.append(DistributedBatchNorm1D(hidden_channels, recompute=True, comm=comm, activation="relu"))
             self.skip_layers.append(nn.Linear(cin, hidden_channels))
         self.in_place_relus = nn.ModuleList([nn.ReLU(inplace=True) for _ in range(num_layers * 3)])
         self.in_place_dropouts = nn.ModuleList([nn.Dropout(dropout) for _ in range(num_layers * 3)])
         self.mlp = nn.Sequential(
             nn.Linear(hidden_channels, hidden_channels),
-            DistributedBatchNorm1D(hidden_channels, recompute=True, comm=comm),
-            nn.ReLU(inplace=True),
+            DistributedBatchNorm1D(hidden_channels, recompute=True, comm=comm, activation="relu"),
+            nn.Identity(),  # position of the reference's nn.ReLU (the activation is fused into the BatchNorm above)
             nn.Dropout(dropout, inplace=False),
             nn.Linear(hidden_channels, out_channels),
         )
@@ -178,9 +180,8 @@ class CommAwareRGAT(nn.Module):
                 temp[dst_t] = temp[dst_t] + self.layers[i][j](outs[dst_t], x_j=outs[src_t], comm_plan=plan)
             outs = []
             for t_idx, t in enumerate(temp):
-                y = self.bn_layers[i](t)
+                y = self.bn_layers[i](t)  # BatchNorm + ReLU
                 y = _2d(y) if fused else y
-                y = self.in_place_relus[(i * 3 + t_idx) % len(self.in_place_relus)](y)
                 outs.append(self.in_place_dropouts[(i * 3 + t_idx) % len(self.in_place_dropouts)](y))
         if bool(int(os.getenv("RGAT_DUMMY_ALL_PARAMS_USE", "0"))):
             dummy = sum((t.reshape(-1)[:1].sum() * 0.0) for t in outs)

@@ -15,6 +15,7 @@ import torch
 from torch import nn
 from torch.autograd import Function
 
+from dgraph_b200.ops import _native as N
 from dgraph_b200.ops.reduce import colsum
 
 
@@ -43,6 +44,69 @@ def _stats(x, comm):
     return mean, var, n
 
 
+def _native_ok(x) -> bool:
+    return (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.shape[1] % 8 == 0 and 8 <= x.shape[1] <= 1024
+            and x.stride(1) == 1 and x.stride(0) % 8 == 0 and x.data_ptr() % 16 == 0 and N.use_native(x))
+
+
+class _NativeBN(Function):
+    """CUDA bf16 path (``csrc/bn_ops.cu``): per direction one statistics kernel pair, ONE all-reduce and one elementwise kernel that
+    reads bf16 and writes bf16 -- no fp32 copy of ``[N, F]``, ``x_hat`` is recomputed from ``x`` instead of stored.  ``act=1`` fuses
+    the ReLU that follows the layer in RGAT (its backward masks ``dy`` with the saved output)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, comm, eps, act):
+        M, F = x.shape
+        dev = x.device
+        buf = torch.empty(2 * F + 1, dtype=torch.float32, device=dev)
+        buf[: 2 * F] = colsum(x, with_sq=True)
+        buf[2 * F:].fill_(float(M))
+        comm.all_reduce(buf)
+        stats = torch.empty((3, F), dtype=torch.float32, device=dev)  # mean, var, rstd
+        lib = N.lib()
+        N.check(lib.dgb_bn_finalize_stats(N.ptr(buf), N.i32(F), N.f32(eps), N.ptr(stats[0]), N.ptr(stats[1]), N.ptr(stats[2]),
+                                          N.stream()), "dgb_bn_finalize_stats")
+        g = None if gamma is None else gamma.detach().reshape(-1).float().contiguous()
+        b = None if beta is None else beta.detach().reshape(-1).float().contiguous()
+        y = torch.empty((M, F), dtype=torch.bfloat16, device=dev)
+        N.check(lib.dgb_bn_apply_bf16(N.ptr(x), N.i64(x.stride(0)), N.i64(M), N.i32(F), N.ptr(stats[0]), N.ptr(stats[2]), N.ptr(g),
+                                      N.ptr(b), N.i32(act), N.ptr(y), N.i64(F), N.stream()), "dgb_bn_apply_bf16")
+        N.count_launch(2)
+        ctx.save_for_backward(x, y if act else None, g, stats, buf)
+        ctx.comm, ctx.act, ctx.has_affine, ctx.gshape = comm, act, gamma is not None, (None if gamma is None else gamma.shape)
+        mean, var = stats[0].view(1, -1), stats[1].view(1, -1)
+        ctx.mark_non_differentiable(mean, var)
+        return y, mean, var
+
+    @staticmethod
+    def backward(ctx, gy, _gm, _gv):
+        x, y, g, stats, buf = ctx.saved_tensors
+        M, F = x.shape
+        dev = x.device
+        gy = gy.contiguous()
+        if gy.dtype != torch.bfloat16:
+            gy = gy.to(torch.bfloat16)
+        lib = N.lib()
+        lib.dgb_bn_bwd_scratch_bytes.restype = __import__("ctypes").c_int64
+        scratch = torch.empty(int(lib.dgb_bn_bwd_scratch_bytes(N.i32(F))) // 4, dtype=torch.float32, device=dev)
+        sums = torch.empty(2 * F, dtype=torch.float32, device=dev)
+        ld_y = 0 if y is None else y.stride(0)
+        N.check(lib.dgb_bn_bwd_stats_bf16(N.ptr(gy), N.i64(F), N.ptr(x), N.i64(x.stride(0)), N.ptr(y), N.i64(ld_y), N.i64(M), N.i32(F),
+                                          N.ptr(stats[0]), N.ptr(stats[2]), N.ptr(scratch), N.ptr(sums), N.stream()),
+                "dgb_bn_bwd_stats_bf16")
+        local = sums.clone() if ctx.has_affine else None  # dgamma / dbeta are summed over the ranks by the optimizer's all-reduce
+        ctx.comm.all_reduce(sums)
+        dx = torch.empty((M, F), dtype=torch.bfloat16, device=dev)
+        N.check(lib.dgb_bn_bwd_dx_bf16(N.ptr(gy), N.i64(F), N.ptr(x), N.i64(x.stride(0)), N.ptr(y), N.i64(ld_y), N.i64(M), N.i32(F),
+                                       N.ptr(stats[0]), N.ptr(stats[2]), N.ptr(g), N.ptr(sums), N.ptr(buf[2 * F:]), N.ptr(dx),
+                                       N.i64(F), N.stream()), "dgb_bn_bwd_dx_bf16")
+        N.count_launch(3)
+        dg = db = None
+        if ctx.has_affine:
+            db, dg = local[:F].view(ctx.gshape), local[F:].view(ctx.gshape)
+        return dx, dg, db, None, None, None
+
+
 class DistributedBN_Impl(Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, comm, eps, recompute):
@@ -66,13 +130,17 @@ class DistributedBN_Impl(Function):
         buf = torch.empty(2 * F, dtype=cd, device=gy.device)
         buf[:F] = gyf.sum(0)
         buf[F:] = (gyf * x_hat).sum(0)
+        # gamma / beta are replicated parameters: every rank returns the partial sum over ITS rows and the optimizer's gradient
+        # all-reduce adds the ranks up, like every other weight gradient (the reference hands every rank the global sum and lets
+        # DDP average it, distributed_layers.py:62-68); dx needs the global sums
+        local = buf.clone()
         ctx.comm.all_reduce(buf)
         dbeta, dgamma = buf[:F], buf[F:]
         gscale = gamma.to(cd).view(1, -1) if gamma is not None else 1.0
         n = ctx.n
         dx = (gscale * rstd) * (gyf - dbeta / n - x_hat * (dgamma / n))
-        dg = dgamma.view(1, -1).to(gamma.dtype) if gamma is not None else None
-        db = dbeta.view(1, -1).to(gamma.dtype) if gamma is not None else None
+        dg = local[F:].view(1, -1).to(gamma.dtype) if gamma is not None else None
+        db = local[:F].view(1, -1).to(gamma.dtype) if gamma is not None else None
         return dx.to(gy.dtype), dg, db, None, None, None
 
 
@@ -82,8 +150,12 @@ class DistributedBN_with_Recompute(DistributedBN_Impl):
 
 class DistributedBatchNorm1D(nn.Module):
     def __init__(self, num_features, eps=1e-5, momentum=0.1, affine=True, track_running_stats=True, recompute=False,
-                 comm=None):
+                 comm=None, activation=None):
+        """``activation="relu"``: the ReLU that follows the layer is applied by the same kernel (CUDA bf16 path) / right after the
+        normalisation (elsewhere); the module then returns the activated tensor."""
         super().__init__()
+        assert activation in (None, "relu")
+        self.activation = activation
         if affine:
             self.gamma = nn.Parameter(torch.ones(1, num_features))
             self.beta = nn.Parameter(torch.zeros(1, num_features))
@@ -106,8 +178,13 @@ class DistributedBatchNorm1D(nn.Module):
         elif x.dim() != 2:
             raise ValueError(f"Expected 2D or 3D input (got {x.dim()}D input)")
         comm = self.comm if self.comm is not None else _NoComm()
+        act = getattr(self, "activation", None)
         if self.training:
-            y, mean, var = DistributedBN_Impl.apply(x, self.gamma, self.beta, comm, self.eps, self.recompute)
+            if _native_ok(x):
+                y, mean, var = _NativeBN.apply(x, self.gamma, self.beta, comm, self.eps, 1 if act == "relu" else 0)
+                act = None
+            else:
+                y, mean, var = DistributedBN_Impl.apply(x, self.gamma, self.beta, comm, self.eps, self.recompute)
             if self.track_running_stats:
                 with torch.no_grad():
                     self.num_batches_tracked += 1
@@ -119,6 +196,8 @@ class DistributedBatchNorm1D(nn.Module):
             if self.gamma is not None:
                 y = y * self.gamma.to(cd) + self.beta.to(cd)
             y = y.to(x.dtype)
+        if act == "relu":
+            y = torch.relu(y)
         return y.unsqueeze(0)
 
 

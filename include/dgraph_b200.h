@@ -54,6 +54,20 @@ int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slot_map, c
 int dgb_mul_cnt(const void* g, int64_t ld_g, const unsigned short* cnt, int64_t ld_c, void* out, int64_t ld_o, int64_t rows,
                 int H, void* stream);
 
+/* ---- distributed BatchNorm (csrc/bn_ops.cu) ----------------------------------------------------------------------------
+ * Reference: DistributedBatchNorm1D (experiments/OGB-LSC/distributed_layers.py:22-74).  Statistics come from dgb_colsum_bf16
+ * (with_sq) + one all-reduce; these kernels do the rest without an fp32 copy of the activations.  act: 0 none, 1 ReLU (its
+ * backward masks dy with the saved output y). */
+int dgb_bn_apply_bf16(const void* x, int64_t ld_x, int64_t M, int N, const float* mean, const float* rstd, const float* gamma,
+                      const float* beta, int act, void* y, int64_t ld_y, void* stream);
+int dgb_bn_finalize_stats(const float* buf, int N, float eps, float* mean, float* var, float* rstd, void* stream);
+int64_t dgb_bn_bwd_scratch_bytes(int N);
+int dgb_bn_bwd_stats_bf16(const void* dy, int64_t ld_dy, const void* x, int64_t ld_x, const void* y, int64_t ld_y, int64_t M, int N,
+                          const float* mean, const float* rstd, float* scratch, float* sums, void* stream);
+int dgb_bn_bwd_dx_bf16(const void* dy, int64_t ld_dy, const void* x, int64_t ld_x, const void* y, int64_t ld_y, int64_t M, int N,
+                       const float* mean, const float* rstd, const float* gamma, const float* sums, const float* n_rows, void* dx,
+                       int64_t ld_dx, void* stream);
+
 /* ---- weight packing (csrc/pack_ops.cu) -------------------------------------------------------------------------------
  * fp32 W = [W_i | W_j] of GraphConvLayer.conv (experiments/OGB/GCN.py:31) -> bf16 wcat [2H, Fp], wcat_t [Fp, 2H] (optional),
  * fp32 bcat [2H] (optional) in one launch per layer and optimizer step. */

@@ -81,16 +81,30 @@ class CommAwareGAT(nn.Module):
     # ---- fused path: edges live with their destination; only source features cross ranks --------------------
     def _forward_halo(self, x, pattern: CommunicationPattern, x_j=None):
         C = self.conv1.out_features
+        src_local = x if (x_j is None or not self.hetero) else x_j
+        kp = pattern.kernel_plan(x.device)
+        if x.is_cuda and x.dtype == torch.bfloat16 and C % 8 == 0:
+            # The attention logit halves are linear in the layer input: s_i = (x W^T) a_i + b = x (a_i W)^T + b, s_j likewise.  They
+            # leave the projection GEMM as extra output columns (rows a_i W / a_j W appended to W), so neither an fp32 copy of the
+            # projected matrices nor a separate mat-vec exists, and s_j travels with its row through the halo exchange.
+            W = self.conv1.weight
+            a = self.project_message.weight.view(-1)
+            pad = W.new_zeros((7, W.shape[1]))
+            w_dst = torch.cat([(a[:C] @ W).unsqueeze(0), pad]).to(x.dtype)  # [8, F_in]: column 0 = s_i
+            w_src = torch.cat([W, (a[C:] @ W).unsqueeze(0), pad]).to(x.dtype)  # [C + 8, F_in]: columns [0, C) = h_j, column C = s_j
+            s_i = linear(x, w_dst)[:, 0].float() + self.project_message.bias.float()
+            hs = linear(src_local, w_src)
+            aug = HaloExchange(self.comm).augmented(hs, pattern)  # exchange [h_j | s_j] rows (C + 8 wide)
+            out = seg_softmax_aggregate(s_i, aug[:, C].float(), aug[:, :C], kp, 0.2)
+            return self._apply_res_and_bias(out, x)
         w = self.conv1.weight.to(x.dtype)
         h = linear(x, w)
-        src_local = x if (x_j is None or not self.hetero) else x_j
         h_src_local = h if src_local is x else linear(src_local, w)
         h_aug = HaloExchange(self.comm).augmented(h_src_local, pattern)  # exchange projected rows (C wide)
         sdt = torch.float64 if x.dtype == torch.float64 else torch.float32  # logits in >= fp32
         a = self.project_message.weight.to(sdt).view(-1)
         s_i = h.to(sdt) @ a[:C] + self.project_message.bias.to(sdt)
         s_j = h_aug.to(sdt) @ a[C:]
-        kp = pattern.kernel_plan(x.device)
         out = seg_softmax_aggregate(s_i, s_j, h_aug, kp, 0.2)
         return self._apply_res_and_bias(out, x)
 

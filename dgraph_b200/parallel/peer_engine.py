@@ -445,6 +445,7 @@ class PeerMemoryEngine(TorchDistEngine):
         self._by_off: Dict[int, dict] = {}
         self._sym_rows: Dict[int, Tuple] = {}
         self._flat_offsets: Dict[int, List[int]] = {}
+        self._ar_parity = 0
         self._timeout_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._timeout_host = self._timeout_ev = None
         self._spins = ctypes.c_longlong(int(os.environ.get("DGRAPH_B200_BARRIER_SPINS", str(1 << 26))))  # read once
@@ -756,15 +757,17 @@ class PeerMemoryEngine(TorchDistEngine):
 
     # ---- small all-reduces over peer memory --------------------------------------------------------
     def all_reduce(self, tensor, op="sum"):
-        """Opt-in (``DGRAPH_B200_PEER_ALLREDUCE=1``, not yet run end to end on hardware): fp32 sums of up to 1 M elements -- BatchNorm
-        statistics, loss scalars -- are published in a symmetric slot and summed by ONE kernel that reads every peer's copy
-        (``dgb_allreduce_sum_f32``; same summation order on every rank, so the results are bit-identical across ranks).  No NCCL
-        call, hence capturable with the device-epoch barriers.  Everything else takes the NCCL path."""
-        if (self._world > 1 and op == "sum" and os.environ.get("DGRAPH_B200_PEER_ALLREDUCE", "0") == "1" and tensor.is_cuda
-                and tensor.dtype == torch.float32 and tensor.is_contiguous() and 0 < tensor.numel() <= (1 << 20)):
+        """Small fp32 sums (BatchNorm statistics, loss scalars; up to 64 K elements) are published in a symmetric slot and summed by
+        ONE kernel that reads every peer's copy (``dgb_allreduce_sum_f32``; same summation order on every rank, so the results are
+        bit-identical across ranks): flag barrier + kernel instead of an NCCL launch, and capturable with the device-epoch barriers.
+        Two slots alternate so that back-to-back reductions need no extra barrier before the slot is rewritten.
+        ``DGRAPH_B200_PEER_ALLREDUCE=0`` sends everything through NCCL, as does anything larger or not a sum."""
+        if (self._world > 1 and op == "sum" and os.environ.get("DGRAPH_B200_PEER_ALLREDUCE", "1") == "1" and tensor.is_cuda
+                and tensor.dtype == torch.float32 and tensor.is_contiguous() and 0 < tensor.numel() <= (1 << 16)):
             n = tensor.numel()
             n4 = (n + 3) // 4 * 4
-            buf, off = self.slot_tensor(("allreduce", n4), (n4,), torch.float32, ring=False)
+            self._ar_parity ^= 1
+            buf, off = self.slot_tensor(("allreduce", n4, self._ar_parity), (n4,), torch.float32, ring=False)
             if n4 != n:
                 buf[n:].zero_()
             buf[:n].copy_(tensor.reshape(-1))

@@ -52,9 +52,11 @@ def parse_args():
     ap.add_argument("--lr", type=float, default=1e-3)
     ap.add_argument("--engine", default=None, help="override DGRAPH_B200_ENGINE (torch | peer)")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--cuda-graph", action="store_true",
-                    help="capture the whole step (fwd+loss+bwd+Adam) in a CUDA graph and replay it (measured on 1 GPU; with several GPUs it "
-                         "switches the peer engine to device-resident barrier epochs -- experimental, not yet run on hardware)")
+    ap.add_argument("--cuda-graph", dest="cuda_graph", action="store_true", default=None,
+                    help="capture the whole step (zero_grad+fwd+loss+bwd+Adam) in a CUDA graph and replay it; with several GPUs the peer "
+                         "engine then keeps its barrier epochs in device memory.  Default: on with several GPUs (the per-rank step is "
+                         "short enough for the host to matter once every step's loss is read back), off with one")
+    ap.add_argument("--no-cuda-graph", dest="cuda_graph", action="store_false")
     ap.add_argument("--cpu", action="store_true", help="CPU/gloo plumbing run (tiny graphs only)")
     return ap.parse_args()
 
@@ -140,7 +142,9 @@ def run_ours(args):
     rank, world, local, dev = setup_dist(args)
     if args.engine:
         os.environ["DGRAPH_B200_ENGINE"] = args.engine
-    if args.cuda_graph and world > 1:  # experimental: barrier epochs in device memory make the multi-GPU step capturable
+    if args.cuda_graph is None:
+        args.cuda_graph = world > 1 and not args.cpu
+    if args.cuda_graph and world > 1:  # barrier epochs in device memory make the multi-GPU step capturable
         os.environ["DGRAPH_B200_DEVICE_EPOCH"] = "1"
     from dgraph_b200 import Communicator
     from dgraph_b200.data import make_graph, contiguous_partition, node_features_and_labels
@@ -192,15 +196,6 @@ def run_ours(args):
         opt.step()
         return loss
 
-    if use_graph:  # same work per step, replayed with one cudaGraphLaunch (utils/cuda_graph.py)
-        from dgraph_b200.utils.cuda_graph import GraphedTrainStep
-
-        eager_step = step
-        graphed = GraphedTrainStep(forward_loss, opt, (xh.to(dev), yh.to(dev)), warmup=2)
-
-        def step(x_dev, y_dev):  # noqa: F811
-            return graphed(x_dev, y_dev).clone()
-
     def sync():
         if world > 1:
             dist.barrier()
@@ -237,6 +232,13 @@ def run_ours(args):
     x_dev, y_dev = feature_buffer(0), yh.to(dev, non_blocking=True)
     x_dev.copy_(xh, non_blocking=True)
     losses = []
+    if use_graph:  # same work per step, replayed with one cudaGraphLaunch (utils/cuda_graph.py); inputs stay in symmetric memory
+        from dgraph_b200.utils.cuda_graph import GraphedTrainStep
+
+        graphed = GraphedTrainStep(forward_loss, opt, (x_dev, y_dev), warmup=2, static_inputs=(x_dev, y_dev))
+
+        def step(x_in, y_in):  # noqa: F811
+            return graphed(x_in, y_in).clone()
 
     def loop_dev(k):
         for _ in range(k):
@@ -265,7 +267,10 @@ def run_ours(args):
         else:
             from dgraph_b200.utils.e2e import make_e2e_loop
 
-            bufs = [(x_dev, y_dev), (feature_buffer(1), torch.empty_like(yh, device=dev))]
+            if use_graph:  # the graph owns x_dev / y_dev: host copies land in two separate buffers and are copied in before each replay
+                bufs = [(torch.empty_like(xh, device=dev), torch.empty_like(yh, device=dev)) for _ in range(2)]
+            else:
+                bufs = [(x_dev, y_dev), (feature_buffer(1), torch.empty_like(yh, device=dev))]
             loop_e2e = make_e2e_loop(step, (xh, yh), bufs, e2e_losses)  # same loop as the reference arm (baseline/ref_bench.py)
 
         loop_e2e(max(2, args.warmup))

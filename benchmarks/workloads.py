@@ -36,6 +36,18 @@ def _pin(t):
     return t.cpu().contiguous().pin_memory()
 
 
+def _graphed(args, world, comm, forward_loss, opt, example_inputs):
+    """`--cuda-graph`: zero_grad + forward + loss + backward + optimizer step captured once and replayed (`utils/cuda_graph.py`); with
+    several ranks the peer engine's barrier epochs live in device memory (`DGRAPH_B200_DEVICE_EPOCH=1`, set in `run` before the
+    engine exists).  Returns the replacement for the eager step, or None."""
+    if not getattr(args, "cuda_graph", False) or not (world == 1 or getattr(comm.engine, "device_epoch", False)):
+        return None
+    from dgraph_b200.utils.cuda_graph import GraphedTrainStep
+
+    g = GraphedTrainStep(forward_loss, opt, example_inputs, warmup=2)
+    return lambda *xs: g(*xs).clone()
+
+
 # ------------------------------------------------------------------------------------------------------------------------------
 def symmetric_shard(V, E, rank, world, dev, cut, window=8192, seed=0):
     """In-neighbour lists of the vertices this rank owns, `[E_loc, 2]` (owned vertex, neighbour) in global ids, of an UNDIRECTED
@@ -112,6 +124,8 @@ def build_papers100m(args, comm, rank, world, dev):
         opt.step()
         return loss
 
+    use_graph = False  # a 25 ms step is not launch-bound
+
     def alloc(tag):
         return ex.symmetric_rows(pat, F, torch.bfloat16, device=dev, tag=tag), torch.empty(n, dtype=torch.long, device=dev)
 
@@ -124,7 +138,7 @@ def build_papers100m(args, comm, rank, world, dev):
                 "global_batch": "full graph", "seq_len": None, "parallelism": f"graph-partition x{world} + DP weights",
                 "partition": f"contiguous blocks, cut_fraction={args.cut}, undirected, duplicate-free, built from per-rank edge shards",
                 "hidden": args.hidden, "l2": "inputs larger than L2", "engine": type(comm.engine).__name__,
-                "labelled": "1 % of the vertices"})
+                "labelled": "1 % of the vertices", "cuda_graph": use_graph})
 
 
 # ------------------------------------------------------------------------------------------------------------------------------
@@ -143,14 +157,21 @@ def build_graphcast(args, comm, rank, world, dev):
     xh, yh = _pin(item["invar"].to(torch.bfloat16)), _pin(item["outvar"].to(torch.bfloat16))
     torch.manual_seed(0)
     model = DGraphCast(cfg, comm).to(dev)
-    opt = FusedAdam(model.parameters(), lr=cfg.training.lr, comm=comm)
+    want_graph = bool(getattr(args, "cuda_graph", False)) and (world == 1 or getattr(comm.engine, "device_epoch", False))
+    opt = FusedAdam(model.parameters(), lr=cfg.training.lr, comm=comm, capturable=want_graph)
+
+    def forward_loss(x, y):
+        return torch.nn.functional.mse_loss(model(x, sg).float(), y.float())
 
     def step(x, y):
         opt.zero_grad()
-        loss = torch.nn.functional.mse_loss(model(x, sg).float(), y.float())
+        loss = forward_loss(x, y)
         loss.backward()
         opt.step()
         return loss
+
+    graphed = _graphed(args, world, comm, forward_loss, opt, (xh.to(dev), yh.to(dev)))
+    step = graphed or step
 
     def alloc(tag):
         return torch.empty_like(xh, device=dev), torch.empty_like(yh, device=dev)
@@ -164,7 +185,8 @@ def build_graphcast(args, comm, rank, world, dev):
                 "graph": f"grid {cfg.data.latlon_res[0]}x{cfg.data.latlon_res[1]} = {cfg.data.latlon_res[0] * cfg.data.latlon_res[1]} nodes, "
                          f"icosahedral multimesh level {cfg.model.mesh_level}",
                 "global_batch": 1, "seq_len": None, "parallelism": f"graph-partition x{world} + DP weights",
-                "l2": "inputs larger than L2", "engine": type(comm.engine).__name__})
+                "l2": "inputs larger than L2", "engine": type(comm.engine).__name__, "cuda_graph": graphed is not None,
+                "fused_mlp_block": os.environ.get("DGRAPH_B200_FUSED_MLP", "0") == "1"})
 
 
 # ------------------------------------------------------------------------------------------------------------------------------
@@ -185,21 +207,28 @@ def build_rgat(args, comm, rank, world, dev):
     torch.manual_seed(0)
     model = CommAwareRGAT(ds.num_features, ds.num_classes, hidden, ds.num_relations, mc.num_layers, mc.heads, comm, dropout=mc.dropout).to(dev)
     model.first_relation_only = args.rgat_relations == "first"
-    opt = FusedAdam(model.parameters(), lr=tc.lr, weight_decay=tc.weight_decay, comm=comm, grad_average=False)
+    want_graph = bool(getattr(args, "cuda_graph", False)) and (world == 1 or getattr(comm.engine, "device_epoch", False))
+    opt = FusedAdam(model.parameters(), lr=tc.lr, weight_decay=tc.weight_decay, comm=comm, grad_average=False, capturable=want_graph)
     train_idx = ds.get_mask("train").to(dev)
     target = ds.get_target("train").to(dev)
     n_global = GetGlobalVal(train_idx.numel(), comm, dev)
     feats_h = tuple(_pin(f.to(torch.bfloat16)) for f in ds.features)
     E_global = float(sum(int(e.shape[0]) for e in ds.edges)) if hasattr(ds, "edges") else 0.0
 
-    def step(*xs):
-        opt.zero_grad()
+    def forward_loss(*xs):
         out = model(list(xs), RELATIONS, ds.patterns)
         out = out[0] if out.dim() == 3 else out
-        loss = torch.nn.functional.cross_entropy(out.index_select(0, train_idx).float(), target, reduction="sum") / n_global
+        return torch.nn.functional.cross_entropy(out.index_select(0, train_idx).float(), target, reduction="sum") / n_global
+
+    def step(*xs):
+        opt.zero_grad()
+        loss = forward_loss(*xs)
         loss.backward()
         opt.step()
         return loss
+
+    graphed = _graphed(args, world, comm, forward_loss, opt, tuple(f.to(dev) for f in feats_h))
+    step = graphed or step
 
     def alloc(tag):
         return tuple(torch.empty_like(f, device=dev) for f in feats_h)
@@ -213,7 +242,7 @@ def build_rgat(args, comm, rank, world, dev):
                          f"institutions, {sc.num_features}-d, {sc.num_classes} classes (reference SyntheticDatasetConfig x{m})",
                 "edges": E_global, "global_batch": "full graph", "seq_len": None, "parallelism": f"graph-partition x{world} + DP weights",
                 "l2": "flushed implicitly: working set >> L2 only at x8; at x1 it is L2-resident (stated)",
-                "engine": type(comm.engine).__name__})
+                "engine": type(comm.engine).__name__, "cuda_graph": graphed is not None})
 
 
 # ------------------------------------------------------------------------------------------------------------------------------
@@ -307,6 +336,8 @@ def run(args, out, clock_sampler):
         os.environ.setdefault("DGRAPH_B200_ARENA_MB", "98304")
     elif args.config == "papers100m":
         os.environ.setdefault("DGRAPH_B200_ARENA_MB", "24576")
+    if getattr(args, "cuda_graph", False) and int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        os.environ["DGRAPH_B200_DEVICE_EPOCH"] = "1"  # barrier epochs in device memory: steps with exchanges become capturable
     from _common import cleanup, init_distributed
     from dgraph_b200.ops import _native
 

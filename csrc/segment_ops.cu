@@ -177,10 +177,11 @@ __device__ __forceinline__ void seg_accumulate(const uint4& v, const uint4& v2, 
 // (p.rows_per_group) and keeps the grid non-persistent: a grid-strided persistent variant was measured 35 % slower because the
 // hardware block scheduler otherwise keeps all SMs inside one compact window of rows, which is what makes the evict_last L2
 // policy on the gathered rows pay.
-template <int MODE, int G, int NC, bool HALO, bool FULL, int AUX>
+template <int MODE, int G, int NC, bool HALO, bool FULL, int AUX, bool TAILPF>
 __device__ __forceinline__ void seg_rows(const SegParams& p, const char* const* s_peer, int r, const int stride, const int n_rows,
                                          const int g, const unsigned gmask) {
   constexpr int UNROLL = 4;
+  constexpr bool PF = TAILPF && HALO && NC == 1 && (MODE == SEG_ADD_RELU || MODE == SEG_SUM);  // prefetch the tail (remote) edges of a row
   constexpr bool USES_MASK = (MODE == SEG_ADD_RELU && AUX != 0) || MODE == SEG_MASKED_SUM;
   constexpr bool MAPPED = USES_MASK && AUX == 2;
   const int nchunk = FULL ? (G * NC) : (p.H >> 3);  // 8-column chunks per row
@@ -261,8 +262,31 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, const char* const* 
         if (MAPPED) my_s = p.slot_map[base + g];
       }
     }
+    // Pull kernels: the remote neighbours of a row sort behind its local ones, i.e. into the tail of its last chunk.  Their loads are
+    // issued here, before the local neighbours are processed, and consumed after them -- in the same order as without the prefetch,
+    // so results are bit-identical -- which gives the NVLink round trip (3-4x a local L2 hit) the whole row to complete.
+    int n_main = n, nt = 0;
+    uint4 vt[PF ? 4 : 1][NC];
+    float wt[PF ? 4 : 1];
+    int st[PF ? 4 : 1];
+    if (PF && base + G >= end) {
+      nt = min(4, n);
+      n_main = n - nt;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (u < nt) {
+          const int j = __shfl_sync(gmask, my_j, n_main + u, G);
+          wt[u] = (MODE == SEG_SUM) ? __shfl_sync(gmask, my_w, n_main + u, G) : 1.f;
+          st[u] = MAPPED ? __shfl_sync(gmask, my_s, n_main + u, G) : 0;
+          const char* row = src_row<HALO>(p, s_peer, src_lane, g * 16, j);
+#pragma unroll
+          for (int c = 0; c < NC; ++c)
+            if (colok[c]) vt[u][c] = ldg_any_hint_v4(row + c * G * 16, pol_keep);
+        }
+      }
+    }
     int t0 = 0;
-    for (; t0 + UNROLL <= n; t0 += UNROLL) {  // full groups: no per-edge predication
+    for (; t0 + UNROLL <= n_main; t0 += UNROLL) {  // full groups: no per-edge predication
       uint4 v[UNROLL][NC], v2[UNROLL][NC];
       uint32_t mb[UNROLL][NC];
       float w[UNROLL];
@@ -297,7 +321,7 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, const char* const* 
       }
       if (USES_MASK && !MAPPED) mp += UNROLL * nchunk;
     }
-    for (; t0 < n; ++t0) {  // tail
+    for (; t0 < n_main; ++t0) {  // tail
       const int j = __shfl_sync(gmask, my_j, t0, G);
       const float w = (MODE == SEG_SUM) ? __shfl_sync(gmask, my_w, t0, G) : 1.f;
       const int sl = MAPPED ? __shfl_sync(gmask, my_s, t0, G) : 0;
@@ -316,6 +340,23 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, const char* const* 
         }
       }
       if (USES_MASK && !MAPPED) mp += nchunk;
+    }
+    if (PF) {  // the prefetched tail edges, in slot order
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (u < nt) {
+#pragma unroll
+          for (int c = 0; c < NC; ++c) {
+            if (colok[c]) {
+              uint32_t mout = 0;
+              seg_accumulate<MODE>(vt[u][c], vt[u][c], rop[c], rop2[c], wt[u], weighted, 0u, acc[c], cn2[c], mout);
+              if (MODE == SEG_ADD_RELU && AUX == 1) stg_cs_u8(mp + c * G, mout);
+              if (MODE == SEG_ADD_RELU && AUX == 2) stg_cs_u8(mask_lane + (int64_t)st[u] * nchunk + c * G, mout);
+            }
+          }
+          if (USES_MASK && !MAPPED) mp += nchunk;
+        }
+      }
     }
   }
 
@@ -360,8 +401,8 @@ __device__ __forceinline__ void seg_rows(const SegParams& p, const char* const* 
   }  // while rows
 }
 
-template <int MODE, int G, int NC, bool HALO>
-__global__ void __launch_bounds__(256, (NC == 1) ? (MODE == SEG_SUM ? 5 : 4) : 1) seg_reduce_kernel(const SegParams p) {
+template <int MODE, int G, int NC, bool HALO, bool TAILPF>
+__global__ void __launch_bounds__(256, (NC == 1) ? (TAILPF ? 3 : (MODE == SEG_SUM ? 5 : 4)) : 1) seg_reduce_kernel(const SegParams p) {
   __shared__ const char* s_peer[HALO ? kMaxPeers : 1];
   if (HALO) {
     if ((int)threadIdx.x < p.world) s_peer[threadIdx.x] = reinterpret_cast<const char*>(p.peer_base[threadIdx.x]);
@@ -380,17 +421,17 @@ __global__ void __launch_bounds__(256, (NC == 1) ? (MODE == SEG_SUM ? 5 : 4) : 1
   if (MODE == SEG_ADD_RELU || MODE == SEG_MASKED_SUM) {
     const int aux = p.mask == nullptr ? 0 : (p.slot_map ? 2 : 1);
     if (full) {
-      if (aux == 2) seg_rows<MODE, G, NC, HALO, true, 2>(p, s_peer, r, stride, r_end, g, gmask);
-      else if (aux == 1) seg_rows<MODE, G, NC, HALO, true, 1>(p, s_peer, r, stride, r_end, g, gmask);
-      else if (MODE == SEG_ADD_RELU) seg_rows<MODE, G, NC, HALO, true, 0>(p, s_peer, r, stride, r_end, g, gmask);
+      if (aux == 2) seg_rows<MODE, G, NC, HALO, true, 2, TAILPF>(p, s_peer, r, stride, r_end, g, gmask);
+      else if (aux == 1) seg_rows<MODE, G, NC, HALO, true, 1, TAILPF>(p, s_peer, r, stride, r_end, g, gmask);
+      else if (MODE == SEG_ADD_RELU) seg_rows<MODE, G, NC, HALO, true, 0, TAILPF>(p, s_peer, r, stride, r_end, g, gmask);
     } else {
-      if (aux == 2) seg_rows<MODE, G, NC, HALO, false, 2>(p, s_peer, r, stride, r_end, g, gmask);
-      else if (aux == 1) seg_rows<MODE, G, NC, HALO, false, 1>(p, s_peer, r, stride, r_end, g, gmask);
-      else if (MODE == SEG_ADD_RELU) seg_rows<MODE, G, NC, HALO, false, 0>(p, s_peer, r, stride, r_end, g, gmask);
+      if (aux == 2) seg_rows<MODE, G, NC, HALO, false, 2, TAILPF>(p, s_peer, r, stride, r_end, g, gmask);
+      else if (aux == 1) seg_rows<MODE, G, NC, HALO, false, 1, TAILPF>(p, s_peer, r, stride, r_end, g, gmask);
+      else if (MODE == SEG_ADD_RELU) seg_rows<MODE, G, NC, HALO, false, 0, TAILPF>(p, s_peer, r, stride, r_end, g, gmask);
     }
   } else {
-    if (full) seg_rows<MODE, G, NC, HALO, true, 0>(p, s_peer, r, stride, r_end, g, gmask);
-    else seg_rows<MODE, G, NC, HALO, false, 0>(p, s_peer, r, stride, r_end, g, gmask);
+    if (full) seg_rows<MODE, G, NC, HALO, true, 0, TAILPF>(p, s_peer, r, stride, r_end, g, gmask);
+    else seg_rows<MODE, G, NC, HALO, false, 0, TAILPF>(p, s_peer, r, stride, r_end, g, gmask);
   }
 }
 
@@ -406,6 +447,9 @@ static int launch_seg(const SegParams& p, cudaStream_t s) {
     rows_per_group = e ? atoi(e) : 8;
     if (rows_per_group < 1 || rows_per_group > 64) rows_per_group = 8;
   }
+  // pull kernels prefetch the tail (remote) edges of every row; DGRAPH_B200_PULL_PREFETCH=0 selects the plain form (A/B switch)
+  const char* pfe = HALO ? getenv("DGRAPH_B200_PULL_PREFETCH") : nullptr;
+  const bool tail_prefetch = HALO && !(pfe && pfe[0] == '0');
   SegParams q = p;
   q.rows_per_group = rows_per_group;
   if (q.ptr_end == nullptr) q.ptr_end = q.ptr + 1;
@@ -414,7 +458,10 @@ static int launch_seg(const SegParams& p, cudaStream_t s) {
   do {                                                                                    \
     const int64_t rows_per_block = (int64_t)warps_per_block * (32 / (G)) * rows_per_group; \
     const int64_t blocks = (p.n_rows + rows_per_block - 1) / rows_per_block;              \
-    seg_reduce_kernel<MODE, G, NC, HALO><<<(unsigned)blocks, warps_per_block * 32, 0, s>>>(q); \
+    if (HALO && (NC) == 1 && tail_prefetch)                                               \
+      seg_reduce_kernel<MODE, G, NC, HALO, HALO && (NC) == 1><<<(unsigned)blocks, warps_per_block * 32, 0, s>>>(q); \
+    else                                                                                  \
+      seg_reduce_kernel<MODE, G, NC, HALO, false><<<(unsigned)blocks, warps_per_block * 32, 0, s>>>(q); \
   } while (0)
   if (chunks <= 4) DGB_LAUNCH(4, 1);
   else if (chunks <= 8) DGB_LAUNCH(8, 1);

@@ -32,11 +32,19 @@ class GraphedTrainStep:
     """
 
     def __init__(self, forward_loss: Callable[..., torch.Tensor], optimizer, example_inputs: Sequence[torch.Tensor],
-                 warmup: int = 3, pool=None):
+                 warmup: int = 3, pool=None, static_inputs: Optional[Sequence[torch.Tensor]] = None):
+        """``static_inputs``: use these tensors as the graph's input buffers instead of clones of ``example_inputs`` -- e.g. features
+        that must live in symmetric memory (``HaloExchange.symmetric_rows``) so that the captured exchange reads them in place."""
         assert torch.cuda.is_available(), "CUDA graphs need a GPU"
         assert getattr(optimizer, "capturable", False), "use FusedAdam(..., capturable=True)"
         self.opt = optimizer
-        self.static_in = [t.clone() for t in example_inputs]
+        if static_inputs is not None:
+            self.static_in = list(static_inputs)
+            for dst, src in zip(self.static_in, example_inputs):
+                if dst.data_ptr() != src.data_ptr():
+                    dst.copy_(src)
+        else:
+            self.static_in = [t.clone() for t in example_inputs]
         self.graph = torch.cuda.CUDAGraph()
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())

@@ -58,6 +58,8 @@ def parse_args():
                          "short enough for the host to matter once every step's loss is read back), off with one")
     ap.add_argument("--no-cuda-graph", dest="cuda_graph", action="store_false")
     ap.add_argument("--cpu", action="store_true", help="CPU/gloo plumbing run (tiny graphs only)")
+    ap.add_argument("--no-powerlaw", action="store_true",
+                    help="skip the second, device-timed measurement on the power-law variant of the graph (config.powerlaw_variant)")
     return ap.parse_args()
 
 
@@ -280,6 +282,41 @@ def run_ours(args):
                "copy_scheme": "double-buffered H2D on a side stream; loss read on the host one step later (every step, inside the "
                               "timed region); identical in both arms"}
 
+    # ---- same model and step on the power-law variant of the graph (hub vertices of degree > 17 k, ids scattered) ---------------
+    powerlaw = None
+    if not args.no_powerlaw and not args.cpu and args.graph == "ogbn-products":
+        del model, opt, kp, pat
+        torch.cuda.empty_cache()
+        g2 = make_graph(args.graph, cut_fraction=args.cut, seed=0, device=dev, scale=args.scale, degree_model="powerlaw")
+        E2 = int(g2.edge_list.shape[0])
+        deg = torch.bincount(g2.edge_list[:, 0], minlength=g2.num_nodes)
+        max_deg, n_hub = int(deg.max()), int((deg > 2048).sum())
+        pat2 = build_communication_pattern(g2.edge_list, contiguous_partition(g2.num_nodes, world, device=dev), rank, world)
+        del g2.edge_list, deg
+        rows2 = pat2.local_vertices_global
+        x2h, y2 = node_features_and_labels(g2.num_nodes, F_in, g2.num_classes, seed=0, device=dev, rows=rows2)
+        x2 = ex.symmetric_rows(pat2, F_pad, cdt, device=dev, tag=2)
+        x2.zero_()
+        x2[:, :F_in] = x2h.to(cdt)
+        idx2 = torch.nonzero((torch.arange(rows2.numel(), device=dev) % 10) == 0, as_tuple=True)[0]
+        pat2.kernel_plan(dev)
+        torch.manual_seed(0)
+        model2 = CommAwareGCN(F_in, args.hidden, g2.num_classes, ex, comm, compute_dtype=cdt).to(dev)
+        opt2 = FusedAdam(model2.parameters(), lr=args.lr, comm=comm)
+
+        def loop2(k):
+            for _ in range(k):
+                opt2.zero_grad()
+                masked_cross_entropy(model2(x2, pat2), y2, idx2).backward()
+                opt2.step()
+
+        loop2(args.warmup)
+        k2 = max(5, args.steps // 2)
+        ms2 = timed(loop2, k2) / k2
+        powerlaw = {"graph": f"{g2.name} V={g2.num_nodes} E={E2}", "max_degree": max_deg, "vertices_with_degree_over_2048": n_hub,
+                    "ms_per_step": ms2, "edges_per_s": E2 / (ms2 * 1e-3), "steps": k2, "timing": "device, eager, max over ranks",
+                    "hub_rows": "rows / columns longer than 2048 slots are split into 512-slot chunks (GraphKernelPlan.hub_plan)"}
+
     # global loss (sum over all labelled vertices / their number) of the first and the last device-arm step: comparable across N
     n_lab = float(train_idx.numel())
     gl = torch.tensor([float(losses[0].detach()) * n_lab, float(losses[-1].detach()) * n_lab, n_lab], dtype=torch.float64, device=dev)
@@ -306,6 +343,7 @@ def run_ours(args):
                                     "into the symmetric slot and the aggregation kernel / one pull kernel reads remote Q rows over NVLink"
                                     if world > 1 and not args.cpu else "none (1 rank)" if world == 1 else "gloo all-to-all"),
                        "gemm": os.environ.get("DGRAPH_B200_GEMM", "tcgen05"), "cuda_graph": use_graph,
+                       "powerlaw_variant": powerlaw,
                        "loss": "fused masked cross-entropy over the labelled rows (10 %)",
                        "grad_row_sparsity": ("exact: classifier and last-conv backward skip rows whose loss gradient is "
                                              "structurally zero" if _sparsity.ENABLED and not args.cpu else "off")},

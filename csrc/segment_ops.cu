@@ -580,18 +580,19 @@ DGB_API int dgb_seg_add_relu_bwd(const int* colptr, const int* row, int64_t n_au
 // dQ[j,:] = sum_{k in CSC seg j} mask[slot_map[k]] ? dOut[row[k],:] : 0, with the ReLU bit masks the forward kernel saved
 // (one byte per edge slot and 8-column chunk): one row gather per edge instead of two, no recomputation.  slot_map = null
 // means the mask rows are already in this walk's slot order (forward used dgb_seg_add_relu_fwd_mapped).  When dP is given,
-// rows j < dp_rows also write dP[j,:] = dOut[j,:] * cnt[j,:] in the same pass.  dQ2 (optional): rows j >= dq_split (the halo rows of
+// rows j < dp_rows also write dP[j,:] = dOut[j,:] * cnt[j,:] in the same pass.  colptr_end (optional, null = colptr + 1): segment j is
+// [colptr[j], colptr_end[j]) -- lets a launch walk the chunks of split hub columns as rows of their own.  dQ2 (optional): rows j >= dq_split (the halo rows of
 // a distributed layer) are written to dQ2[j - dq_split, :] -- the symmetric slot their owners pull-reduce from; with dq2_skip_empty
 // those of them that have no edge in this (restricted) walk are not written at all (the owners' restricted plan never reads them).
-DGB_API int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slot_map, const unsigned char* mask,
-                               int64_t n_aug, int H, const void* dOut, int64_t ld_g, void* dQ, int64_t ld_dq,
+DGB_API int dgb_seg_masked_sum(const int* colptr, const int* colptr_end, const int* row, const int* slot_map,
+                               const unsigned char* mask, int64_t n_aug, int H, const void* dOut, int64_t ld_g, void* dQ, int64_t ld_dq,
                                const unsigned short* cnt, int64_t ld_cnt, void* dP, int64_t ld_dp, int64_t dp_rows,
                                void* dQ2, int64_t ld_dq2, int64_t dq_split, int dq2_skip_empty, void* stream) {
   if (H % 8 || ld_g % 8 || ld_dq % 8 || !fits32(ld_g * 2) || !mask || (dP && (ld_dp % 8 || ld_cnt % 8 || !cnt)) ||
       (dQ2 && (ld_dq2 % 8 || !aligned16(dQ2))))
     return (int)cudaErrorInvalidValue;
   SegParams p{};
-  p.ptr = colptr; p.idx = row; p.n_rows = n_aug; p.H = H;
+  p.ptr = colptr; p.ptr_end = colptr_end; p.idx = row; p.n_rows = n_aug; p.H = H;
   p.src = (const __nv_bfloat16*)dOut; p.ld_src_b = (uint32_t)(ld_g * 2);
   p.mask = const_cast<unsigned char*>(mask); p.slot_map = slot_map;
   p.out = (__nv_bfloat16*)dQ; p.ld_out = ld_dq;

@@ -32,19 +32,40 @@ class SyntheticGraph:
 
 
 def symmetric_locality_graph(num_nodes: int, num_directed_edges: int, cut_fraction: float = 0.1,
-                             window: Optional[int] = None, seed: int = 0, device="cpu") -> torch.Tensor:
+                             window: Optional[int] = None, seed: int = 0, device="cpu", degree_model: str = "uniform",
+                             zipf_exponent: float = 0.55) -> torch.Tensor:
     """Symmetric edge list with ~``num_directed_edges`` rows: a fraction ``1 - cut_fraction`` of the undirected pairs
-    connects vertices within ``window`` ids of each other, the rest are uniform over the whole id range."""
+    connects vertices within ``window`` ids of each other, the rest are uniform over the whole id range.
+
+    ``degree_model="powerlaw"``: edge endpoints are drawn with probability proportional to ``rank^-zipf_exponent`` over a random
+    permutation of the vertices (Chung-Lu style), which gives the heavy-tailed degrees of a real co-purchase graph -- at the
+    ogbn-products size a few vertices of degree > 17,000 (the real graph's maximum is 17,481), scattered over the id range -- instead
+    of the near-Poisson degrees of the uniform model.  The locality window widens to 65,536 ids so that a hub finds enough distinct
+    neighbours."""
     dev = torch.device(device)
     g = torch.Generator(device=dev).manual_seed(seed)
-    n_und = int(num_directed_edges // 2 * 1.02) + 16  # slack for self loops / duplicates removed below
+    powerlaw = degree_model == "powerlaw"
+    assert degree_model in ("uniform", "powerlaw")
+    n_und = int(num_directed_edges // 2 * (1.08 if powerlaw else 1.02)) + 16  # slack for self loops / duplicates removed below
     if window is None:
-        window = max(16, min(num_nodes // 64, 8192))
-    u = torch.randint(0, num_nodes, (n_und,), generator=g, device=dev)
+        window = max(16, min(num_nodes // 64, 65536 if powerlaw else 8192))
+    if powerlaw:
+        w = torch.arange(1, num_nodes + 1, device=dev, dtype=torch.float64).pow_(-zipf_exponent)
+        cdf = torch.cumsum(w, 0)
+        cdf /= cdf[-1].clone()
+        perm = torch.randperm(num_nodes, generator=g, device=dev)
+
+        def draw(k):
+            r = torch.rand(k, generator=g, device=dev, dtype=torch.float64)
+            return perm[torch.searchsorted(cdf, r).clamp_(max=num_nodes - 1)]
+
+        u = draw(n_und)
+    else:
+        u = torch.randint(0, num_nodes, (n_und,), generator=g, device=dev)
     off = torch.randint(1, window + 1, (n_und,), generator=g, device=dev)
     sign = torch.randint(0, 2, (n_und,), generator=g, device=dev) * 2 - 1
     local_v = (u + off * sign) % num_nodes
-    far_v = torch.randint(0, num_nodes, (n_und,), generator=g, device=dev)
+    far_v = draw(n_und) if powerlaw else torch.randint(0, num_nodes, (n_und,), generator=g, device=dev)
     is_far = torch.rand(n_und, generator=g, device=dev) < cut_fraction
     v = torch.where(is_far, far_v, local_v)
     keep = u != v
@@ -58,11 +79,11 @@ def symmetric_locality_graph(num_nodes: int, num_directed_edges: int, cut_fracti
 
 
 def make_graph(name: str = "ogbn-products", cut_fraction: float = 0.1, seed: int = 0, device="cpu",
-               scale: float = 1.0) -> SyntheticGraph:
+               scale: float = 1.0, degree_model: str = "uniform") -> SyntheticGraph:
     V, E, F, C = SHAPES[name]
     V, E = max(int(V * scale), 64), max(int(E * scale), 256)
-    e = symmetric_locality_graph(V, E, cut_fraction=cut_fraction, seed=seed, device=device)
-    return SyntheticGraph(V, e, F, C, name=f"{name}-shaped")
+    e = symmetric_locality_graph(V, E, cut_fraction=cut_fraction, seed=seed, device=device, degree_model=degree_model)
+    return SyntheticGraph(V, e, F, C, name=f"{name}-shaped" + ("-powerlaw" if degree_model == "powerlaw" else ""))
 
 
 def contiguous_partition(num_nodes: int, world_size: int, device="cpu") -> torch.Tensor:

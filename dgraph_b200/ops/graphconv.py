@@ -64,9 +64,52 @@ def _aggregate(kp, ptr, ptr_end, idx, n_local, H, P, ld_p, Q, ld_q, out, cnt, ma
     N.count_launch()
 
 
+def _aggregate_rows(kp, idx, n_local, H, P, ld_p, Q, ld_q, out, cnt, mask, smap, peer):
+    """The whole forward aggregation: one launch, plus -- on graphs with hub vertices -- a second small launch over the chunks of the
+    over-long rows (``GraphKernelPlan.hub_plan``) whose partial sums / counts are added up here."""
+    hp = kp.hub_plan("csr")
+    if hp is None:
+        return _aggregate(kp, kp.rowptr, None, idx, n_local, H, P, ld_p, Q, ld_q, out, cnt, mask, smap, 0, peer)
+    _aggregate(kp, kp.rowptr, hp.main_end, idx, n_local, H, P, ld_p, Q, ld_q, out, cnt, mask, smap, 0, peer)  # hub rows: empty -> zeros
+    nv = hp.vrow.numel()
+    Pv = P.index_select(0, hp.vrow).contiguous()
+    part = torch.empty((nv, H), dtype=torch.bfloat16, device=P.device)
+    pcnt = torch.empty((nv, H), dtype=torch.uint16, device=P.device) if cnt is not None else None
+    _aggregate(kp, hp.vbeg, hp.vend, idx, nv, H, Pv, H, Q, ld_q, part, pcnt, mask, smap, 0, peer)
+    nh = hp.hubs.numel()
+    out.index_copy_(0, hp.hubs, torch.zeros((nh, H), dtype=torch.float32, device=P.device).index_add_(0, hp.seg, part.float())
+                    .to(torch.bfloat16))
+    if cnt is not None:
+        tot = torch.zeros((nh, H), dtype=torch.int32, device=P.device).index_add_(0, hp.seg, pcnt.view(torch.int16).to(torch.int32) & 0xFFFF)
+        cnt.view(torch.int16).index_copy_(0, hp.hubs, tot.to(torch.int16))  # degree <= 65535 is checked: the sum fits 16 bits
+
+
+def _masked_sum_cols(kp, full_walk, colptr, row, slot_map, mask, n_aug, H, g, dQ, ld_dq, cnt, dP, ld_dp, dp_rows, dQ2=None, ld_dq2=0,
+                     split=0, skip_empty=False):
+    """The whole backward CSC walk; with hub columns (``full_walk`` only: a walk restricted to the labelled rows has no long
+    columns) their chunks run as rows of a second small launch and are added up here."""
+    hp = kp.hub_plan("csc") if full_walk else None
+    if hp is None:
+        return _masked_sum(colptr, row, slot_map, mask, n_aug, H, g, dQ, ld_dq, cnt, dP, ld_dp, dp_rows, dQ2, ld_dq2, split, skip_empty)
+    _masked_sum(colptr, row, slot_map, mask, n_aug, H, g, dQ, ld_dq, cnt, dP, ld_dp, dp_rows, dQ2, ld_dq2, split, skip_empty,
+                colptr_end=hp.main_end)
+    nv = hp.vrow.numel()
+    part = torch.empty((nv, H), dtype=torch.bfloat16, device=g.device)
+    _masked_sum(hp.vbeg, row, slot_map, mask, nv, H, g, part, H, None, None, 0, 0, colptr_end=hp.vend)
+    tot = torch.zeros((hp.hubs.numel(), H), dtype=torch.float32, device=g.device).index_add_(0, hp.seg, part.float()).to(torch.bfloat16)
+    if dQ2 is None:
+        dQ.index_copy_(0, hp.hubs, tot)
+    else:  # hub columns that are halo rows live in the symmetric slot
+        loc = hp.hubs < split
+        if bool(loc.any()):
+            dQ.index_copy_(0, hp.hubs[loc], tot[loc])
+        if bool((~loc).any()):
+            dQ2.index_copy_(0, hp.hubs[~loc] - split, tot[~loc])
+
+
 def _masked_sum(colptr, row, slot_map, mask, n_aug, H, g, dQ, ld_dq, cnt, dP, ld_dp, dp_rows, dQ2=None, ld_dq2=0, split=0,
-                skip_empty=False):
-    N.check(N.lib().dgb_seg_masked_sum(N.ptr(colptr), N.ptr(row), N.ptr(slot_map), N.ptr(mask), N.i64(n_aug), N.i32(H), N.ptr(g),
+                skip_empty=False, colptr_end=None):
+    N.check(N.lib().dgb_seg_masked_sum(N.ptr(colptr), N.ptr(colptr_end), N.ptr(row), N.ptr(slot_map), N.ptr(mask), N.i64(n_aug), N.i32(H), N.ptr(g),
                                        N.i64(H), N.ptr(dQ), N.i64(ld_dq), N.ptr(cnt), N.i64(H), N.ptr(dP), N.i64(ld_dp),
                                        N.i64(dp_rows), N.ptr(dQ2), N.i64(ld_dq2), N.i64(split), N.i32(1 if skip_empty else 0),
                                        N.stream()),
@@ -94,6 +137,8 @@ class _GraphConvFused(Function):
         smap = kp.csr_to_csc() if (mask is not None and S.MASK_IN_CSC_ORDER) else None
 
         def aggregate(ptr, ptr_end, accumulate):
+            if ptr is kp.rowptr and ptr_end is None and not accumulate:
+                return _aggregate_rows(kp, kp.col, n_local, H, P, 2 * H, Q, 2 * H, out, cnt, mask, smap, None)
             _aggregate(kp, ptr, ptr_end, kp.col, n_local, H, P, 2 * H, Q, 2 * H, out, cnt, mask, smap, accumulate, None)
 
         # DGRAPH_B200_OVERLAP (opt-in, default "0" = pull on the main stream): "gemm" overlaps only the local-row GEMM above with
@@ -135,7 +180,8 @@ class _GraphConvFused(Function):
         dPQ = torch.empty((n_aug, 2 * H), dtype=torch.bfloat16, device=dev)
         dQ = dPQ[:, H:]
         # one CSC walk writes dQ (masked sums) for all rows and dP = g * cnt for the local rows
-        _masked_sum(colptr, row, None if ctx.mask_csc else slot_map, mask, n_aug, H, g, dQ, 2 * H, cnt, dPQ, 2 * H, n)
+        _masked_sum_cols(kp, hint is None, colptr, row, None if ctx.mask_csc else slot_map, mask, n_aug, H, g, dQ, 2 * H, cnt, dPQ,
+                         2 * H, n)
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty((n_aug, x_aug.shape[1]), dtype=torch.bfloat16, device=dev)
@@ -179,10 +225,10 @@ class _GraphConvPullQ(Function):
                                               N.i64(4 * H), N.ptr(info.halo_owner), N.ptr(info.halo_row), N.i64(info.rot),
                                               N.stream()), "dgb_halo_pull")
                 N.count_launch()
-            _aggregate(kp, kp.rowptr, None, kp.col, n, H, P, 2 * H, Q, 2 * H, out, cnt, mask, None, 0, None)
+            _aggregate_rows(kp, kp.col, n, H, P, 2 * H, Q, 2 * H, out, cnt, mask, None, None)
         else:
-            _aggregate(kp, kp.rowptr, None, kp.col_peer(info.peer_shift), n, H, P, 2 * H, Q, 2 * H, out, cnt, mask, None, 0,
-                       (q_table, engine.get_world_size(), info.peer_shift, 2 * H))
+            _aggregate_rows(kp, kp.col_peer(info.peer_shift), n, H, P, 2 * H, Q, 2 * H, out, cnt, mask, None,
+                            (q_table, engine.get_world_size(), info.peer_shift, 2 * H))
         engine.mark_read(off)
         ctx.save_for_backward(x, wcat_t, cnt, mask)
         ctx.kp, ctx.f_in, ctx.H, ctx.engine, ctx.pat, ctx.tag = kp, f_in, H, engine, pat, tag
@@ -206,8 +252,8 @@ class _GraphConvPullQ(Function):
         # their halo copies those are (engine.restricted_reduce_plan) and read only them; the walk does not even write the others.
         rplan = None if hint is None else engine.restricted_reduce_plan(info, kp, hint[0], colptr)
         # one CSC walk: dQ of owned rows -> dPQ, dQ of halo rows -> the symmetric slot, dP = g * cnt
-        _masked_sum(colptr, row, slot_map, mask, kp.num_aug, H, g, dQ, 2 * H, cnt, dPQ, 2 * H, n, dQh, H, n,
-                    skip_empty=rplan is not None)
+        _masked_sum_cols(kp, hint is None, colptr, row, slot_map, mask, kp.num_aug, H, g, dQ, 2 * H, cnt, dPQ, 2 * H, n, dQh, H, n,
+                         skip_empty=rplan is not None)
         engine.barrier_on_stream()
         engine.halo_grad_reduce_inplace(info, dQ, 2 * H, H, goff, H, plan=rplan)  # dQ[b] += sum over the holders of b's halo copies
         engine.mark_read(goff)

@@ -180,7 +180,7 @@ class _GraphConvAgg(Function):
             dQ = torch.empty((kp.num_aug, H), dtype=torch.bfloat16, device=g.device)
             colptr, row, slot_map = (kp.colptr, kp.row, kp.csc_to_csr) if hint is None else kp.restricted_csc(hint[0])
             N.check(N.lib().dgb_seg_masked_sum(
-                N.ptr(colptr), N.ptr(row), N.ptr(None if ctx.mask_csc else slot_map), N.ptr(mask),
+                N.ptr(colptr), N.ptr(None), N.ptr(row), N.ptr(None if ctx.mask_csc else slot_map), N.ptr(mask),
                 N.i64(kp.num_aug), N.i32(H), N.ptr(g),
                 N.i64(H), N.ptr(dQ), N.i64(H), N.ptr(None), N.i64(0), N.ptr(None), N.i64(0), N.i64(0), N.ptr(None), N.i64(0),
                 N.i64(0), N.i32(0), N.stream()),

@@ -9,6 +9,7 @@ No counterpart in the reference, which keeps COO + ``scatter_add`` atomics (``ex
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import Optional
 
@@ -16,6 +17,21 @@ import torch
 
 
 MAX_COUNTED_DEGREE = 65535  # uint16 per-(row, column) active-edge counters of the add-ReLU aggregation kernel
+# One lane group walks one CSR / CSC segment.  Segments longer than HUB_DEGREE (hub vertices of a power-law graph: ogbn-products has
+# a vertex of degree 17,481) are cut into chunks of HUB_CHUNK slots that run as rows of their own in a second, small launch and are
+# added up afterwards, so a hub costs HUB_CHUNK slots of serial work instead of its whole degree.
+HUB_DEGREE = int(os.environ.get("DGRAPH_B200_HUB_DEGREE", "2048"))
+HUB_CHUNK = int(os.environ.get("DGRAPH_B200_HUB_CHUNK", "512"))
+
+
+@dataclass
+class HubPlan:
+    hubs: torch.Tensor  # int64 [n_hubs]  segments longer than HUB_DEGREE
+    vrow: torch.Tensor  # int64 [n_virtual]  segment each chunk belongs to
+    vbeg: torch.Tensor  # int32 [n_virtual]  first slot of the chunk
+    vend: torch.Tensor  # int32 [n_virtual]  one past its last slot
+    main_end: torch.Tensor  # int32 [n_segments]  end pointers of the main launch: hub segments are empty there
+    seg: torch.Tensor  # int64 [n_virtual]  index into `hubs` of each chunk
 
 
 @dataclass
@@ -52,6 +68,31 @@ class GraphKernelPlan:
             d = int((rp[1:] - rp[:-1]).max()) if rp.numel() > 1 else 0
             self._max_row_degree = d
         return d
+
+    def hub_plan(self, side: str = "csr") -> Optional[HubPlan]:
+        """Chunks of the over-long segments of the CSR (``side="csr"``) or CSC walk, or None when there are none (one device-to-host
+        read, cached)."""
+        cache = self.__dict__.setdefault("_hub_plans", {})
+        if side in cache:
+            return cache[side]
+        ptr = (self.rowptr if side == "csr" else self.colptr).long()
+        deg = ptr[1:] - ptr[:-1]
+        hubs = torch.nonzero(deg > HUB_DEGREE, as_tuple=True)[0]
+        plan = None
+        if hubs.numel():
+            nch = (deg[hubs] + HUB_CHUNK - 1) // HUB_CHUNK
+            seg = torch.repeat_interleave(torch.arange(hubs.numel(), device=ptr.device), nch)
+            first = torch.cumsum(nch, 0) - nch
+            k = torch.arange(int(nch.sum()), device=ptr.device) - first[seg]
+            vrow = hubs[seg]
+            vbeg = ptr[vrow] + k * HUB_CHUNK
+            vend = torch.minimum(vbeg + HUB_CHUNK, ptr[vrow + 1])
+            main_end = ptr[1:].clone()
+            main_end[hubs] = ptr[hubs]
+            it = self.rowptr.dtype
+            plan = HubPlan(hubs, vrow, vbeg.to(it).contiguous(), vend.to(it).contiguous(), main_end.to(it).contiguous(), seg)
+        cache[side] = plan
+        return plan
 
     def csr_to_csc(self) -> torch.Tensor:
         """CSC slot of each CSR slot (inverse of ``csc_to_csr``), built on first use.  The forward add-ReLU kernel writes its

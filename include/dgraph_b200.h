@@ -47,7 +47,7 @@ int dgb_seg_add_relu_fwd_ex(const int* ptr, const int* ptr_end, const int* idx, 
                             const void* const* peer_base, int world, int peer_shift, int64_t ld_peer, void* stream);
 int dgb_seg_add_relu_bwd(const int* colptr, const int* row, int64_t n_aug, int H, const void* dOut, int64_t ld_g,
                          const void* P, int64_t ld_p, const void* Q, int64_t ld_q, void* dQ, int64_t ld_dq, void* stream);
-int dgb_seg_masked_sum(const int* colptr, const int* row, const int* slot_map, const unsigned char* mask, int64_t n_aug,
+int dgb_seg_masked_sum(const int* colptr, const int* colptr_end, const int* row, const int* slot_map, const unsigned char* mask, int64_t n_aug,
                        int H, const void* dOut, int64_t ld_g, void* dQ, int64_t ld_dq, const unsigned short* cnt,
                        int64_t ld_cnt, void* dP, int64_t ld_dp, int64_t dp_rows, void* dQ2, int64_t ld_dq2, int64_t dq_split,
                        int dq2_skip_empty, void* stream);

@@ -208,3 +208,35 @@ def test_packed_weights_kernel_and_cache():
     w2 = packed_weights(w, b, f_in, Fp)[0]
     _wcache.bump()  # native optimizer kernels: explicit invalidation
     assert packed_weights(w, b, f_in, Fp)[0] is not w2
+
+
+def test_hub_rows_are_split_and_match_the_unsplit_math():
+    """A vertex of degree 5,000 (> GraphKernelPlan HUB_DEGREE): its CSR row and CSC column run as 512-slot chunks in a second launch
+    whose partial sums / counts are added up; forward and all gradients match the fp32 PyTorch formulation of the layer."""
+    from dgraph_b200.ops.graphconv import graphconv_fused
+    from dgraph_b200.ops.segment import graphconv_aggregate_ref
+    from dgraph_b200.parallel.kernel_plan import GraphKernelPlan
+
+    torch.manual_seed(4)
+    V, F, H = 6000, 32, 64
+    hub = torch.arange(1, 5001)
+    e = torch.cat([torch.stack([torch.zeros_like(hub), hub], 1), torch.stack([hub, torch.zeros_like(hub)], 1),
+                   random_graph(V, 6, seed=2, symmetric=True)])
+    e = torch.unique(e, dim=0).cuda()
+    kp = GraphKernelPlan.from_edges(e, V, V, device="cuda")
+    assert kp.hub_plan("csr") is not None and kp.hub_plan("csc") is not None and kp.max_row_degree() >= 5000
+    x = torch.randn(V, F, device="cuda").bfloat16().requires_grad_(True)
+    w = (torch.randn(H, 2 * F, device="cuda") * 0.1).requires_grad_(True)
+    b = (torch.randn(H, device="cuda") * 0.1).requires_grad_(True)
+    go = torch.randn(V, H, device="cuda").bfloat16()
+    out = graphconv_fused(x, w, b, kp, V, F)
+    dx, dw, db = torch.autograd.grad(out, [x, w, b], go)
+    xr = x.detach().float().requires_grad_(True)
+    wr = w.detach().bfloat16().float().requires_grad_(True)
+    br = b.detach().clone().requires_grad_(True)
+    ref = graphconv_aggregate_ref(xr @ wr[:, :F].t() + br, xr @ wr[:, F:].t(), kp)
+    rx, rw, rb = torch.autograd.grad(ref, [xr, wr, br], go.float())
+    assert torch.allclose(out.float(), ref.detach(), rtol=3e-2, atol=0.02 * float(ref.abs().max()))
+    assert torch.allclose(dx.float(), rx, rtol=5e-2, atol=0.03 * float(rx.abs().max()))
+    assert torch.allclose(dw, rw, rtol=5e-2, atol=0.03 * float(rw.abs().max()))
+    assert torch.allclose(db, rb, rtol=5e-2, atol=0.03 * float(rb.abs().max()))

@@ -1,0 +1,142 @@
+"""One pass over every kernel family that sits on a default code path, at sizes large enough to be meaningful and small enough for
+`ncu --set full` (about 40 replays per launch).  Not a benchmark: it exists so that ONE `ncu` capture yields a row per kernel for
+`profiles/ncu_kernel_families.md` (`benchmarks/ncu_summary.py`).
+
+    python benchmarks/kernel_zoo.py                                  # plain run first (must exit 0)
+    ncu --set full --clock-control none --import-source on -k regex:dgb -o gpurun_out/zoo python benchmarks/kernel_zoo.py
+
+Families: tcgen05 GEMM / B-resident GEMM / gather-GEMM / split-K weight gradient (plain and gathered), CSR / CSC segment kernels
+(local and pull variants), halo pull, halo-gradient pull-reduce, peer row gather, fused gradient-sum + Adam, segment softmax
+forward / backward, LayerNorm forward / backward, fused GraphCast MLP block, masked cross-entropy, BatchNorm apply / backward,
+column sums, weight packing.  Peer kernels run with W ranks emulated as W buffers of this process (pointers are pointers).
+"""
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "experiments", "OGB-LSC"))
+
+
+def gcn_one_rank(scale):
+    from dgraph_b200 import Communicator
+    from dgraph_b200.data import contiguous_partition, make_graph, node_features_and_labels
+    from dgraph_b200.models.gcn import CommAwareGCN
+    from dgraph_b200.ops.loss import masked_cross_entropy
+    from dgraph_b200.optim import FusedAdam
+    from dgraph_b200.parallel import HaloExchange, build_communication_pattern
+    from dgraph_b200.parallel.local_engine import LocalEngine
+
+    dev = torch.device("cuda")
+    g = make_graph("ogbn-products", device=dev, scale=scale)
+    comm = Communicator._from_engine(LocalEngine(), backend="single")
+    pat = build_communication_pattern(g.edge_list, contiguous_partition(g.num_nodes, 1, device=dev), 0, 1)
+    x, y = node_features_and_labels(g.num_nodes, g.num_features, g.num_classes, device=dev)
+    xd = torch.zeros(g.num_nodes, 104, dtype=torch.bfloat16, device=dev)
+    xd[:, :100] = x.to(torch.bfloat16)
+    idx = torch.arange(0, g.num_nodes, 10, device=dev)
+    model = CommAwareGCN(100, 256, g.num_classes, HaloExchange(comm), comm, compute_dtype=torch.bfloat16).to(dev)
+    opt = FusedAdam(model.parameters(), lr=1e-3)
+    for _ in range(2):
+        opt.zero_grad()
+        masked_cross_entropy(model(xd, pat), y, idx).backward()
+        opt.step()
+
+
+def gcn_pull_emulated(W=2, V=200_000):
+    from tests._graphs import partition
+    from tests.test_graphconv_pull_gpu import _make_engines
+
+    from dgraph_b200.data.synthetic import symmetric_locality_graph
+    from dgraph_b200.ops.graphconv import graphconv_pull_q
+    from dgraph_b200.parallel import build_all_patterns
+
+    e = symmetric_locality_graph(V, V * 24, cut_fraction=0.1, device="cuda").cpu()
+    pats = build_all_patterns(e, partition(V, W, "contiguous"), W)
+    engines = _make_engines(W, pats, arena_bytes=1 << 30)
+    F, H = 256, 256
+    w = (torch.randn(H, 2 * F, device="cuda") * 0.05).requires_grad_(True)
+    b = torch.zeros(H, device="cuda", requires_grad=True)
+    for mode in ("kernel", "buffer"):
+        os.environ["DGRAPH_B200_PULL"] = mode
+        xs = [torch.randn(p.num_local_vertices, F, device="cuda").bfloat16().requires_grad_(True) for p in pats]
+        for _ in range(2):
+            outs = [graphconv_pull_q(xs[r], w, b, pats[r].kernel_plan("cuda"), F, engines[r], pats[r], tag=mode) for r in range(W)]
+        for r in range(W):
+            outs[r].backward(torch.ones_like(outs[r]), retain_graph=False)
+    os.environ.pop("DGRAPH_B200_PULL", None)
+    # fused gradient sum + Adam over the "ranks"
+    from dgraph_b200.ops import _native as N
+
+    n = 1 << 20
+    g = [torch.randn(n, device="cuda") for _ in range(W)]
+    table = torch.tensor([t.data_ptr() for t in g], dtype=torch.int64, device="cuda")
+    p, m, v = torch.randn(n, device="cuda"), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    N.check(N.lib().dgb_adam_allreduce(N.ptr(p), N.ptr(table), N.i32(W), N.ptr(m), N.ptr(v), N.ptr(None), N.i64(n), N.f32(1e-3),
+                                       N.f32(0.9), N.f32(0.999), N.f32(1e-8), N.f32(0.0), N.f32(1.0 / W), N.i32(1), N.stream()), "adam")
+
+
+def rgat_one_rank():
+    from config import ModelConfig
+    from dgraph_b200 import Communicator
+    from dgraph_b200.data.hetero import RELATIONS, SyntheticHeterogeneousDataset
+    from dgraph_b200.models.rgat import CommAwareRGAT
+    from dgraph_b200.optim import FusedAdam
+    from dgraph_b200.parallel.local_engine import LocalEngine
+
+    dev = torch.device("cuda")
+    comm = Communicator._from_engine(LocalEngine(), backend="single")
+    ds = SyntheticHeterogeneousDataset(0, 1, 32768 * 4, 16384 * 4, 256 * 4, 16, 153, comm=comm)
+    ds.prepare_plans(fused=True)
+    ds.to(dev)
+    mc = ModelConfig()
+    model = CommAwareRGAT(ds.num_features, ds.num_classes, 64, ds.num_relations, mc.num_layers, mc.heads, comm).to(dev)
+    opt = FusedAdam(model.parameters(), lr=1e-4)
+    xs = [f.to(torch.bfloat16) for f in ds.features]
+    idx, tgt = ds.get_mask("train").to(dev), ds.get_target("train").to(dev)
+    for _ in range(2):
+        opt.zero_grad()
+        out = model(xs, RELATIONS, ds.patterns)
+        torch.nn.functional.cross_entropy(out.index_select(0, idx).float(), tgt).backward()
+        opt.step()
+
+
+def graphcast_one_rank(fused):
+    from dgraph_b200.communicator import Communicator
+    from dgraph_b200.data.graphcast_graph import DistributedGraphCastGraphGenerator, SyntheticWeatherDataset
+    from dgraph_b200.models.graphcast import Config, DGraphCast
+    from dgraph_b200.optim import FusedAdam
+    from dgraph_b200.parallel.local_engine import LocalEngine
+
+    from dgraph_b200.ops import mlp_fused
+
+    mlp_fused.ENABLED = bool(fused)
+    cfg = Config()
+    cfg.data.latlon_res, cfg.model.mesh_level = (181, 360), 5
+    comm = Communicator._from_engine(LocalEngine(), backend="single")
+    sg = DistributedGraphCastGraphGenerator(cfg.data.latlon_res, cfg.model.mesh_level).shard(0, 1).to("cuda", torch.bfloat16)
+    d = SyntheticWeatherDataset(73, cfg.data.latlon_res)[0]
+    x, y = d["invar"].cuda().bfloat16(), d["outvar"].cuda().bfloat16()
+    model = DGraphCast(cfg, comm).cuda()
+    opt = FusedAdam(model.parameters(), lr=1e-3)
+    for _ in range(2):
+        opt.zero_grad()
+        torch.nn.functional.mse_loss(model(x, sg).float(), y.float()).backward()
+        opt.step()
+
+
+def main():
+    torch.manual_seed(0)
+    gcn_one_rank(float(os.environ.get("ZOO_SCALE", "0.25")))
+    gcn_pull_emulated()
+    rgat_one_rank()
+    graphcast_one_rank(False)
+    graphcast_one_rank(True)
+    torch.cuda.synchronize()
+    print("kernel zoo ok")
+
+
+if __name__ == "__main__":
+    main()

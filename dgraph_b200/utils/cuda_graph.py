@@ -38,6 +38,10 @@ class GraphedTrainStep:
         assert torch.cuda.is_available(), "CUDA graphs need a GPU"
         assert getattr(optimizer, "capturable", False), "use FusedAdam(..., capturable=True)"
         self.opt = optimizer
+        # The graph replays raw addresses.  Everything the captured region reads besides its inputs -- label / index tensors, plans,
+        # the model -- is reachable from this closure and must stay allocated for as long as the graph can be replayed (a caller that
+        # built the closure in a function and kept only the step would otherwise free them, and replays would read recycled memory).
+        self.forward_loss = forward_loss
         if static_inputs is not None:
             self.static_in = list(static_inputs)
             for dst, src in zip(self.static_in, example_inputs):

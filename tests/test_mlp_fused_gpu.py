@@ -1,13 +1,9 @@
-"""One-kernel GraphCast MLP block (csrc/mlp_fused_tcgen05.cu) vs the fp32 PyTorch statement of the same block.  The kernel is
-experimental and opt-in: these tests run only with ``DGRAPH_B200_FUSED_MLP=1`` (it was written after the round's GPU budget was
-spent and has not run on hardware yet)."""
-import os
-
+"""One-kernel GraphCast MLP block (csrc/mlp_fused_tcgen05.cu, the default for the block shapes it supports) vs the fp32 PyTorch
+statement of the same block."""
 import pytest
 import torch
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("DGRAPH_B200_FUSED_MLP", "0") != "1", reason="opt-in experimental kernel")]
+pytestmark = [pytest.mark.gpu]
 
 
 def _case(M, widths, n_rows, with_idx, with_res, seed=0):

@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--rgat-relations", default="all", choices=["all", "first"],
                     help="rgat: 'first' mirrors the reference as shipped, which processes relation 0 only (RGAT.py:356-358)")
     ap.add_argument("--halo-max-rows", type=int, default=10_000_000)
+    ap.add_argument("--halo-min-rows", type=int, default=1_000)
     ap.add_argument("--graph", default="ogbn-products")
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the graph (debug only; <1 is NOT the named config)")
     ap.add_argument("--hidden", type=int, default=256)
@@ -237,7 +238,9 @@ def run_ours(args):
     if use_graph:  # same work per step, replayed with one cudaGraphLaunch (utils/cuda_graph.py); inputs stay in symmetric memory
         from dgraph_b200.utils.cuda_graph import GraphedTrainStep
 
+        snap = opt.snapshot()  # capture trains for three steps (two eager warm-ups + the captured one): undo them, so that the first
         graphed = GraphedTrainStep(forward_loss, opt, (x_dev, y_dev), warmup=2, static_inputs=(x_dev, y_dev))
+        opt.restore(snap)      # reported loss is the loss of the initial weights, as without a graph
 
         def step(x_in, y_in):  # noqa: F811
             return graphed(x_in, y_in).clone()

@@ -3,7 +3,8 @@
 `profiles/ncu_kernel_families.md` (`benchmarks/ncu_summary.py`).
 
     python benchmarks/kernel_zoo.py                                  # plain run first (must exit 0)
-    ncu --set full --clock-control none --import-source on -k regex:dgb -o gpurun_out/zoo python benchmarks/kernel_zoo.py
+    ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:dgb:: -o gpurun_out/zoo \
+        python benchmarks/kernel_zoo.py
 
 Families: tcgen05 GEMM / B-resident GEMM / gather-GEMM / split-K weight gradient (plain and gathered), CSR / CSC segment kernels
 (local and pull variants), halo pull, halo-gradient pull-reduce, peer row gather, fused gradient-sum + Adam, segment softmax
@@ -15,6 +16,7 @@ import sys
 
 import torch
 
+STEPS = int(os.environ.get("ZOO_STEPS", "1"))
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "experiments", "OGB-LSC"))
@@ -39,7 +41,7 @@ def gcn_one_rank(scale):
     idx = torch.arange(0, g.num_nodes, 10, device=dev)
     model = CommAwareGCN(100, 256, g.num_classes, HaloExchange(comm), comm, compute_dtype=torch.bfloat16).to(dev)
     opt = FusedAdam(model.parameters(), lr=1e-3)
-    for _ in range(2):
+    for _ in range(STEPS):
         opt.zero_grad()
         masked_cross_entropy(model(xd, pat), y, idx).backward()
         opt.step()
@@ -96,7 +98,7 @@ def rgat_one_rank():
     opt = FusedAdam(model.parameters(), lr=1e-4)
     xs = [f.to(torch.bfloat16) for f in ds.features]
     idx, tgt = ds.get_mask("train").to(dev), ds.get_target("train").to(dev)
-    for _ in range(2):
+    for _ in range(STEPS):
         opt.zero_grad()
         out = model(xs, RELATIONS, ds.patterns)
         torch.nn.functional.cross_entropy(out.index_select(0, idx).float(), tgt).backward()
@@ -121,7 +123,7 @@ def graphcast_one_rank(fused):
     x, y = d["invar"].cuda().bfloat16(), d["outvar"].cuda().bfloat16()
     model = DGraphCast(cfg, comm).cuda()
     opt = FusedAdam(model.parameters(), lr=1e-3)
-    for _ in range(2):
+    for _ in range(STEPS):
         opt.zero_grad()
         torch.nn.functional.mse_loss(model(x, sg).float(), y.float()).backward()
         opt.step()

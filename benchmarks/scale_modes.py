@@ -31,7 +31,7 @@ MODES = {  # name -> (DGRAPH_B200_GCN_EXCHANGE, DGRAPH_B200_PULL, extra environm
     "pull_buffer": ("auto", "buffer", {}),
     "exchange_x": ("x", None, {}),
     "overlap_gemm": ("auto", None, {"DGRAPH_B200_OVERLAP": "gemm"}),
-    "pull_noprefetch": ("auto", "kernel", {"DGRAPH_B200_PULL_PREFETCH": "0"}),
+    "pull_prefetch": ("auto", "kernel", {"DGRAPH_B200_PULL_PREFETCH": "1"}),
 }
 _EXTRA_KEYS = sorted({k for m in MODES.values() for k in m[2]})
 

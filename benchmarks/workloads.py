@@ -44,7 +44,9 @@ def _graphed(args, world, comm, forward_loss, opt, example_inputs):
         return None
     from dgraph_b200.utils.cuda_graph import GraphedTrainStep
 
+    snap = opt.snapshot()  # undo the three training steps the capture performs: losses then start from the initial weights
     g = GraphedTrainStep(forward_loss, opt, example_inputs, warmup=2)
+    opt.restore(snap)
     return lambda *xs: g(*xs).clone()
 
 
@@ -252,7 +254,7 @@ HALO_HEADLINE = (1_000_000, 256)
 
 
 def halo_points(args):
-    rows = [r for r in HALO_ROWS if r <= args.halo_max_rows]
+    rows = [r for r in HALO_ROWS if getattr(args, "halo_min_rows", 0) <= r <= args.halo_max_rows]
     return [(r, F) for r in rows for F in HALO_F]
 
 
@@ -312,6 +314,9 @@ def run_halo(args, comm, rank, world, dev, out, clock_sampler):
                 headline["e2e"] = {"value": float(nb) / float(te) / 1e6, "unit": "GB/s", "ms_per_step": float(te),
                                    "h2d_bytes_per_step": int(xh.numel() * 2), "d2h_bytes_per_step": 4}
         del x, xg, pat, gph
+        if hasattr(comm.engine, "reset_arena"):  # the arena never frees single slots: start over for the next point
+            torch.cuda.synchronize()
+            comm.engine.reset_arena()
     clocks = clock_sampler.stop() if rank == 0 else None
     if rank == 0:
         print(json.dumps({
@@ -335,7 +340,7 @@ def run(args, out, clock_sampler):
     if args.config == "halo":
         os.environ.setdefault("DGRAPH_B200_ARENA_MB", "98304")
     elif args.config == "papers100m":
-        os.environ.setdefault("DGRAPH_B200_ARENA_MB", "24576")
+        os.environ.setdefault("DGRAPH_B200_ARENA_MB", "65536")
     if getattr(args, "cuda_graph", False) and int(os.environ.get("WORLD_SIZE", "1")) > 1:
         os.environ["DGRAPH_B200_DEVICE_EPOCH"] = "1"  # barrier epochs in device memory: steps with exchanges become capturable
     from _common import cleanup, init_distributed

@@ -447,9 +447,11 @@ static int launch_seg(const SegParams& p, cudaStream_t s) {
     rows_per_group = e ? atoi(e) : 8;
     if (rows_per_group < 1 || rows_per_group > 64) rows_per_group = 8;
   }
-  // pull kernels prefetch the tail (remote) edges of every row; DGRAPH_B200_PULL_PREFETCH=0 selects the plain form (A/B switch)
+  // DGRAPH_B200_PULL_PREFETCH=1: pull kernels issue the loads of a row's tail (remote) edges before its local ones.  Measured on
+  // 8 x B200 (products-shaped GCN step): 3.94 ms with, 3.61 ms without -- the 16 extra live registers cost a resident block per SM
+  // (80 vs 64 registers), which hurts the local gathers more than the earlier NVLink loads help.  Off by default.
   const char* pfe = HALO ? getenv("DGRAPH_B200_PULL_PREFETCH") : nullptr;
-  const bool tail_prefetch = HALO && !(pfe && pfe[0] == '0');
+  const bool tail_prefetch = HALO && pfe && pfe[0] == '1';
   SegParams q = p;
   q.rows_per_group = rows_per_group;
   if (q.ptr_end == nullptr) q.ptr_end = q.ptr + 1;

@@ -136,6 +136,23 @@ class FusedAdam(torch.optim.Optimizer):
             self.flat_p.sub_(lr * (self.flat_m / c1) / (self.flat_v.sqrt() / math.sqrt(c2) + eps))
         return loss
 
+    # -- in-memory snapshot (e.g. around the warm-up steps a CUDA-graph capture needs) ----------------------------------------------
+    def snapshot(self):
+        """Parameters, moments and step counter as device copies; :meth:`restore` writes them back in place (views stay attached)."""
+        snap = {"p": self.flat_p.clone(), "m": self.flat_m.clone(), "v": self.flat_v.clone(), "step": self._step}
+        if self.capturable:
+            snap["dev_step"] = self._dev_step.clone()
+        return snap
+
+    def restore(self, snap) -> None:
+        self.flat_p.copy_(snap["p"])
+        self.flat_m.copy_(snap["m"])
+        self.flat_v.copy_(snap["v"])
+        self._step = snap["step"]
+        if self.capturable and "dev_step" in snap:
+            self._dev_step.copy_(snap["dev_step"])
+        _wcache.bump()
+
     # -- torch.optim.Adam-compatible checkpoint format ---------------------------------------------
     def state_dict(self):
         state = {}

@@ -662,6 +662,20 @@ class PeerMemoryEngine(TorchDistEngine):
                     if e["off"] == off:
                         e["busy"] = False
 
+    def reset_arena(self):
+        """Forget every slot and start allocating from the bottom of the arena again (the arena is a bump allocator: slots are
+        never freed one by one).  COLLECTIVE and only legal when no tensor handed out by ``slot_tensor`` / ``symmetric_rows`` is in
+        use any more -- e.g. between the points of a bandwidth sweep.  Ends with a barrier on the stream."""
+        if self.arena is None:
+            return
+        self.barrier_on_stream("world")
+        self._rings.clear()
+        self._by_off.clear()
+        self._sym_rows.clear()
+        self._flat_offsets.clear()
+        self.arena._slots.clear()
+        self.arena._top = 2 * _ALIGN
+
     def new_step(self):
         """Mark every ring entry reusable (call once per training step when running without autograd)."""
         for entries in self._rings.values():

@@ -156,7 +156,10 @@ class _PatternPeerInfo:
         self.rot = int(pat.recv_offset[(r + 1) % W]) if W > 1 else 0
         if self.rot >= max(self.n_halo, 1):
             self.rot = 0
-        counts = engine.all_gather_ints([self.n_nbr_local, self.n_halo, int(pat.send_offset[-1])])
+        remote_edges = int((pat.local_edge_list[:, 1] >= self.n_nbr_local).sum()) if self.n_halo else 0
+        counts = engine.all_gather_ints([self.n_nbr_local, self.n_halo, int(pat.send_offset[-1]), remote_edges])
+        # how often the remote edges of the whole graph re-read a halo row on average: the input of the (collective) pull-route choice
+        self.halo_reuse = sum(c[3] for c in counts) / max(sum(c[1] for c in counts), 1)
         self.nbr_local_all = [c[0] for c in counts]
         self.max_nbr_local = max(self.nbr_local_all)
         self.max_aug = max(c[0] + c[1] for c in counts)
@@ -594,14 +597,14 @@ class PeerMemoryEngine(TorchDistEngine):
         it runs (each remote edge costs one NVLink row read, nothing is staged).  ``"buffer"``: one pull kernel copies every halo
         row once into local memory first.  Peer loads bypass the local L2, so re-reads cross NVLink again: ``auto`` takes the
         in-kernel route only while the remote edges re-read a halo row fewer than ``DGRAPH_B200_PULL_REUSE`` (1.6) times on
-        average.  A rank decides for itself: both routes read the same slots behind the same barrier."""
+        average OVER ALL RANKS.  The choice must be the same on every rank -- the two routes use differently sized symmetric slots,
+        and a rank that chose differently would shift every later slot offset -- so it is made from the all-gathered totals."""
         mode = os.environ.get("DGRAPH_B200_PULL", "auto")
         if mode in ("kernel", "buffer"):
             return mode
         c = getattr(info, "_pull_mode", None)
         if c is None:
-            reuse = kp.remote_edge_count() / max(info.n_halo, 1)
-            c = info._pull_mode = "kernel" if reuse < float(os.environ.get("DGRAPH_B200_PULL_REUSE", "1.6")) else "buffer"
+            c = info._pull_mode = "kernel" if info.halo_reuse < float(os.environ.get("DGRAPH_B200_PULL_REUSE", "1.6")) else "buffer"
         return c
 
     def halo_grad_reduce_inplace(self, info, gx, ld_gx, H, slot_off, ld_slot, plan=None):

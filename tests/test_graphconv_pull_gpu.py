@@ -15,7 +15,7 @@ pytestmark = [pytest.mark.gpu, pytest.mark.timeout(180)]
 def _make_engines(W, pats, arena_bytes=64 << 20):
     from dgraph_b200.parallel.peer_engine import PeerMemoryEngine, SymmetricArena
 
-    counts = [[p.num_local_vertices, p.num_halo_vertices, int(p.send_offset[-1])] for p in pats]
+    counts = [[p.num_local_vertices, p.num_halo_vertices, int(p.send_offset[-1]), 0] for p in pats]
     bufs = [torch.zeros(arena_bytes, dtype=torch.uint8, device="cuda") for _ in range(W)]
     ptrs = [b.data_ptr() for b in bufs]
 
@@ -38,7 +38,7 @@ def _make_engines(W, pats, arena_bytes=64 << 20):
             return self._world
 
         def all_gather_ints(self, vals):
-            assert len(vals) == 3
+            assert len(vals) == 4
             return counts
 
         def barrier_on_stream(self):

@@ -37,7 +37,7 @@ def test_halo_pull_and_grad_reduce_emulated(W, F):
     e = random_graph(V, 6, seed=W, symmetric=False)
     part = partition(V, W, "random")
     pats = build_all_patterns(e, part, W)
-    counts = [[p.num_local_vertices, p.num_halo_vertices, int(p.send_offset[-1])] for p in pats]
+    counts = [[p.num_local_vertices, p.num_halo_vertices, int(p.send_offset[-1]), 0] for p in pats]
     infos = [_PatternPeerInfo(_FakeEngine(r, W, counts), pats[r]) for r in range(W)]
     max_aug = max(c[0] + c[1] for c in counts)
     xg = torch.randn(V, F, device="cuda").bfloat16()
@@ -118,7 +118,7 @@ def test_fused_pull_kernels_emulated(W):
     e = random_graph(V, 7, seed=W + 5, symmetric=False)
     part = partition(V, W, "random")
     pats = build_all_patterns(e, part, W)
-    counts = [[p.num_local_vertices, p.num_halo_vertices, int(p.send_offset[-1])] for p in pats]
+    counts = [[p.num_local_vertices, p.num_halo_vertices, int(p.send_offset[-1]), 0] for p in pats]
     infos = [_PatternPeerInfo(_FakeEngine(r, W, counts), pats[r]) for r in range(W)]
     xg = torch.randn(V, F, device="cuda").bfloat16()
     nmax = max(c[0] for c in counts)

@@ -11,7 +11,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "dgraph_b200", "lib", "libdgraph_b200.so")
-PROOF = ["UTCHMMA", "UTMALDG", "UTMASTG", "LDTM", "UTCBAR", "SYNCS", "HADD2.BF16_V2", "HFMA2.BF16_V2", "HSET2.BF16_V2",
+PROOF = ["UTCHMMA", "UTMALDG", "UTMASTG", "LDTM", "UTCBAR", "SYNCS", "HADD2.BF16_V2", "HFMA2.BF16_V2", "HFMA2.BF16_V2.RELU", "FHADD.BF16", "HSET2.BF16_V2",
          "HMNMX2.BF16_V2", "LDG.E.NA.128", "LDG.E.128", "STG.E.EF", "RED.E", "ATOMG", "STRONG.SYS", "R2P", "SHFL", "MUFU"]
 
 

@@ -18,6 +18,19 @@
     if (e__ != cudaSuccess) return (int)e__;       \
   } while (0)
 
+// The opt-in for more than 48 KB of dynamic shared memory is a per-DEVICE attribute of a kernel: remember it per device, so that a
+// process driving several GPUs configures the kernel on each of them (a single per-process flag left the second device unconfigured).
+#define DGB_OPT_IN_SMEM(kern, bytes)                                                                     \
+  do {                                                                                                   \
+    static bool configured__[64] = {false};                                                              \
+    int dev__ = 0;                                                                                       \
+    DGB_CUDA(cudaGetDevice(&dev__));                                                                     \
+    if (dev__ < 0 || dev__ >= 64 || !configured__[dev__]) {                                              \
+      DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)));  \
+      if (dev__ >= 0 && dev__ < 64) configured__[dev__] = true;                                         \
+    }                                                                                                    \
+  } while (0)
+
 namespace dgb {
 
 constexpr int kWarp = 32;

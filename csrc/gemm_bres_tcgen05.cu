@@ -214,11 +214,7 @@ template <int BLOCK_N, int ACT>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tcm, const Params& p, int smem_bytes,
                   cudaStream_t stream) {
   auto kern = gemm_bres_kernel<BLOCK_N, ACT>;
-  static bool configured = false;
-  if (!configured) {
-    DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-    configured = true;
-  }
+  DGB_OPT_IN_SMEM(kern, SMEM_LIMIT);
   int dev = 0, sms = 0;
   DGB_CUDA(cudaGetDevice(&dev));
   DGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));

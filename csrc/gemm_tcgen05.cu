@@ -329,11 +329,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
                        cudaStream_t stream) {
   using L = SmemLayout<BLOCK_N>;
   auto kern = gemm_bf16_tn_kernel<BLOCK_N, OUT_F32, GATHER, ACT, STORE_TMA>;
-  static bool configured = false;
-  if (!configured) {
-    DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
-    configured = true;
-  }
+  DGB_OPT_IN_SMEM(kern, L::TOTAL);
   int dev = 0, sms = 0;
   DGB_CUDA(cudaGetDevice(&dev));
   DGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));

@@ -185,11 +185,7 @@ static int launch_wgrad(const CUtensorMap& tg, const CUtensorMap& tx, float* dW,
                         const void* X, int64_t ldx, const int* x_idx, cudaStream_t s) {
   using L = WgSmem<BN2>;
   auto kern = gemm_wgrad_kernel<BN2, GX>;
-  static bool configured = false;
-  if (!configured) {
-    DGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
-    configured = true;
-  }
+  DGB_OPT_IN_SMEM(kern, L::TOTAL);
   int dev = 0, sms = 0;
   DGB_CUDA(cudaGetDevice(&dev));
   DGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));

@@ -406,11 +406,7 @@ DGB_API int dgb_mlp2_ln_fused_bf16(int n_seg, const void* const* seg_base, const
   if (rc) return rc;
   rc = make_tmap_bf16_2d(&t_y, y, (uint64_t)M, BN, (uint64_t)ld_y, 32, 64);
   if (rc) return rc;
-  static bool configured = false;
-  if (!configured) {
-    DGB_CUDA(cudaFuncSetAttribute(mlp2_ln_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_TOTAL));
-    configured = true;
-  }
+  DGB_OPT_IN_SMEM(mlp2_ln_fused_kernel, SMEM_TOTAL);
   int dev = 0, sms = 0;
   DGB_CUDA(cudaGetDevice(&dev));
   DGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));

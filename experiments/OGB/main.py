@@ -38,11 +38,15 @@ def _run_experiment(dataset, comm, lr, epochs, log_prefix, hidden_dims, num_clas
     cdt = torch.bfloat16 if device.type == "cuda" else torch.float32
     in_dim = x.shape[1]
     pad = (-in_dim) % 8
-    x = torch.nn.functional.pad(x, (0, pad)).to(device, cdt)
     y = y.to(device)
     pat.to(device)
+    exchanger = HaloExchange(comm)
+    # the features live where the first layer's exchange can use them in place (symmetric memory on the peer engine)
+    xs = exchanger.symmetric_rows(pat, in_dim + pad, cdt, device=device)
+    xs.copy_(torch.nn.functional.pad(x, (0, pad)).to(device, cdt))
+    x = xs
     masks = {k: v.to(device) for k, v in dataset.get_masks().items()}
-    model = CommAwareGCN(in_dim, hidden_dims, num_classes, HaloExchange(comm), comm, compute_dtype=cdt).to(device)
+    model = CommAwareGCN(in_dim, hidden_dims, num_classes, exchanger, comm, compute_dtype=cdt).to(device)
     opt = FusedAdam(model.parameters(), lr=lr, comm=comm)
     crit = torch.nn.CrossEntropyLoss()
     train_idx = torch.nonzero(masks["train_mask"], as_tuple=True)[0]  # index form once, outside the epoch loop

@@ -192,8 +192,11 @@ def test_reference_local_kernel_tests_pass_against_this_package_gpu(tmp_path):
     import subprocess
     import sys
 
-    f = "/root/reference/tests/test_local_kernels.py"
-    if not os.path.exists(f):
+    # the GPU boxes have no /root/reference: fall back to the unmodified copy that tools/install_reference.sh keeps next to the
+    # reference install (baseline/_ref travels to the box)
+    cands = ["/root/reference/tests/test_local_kernels.py", os.path.join(ROOT, "baseline", "_ref", "tests", "test_local_kernels.py")]
+    f = next((c for c in cands if os.path.exists(c)), None)
+    if f is None:
         pytest.skip("reference tree not available")
     env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
     r = subprocess.run([sys.executable, "-m", "pytest", f, "-q", "-p", "no:cacheprovider", "--rootdir", str(tmp_path)],

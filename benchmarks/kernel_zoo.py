@@ -48,16 +48,14 @@ def gcn_one_rank(scale):
 
 
 def gcn_pull_emulated(W=2, V=200_000):
-    from tests._graphs import partition
-    from tests.test_graphconv_pull_gpu import _make_engines
-
-    from dgraph_b200.data.synthetic import symmetric_locality_graph
+    from dgraph_b200.data.synthetic import contiguous_partition, symmetric_locality_graph
     from dgraph_b200.ops.graphconv import graphconv_pull_q
     from dgraph_b200.parallel import build_all_patterns
+    from dgraph_b200.parallel.peer_engine import emulated_engines
 
     e = symmetric_locality_graph(V, V * 24, cut_fraction=0.1, device="cuda").cpu()
-    pats = build_all_patterns(e, partition(V, W, "contiguous"), W)
-    engines = _make_engines(W, pats, arena_bytes=1 << 30)
+    pats = build_all_patterns(e, contiguous_partition(V, W), W)
+    engines = emulated_engines(pats, arena_bytes=1 << 30)
     F, H = 256, 256
     w = (torch.randn(H, 2 * F, device="cuda") * 0.05).requires_grad_(True)
     b = torch.zeros(H, device="cuda", requires_grad=True)

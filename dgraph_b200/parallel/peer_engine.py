@@ -849,3 +849,45 @@ class PeerMemoryEngine(TorchDistEngine):
                 dist.barrier()
             self.arena.close()
             self.arena = None
+
+
+def emulated_engines(patterns, arena_bytes: int = 64 << 20) -> List["PeerMemoryEngine"]:
+    """``W = len(patterns)`` peer-memory engines inside ONE process on the current GPU: every "rank's" symmetric arena is an ordinary
+    device buffer (a peer pointer is just a pointer), barriers are no-ops, and the caller runs every phase rank after rank on one
+    stream -- so no kernel ever waits for another one.  What a rank reads from its peers is whatever they wrote before, hence run
+    each phase twice when the result matters (the first pass fills the slots).  For tests, single-GPU profiling of the peer kernels
+    (`benchmarks/kernel_zoo.py`) and the smoke test; real runs use one process per GPU."""
+    W = len(patterns)
+    counts = [[p.num_local_vertices if p.num_neighbor_local_vertices is None else p.num_neighbor_local_vertices, p.num_halo_vertices,
+               int(p.send_offset[-1]), 0] for p in patterns]
+    bufs = [torch.zeros(arena_bytes, dtype=torch.uint8, device="cuda") for _ in range(W)]
+    ptrs = [b.data_ptr() for b in bufs]
+
+    class _Emulated(PeerMemoryEngine):
+        def __init__(self, rank):  # noqa: D401 - no process group: everything the kernels need is set by hand
+            self._rank, self._world, self._group = rank, W, None
+            self._job_rank, self._job_world = rank, W
+            self._ranks_per_graph = -1
+            self.device = torch.device("cuda", torch.cuda.current_device())
+            self._epoch, self._epoch_all, self._uid, self._ar_parity = 0, 0, 0, 0
+            self._rings, self._by_off, self._sym_rows, self._flat_offsets = {}, {}, {}, {}
+            self._timeout_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self._timeout_host = self._timeout_ev = None
+            self.device_epoch = False
+            self.arena = SymmetricArena(arena_bytes, rank, W, self.device, local_ptrs=ptrs)
+            self._keep = bufs
+
+        def get_rank(self):
+            return self._rank
+
+        def get_world_size(self):
+            return self._world
+
+        def all_gather_ints(self, vals):
+            assert len(vals) == 4, "emulation knows the pattern counts only"
+            return counts
+
+        def barrier_on_stream(self, scope: str = "graph"):
+            self._epoch += 1
+
+    return [_Emulated(r) for r in range(W)]

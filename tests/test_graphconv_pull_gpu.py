@@ -13,38 +13,10 @@ pytestmark = [pytest.mark.gpu, pytest.mark.timeout(180)]
 
 
 def _make_engines(W, pats, arena_bytes=64 << 20):
-    from dgraph_b200.parallel.peer_engine import PeerMemoryEngine, SymmetricArena
+    from dgraph_b200.parallel.peer_engine import emulated_engines
 
-    counts = [[p.num_local_vertices, p.num_halo_vertices, int(p.send_offset[-1]), 0] for p in pats]
-    bufs = [torch.zeros(arena_bytes, dtype=torch.uint8, device="cuda") for _ in range(W)]
-    ptrs = [b.data_ptr() for b in bufs]
-
-    class _Emu(PeerMemoryEngine):
-        def __init__(self, rank):  # noqa: D401 - no process group: everything the kernels need is set by hand
-            self._rank, self._world, self._group = rank, W, None
-            self._ranks_per_graph = -1
-            self.device = torch.device("cuda", torch.cuda.current_device())
-            self._epoch, self._uid = 0, 0
-            self._rings, self._by_off, self._sym_rows = {}, {}, {}
-            self._timeout_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
-            self.device_epoch = False
-            self.arena = SymmetricArena(arena_bytes, rank, W, self.device, local_ptrs=ptrs)
-            self._keep = bufs
-
-        def get_rank(self):
-            return self._rank
-
-        def get_world_size(self):
-            return self._world
-
-        def all_gather_ints(self, vals):
-            assert len(vals) == 4
-            return counts
-
-        def barrier_on_stream(self):
-            self._epoch += 1
-
-    return [_Emu(r) for r in range(W)]
+    assert len(pats) == W
+    return emulated_engines(pats, arena_bytes)
 
 
 @pytest.mark.parametrize("W,mode,how", [(2, "kernel", "random"), (3, "kernel", "random"), (3, "buffer", "random"),

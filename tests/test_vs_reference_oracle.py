@@ -185,7 +185,6 @@ def test_reference_single_process_test_files_pass_against_this_package(tmp_path)
 
 
 @pytest.mark.gpu
-@pytest.mark.xfail(strict=False, reason="added after the round's GPU budget was spent: first hardware run decides (XPASS expected)")
 def test_reference_local_kernel_tests_pass_against_this_package_gpu(tmp_path):
     """The reference's ``tests/test_local_kernels.py`` (its 1-GPU test of the ``torch_local`` extension), unmodified, with
     ``DGraph.torch_local`` resolving to this repository's launchers (``csrc/rank_local.cu``)."""

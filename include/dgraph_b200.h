@@ -187,16 +187,17 @@ int dgb_masked_ce_bwd(const void* logits, int64_t ld, int is_f32, const int64_t*
                               int64_t n_sel, int C, const float* lse, const float* gout, void* dsel, int64_t ld_o,
                               void* stream);
 
-/* Experimental: the same GEMM with the B operand resident in shared memory (small K).  Returns 801 (cudaErrorNotSupported) when
- * the shape does not fit; opt-in through DGRAPH_B200_GEMM_BRES=1, not yet validated on hardware.  No counterpart in the reference. */
+/* The same GEMM with its N tile of B resident in shared memory and 5-8 A stages (tall-skinny, small K): the Python layer takes it
+ * for K <= 128 (2.45 M x 256 x 104: 0.47 -> 0.32 ms on B200).  Returns 801 (cudaErrorNotSupported) when the shape does not fit.  No
+ * counterpart in the reference. */
 int dgb_gemm_bf16_tn_bres(const void* A, int64_t lda, const void* B, int64_t ldb, void* C, int64_t ldc, int M, int N, int K,
                           const float* bias, int act, void* stream);
 
-/* Experimental: a whole GraphCast MLP block in one kernel (csrc/mlp_fused_tcgen05.cu),
+/* A whole GraphCast MLP block in one kernel (csrc/mlp_fused_tcgen05.cu; the default for the block shapes it handles),
  *   y = LayerNorm(SiLU(cat_s(A_s[idx_s]) @ W1^T + b1) @ W2^T + b2) * gamma + beta (+ residual),   hidden = out = 128;
  * reference: MeshGraphMLP inside MeshEdgeBlock / MeshNodeBlock, experiments/GraphCast/layers.py:24-75,136-143,205-216 (nine ATen
  * kernels there).  W1p as for dgb_gather_gemm_bf16; pre / z / mean / rstd are saved for the backward.  Returns 801 when the
- * shapes or alignments are not handled; opt-in through DGRAPH_B200_FUSED_MLP=1, not yet validated on hardware. */
+ * shapes or alignments are not handled (the caller then runs the gather-GEMM / GEMM / LayerNorm chain). */
 int dgb_mlp2_ln_fused_bf16(int n_seg, const void* const* seg_base, const int64_t* seg_ld, const int* const* seg_idx,
                            const int* seg_k, const void* W1p, int64_t ldw1, const float* b1, const void* W2, int64_t ldw2,
                            const float* b2, const float* gamma, const float* beta, float eps, const void* residual,

@@ -7,7 +7,12 @@ region: this file only generates the synthetic inputs (the same generators as ou
   rgat        reference `CommAwareRGAT` (`experiments/OGB-LSC/RGAT.py:271-382`, CommPlan gather / scatter + `torch_local`) + its
               `SyntheticHeterogeneousDataset` + DDP + Adam, the step of `Trainer.train` (`Trainer.py:131-146`) without its prints,
               `empty_cache()` and per-epoch device synchronisation.
-  graphcast   unavailable: the reference's GraphCast cannot be instantiated as shipped.
+  graphcast   one GPU only: the reference's unmodified `model.py` / `layers.py` (`DGraphCast`, 1,025,627 parameters, fp32) + Adam + MSE.  Two
+              pieces of the reference cannot be used as shipped and are replaced OUTSIDE `baseline/_ref`: its
+              `SingleProcessDummyCommunicator` is abstract (a 20-line concrete equivalent is defined below, same `torch.gather` /
+              `scatter_add` bodies), and its graph generator cannot construct its graph object, so the static graph comes from this
+              repository's generator (same field names, same 0.25 degree sizes).  More than one rank: unavailable (distributed wiring
+              incomplete upstream).
   papers100m  unavailable: the reference has no GraphSAGE model and needs the global edge list on every rank.
 """
 from __future__ import annotations
@@ -173,13 +178,92 @@ def _rgat(args, out, sampler):
     dist.destroy_process_group()
 
 
+def _graphcast(args, out, sampler):
+    from benchmarks.runner import Workload, run_workload
+
+    sys.path.insert(0, os.path.join(REF, "experiments", "GraphCast"))
+    import graphcast_config
+    from DGraph.CommunicatorBase import CommunicatorBase
+    from model import DGraphCast
+
+    rank, world, local, dev = _setup()
+    if world != 1:
+        dist.destroy_process_group()
+        return _unavailable(out, "reference GraphCast has no working multi-rank path (SURVEY.md Q7); its reference arm is one GPU only")
+
+    class _SingleProcessCommunicator(CommunicatorBase):
+        """Concrete stand-in for the reference's abstract `SingleProcessDummyCommunicator` (`experiments/GraphCast/dist_utils.py:8-46`):
+        the same two tensor expressions, plus the abstract methods it forgot."""
+
+        def __init__(self):
+            super().__init__()
+            self.backend, self._ranks_per_sample = "single", 1
+
+        def init_process_group(self, *a, **k):
+            return self
+
+        def get_rank(self):
+            return 0
+
+        def get_world_size(self):
+            return 1
+
+        def barrier(self):
+            pass
+
+        def destroy(self):
+            pass
+
+        def scatter(self, tensor, src, rank_mappings, num_local_nodes):
+            src = src.unsqueeze(-1).expand(-1, tensor.shape[-1])
+            return torch.zeros(num_local_nodes, tensor.shape[1]).to(tensor.device).scatter_add(0, src, tensor)
+
+        def gather(self, tensor, dst, rank_mappings):
+            return torch.gather(tensor, 0, dst.unsqueeze(-1).expand(-1, tensor.shape[-1]))
+
+    # static graph and data: this repository's generators (data only, outside the timed region)
+    from dgraph_b200.data.graphcast_graph import DistributedGraphCastGraphGenerator, SyntheticWeatherDataset
+
+    cfg = graphcast_config.Config()
+    res, level = (721, 1440), cfg.model.mesh_level
+    if args.scale < 1.0:  # debug only
+        res, level = (max(int(721 * args.scale), 19), max(int(1440 * args.scale), 36)), max(2, int(round(6 + torch.log2(torch.tensor(args.scale)).item())))
+        cfg.model.mesh_level = level
+    sg = DistributedGraphCastGraphGenerator(res, level, multi=cfg.model.multimesh).shard(0, 1).to(dev, torch.float32)
+    for n in list(sg.__dataclass_fields__):
+        v = getattr(sg, n)
+        if isinstance(v, torch.Tensor) and not v.is_floating_point():
+            setattr(sg, n, v.long())
+    item = SyntheticWeatherDataset(cfg.model.input_grid_dim, res, num_samples=2, grid_rows=sg.grid_rows_global.cpu())[0]
+    xh, yh = item["invar"].float().contiguous().pin_memory(), item["outvar"].float().contiguous().pin_memory()
+    torch.manual_seed(0)
+    model = DGraphCast(cfg, _SingleProcessCommunicator()).to(dev)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+
+    def step(x, y):
+        opt.zero_grad()
+        loss = torch.nn.functional.mse_loss(model(x.unsqueeze(0), sg), y)
+        loss.backward()
+        opt.step()
+        return loss
+
+    wl = Workload(
+        metric="GraphCast 0.25 degree training step time (zero_grad+fwd+MSE+bwd+Adam)", unit="ms", work_per_step=0.0, dtype="fp32",
+        host_inputs=(xh, yh), alloc_inputs=lambda tag: (torch.empty_like(xh, device=dev), torch.empty_like(yh, device=dev)), step=step,
+        loss_weight=float(xh.shape[0]),
+        config={"model": f"reference DGraphCast (model.py / layers.py unmodified, {sum(p.numel() for p in model.parameters())} parameters, fp32) + "
+                         "torch.optim.Adam; single-process communicator and static graph from outside baseline/_ref (the reference's own "
+                         "cannot be instantiated as shipped, SURVEY Q7)",
+                "graph": f"grid {res[0]}x{res[1]} = {res[0] * res[1]} nodes, icosahedral multimesh level {level} (this repository's generator)",
+                "global_batch": 1, "seq_len": None, "parallelism": "1 GPU", "l2": "inputs larger than L2"})
+    run_workload(wl, args, rank, world, dev, "reference", out, sampler)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
 def run(args, out, sampler):
     if not os.path.isdir(os.path.join(REF, "DGraph")):
         return _unavailable(out, "baseline/_ref is missing: run tools/install_reference.sh (offline pip install of /root/reference)")
-    if args.config == "graphcast":
-        return _unavailable(out, "reference GraphCast cannot be instantiated as shipped: SingleProcessDummyCommunicator is abstract, "
-                                 "DistributedGraphCastGraph is built with a non-existent field, dataset and trainer disagree on arguments "
-                                 "(SURVEY.md Q7); timing it would mean patching the reference")
     if args.config == "papers100m":
         return _unavailable(out, "reference has no GraphSAGE model and its plan builder needs the global edge list (26 GB of int64 pairs) "
                                  "on every rank")
@@ -188,7 +272,7 @@ def run(args, out, sampler):
     sys.path.insert(0, REF)  # ahead of the repo root, whose DGraph/ directory is our import-compatible shim
     assert "DGraph" not in sys.modules, "our DGraph shim was imported before the reference"
     try:
-        (_halo if args.config == "halo" else _rgat)(args, out, sampler)
+        {"halo": _halo, "rgat": _rgat, "graphcast": _graphcast}[args.config](args, out, sampler)
     except torch.OutOfMemoryError as e:
         _unavailable(out, f"reference ran out of device memory: {str(e)[:200]}")
     except Exception as e:  # noqa: BLE001

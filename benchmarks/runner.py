@@ -83,7 +83,7 @@ def run_workload(wl: Workload, args, rank: int, world: int, dev, impl: str, out,
                "copy_scheme": "double-buffered H2D on a side stream; loss read on the host one step later (every step, inside the "
                               "timed region); identical in both arms"}
     w = float(wl.loss_weight if wl.loss_weight is not None else 1.0)
-    gl = torch.tensor([float(losses[0]) * w, float(losses[-1]) * w, w], dtype=torch.float64, device=dev)
+    gl = torch.tensor([float(losses[0].detach()) * w, float(losses[-1].detach()) * w, w], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(gl)
     if rank == 0:

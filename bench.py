@@ -11,8 +11,16 @@ Scaling is *strong*: the same 2.45 M-node / 61.9 M-edge graph is split over N GP
 
 Two arms:
   * ours      -- dgraph_b200 (bf16 compute, fp32 master weights + fused Adam), public API: Communicator,
-                 build_communication_pattern, HaloExchange, CommAwareGCN, FusedAdam.
+                 build_communication_pattern, HaloExchange (features in ``symmetric_rows``), CommAwareGCN, FusedAdam.  With several
+                 GPUs the step is captured once and replayed as a CUDA graph (``--no-cuda-graph`` for eager).
   * reference -- the unmodified LBANN/DGraph NCCL path installed under baseline/_ref (fp32), see baseline/ref_bench.py.
+Both arms run the same end-to-end loop (``dgraph_b200/utils/e2e.py``) for the ``e2e`` entry and report the GLOBAL loss of the first and
+last step.  The line also carries ``config.powerlaw_variant``: the same model and step, device-timed, on the power-law variant of the
+graph (hub vertices of degree > 17 k; ``--no-powerlaw`` skips it).
+
+Other workloads, same JSON line (``benchmarks/workloads.py``, reference arms in ``baseline/ref_workloads.py``):
+``--config papers100m`` (GraphSAGE, 111 M nodes over 8 GPUs; weak scaling for fewer), ``--config graphcast``, ``--config rgat``
+(``--rgat-mult 8`` for the 8x graph, ``--rgat-relations first`` to mirror the reference), ``--config halo`` (bandwidth sweep, field ``sweep``).
 """
 from __future__ import annotations
 

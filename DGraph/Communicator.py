@@ -6,6 +6,11 @@ import types
 
 from dgraph_b200.communicator import Communicator, SUPPORTED_BACKENDS  # noqa: F401
 
+# The reference's back-end tests write ``import DGraph.Communicator as Comm; Comm.Communicator.init_process_group(...)``
+# (``tests/test_mpi_backend.py:2,16``, ``test_nccl_backend.py:17``).  On Python >= 3.7 that import binds ``Comm`` to the package
+# attribute, i.e. to the class, so the spelling needs the class to be reachable from itself.
+Communicator.Communicator = Communicator
+
 
 class _ClassLikeModule(types.ModuleType):
     def __call__(self, *a, **k):

@@ -1,5 +1,5 @@
-// F4: one kernel for a whole GraphCast MLP block (experimental, opt-in with DGRAPH_B200_FUSED_MLP=1; compiled and inspected,
-// not yet run on hardware):
+// F4: one kernel for a whole GraphCast MLP block (the default GraphCast path; DGRAPH_B200_FUSED_MLP=0 selects the three-kernel
+// chain; numerics: tests/test_mlp_fused_gpu.py):
 //
 //     pre = cat([A_0[idx_0], A_1[idx_1], A_2[idx_2]], 1) @ W1^T + b1          (gather-GEMM, tcgen05, K streamed)
 //     h   = SiLU(pre)                                                          (TMEM -> registers -> swizzled smem, never HBM)

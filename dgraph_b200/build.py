@@ -83,7 +83,8 @@ HOST_LIB = OUT_DIR / "libdgraph_b200_host.so"
 
 
 def build_host(force: bool = False) -> Path:
-    """Host-only C++ runtime pieces (``csrc/host/*.cpp``: the multilevel graph partitioner) -> ``libdgraph_b200_host.so``.
+    """Host-only C++ runtime pieces (``csrc/host/*.cpp``: the multilevel graph partitioner, the shared-memory one-sided
+    windows of the CPU engine) -> ``libdgraph_b200_host.so``.
     Separate from the CUDA library so that a host-code change never triggers an nvcc rebuild."""
     srcs = sorted((CSRC / "host").glob("*.cpp"))
     if not srcs:
@@ -99,7 +100,7 @@ def build_host(force: bool = False) -> Path:
     cxx = os.environ.get("CXX") or shutil.which("g++") or shutil.which("c++")
     if not cxx:
         raise RuntimeError("no C++ compiler found")
-    cmd = [cxx, "-O3", "-std=c++17", "-shared", "-fPIC", "-fvisibility=hidden", "-o", str(HOST_LIB), *map(str, srcs)]
+    cmd = [cxx, "-O3", "-std=c++17", "-shared", "-fPIC", "-fvisibility=hidden", "-pthread", "-o", str(HOST_LIB), *map(str, srcs), "-lrt"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"host build failed:\n{r.stderr[-4000:]}")

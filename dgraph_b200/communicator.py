@@ -8,8 +8,10 @@ Parity: reference ``DGraph/Communicator.py:21-141`` -- same constructor, static 
 Backend strings: ``"nccl"``, ``"mpi"``, ``"nvshmem"`` are kept for API compatibility.  On a CUDA
 box every one of them maps to the single sm_100a peer-memory engine (``PeerMemoryEngine``: NVLink loads/stores
 issued from inside the kernels, NCCL only for bootstrap and small metadata); ``DGRAPH_B200_ENGINE=torch``
-selects the plain ``torch.distributed`` baseline engine instead.  On a CPU-only box they map to gloo.  Extra
-names: ``"gloo"``, ``"torch"`` (baseline engine), ``"b200"`` (peer-memory engine, explicit).
+selects the plain ``torch.distributed`` baseline engine instead.  On a CPU-only box ``"nccl"`` / ``"nvshmem"`` map to gloo and
+``"mpi"`` to the one-sided shared-memory window engine (``parallel/shm_engine.py``: remote-memory-access epochs like the
+reference's MPI engine, gloo for collectives; ``DGRAPH_B200_ENGINE=torch`` or a missing C++ compiler give plain gloo).  Extra
+names: ``"gloo"``, ``"torch"`` (baseline engine), ``"b200"`` (peer-memory engine, explicit), ``"shm"`` (window engine, explicit).
 """
 from __future__ import annotations
 
@@ -21,7 +23,7 @@ import torch
 from dgraph_b200.communicator_base import CommunicatorBase
 
 SUPPORTED_BACKENDS = ["nccl", "mpi", "nvshmem"]
-_EXTRA_BACKENDS = ["gloo", "torch", "b200", "emulated", "single"]
+_EXTRA_BACKENDS = ["gloo", "torch", "b200", "shm", "emulated", "single"]
 
 
 def _make_engine(backend: str, **kwargs):
@@ -38,8 +40,12 @@ def _make_engine(backend: str, **kwargs):
         import torch.distributed as dist
 
         if dist.is_available() and dist.is_initialized() and 0 < int(rpg) < dist.get_world_size():
-            return _make_hybrid_engine(int(rpg), use_cuda, **kwargs)
-    if backend == "gloo" or not use_cuda:
+            return _make_hybrid_engine(int(rpg), use_cuda, _backend=backend, **kwargs)
+    if _wants_windows(backend, use_cuda, forced):
+        from dgraph_b200.parallel.shm_engine import ShmWindowEngine
+
+        return ShmWindowEngine(**kwargs)
+    if backend in ("gloo", "shm") or not use_cuda:
         return TorchDistEngine(dist_backend="gloo", **kwargs)
     if backend == "torch" or forced == "torch":
         return TorchDistEngine(dist_backend="nccl", **kwargs)
@@ -48,7 +54,16 @@ def _make_engine(backend: str, **kwargs):
     return PeerMemoryEngine(**kwargs)
 
 
-def _make_hybrid_engine(rpg: int, use_cuda: bool, **kwargs):
+def _wants_windows(backend: str, use_cuda: bool, forced: str) -> bool:
+    """``"shm"`` anywhere, ``"mpi"`` on a CPU-only box: the one-sided shared-memory engine, when its host library can be built."""
+    if backend == "shm" or (backend == "mpi" and not use_cuda and forced != "torch"):
+        from dgraph_b200.parallel import shm_engine
+
+        return shm_engine.available()
+    return False
+
+
+def _make_hybrid_engine(rpg: int, use_cuda: bool, _backend: str = "nccl", **kwargs):
     """Hybrid data-parallel x graph-partition layout (SURVEY §2.5): the world is cut into ``world / ranks_per_graph`` replicas;
     each replica partitions one graph over its ``ranks_per_graph`` ranks.  Halo exchanges / plan collectives run inside the
     replica's process group, gradient all-reduces over the whole world.  (The reference only does the rank arithmetic,
@@ -70,6 +85,10 @@ def _make_hybrid_engine(rpg: int, use_cuda: bool, **kwargs):
         from dgraph_b200.parallel.peer_engine import PeerMemoryEngine
 
         eng = PeerMemoryEngine(ranks_per_graph=rpg, group=mine, **kw)
+    elif _wants_windows(_backend, use_cuda, os.environ.get("DGRAPH_B200_ENGINE", "").lower()):
+        from dgraph_b200.parallel.shm_engine import ShmWindowEngine
+
+        eng = ShmWindowEngine(ranks_per_graph=rpg, group=mine, **kw)  # one window set per replica
     else:
         eng = TorchDistEngine(dist_backend="nccl" if use_cuda else "gloo", group=mine, ranks_per_graph=rpg, **kw)
     eng.replica_id, eng.num_replicas, eng.global_rank, eng.global_world = rank // rpg, world // rpg, rank, world

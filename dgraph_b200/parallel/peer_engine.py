@@ -452,7 +452,7 @@ class PeerMemoryEngine(TorchDistEngine):
         self._timeout_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._timeout_host = self._timeout_ev = None
         self._spins = ctypes.c_longlong(int(os.environ.get("DGRAPH_B200_BARRIER_SPINS", str(1 << 26))))  # read once
-        # opt-in (DGRAPH_B200_DEVICE_EPOCH=1, not yet run on hardware): barrier epochs counted in device memory, so a training step
+        # DGRAPH_B200_DEVICE_EPOCH=1 (what `bench.py` sets for its multi-GPU CUDA-graph runs): barrier epochs counted in device memory, so a training step
         # with exchanges can be captured in a CUDA graph.  Fixed at construction: the two barrier forms must never be mixed.
         self.device_epoch = os.environ.get("DGRAPH_B200_DEVICE_EPOCH", "0") == "1"
         self._epoch_dev = torch.zeros(1, dtype=torch.int32, device=self.device)

@@ -11,7 +11,7 @@ Requirements on the captured region (all met by this package's single-GPU path):
 * values that change per step live in device memory: ``FusedAdam(capturable=True)`` keeps ``t`` and the learning rate there;
 * inputs are copied into static buffers before each replay; outputs are read from static tensors.
 Multi-GPU: the peer-memory engine normally passes the barrier epoch as a kernel argument (frozen at capture time); with
-``DGRAPH_B200_DEVICE_EPOCH=1`` (set before the communicator is created; experimental, not yet run on hardware) the epoch, like the
+``DGRAPH_B200_DEVICE_EPOCH=1`` (set before the communicator is created; `bench.py` does so for its multi-GPU runs) the epoch, like the
 optimizer step, is read from and advanced in device memory, and a step with halo exchanges can be captured.  Every rank must
 capture and replay the same sequence (the barriers inside the graph still wait for all peers).
 """

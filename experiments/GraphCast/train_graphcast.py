@@ -50,7 +50,7 @@ def main(batch_size: int = 1, is_distributed: bool = False, test_run: bool = Fal
     assert backend in ("single", "nccl", "nvshmem", "mpi")
     assert batch_size == 1, "full-graph training: one sample per step (as the reference)"
     world_env = int(os.environ.get("WORLD_SIZE", "1"))
-    if cuda_graph and world_env > 1:  # experimental: device-resident barrier epochs make steps with halo exchanges capturable
+    if cuda_graph and world_env > 1:  # device-resident barrier epochs make steps with halo exchanges capturable
         os.environ["DGRAPH_B200_DEVICE_EPOCH"] = "1"
     hybrid = is_distributed and 0 < procs_per_graph < world_env and world_env % procs_per_graph == 0
     # hybrid data-parallel x graph-partition: `procs_per_graph` ranks share one sample's graph, replicas take different samples

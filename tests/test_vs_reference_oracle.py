@@ -184,6 +184,31 @@ def test_reference_single_process_test_files_pass_against_this_package(tmp_path)
     assert int(tail.split(" passed")[0].split()[-1]) >= 39, tail
 
 
+@pytest.mark.timeout(300)
+def test_reference_mpi_backend_tests_pass_against_this_package(tmp_path):
+    """The reference's ``tests/test_mpi_backend.py`` (written for ``mpirun -n 2``: init, one-sided gather, one-sided scatter through
+    ``Communicator.init_process_group("mpi")``), unmodified, as two CPU ranks started by ``tools/run_ranks.py``.  On a CPU box
+    ``"mpi"`` is the shared-memory window engine (``parallel/shm_engine.py``), so the reference's cases exercise the same
+    fence / get / accumulate epochs its mpi4py engine would."""
+    import subprocess
+    import sys
+
+    from dgraph_b200.parallel import shm_engine
+
+    f = "/root/reference/tests/test_mpi_backend.py"
+    if not os.path.exists(f):
+        pytest.skip("reference tree not available")
+    if not shm_engine.available():
+        pytest.skip("host library cannot be built (no C++ compiler)")
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT", "TORCHELASTIC_USE_AGENT_STORE"):
+        env.pop(k, None)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "run_ranks.py"), "-n", "2", "--timeout", "240", "--", sys.executable,
+                        "-m", "pytest", f, "-q", "-p", "no:cacheprovider", "--rootdir", str(tmp_path)],
+                       capture_output=True, text=True, cwd=str(tmp_path), env=env, timeout=280)
+    assert r.returncode == 0 and "3 passed" in r.stdout, r.stdout[-3000:] + r.stderr[-1000:]
+
+
 @pytest.mark.gpu
 def test_reference_local_kernel_tests_pass_against_this_package_gpu(tmp_path):
     """The reference's ``tests/test_local_kernels.py`` (its 1-GPU test of the ``torch_local`` extension), unmodified, with

@@ -24,18 +24,32 @@ def masked_cross_entropy_ref(logits: torch.Tensor, labels: torch.Tensor, idx: Op
     return F.cross_entropy(up(logits.index_select(0, idx)), labels.reshape(-1).index_select(0, idx))
 
 
-def _rows_unique(idx: torch.Tensor, V: int) -> bool:
-    """``idx`` lists every row at most once (one device-to-host read per index tensor and version, then cached on the tensor)."""
+def _row_support(idx: torch.Tensor):
+    """``None`` when ``idx`` lists every row at most once, else ``(unique rows, position of every entry among them)``.  One
+    device-to-host read per index tensor and version; the result is cached on the tensor, so the unique-row tensor is the same object
+    every step (consumers of the row-support hint cache per-label-set plans on its identity)."""
     tag = (idx.data_ptr(), idx.numel(), idx._version)
-    hit = getattr(idx, "_dgb_unique", None)
+    hit = getattr(idx, "_dgb_support", None)
     if hit is not None and hit[0] == tag:
         return hit[1]
-    u = bool(torch.bincount(idx, minlength=1).max() <= 1) if idx.numel() else True
+    sup = None
+    if idx.numel() and bool(torch.bincount(idx, minlength=1).max() > 1):
+        uniq, inv = torch.unique(idx, return_inverse=True)
+        sup = (uniq.contiguous(), inv.contiguous())
     try:
-        idx._dgb_unique = (tag, u)
+        idx._dgb_support = (tag, sup)
     except Exception:  # noqa: BLE001
         pass
-    return u
+    return sup
+
+
+def _merge_duplicate_rows(dsel: torch.Tensor, sup) -> torch.Tensor:
+    """Compact gradient rows of the unique rows: a row listed k times counts k times in the loss, so its k rows add up (fp32 sum,
+    rounded once)."""
+    uniq, inv = sup
+    acc = torch.zeros((uniq.numel(), dsel.shape[1]), dtype=torch.float32, device=dsel.device)
+    acc.index_add_(0, inv, dsel.float())
+    return acc.to(dsel.dtype)
 
 
 class _MaskedCE(Function):
@@ -68,12 +82,14 @@ class _MaskedCE(Function):
         if idx is None:
             return dsel[:, :C].to(logits.dtype), None, None
         dlogits = torch.zeros((V, C), dtype=logits.dtype, device=logits.device)
-        if _rows_unique(idx, V):
-            dlogits.index_copy_(0, idx, dsel[:, :C].to(logits.dtype))
-            if logits.dtype == torch.bfloat16:
-                _sparsity.put(dlogits, idx, dsel)  # padded compact rows [n_sel, ld_o]
-        else:  # a row listed twice counts twice in the loss: its gradient rows add up, and the compact rows are no longer "the rows"
-            dlogits.index_add_(0, idx, dsel[:, :C].to(logits.dtype))
+        # The hint is left on every call, whatever the index tensor holds: in a distributed step the consumers choose collective
+        # code paths by its presence, so it must not depend on one rank's data (duplicates on one rank only, an empty label set).
+        sup = _row_support(idx)
+        if sup is not None:
+            idx, dsel = sup[0], _merge_duplicate_rows(dsel, sup)
+        dlogits.index_copy_(0, idx, dsel[:, :C].to(logits.dtype))
+        if logits.dtype == torch.bfloat16:
+            _sparsity.put(dlogits, idx, dsel)  # padded compact rows [n_sel, ld_o]
         return dlogits, None, None
 
 

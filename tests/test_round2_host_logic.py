@@ -110,3 +110,22 @@ def test_bench_workload_modules_parse_and_declare_every_config():
     src = open(os.path.join(ROOT, "bench.py")).read()
     for cfg in ("products", "papers100m", "graphcast", "rgat", "halo"):
         assert f'"{cfg}"' in src
+
+
+def test_duplicate_label_rows_merge_into_unique_support():
+    """The loss's row-support hint for an index tensor with repeated rows: the compact rows of the unique rows equal what
+    `index_add_` over the repeated list gives, and the unique-row tensor is the same object on every call."""
+    from dgraph_b200.ops.loss import _merge_duplicate_rows, _row_support
+
+    g = torch.Generator().manual_seed(0)
+    V, C = 50, 8
+    idx = torch.randint(0, V, (40,), generator=g)
+    assert _row_support(torch.arange(0, V, 3)) is None and _row_support(torch.zeros(0, dtype=torch.long)) is None
+    sup = _row_support(idx)
+    assert sup is not None and _row_support(idx)[0] is sup[0]
+    dsel = torch.randn(40, C, generator=g).bfloat16()
+    merged = _merge_duplicate_rows(dsel, sup)
+    dense = torch.zeros(V, C).index_add_(0, idx, dsel.float())
+    got = torch.zeros(V, C).index_copy_(0, sup[0], merged.float())
+    assert torch.allclose(got, dense, atol=2e-2, rtol=1e-2)
+    assert torch.equal(torch.nonzero(dense.abs().sum(1)).flatten(), sup[0])

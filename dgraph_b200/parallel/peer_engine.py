@@ -11,10 +11,12 @@ pull kernel over a **symmetric arena**:
   ``peer_base[r] + offset`` and nothing is allocated or registered on the hot path;
 * a 64-entry signal pad for epoch-flag barriers that run as tiny kernels **on the compute stream** (no host sync).
 
-Halo exchange forward  = copy ``x`` into the slot's first rows, barrier, ONE pull kernel that writes the halo rows
-right behind them -> the slot *is* ``cat([x, halo])``.  Backward = copy halo-row gradients into a slot, barrier, ONE
-deterministic pull-reduce kernel on the owners.  Gradient all-reduce + Adam = ONE kernel reading all peers' flat
-gradient buffers.
+Producers write straight into slots (the GEMM's ``out=`` is the slot that peers read; features live in ``symmetric_rows``
+buffers), so an exchange is a barrier plus the consumer: either the aggregation kernel reads remote rows from the owners while it
+runs, or ONE pull kernel lands every halo row behind the owned rows of the same slot (``pull_mode``).  Backward: the CSC walk writes
+halo-row gradients into a slot, barrier, ONE deterministic pull-reduce kernel on the owners, in place.  Gradient all-reduce + Adam
+= ONE kernel reading all peers' flat gradient buffers.  Every decision that changes which slots exist or how large they are is
+taken from all-gathered totals: slot offsets must be identical on all ranks.
 """
 from __future__ import annotations
 
@@ -538,6 +540,7 @@ class PeerMemoryEngine(TorchDistEngine):
             off = self.arena.slot(f"{rk}#{len(entries)}", max(nbytes, 16))
             pick = {"off": off, "busy": False, "read_epoch": -1}
             entries.append(pick)
+            self._check_symmetric(rk, off, nbytes)
         guard = None
         if ring and track:
             pick["busy"] = True
@@ -545,6 +548,23 @@ class PeerMemoryEngine(TorchDistEngine):
         self._by_off[pick["off"]] = pick
         self.note_write(pick["off"])
         return self.arena.tensor(pick["off"], shape, dtype, guard), pick["off"]
+
+    def _check_symmetric(self, rk, off: int, nbytes: int) -> None:
+        """``DGRAPH_B200_VALIDATE=1``: every new slot is compared across the ranks of the replica (one small all-gather per
+        allocation, i.e. during the first steps only).  Peers address a slot as ``peer_base + offset``, so a rank that allocated a
+        different slot at this point -- a data-dependent branch, a ring that grew on one rank only -- would make every later
+        exchange read the wrong memory without any error."""
+        from dgraph_b200.utils.debug import validate_enabled
+
+        if not validate_enabled() or self._world == 1 or not getattr(self.arena, "_owned", False):
+            return
+        mine = torch.tensor([off, nbytes], dtype=torch.long, device=self.device)
+        allv = [torch.zeros_like(mine) for _ in range(self._world)]
+        dist.all_gather(allv, mine, group=self._group)
+        seen = [tuple(v.tolist()) for v in allv]
+        if any(v != seen[0] for v in seen):
+            raise RuntimeError(f"symmetric slot {rk} differs between ranks (offset, bytes per rank: {seen}): the ranks did not "
+                               "allocate the same slots in the same order")
 
     def note_write(self, off):
         """This rank is about to overwrite slot ``off``.  Peers read it during epoch ``read_epoch``; they are provably done once any

@@ -244,14 +244,16 @@ def run_ours(args):
     x_dev.copy_(xh, non_blocking=True)
     losses = []
     if use_graph:  # same work per step, replayed with one cudaGraphLaunch (utils/cuda_graph.py); inputs stay in symmetric memory
-        from dgraph_b200.utils.cuda_graph import GraphedTrainStep
+        from dgraph_b200.utils.cuda_graph import GraphedTrainStep, capture_or_eager
 
         snap = opt.snapshot()  # capture trains for three steps (two eager warm-ups + the captured one): undo them, so that the first
-        graphed = GraphedTrainStep(forward_loss, opt, (x_dev, y_dev), warmup=2, static_inputs=(x_dev, y_dev))
+        graphed = capture_or_eager(lambda: GraphedTrainStep(forward_loss, opt, (x_dev, y_dev), warmup=2, static_inputs=(x_dev, y_dev)),
+                                   world)
         opt.restore(snap)      # reported loss is the loss of the initial weights, as without a graph
-
-        def step(x_in, y_in):  # noqa: F811
-            return graphed(x_in, y_in).clone()
+        use_graph = graphed is not None  # a failed capture leaves every rank on the eager step (and the JSON line says so)
+        if use_graph:
+            def step(x_in, y_in):  # noqa: F811
+                return graphed(x_in, y_in).clone()
 
     def loop_dev(k):
         for _ in range(k):

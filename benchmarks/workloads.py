@@ -42,12 +42,12 @@ def _graphed(args, world, comm, forward_loss, opt, example_inputs):
     engine exists).  Returns the replacement for the eager step, or None."""
     if not getattr(args, "cuda_graph", False) or not (world == 1 or getattr(comm.engine, "device_epoch", False)):
         return None
-    from dgraph_b200.utils.cuda_graph import GraphedTrainStep
+    from dgraph_b200.utils.cuda_graph import GraphedTrainStep, capture_or_eager
 
     snap = opt.snapshot()  # undo the three training steps the capture performs: losses then start from the initial weights
-    g = GraphedTrainStep(forward_loss, opt, example_inputs, warmup=2)
+    g = capture_or_eager(lambda: GraphedTrainStep(forward_loss, opt, example_inputs, warmup=2), world)
     opt.restore(snap)
-    return lambda *xs: g(*xs).clone()
+    return None if g is None else (lambda *xs: g(*xs).clone())
 
 
 # ------------------------------------------------------------------------------------------------------------------------------

@@ -17,6 +17,7 @@ capture and replay the same sequence (the barriers inside the graph still wait f
 """
 from __future__ import annotations
 
+import sys
 from typing import Callable, Optional, Sequence
 
 import torch
@@ -76,3 +77,23 @@ class GraphedTrainStep:
         self.graph.replay()
         N.count_launch(self.launches_per_replay)  # keep the launch accounting of bench.py truthful under replay
         return self.static_loss
+
+
+def capture_or_eager(make: Callable[[], GraphedTrainStep], world: int = 1) -> Optional[GraphedTrainStep]:
+    """``make()`` builds a :class:`GraphedTrainStep`.  When the capture raises on any rank, EVERY rank gets ``None`` and keeps
+    stepping eagerly (the ranks agree through one small all-reduce): nothing ran on the device during the failed capture, so the
+    barrier epochs in device memory are still in step.  The caller restores the optimizer snapshot either way."""
+    err = None
+    try:
+        g = make()
+    except Exception as e:  # noqa: BLE001 - reported below; eager stepping is always available
+        g, err = None, e
+    ok = torch.tensor([0 if g is None else 1], dtype=torch.int32, device="cuda")
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    if int(ok) == 1:
+        return g
+    print(f"CUDA-graph capture failed{'' if err is None else f' ({type(err).__name__}: {err})'}; stepping eagerly", file=sys.stderr)
+    return None

@@ -182,3 +182,71 @@ def test_window_single_rank_roundtrip():
     with pytest.raises(RuntimeError, match="outside"):
         win.get_rows(torch.tensor([1 << 40]), torch.zeros(1, dtype=torch.int32), torch.empty(1, 4))
     win.close()
+
+
+def _train(model, opt, x, y, pat, V, steps, sync=None):
+    losses = []
+    for _ in range(steps):
+        opt.zero_grad()
+        loss = torch.nn.functional.cross_entropy(model(x, pat), y, reduction="sum") / V
+        loss.backward()
+        if sync is not None:
+            for p in model.parameters():
+                sync(p.grad)
+        opt.step()
+        losses.append(float(loss.detach()))
+    return losses
+
+
+def _train_worker(rank, W, port, e, V, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(W))
+    dist.init_process_group("gloo", rank=rank, world_size=W)
+    from dgraph_b200 import Communicator
+    from dgraph_b200.models.gcn import CommAwareGCN
+    from dgraph_b200.parallel import HaloExchange, build_communication_pattern
+
+    comm = Communicator.init_process_group("mpi")
+    part = partition(V, W, "random")
+    pat = build_communication_pattern(e, part, rank, W)
+    g = torch.Generator().manual_seed(5)
+    xg = torch.randn(V, 6, generator=g, dtype=torch.float64)
+    yg = torch.randint(0, 4, (V,), generator=g)
+    torch.manual_seed(0)
+    model = CommAwareGCN(6, 8, 4, HaloExchange(comm), comm).double()
+    gids = pat.local_vertices_global
+    epoch0 = comm.engine.window.epoch
+    losses = _train(model, torch.optim.SGD(model.parameters(), lr=0.05), xg[gids], yg[gids], pat, V, 3, sync=comm.all_reduce)
+    total = torch.tensor(losses, dtype=torch.float64)
+    dist.all_reduce(total)
+    ret[rank] = (total.tolist(), [p.detach().clone() for p in model.parameters()], comm.engine.window.epoch - epoch0)
+    dist.barrier()
+    comm.engine.window.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(240)
+def test_gcn_training_over_windows_equals_single_process():
+    """Two ranks, every halo exchange (forward and backward) a one-sided `put` epoch: same losses and weights as one process."""
+    from dgraph_b200 import Communicator
+    from dgraph_b200.models.gcn import CommAwareGCN
+    from dgraph_b200.parallel import HaloExchange, build_communication_pattern
+    from dgraph_b200.parallel.local_engine import LocalEngine
+
+    W, V = 2, 80
+    e = random_graph(V, 6, seed=11, symmetric=True)
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_train_worker, args=(W, _free_port(), e, V, ret), nprocs=W, join=True)
+    comm = Communicator._from_engine(LocalEngine(), backend="single")
+    pat = build_communication_pattern(e, torch.zeros(V, dtype=torch.long), 0, 1)
+    g = torch.Generator().manual_seed(5)
+    xg = torch.randn(V, 6, generator=g, dtype=torch.float64)
+    yg = torch.randint(0, 4, (V,), generator=g)
+    torch.manual_seed(0)
+    model = CommAwareGCN(6, 8, 4, HaloExchange(comm), comm).double()
+    want = _train(model, torch.optim.SGD(model.parameters(), lr=0.05), xg, yg, pat, V, 3)
+    for r in range(W):
+        losses, params, fences = ret[r]
+        assert all(abs(a - b) < 1e-10 for a, b in zip(losses, want)), (losses, want)
+        assert all(torch.allclose(a, b, atol=1e-10) for a, b in zip(params, model.parameters()))
+        assert fences == 3 * (2 + 1) * 2  # steps x (two forward exchanges + one backward: the features need no gradient) x two fences

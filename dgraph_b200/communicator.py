@@ -26,6 +26,19 @@ SUPPORTED_BACKENDS = ["nccl", "mpi", "nvshmem"]
 _EXTRA_BACKENDS = ["gloo", "torch", "b200", "shm", "emulated", "single"]
 
 
+def _spans_nodes() -> bool:
+    """True when the launcher says the job has ranks on more than one node (``torchrun`` exports ``LOCAL_WORLD_SIZE``; SLURM
+    ``SLURM_NNODES``).  The peer-memory engine maps every rank's arena through CUDA IPC, which ends at the node boundary."""
+    try:
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        local = int(os.environ.get("LOCAL_WORLD_SIZE", "0"))
+        if local > 0:
+            return world > local
+        return int(os.environ.get("SLURM_NNODES", os.environ.get("SLURM_JOB_NUM_NODES", "1"))) > 1 and world > 1
+    except ValueError:
+        return False
+
+
 def _make_engine(backend: str, **kwargs):
     from dgraph_b200.parallel.collective_engine import TorchDistEngine
 
@@ -48,6 +61,11 @@ def _make_engine(backend: str, **kwargs):
     if backend in ("gloo", "shm") or not use_cuda:
         return TorchDistEngine(dist_backend="gloo", **kwargs)
     if backend == "torch" or forced == "torch":
+        return TorchDistEngine(dist_backend="nccl", **kwargs)
+    if _spans_nodes() and backend != "b200":
+        import warnings
+
+        warnings.warn("ranks on several nodes: using the NCCL engine (the peer-memory engine covers the GPUs of one NVLink domain)")
         return TorchDistEngine(dist_backend="nccl", **kwargs)
     from dgraph_b200.parallel.peer_engine import PeerMemoryEngine
 
@@ -80,7 +98,7 @@ def _make_hybrid_engine(rpg: int, use_cuda: bool, _backend: str = "nccl", **kwar
         if rank // rpg == g:
             mine = grp
     kw = {k: v for k, v in kwargs.items() if k != "ranks_per_graph"}
-    if use_cuda and os.environ.get("DGRAPH_B200_ENGINE", "peer") != "torch":
+    if use_cuda and os.environ.get("DGRAPH_B200_ENGINE", "peer") != "torch" and not _spans_nodes():
         # halo / plan traffic over NVLink inside the replica, ONE fused gradient-sum + Adam kernel over the whole job
         from dgraph_b200.parallel.peer_engine import PeerMemoryEngine
 

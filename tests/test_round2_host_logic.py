@@ -129,3 +129,21 @@ def test_duplicate_label_rows_merge_into_unique_support():
     got = torch.zeros(V, C).index_copy_(0, sup[0], merged.float())
     assert torch.allclose(got, dense, atol=2e-2, rtol=1e-2)
     assert torch.equal(torch.nonzero(dense.abs().sum(1)).flatten(), sup[0])
+
+
+def test_multi_node_launch_is_detected(monkeypatch):
+    """Peer memory (CUDA IPC) ends at the node boundary: a launch with ranks on several nodes selects the NCCL engine."""
+    from dgraph_b200.communicator import _spans_nodes
+
+    for k in ("WORLD_SIZE", "LOCAL_WORLD_SIZE", "SLURM_NNODES", "SLURM_JOB_NUM_NODES"):
+        monkeypatch.delenv(k, raising=False)
+    assert not _spans_nodes()
+    monkeypatch.setenv("WORLD_SIZE", "8")
+    monkeypatch.setenv("LOCAL_WORLD_SIZE", "8")
+    assert not _spans_nodes()
+    monkeypatch.setenv("WORLD_SIZE", "16")
+    assert _spans_nodes()
+    monkeypatch.delenv("LOCAL_WORLD_SIZE")
+    assert not _spans_nodes()
+    monkeypatch.setenv("SLURM_NNODES", "2")
+    assert _spans_nodes()

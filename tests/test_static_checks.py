@@ -35,3 +35,41 @@ def test_every_native_symbol_named_in_python_is_exported():
             used.setdefault(m.group(1), set()).add(rel)
     missing = {k: sorted(v) for k, v in used.items() if k not in have}
     assert not missing, f"named in Python but not exported by the libraries: {missing}"
+
+
+def _strip_comments(text):
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return re.sub(r"//[^\n]*", "", text)
+
+
+def _param_counts(text, terminator):
+    out = {}
+    for m in re.finditer(r"\b(dgb_[a-z0-9_]+)\s*\(([^;{()]*)\)\s*" + terminator, _strip_comments(text), flags=re.S):
+        args = m.group(2).strip()
+        out[m.group(1)] = 0 if args in ("", "void") else len(args.split(","))
+    return out
+
+
+def test_ctypes_call_sites_pass_as_many_arguments_as_the_c_prototypes_take():
+    """ctypes does not check argument counts: a call site that lags behind a changed signature would pass garbage.  Every
+    `lib.dgb_*(...)` call in the tree is compared with the header, and the header with the definitions in `csrc/`."""
+    import ast
+
+    protos = _param_counts(open(os.path.join(ROOT, "include", "dgraph_b200.h")).read(), ";")
+    assert len(protos) >= 50
+    defs = {}
+    for f in glob.glob(os.path.join(ROOT, "csrc", "*.cu")):
+        defs.update(_param_counts(open(f).read(), r"\{"))
+    assert {k: (v, defs.get(k)) for k, v in protos.items() if defs.get(k) != v} == {}
+    bad = []
+    for f in glob.glob(os.path.join(ROOT, "**", "*.py"), recursive=True):
+        rel = os.path.relpath(f, ROOT)
+        if rel.startswith(("baseline/_ref", "gpurun_out", "build")):
+            continue
+        for node in ast.walk(ast.parse(open(f).read())):
+            if (isinstance(node, ast.Call) and isinstance(node.func, ast.Attribute) and node.func.attr.startswith("dgb_")
+                    and not any(isinstance(a, ast.Starred) for a in node.args) and not node.keywords):
+                want = protos.get(node.func.attr)
+                if want is None or want != len(node.args):
+                    bad.append((rel, node.lineno, node.func.attr, len(node.args), want))
+    assert not bad, bad

@@ -73,3 +73,40 @@ def test_ctypes_call_sites_pass_as_many_arguments_as_the_c_prototypes_take():
                 if want is None or want != len(node.args):
                     bad.append((rel, node.lineno, node.func.attr, len(node.args), want))
     assert not bad, bad
+
+
+def test_ctypes_call_sites_pass_the_kinds_of_arguments_the_prototypes_take():
+    """int vs int64_t vs float vs pointer, for every argument written as a recognisable wrapper (`N.ptr`, `N.i32`, `N.i64`, `N.f32`,
+    `N.stream`, `ctypes.c_*`): a float handed to an integer slot (or the reverse) travels in the wrong register class."""
+    import ast
+
+    def kind(param):
+        if "*" in param:
+            return "ptr"
+        base = re.sub(r"\b[A-Za-z_][A-Za-z0-9_]*$", "", param.strip()).replace("const", "").strip()
+        return {"float": "f32", "double": "f64", "int": "i32", "unsigned": "i32", "unsigned int": "i32", "uint32_t": "i32",
+                "int32_t": "i32", "int64_t": "i64", "long long": "i64", "size_t": "i64", "uint64_t": "i64"}.get(base, "?" + base)
+
+    protos = {}
+    hdr = _strip_comments(open(os.path.join(ROOT, "include", "dgraph_b200.h")).read())
+    for m in re.finditer(r"\b(dgb_[a-z0-9_]+)\s*\(([^;{()]*)\)\s*;", hdr, flags=re.S):
+        args = m.group(2).strip()
+        protos[m.group(1)] = [] if args in ("", "void") else [kind(a) for a in args.split(",")]
+    assert not {k for v in protos.values() for k in v if k.startswith("?")}
+    wrappers = {"ptr": "ptr", "stream": "ptr", "byref": "ptr", "c_void_p": "ptr", "c_char_p": "ptr", "i32": "i32", "c_int": "i32",
+                "c_uint": "i32", "i64": "i64", "c_longlong": "i64", "c_int64": "i64", "c_uint64": "i64", "c_size_t": "i64",
+                "f32": "f32", "c_float": "f32", "c_double": "f64"}
+    bad = []
+    for f in glob.glob(os.path.join(ROOT, "**", "*.py"), recursive=True):
+        rel = os.path.relpath(f, ROOT)
+        if rel.startswith(("baseline/_ref", "gpurun_out", "build")):
+            continue
+        for node in ast.walk(ast.parse(open(f).read())):
+            if isinstance(node, ast.Call) and isinstance(node.func, ast.Attribute) and node.func.attr in protos:
+                for i, (a, want) in enumerate(zip(node.args, protos[node.func.attr])):
+                    if isinstance(a, ast.Call):
+                        fn = a.func.attr if isinstance(a.func, ast.Attribute) else getattr(a.func, "id", "")
+                        got = wrappers.get(fn)
+                        if got is not None and got != want:
+                            bad.append((rel, node.lineno, node.func.attr, i, got, want))
+    assert not bad, bad

@@ -6,7 +6,7 @@
 //   * peers map each other's segments once and re-map lazily when the owner has published a new generation;
 //   * a fence is an epoch flag per rank (store-release of my epoch, acquire-spin until every peer's epoch has caught up) with a
 //     bounded wait, so that a rank that died is reported instead of hanging the job;
-//   * gets are row memcpys out of the owner's segment, accumulates are lock-free float adds into it, both run over a small
+//   * gets are row memcpys out of the owner's segment, accumulates are row-locked vector adds into it (one lock byte per row), both run over a small
 //     thread pool for large requests.  Nothing is allocated or mapped between the two fences of an access epoch.
 //
 // The Python side is dgraph_b200/parallel/shm_engine.py.  Exported with C linkage; every call returns 0 on success.
@@ -45,6 +45,7 @@ struct alignas(64) Control {
     std::atomic<uint64_t> gen;    // generation of the owner's data segment
     std::atomic<uint64_t> bytes;  // capacity of that generation
     std::atomic<uint32_t> abort;  // set by anyone who gave up waiting
+    std::atomic<int64_t> lock_off;  // byte offset of the owner's per-row lock bytes for the coming accumulate epoch (-1: none)
 };
 constexpr uint64_t MAGIC = 0x4447425f57494e31ull;  // "DGB_WIN1"
 
@@ -207,6 +208,7 @@ DGBH_API void* dgbh_win_open(const char* job, int rank, int world, uint64_t byte
     ctl->gen.store(0, std::memory_order_relaxed);
     ctl->bytes.store(bytes, std::memory_order_relaxed);
     ctl->abort.store(0, std::memory_order_relaxed);
+    ctl->lock_off.store(-1, std::memory_order_relaxed);
     ctl->magic.store(MAGIC, std::memory_order_release);
     Peer& me = w->peers[rank];
     me.ctl = ctl;
@@ -335,7 +337,10 @@ DGBH_API int dgbh_win_put(void* h, int peer, int64_t dst_off, const void* src, i
 }
 
 // segment(owner[i])[base_off + row[i] * F ...] += src[i * F ...]   (elem_bytes 4: float, 8: double); concurrent adds from any
-// number of ranks to the same element are safe (compare-and-swap loop per element)
+// number of ranks and threads to the same row are safe.  An owner that published a lock array (dgbh_win_set_lock_offset, before the
+// epoch's opening fence; one zeroed byte per row at segment[lock_off + row]) has its rows locked with one atomic exchange, added with
+// plain vector adds and released with one store: two atomics per row instead of one compare-and-swap loop per element.  Owners
+// without a lock array (-1) get the compare-and-swap loop.
 DGBH_API int dgbh_win_accumulate_rows(void* h, const int64_t* row, const int32_t* owner, int64_t n, int64_t F, int elem_bytes, int64_t base_off,
                                       const void* src) {
     auto* w = static_cast<Window*>(h);
@@ -350,7 +355,33 @@ DGBH_API int dgbh_win_accumulate_rows(void* h, const int64_t* row, const int32_t
             const Peer& pe = w->peers[p];
             const int64_t off = base_off + row[i] * row_bytes;
             if (row[i] < 0 || (uint64_t)(off + row_bytes) > pe.bytes) { rc = ERR_BOUNDS; return; }
-            if (elem_bytes == 4) {
+            const int64_t lock_off = pe.ctl->lock_off.load(std::memory_order_relaxed);  // ordered by the fence's acquire
+            if (lock_off >= 0) {
+                if ((uint64_t)(lock_off + row[i] + 1) > pe.bytes) { rc = ERR_BOUNDS; return; }
+                auto* lock = reinterpret_cast<unsigned char*>(pe.data + lock_off + row[i]);
+                unsigned spins = 0;
+                double t0 = 0;
+                while (__atomic_exchange_n(lock, (unsigned char)1, __ATOMIC_ACQUIRE)) {
+                    if ((++spins & 0xFFFF) == 0) {  // a holder that died would otherwise stall everybody for ever
+                        if (t0 == 0) t0 = now_ms();
+                        if (pe.ctl->abort.load(std::memory_order_relaxed)) { rc = ERR_ABORTED; return; }
+                        if (now_ms() - t0 > 120000.0) { rc = ERR_TIMEOUT; return; }
+                    }
+#if defined(__x86_64__) || defined(__i386__)
+                    __builtin_ia32_pause();
+#endif
+                }
+                if (elem_bytes == 4) {
+                    auto* d = reinterpret_cast<float*>(pe.data + off);
+                    const float* s = static_cast<const float*>(src) + i * F;
+                    for (int64_t c = 0; c < F; ++c) d[c] += s[c];
+                } else {
+                    auto* d = reinterpret_cast<double*>(pe.data + off);
+                    const double* s = static_cast<const double*>(src) + i * F;
+                    for (int64_t c = 0; c < F; ++c) d[c] += s[c];
+                }
+                __atomic_store_n(lock, (unsigned char)0, __ATOMIC_RELEASE);
+            } else if (elem_bytes == 4) {
                 auto* d = reinterpret_cast<float*>(pe.data + off);
                 const float* s = static_cast<const float*>(src) + i * F;
                 for (int64_t c = 0; c < F; ++c) atomic_add_f32(d + c, s[c]);
@@ -362,6 +393,14 @@ DGBH_API int dgbh_win_accumulate_rows(void* h, const int64_t* row, const int32_t
         }
     });
     return rc.load();
+}
+
+// Publish (or withdraw, -1) the offset of this rank's lock bytes; takes effect for peers at the next fence.
+DGBH_API int dgbh_win_set_lock_offset(void* h, int64_t off) {
+    auto* w = static_cast<Window*>(h);
+    if (!w) return ERR_ARG;
+    w->peers[w->rank].ctl->lock_off.store(off, std::memory_order_relaxed);
+    return OK;
 }
 
 DGBH_API int dgbh_win_aborted(void* h) {

@@ -7,7 +7,7 @@ owner map, ``rank_mapping=None`` meaning an even contiguous split, the row insid
 scatter being each other's backward, and the one-sided ``put`` that honours ``remote_offsets`` (``Engine.py:67-86``).  What is
 different: the window is created once and grown on demand instead of ``Win.Create`` / ``Win.Free`` per call, the per-row loop runs in
 C++ over a few threads instead of one Python iteration per row, duplicate targets need no local pre-reduction (the accumulate is a
-lock-free add), and fences are bounded so that a dead rank raises instead of hanging the job.
+row-locked add), and fences are bounded so that a dead rank raises instead of hanging the job.
 
 Collectives (plan building, ``comm_plan=`` gather / scatter, all-reduce, barrier) go through gloo, inherited from
 :class:`TorchDistEngine`.  On a GPU box the one-sided engine is :class:`PeerMemoryEngine` (NVLink loads and stores issued from inside
@@ -54,6 +54,7 @@ def _lib():
         lib.dgbh_win_put.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int64]
         lib.dgbh_win_accumulate_rows.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64,
                                                  ctypes.c_int, ctypes.c_int64, ctypes.c_void_p]
+        lib.dgbh_win_set_lock_offset.argtypes = [ctypes.c_void_p, ctypes.c_int64]
         lib.dgbh_win_aborted.argtypes = [ctypes.c_void_p]
         lib.dgbh_win_close.argtypes = [ctypes.c_void_p]
         lib.dgbh_win_close.restype = None
@@ -80,6 +81,7 @@ class ShmWindow:
         if not self._h:
             raise RuntimeError(f"cannot create the shared-memory window {job!r} (see stderr)")
         self._view = None
+        self._locks_published = False
         self._finalizer = weakref.finalize(self, _lib().dgbh_win_close, self._h)
 
     def _check(self, rc: int, what: str) -> None:
@@ -111,9 +113,13 @@ class ShmWindow:
             self._view = None
 
     def region(self, rows: int, F: int, dtype: torch.dtype) -> torch.Tensor:
-        """``[rows, F]`` view of the start of this rank's window."""
+        """``[rows, F]`` view of the start of this rank's window (withdraws a lock array published by :meth:`accumulator`: the bytes
+        it occupied are data again)."""
         n = rows * F * torch.empty((), dtype=dtype).element_size()
         self.reserve(n)
+        if self._locks_published:
+            self._check(_lib().dgbh_win_set_lock_offset(self._h, -1), "set_lock_offset")
+            self._locks_published = False
         return self.bytes_view()[:n].view(dtype).view(rows, F)
 
     def fence(self) -> None:
@@ -127,10 +133,26 @@ class ShmWindow:
                                              out.shape[1] * out.element_size(), 0, out.data_ptr()), "get")
 
     def accumulate_rows(self, rows: torch.Tensor, owners: torch.Tensor, src: torch.Tensor) -> None:
+        """``window(owners[i])[rows[i]] += src[i]``; rows of owners that opened the epoch with :meth:`accumulator` are locked one at a
+        time and added with plain vector adds, others are added element by element with compare-and-swap."""
         rows, owners = rows.to(torch.int64).contiguous(), owners.to(torch.int32).contiguous()
         assert src.is_contiguous() and src.dim() == 2 and src.dtype in (torch.float32, torch.float64) and src.shape[0] == rows.numel()
         self._check(_lib().dgbh_win_accumulate_rows(self._h, rows.data_ptr(), owners.data_ptr(), rows.numel(), src.shape[1],
                                                     src.element_size(), 0, src.data_ptr()), "accumulate")
+
+    def accumulator(self, rows: int, F: int, dtype: torch.dtype) -> torch.Tensor:
+        """Zeroed ``[rows, F]`` region at the head of this rank's window with one zeroed lock byte per row behind it, published to the
+        peers (call before the epoch's opening fence)."""
+        n = rows * F * torch.empty((), dtype=dtype).element_size()
+        lock_off = (n + 63) // 64 * 64
+        self.reserve(lock_off + rows)
+        view = self.bytes_view()
+        view[lock_off:lock_off + rows].zero_()
+        region = view[:n].view(dtype).view(rows, F)
+        region.zero_()
+        self._check(_lib().dgbh_win_set_lock_offset(self._h, lock_off), "set_lock_offset")
+        self._locks_published = True
+        return region
 
     def put(self, peer: int, dst_offset_bytes: int, src: torch.Tensor) -> None:
         assert src.is_contiguous()
@@ -187,8 +209,7 @@ def _win_scatter_add(engine, v2d: torch.Tensor, rows: torch.Tensor, owners: torc
     host = src if not src.is_cuda else src.cpu()
     acc_dtype = host.dtype if host.dtype in (torch.float32, torch.float64) else torch.float32
     host = host.to(acc_dtype).contiguous()
-    region = win.region(n_rows_local, host.shape[1], acc_dtype)
-    region.zero_()
+    region = win.accumulator(n_rows_local, host.shape[1], acc_dtype)  # zeroed rows + one lock byte per row, offset published
     win.fence()
     win.accumulate_rows(rows, owners, host)
     win.fence()

@@ -179,6 +179,19 @@ def test_window_single_rank_roundtrip():
     win.fence()
     want = x.clone().index_add_(0, rows, torch.ones(4, 4))
     assert torch.equal(win.region(12, 4, torch.float32), want)
+    # the same accumulate through an accumulator (zeroed rows + published lock bytes: row-locked vector adds), then through a plain
+    # region again (lock array withdrawn: the bytes behind the rows are data, element-wise compare-and-swap adds)
+    acc = win.accumulator(12, 4, torch.float32)
+    win.fence()
+    win.accumulate_rows(rows, torch.zeros(4, dtype=torch.int32), torch.ones(4, 4))
+    win.fence()
+    assert torch.equal(acc, torch.zeros(12, 4).index_add_(0, rows, torch.ones(4, 4)))
+    big = win.region(64, 4, torch.float32)  # covers the bytes the lock array used
+    big.fill_(1.0)
+    win.fence()
+    win.accumulate_rows(torch.arange(64), torch.zeros(64, dtype=torch.int32), torch.ones(64, 4))
+    win.fence()
+    assert torch.equal(big, torch.full((64, 4), 2.0))
     with pytest.raises(RuntimeError, match="outside"):
         win.get_rows(torch.tensor([1 << 40]), torch.zeros(1, dtype=torch.int32), torch.empty(1, 4))
     win.close()

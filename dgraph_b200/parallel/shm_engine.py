@@ -9,8 +9,8 @@ different: the window is created once and grown on demand instead of ``Win.Creat
 C++ over a few threads instead of one Python iteration per row, duplicate targets need no local pre-reduction (the accumulate is a
 row-locked add), and fences are bounded so that a dead rank raises instead of hanging the job.
 
-Collectives (plan building, ``comm_plan=`` gather / scatter, all-reduce, barrier) go through gloo, inherited from
-:class:`TorchDistEngine`.  On a GPU box the one-sided engine is :class:`PeerMemoryEngine` (NVLink loads and stores issued from inside
+``comm_plan=`` gather / scatter run as window epochs too (every edge addresses ``(owner, row)``; the plan's send lists are not
+needed).  Collectives (plan building, all-reduce, barrier) go through gloo, inherited from :class:`TorchDistEngine`.  On a GPU box the one-sided engine is :class:`PeerMemoryEngine` (NVLink loads and stores issued from inside
 the kernels); this one is what ``backend="mpi"`` selects on a CPU-only box.
 """
 from __future__ import annotations
@@ -284,10 +284,19 @@ class ShmWindowEngine(TorchDistEngine):
     def Detach(win) -> None:  # noqa: N802
         return None
 
+    def _plan_one_sided(self, t: torch.Tensor, plan) -> bool:
+        """Plans that know where every edge's row lives (``edge_owner`` / ``edge_owner_row``, set by the plan builders) are served
+        with window epochs; the choice depends on the plan type and the tensor's rank only, so every rank makes the same one."""
+        return (self._world > 1 and getattr(plan, "edge_owner", None) is not None and not t.is_cuda
+                and (t.dim() == 2 or (t.dim() == 3 and t.shape[0] == 1)))
+
     # ---- vector-addressed one-sided gather / scatter ----------------------------------------------------------------------------------
     def gather(self, src_tensor=None, indices=None, rank_mappings=None, *, comm_plan=None, **kwargs):
         src_tensor, rank_mappings, _ = self._reference_keywords(src_tensor, rank_mappings, None, kwargs)
-        if comm_plan is not None or hasattr(indices, "boundary_edge_idx"):
+        plan = comm_plan if comm_plan is not None else (indices if hasattr(indices, "boundary_edge_idx") else None)
+        if plan is not None:
+            if self._plan_one_sided(src_tensor, plan):  # every edge reads its row from the owner's window: no send lists needed
+                return _WindowGather.apply(src_tensor, plan.edge_owner_row, plan.edge_owner, self)
             return super().gather(src_tensor, indices, rank_mappings, comm_plan=comm_plan, **kwargs)
         assert indices.dtype in (torch.long, torch.int), f"Indices must be long or int, found {indices.dtype}"
         assert src_tensor.dim() == 2 or src_tensor.shape[0] == 1, "one graph per call: [1, N, F] or [N, F]"
@@ -296,7 +305,10 @@ class ShmWindowEngine(TorchDistEngine):
 
     def scatter(self, src_tensor=None, indices=None, rank_mappings=None, output_size=None, *, comm_plan=None, **kwargs):
         src_tensor, rank_mappings, output_size = self._reference_keywords(src_tensor, rank_mappings, output_size, kwargs)
-        if comm_plan is not None or hasattr(indices, "boundary_edge_idx"):
+        plan = comm_plan if comm_plan is not None else (indices if hasattr(indices, "boundary_edge_idx") else None)
+        if plan is not None:
+            if self._plan_one_sided(src_tensor, plan):
+                return _WindowScatter.apply(src_tensor, plan.edge_owner_row, plan.edge_owner, int(plan.num_local_vertices), self)
             return super().scatter(src_tensor, indices, rank_mappings, output_size, comm_plan=comm_plan, **kwargs)
         # the reference's MPI engine takes (tensor, indices, num_output_rows, rank_mapping=None): a row count in third position
         if isinstance(rank_mappings, int) and (output_size is None or isinstance(output_size, torch.Tensor)):

@@ -101,6 +101,23 @@ def _worker(rank, W, port, ret):
     need = torch.zeros(V, dtype=torch.float64).index_add_(0, pairs[:, 1], torch.ones(pairs.shape[0], dtype=torch.float64))
     checks["halo_put_bwd"] = torch.allclose(xl.grad[:, 0], need[pat.local_vertices_global])
 
+    # comm_plan= gather / scatter as window epochs (every edge reads / adds at (owner, row)); forward and backward vs the global graph
+    from dgraph_b200.parallel.comm_plan import COO_to_NCCLCommPlan
+
+    off = torch.tensor([n * r for r in range(W + 1)])
+    mine = torch.nonzero((e[:, 0] >= off[rank]) & (e[:, 0] < off[rank + 1]), as_tuple=True)[0]
+    plan = COO_to_NCCLCommPlan(rank, W, e[:, 1], mine, off)
+    xp = xg[lo:lo + n].clone().unsqueeze(0).requires_grad_(True)
+    epoch0 = eng.window.epoch
+    got = comm.gather(xp, comm_plan=plan)
+    checks["plan_gather"] = torch.equal(got[0], xg[e[mine, 1]]) and eng.window.epoch == epoch0 + 2
+    got.sum().backward()
+    indeg = torch.bincount(e[:, 1], minlength=V).to(torch.float64)
+    checks["plan_gather_bwd"] = torch.allclose(xp.grad[0, :, 0], indeg[lo:lo + n])
+    ev = torch.randn(e.shape[0], F, generator=torch.Generator().manual_seed(21), dtype=torch.float64)
+    sc = comm.scatter(ev[mine].unsqueeze(0), comm_plan=plan)
+    checks["plan_scatter"] = torch.allclose(sc[0], torch.zeros(V, F, dtype=torch.float64).index_add_(0, e[:, 1], ev)[lo:lo + n], atol=1e-12)
+
     # collectives still work (gloo), and a fence that a rank never reaches is reported instead of hanging
     t = torch.ones(1, dtype=torch.float64) * (rank + 1)
     comm.all_reduce(t)

@@ -8,8 +8,8 @@ Parity: reference ``DGraph/Communicator.py:21-141`` -- same constructor, static 
 Backend strings: ``"nccl"``, ``"mpi"``, ``"nvshmem"`` are kept for API compatibility.  On a CUDA
 box every one of them maps to the single sm_100a peer-memory engine (``PeerMemoryEngine``: NVLink loads/stores
 issued from inside the kernels, NCCL only for bootstrap and small metadata); ``DGRAPH_B200_ENGINE=torch``
-selects the plain ``torch.distributed`` baseline engine instead.  On a CPU-only box ``"nccl"`` / ``"nvshmem"`` map to gloo and
-``"mpi"`` to the one-sided shared-memory window engine (``parallel/shm_engine.py``: remote-memory-access epochs like the
+selects the plain ``torch.distributed`` baseline engine instead.  On a CPU-only box ``"nccl"`` maps to gloo and the one-sided
+back-ends ``"mpi"`` / ``"nvshmem"`` to the one-sided shared-memory window engine (``parallel/shm_engine.py``: remote-memory-access epochs like the
 reference's MPI engine, gloo for collectives; ``DGRAPH_B200_ENGINE=torch`` or a missing C++ compiler give plain gloo).  Extra
 names: ``"gloo"``, ``"torch"`` (baseline engine), ``"b200"`` (peer-memory engine, explicit), ``"shm"`` (window engine, explicit).
 """
@@ -73,8 +73,9 @@ def _make_engine(backend: str, **kwargs):
 
 
 def _wants_windows(backend: str, use_cuda: bool, forced: str) -> bool:
-    """``"shm"`` anywhere, ``"mpi"`` on a CPU-only box: the one-sided shared-memory engine, when its host library can be built."""
-    if backend == "shm" or (backend == "mpi" and not use_cuda and forced != "torch"):
+    """``"shm"`` anywhere, the reference's one-sided back-ends (``"mpi"``, ``"nvshmem"``) on a CPU-only box: the one-sided
+    shared-memory engine, when its host library can be built."""
+    if backend == "shm" or (backend in ("mpi", "nvshmem") and not use_cuda and forced != "torch"):
         from dgraph_b200.parallel import shm_engine
 
         return shm_engine.available()

@@ -113,7 +113,7 @@ class ShmWindow:
             self._view = None
 
     def region(self, rows: int, F: int, dtype: torch.dtype) -> torch.Tensor:
-        """``[rows, F]`` view of the start of this rank's window (withdraws a lock array published by :meth:`accumulator`: the bytes
+        """``[rows, F]`` view of the start of this rank's window, valid until the window grows (withdraws a lock array published by :meth:`accumulator`: the bytes
         it occupied are data again)."""
         n = rows * F * torch.empty((), dtype=dtype).element_size()
         self.reserve(n)
@@ -123,6 +123,8 @@ class ShmWindow:
         return self.bytes_view()[:n].view(dtype).view(rows, F)
 
     def fence(self) -> None:
+        """Closes the current access epoch and opens the next.  A fence that timed out raises on this rank and marks the window set
+        aborted: every later fence on any rank raises at once ("another rank reported a failure") -- build a new engine to go on."""
         self._check(_lib().dgbh_win_fence(self._h, self.timeout_ms), "fence")
 
     def get_rows(self, rows: torch.Tensor, owners: torch.Tensor, out: torch.Tensor, out_rows: Optional[torch.Tensor] = None) -> None:

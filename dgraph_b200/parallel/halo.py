@@ -3,10 +3,12 @@
 Parity: reference ``DGraph/distributed/haloExchange.py:9-223`` (``HaloExchangeImpl``, ``HaloExchange``,
 ``DGraphMessagePassing``; same call signatures, 1-D and 2-D buffers).
 
-On the peer-memory engine the exchange is ONE pull kernel (``ops.halo_pull``): it reads the boundary rows
-straight out of the owners' feature matrices over NVLink, so there is no send-side index kernel, no
-all-to-all and no staging buffer; its backward is ONE push-reduce kernel.  The torch engines take the
-reference's route (index -> ``put`` -> autograd index_add).
+On the peer-memory engine a standalone exchange is ONE pull kernel (``dgb_halo_pull``): it reads the boundary rows straight out
+of the owners' feature matrices over NVLink into the rows behind the local ones -- no send-side index kernel, no all-to-all, no
+staging buffer, no ``cat`` -- and its backward is ONE deterministic pull-reduce kernel on the owners.  (The GCN / SAGE layers go one
+step further and read remote rows inside their aggregation kernels, ``ops/graphconv.py``; this module is the general-purpose
+exchange that GraphCast, user layers and the reference-style ``DGraphMessagePassing`` use.)  The torch engines take the
+reference's route (index -> ``put`` -> autograd index_add); the CPU window engine does the ``put`` one-sidedly.
 """
 from __future__ import annotations
 

@@ -103,6 +103,7 @@ class DGraphMessagePassing(nn.Module):
 
     def forward(self, local_node_features: torch.Tensor, comm_pattern: CommunicationPattern,
                 local_edge_features: Optional[torch.Tensor] = None) -> torch.Tensor:
-        halo = self.exchanger(local_node_features, comm_pattern)
-        aug = torch.cat([local_node_features, halo], dim=0)
+        # one buffer holding [local | halo]: on the peer-memory engine the halo rows are pulled in right behind the local ones, so the
+        # reference's ``cat`` (``haloExchange.py:214``) costs nothing; elsewhere ``augmented`` is exchange + ``torch.cat``
+        aug = self.exchanger.augmented(local_node_features, comm_pattern)
         return self.message_passing_layer(aug, comm_pattern.local_edge_list, local_edge_features)

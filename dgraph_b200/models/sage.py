@@ -1,7 +1,8 @@
 """GraphSAGE (mean aggregator) for vertex-partitioned full-graph training -- north-star config 3 (ogbn-papers100M-shaped).
 
-Not in the reference.  Layer: ``h_i = act(W_self x_i + W_nbr mean_{j in N(i)} x_j + b)``; per layer ONE halo
-pull of the neighbour rows, ONE bf16 CSR mean-aggregation kernel (``ops.segment_mean``, fp32 accumulate) and ONE tcgen05
+Not in the reference.  Layer: ``h_i = act(W_self x_i + W_nbr mean_{j in N(i)} x_j + b)``; per layer ONE bf16 CSR
+mean-aggregation kernel (fp32 accumulate) that reads the rows of remote neighbours from their owners over NVLink while it reduces
+(``PeerMemoryEngine.aggregate_pull``; or ONE halo pull first when the graph re-reads halo rows often, ``pull_mode``) and ONE tcgen05
 gather-GEMM over the two un-concatenated sources ``[x_local | agg]``."""
 from __future__ import annotations
 

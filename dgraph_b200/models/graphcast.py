@@ -118,7 +118,7 @@ class MeshGraphMLP(nn.Module):
             w = torch.cat(parts, dim=1)
         if (_mlp_fused.ENABLED and len(mods) == 4 and fused_silu and isinstance(mods[2], nn.Linear)
                 and isinstance(mods[3], nn.LayerNorm) and _mlp_fused.supported(srcs, w, mods[2].weight, residual)):
-            # opt-in (DGRAPH_B200_FUSED_MLP=1): the whole block in ONE kernel, h never leaves the SM (csrc/mlp_fused_tcgen05.cu)
+            # default (DGRAPH_B200_FUSED_MLP=0 turns it off): the whole block in ONE kernel, h never leaves the SM (csrc/mlp_fused_tcgen05.cu)
             return _mlp_fused.mlp2_ln_fused(srcs, idxs, w, first.bias, mods[2].weight, mods[2].bias, mods[3].weight, mods[3].bias,
                                             mods[3].eps, residual, scatter_plans=scatter_plans)
         h = gather_linear(srcs, idxs, w, first.bias, act="silu" if fused_silu else None, scatter_plans=scatter_plans)

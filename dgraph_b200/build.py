@@ -49,6 +49,8 @@ def sources():
 
 def build(force: bool = False, verbose: bool = False) -> Path:
     srcs = sources()
+    if not srcs and LIB.exists():  # installed package: built at install time, sources not shipped
+        return LIB
     hdrs = sorted(CSRC.glob("*.cuh")) + sorted((ROOT / "include").glob("*.h"))
     stamp = OUT_DIR / ".build_stamp"
     digest = _digest(srcs + hdrs)
@@ -88,6 +90,8 @@ def build_host(force: bool = False) -> Path:
     Separate from the CUDA library so that a host-code change never triggers an nvcc rebuild."""
     srcs = sorted((CSRC / "host").glob("*.cpp"))
     if not srcs:
+        if HOST_LIB.exists():  # installed package: the library was built at install time and the sources stayed behind
+            return HOST_LIB
         raise RuntimeError("no host sources")
     stamp = OUT_DIR / ".build_stamp_host"
     h = hashlib.sha1()

@@ -16,6 +16,10 @@ def _native_build():
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     print("dgraph_b200: built", mod.build())
+    try:  # host-only C++ (partitioner, shared-memory windows); the Python side has fallbacks without it
+        print("dgraph_b200: built", mod.build_host())
+    except Exception as e:  # noqa: BLE001
+        print("dgraph_b200: host library not built:", e)
 
 
 class BuildPy(build_py):

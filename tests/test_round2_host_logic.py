@@ -3,6 +3,8 @@ power-law graph generator, symmetric edge shards, the packed-weight cache and th
 import ast
 import os
 
+import pytest
+
 import torch
 
 from dgraph_b200.parallel import build_all_patterns
@@ -147,3 +149,13 @@ def test_multi_node_launch_is_detected(monkeypatch):
     assert not _spans_nodes()
     monkeypatch.setenv("SLURM_NNODES", "2")
     assert _spans_nodes()
+
+
+def test_installed_package_uses_the_prebuilt_libraries(tmp_path, monkeypatch):
+    """A pip-installed copy ships `lib/*.so` but not `csrc/`: `build()` / `build_host()` hand back the libraries built at install time."""
+    from dgraph_b200 import build as B
+
+    if not (B.LIB.exists() and B.HOST_LIB.exists()):
+        pytest.skip("libraries not built")
+    monkeypatch.setattr(B, "CSRC", tmp_path)  # no sources anywhere below
+    assert B.build() == B.LIB and B.build_host() == B.HOST_LIB

@@ -13,7 +13,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 DEFAULT = ["dgraph_b200", "DGraph", "bench.py", "__graft_entry__.py", "benchmarks", "baseline/ref_bench.py", "baseline/ref_workloads.py",
-           "experiments", "tools"]
+           "experiments", "tools", "tests"]
 
 
 def module_bindings(tree: ast.Module):

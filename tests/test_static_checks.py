@@ -110,3 +110,19 @@ def test_ctypes_call_sites_pass_the_kinds_of_arguments_the_prototypes_take():
                         if got is not None and got != want:
                             bad.append((rel, node.lineno, node.func.attr, i, got, want))
     assert not bad, bad
+
+
+def test_host_header_declares_every_host_export_with_the_definitions_parameter_count():
+    lib = os.path.join(ROOT, "dgraph_b200", "lib", "libdgraph_b200_host.so")
+    if not os.path.exists(lib):
+        pytest.skip("host library not built")
+    hdr = _strip_comments(open(os.path.join(ROOT, "include", "dgraph_b200_host.h")).read())
+    decl = {m.group(1): (0 if m.group(2).strip() in ("", "void") else len(m.group(2).split(",")))
+            for m in re.finditer(r"\b(dgbh?_[a-z0-9_]+)\s*\(([^;{()]*)\)\s*;", hdr, flags=re.S)}
+    exports = {s for s in _exports(lib) if s.startswith(("dgb_", "dgbh_"))}
+    assert exports == set(decl), (exports ^ set(decl))
+    defs = {}
+    for f in glob.glob(os.path.join(ROOT, "csrc", "host", "*.cpp")):
+        for m in re.finditer(r"\b(dgbh?_[a-z0-9_]+)\s*\(([^;{()]*)\)\s*\{", _strip_comments(open(f).read()), flags=re.S):
+            defs[m.group(1)] = 0 if m.group(2).strip() in ("", "void") else len(m.group(2).split(","))
+    assert {k: (v, defs.get(k)) for k, v in decl.items() if defs.get(k) != v} == {}

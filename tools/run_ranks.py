@@ -10,6 +10,7 @@ import argparse
 import os
 import subprocess
 import sys
+import tempfile
 import time
 
 
@@ -21,11 +22,13 @@ def main() -> int:
     a = ap.parse_args()
     cmd = a.cmd[1:] if a.cmd and a.cmd[0] == "--" else a.cmd
     assert cmd, "no command"
-    procs = []
+    procs, logs = [], []
     for r in range(a.n):
         env = dict(os.environ, RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE=str(a.n), OMP_NUM_THREADS=os.environ.get("OMP_NUM_THREADS", "1"))
-        out = None if r == 0 else subprocess.DEVNULL  # rank 0 reports; the others would interleave the same lines
-        procs.append(subprocess.Popen(cmd, env=env, stdout=out, stderr=None if r == 0 else subprocess.STDOUT))
+        # rank 0 reports live; the others would interleave the same lines, so theirs are kept and shown only when they fail
+        log = None if r == 0 else tempfile.TemporaryFile(mode="w+")
+        logs.append(log)
+        procs.append(subprocess.Popen(cmd, env=env, stdout=log, stderr=None if r == 0 else subprocess.STDOUT))
     t0, codes = time.time(), [None] * a.n
     while any(c is None for c in codes):
         for i, p in enumerate(procs):
@@ -37,6 +40,10 @@ def main() -> int:
                     p.kill()
                     codes[i] = 124
         time.sleep(0.05)
+    for r, (code, log) in enumerate(zip(codes, logs)):
+        if log is not None and code != 0:
+            log.seek(0)
+            print(f"---- rank {r} (exit {code}), last lines ----\n" + "".join(log.readlines()[-40:]), file=sys.stderr)
     print(f"rank exit codes: {codes}")
     return max(codes)
 
